@@ -1,0 +1,182 @@
+/*
+ * sdrx_b200 -- C ABI of the B200-native sdrx per-channel DSP chain.
+ *
+ * This is the drop-in boundary.  Plain pointers and sizes only; the caller owns
+ * every host buffer, the engine owns all device memory.  Citations are file:line under
+ * /root/reference/src of the interface each entry point replaces.
+ *
+ *   Boundary A (channelizer)   replaces sdrx.cpp:327-346  (the per-channel msd.decimate loop of
+ *                              data_cb) and, one channel at a time, MSD::decimate msd.hpp:75
+ *                              and DS::addJob ds.hpp:43.
+ *   Boundary B (demod/squelch) replaces sdrx.cpp:452-573 (AGC, AM envelope, LfAGC, ramps, pan
+ *                              mix, window+FFT, SNR squelch) and :646-656 (FIR2, float->s16).
+ *   Ingest                     replaces rtl_dev.cpp:316-341 / airspy_dev.cpp:355-405 (raw->float
+ *                              and block power), fused into the first kernel.
+ *
+ * Error convention: the reference's DSP classes cannot fail (void / value returns,
+ * SURVEY.md §8b "Error conventions"); every function here that can hit a CUDA error returns int:
+ * 0 on success, a negative sdrx_status otherwise, and sdrx_last_error() gives the text.  There is
+ * no CPU fallback: without a usable CUDA device creation fails with SDRX_ERR_CUDA.
+ *
+ * Threading: one engine per GPU, not re-entrant per engine (the reference calls side A from one
+ * device thread and side B from the ALSA thread; here both sides of one block are queued on the
+ * engine's CUDA streams by whichever host thread calls).
+ */
+#ifndef SDRX_B200_H
+#define SDRX_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SDRX_CH_IQ_BUF_SIZE 512   /* sdrx.cpp:129 CH_IQ_BUF_SIZE == FFT_SIZE */
+#define SDRX_MAX_STAGES 8
+
+typedef enum {
+    SDRX_OK = 0,
+    SDRX_ERR_ARG = -1,        /* bad argument / configuration                                  */
+    SDRX_ERR_CUDA = -2,       /* CUDA runtime error or no device                               */
+    SDRX_ERR_STATE = -3,      /* call out of order (e.g. get before push)                      */
+    SDRX_ERR_UNSUPPORTED = -4 /* configuration outside what the engine implements              */
+} sdrx_status;
+
+/* Wire formats of one IQ block (interleaved I,Q).
+ *   U8   rtl_sdr / librtlsdr: float = u8/127.5f - 1.0f          rtl_dev.cpp:320-323
+ *   S16  airspy INT16_IQ:     float = s16 * (1/32768)           libairspy airspy.c:58-62,:304
+ *   F32  airspy FLOAT32_IQ == iqsample_t                        airspy_dev.cpp:355-357           */
+typedef enum { SDRX_FMT_U8 = 0, SDRX_FMT_S16 = 1, SDRX_FMT_F32 = 2 } sdrx_iq_format;
+
+/* flags for sdrx_engine_config.flags */
+#define SDRX_FLAG_FORCE_GENERIC 0x1u  /* never take the specialised channel-bank kernel         */
+#define SDRX_FLAG_NO_DEMOD      0x2u  /* channelizer only (boundary A); skip boundary B kernels  */
+
+typedef struct sdrx_engine sdrx_engine;
+
+/* Everything sdrx.cpp:1584-1714 sets up per run.  Arrays are copied at creation. */
+typedef struct {
+    int            device;          /* CUDA device ordinal                                        */
+    int            n_channels;      /* settings.channels.size()                                   */
+    int            translator_len;  /* N (sdrx.cpp:1571-1583)                                     */
+    const float   *translators;     /* [C][N][2] re,im; row ignored where has_translator[c]==0     */
+    const uint8_t *has_translator;  /* [C]; 0 == empty translator vector (ch_offset==0, :1685)     */
+    int            n_stages;        /* MSD::Stage list (msd.hpp:46-49)                             */
+    const int     *m;               /* [n_stages] down-sampling factors                            */
+    const int     *ntaps;           /* [n_stages] (odd, symmetric taps; msd.hpp:169-170)           */
+    const float   *taps;            /* concatenated                                                */
+    unsigned       block_len;       /* largest block (complex samples) push_block will be given   */
+    const float   *sql_level;       /* [C] dB, Channel::sql_level (sdrx.cpp:215); NULL -> 9.0      */
+    const int     *pos;             /* [C] audio position -2..2 (sdrx.cpp:1024-1044); NULL -> 0    */
+    /* AGC / LfAGC run parameters.  Zero-initialised fields take the values sdrx.cpp:1702-1710 sets:
+     * reference 1, attack 1, decay 0.01, max gain 300 (AGC) / 200 (LfAGC), alpha .01 / .005; the
+     * detectors start from the constructors' reference (0.25, agc.hpp:30,:86).                   */
+    float          agc_attack, agc_decay, agc_reference, agc_max_gain, agc_alpha;
+    float          lf_attack, lf_decay, lf_reference, lf_max_gain, lf_alpha;
+    int            use_lf_agc;      /* --lf-agc (sdrx.cpp:1710)                                    */
+    float          lf_gain_db;      /* --volume: FIR2::setGain (sdrx.cpp:881)                      */
+    const float   *fir2_taps;       /* coeff_bp4am_channel (coeffs.hpp:1812)                       */
+    int            fir2_ntaps;
+    const float   *passband_shape;  /* [512] coeffs.hpp:2018                                       */
+    const float   *ramp_up;         /* [512] coeffs.hpp:2541                                       */
+    const float   *ramp_down;       /* [512] coeffs.hpp:3064                                       */
+    unsigned       flags;
+} sdrx_engine_config;
+
+/* Per-block outputs of boundary B.  Any pointer may be NULL. */
+typedef struct {
+    float   *audio;      /* [C][512]  the sample that is mixed per channel (0 where none)          */
+    uint8_t *sql_state;  /* [C]       squelch state after this block's decision (sdrx.cpp:569-573)  */
+    float   *snr;        /* [C]       sdrx.cpp:566                                                  */
+    float   *mix_pre;    /* [1024]    stereo mix before FIR2 (sdrx.cpp:471-532)                     */
+    float   *mix;        /* [1024]    after FIR2 (sdrx.cpp:646)                                     */
+    int16_t *pcm;        /* [1024]    sdrx.cpp:649-656                                              */
+    float   *pwr_dbfs;   /* [1]       Metadata.pwr_dbfs (rtl_dev.cpp:329-341)                       */
+    float   *agc_gain;   /* [C]       AGC::gain()   (agc.hpp:46)                                    */
+    float   *lf_gain;    /* [C]       LfAGC::gain() (agc.hpp:101)                                   */
+} sdrx_block_outputs;
+
+const char *sdrx_last_error(void);
+const char *sdrx_version(void);
+int  sdrx_device_count(void);
+
+int  sdrx_engine_create(const sdrx_engine_config *cfg, sdrx_engine **out);
+void sdrx_engine_destroy(sdrx_engine *e);
+
+/* One 32 ms block through the whole chain (data_cb, sdrx.cpp:306 + alsa_write_cb, :420), queued
+ * asynchronously.  `raw` is a HOST pointer in `fmt`; it is staged to the device with
+ * cudaMemcpyAsync from pinned memory (directly when `raw` came from sdrx_host_alloc, through the
+ * engine's own pinned double buffer otherwise) and may be reused as soon as the call returns
+ * unless it is pinned, in which case after sdrx_engine_sync / any get.  n_samples may be any
+ * length <= block_len for the channelizer; boundary B runs only when the chain yielded exactly
+ * 512 output samples per channel.                                                               */
+int  sdrx_engine_push_block(sdrx_engine *e, const void *raw, int fmt, unsigned n_samples);
+/* Same with the block already resident in device memory (`d_raw` a device pointer). */
+int  sdrx_engine_push_block_device(sdrx_engine *e, const void *d_raw, int fmt, unsigned n_samples);
+/* Number of channel IQ samples per channel the last pushed block produced. */
+int  sdrx_engine_last_out_len(sdrx_engine *e, unsigned *out_len);
+/* Boundary A result: the CRB chunk iqsample_t[C][512] (sdrx.cpp:343-344). Waits for the block. */
+int  sdrx_engine_get_channel_iq(sdrx_engine *e, float *ch_iq);
+/* Boundary B results. Waits for the block. */
+int  sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
+/* Boundary B on caller-supplied channel IQ (host, [C][512][2]) instead of the channelizer's. */
+int  sdrx_engine_demod_block(sdrx_engine *e, const float *ch_iq, float pwr_dbfs);
+int  sdrx_engine_sync(sdrx_engine *e);
+
+/* Carried state (MSD delay lines + trans_pos, AGC/LfAGC gain+power, squelch states, FIR2 ring):
+ * what the reference keeps in its objects between blocks (SURVEY.md §5 checkpoint/resume). */
+size_t sdrx_engine_state_size(sdrx_engine *e);
+int  sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size);
+int  sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t size);
+int  sdrx_engine_reset(sdrx_engine *e);
+
+/* Introspection for the bench / tests. */
+void    *sdrx_engine_stream(sdrx_engine *e);          /* cudaStream_t the hot kernels run on       */
+uint64_t sdrx_engine_launch_count(sdrx_engine *e);    /* kernels launched so far                   */
+int      sdrx_engine_uses_fast_path(sdrx_engine *e);  /* 1 when the specialised channel bank runs  */
+/* Device-timed duration (ms, CUDA events on the engine stream) of the channel-bank kernel(s) and of
+ * the whole block for the last pushed block; valid after a sync. */
+int      sdrx_engine_last_timing(sdrx_engine *e, float *bank_ms, float *block_ms);
+int      sdrx_engine_set_timing(sdrx_engine *e, int enable);
+
+/* Pinned host memory for zero-staging push_block / get_*.  */
+void *sdrx_host_alloc(size_t bytes);
+void  sdrx_host_free(void *p);
+/* Device memory helpers for callers that keep IQ resident (bench `value` leg, file replay). */
+void *sdrx_device_alloc(int device, size_t bytes);
+void  sdrx_device_free(int device, void *p);
+int   sdrx_device_upload(int device, void *d_dst, const void *h_src, size_t bytes);
+
+/* Set-up helpers that must match the reference bit for bit and therefore run on the host with the
+ * same libm: translator table sdrx.cpp:1682-1690, Hamming window sdrx.cpp:898-900. */
+void sdrx_make_translator(int N, int z, int ch_offset, float *out /* [N][2] */);
+void sdrx_make_window(float *out /* [512] */);
+
+/* ---- single-object surface behind the drop-in C++ classes (msd.hpp / agc.hpp / fir.hpp) ---- */
+typedef struct sdrx_msd sdrx_msd;
+int    sdrx_msd_create(const float *translator, int N, int n_stages, const int *m, const int *ntaps,
+                       const float *taps, int use_ftfir, int device, sdrx_msd **out);   /* msd.hpp:54 */
+int    sdrx_msd_clone(const sdrx_msd *src, sdrx_msd **out);                             /* MSD copy   */
+void   sdrx_msd_destroy(sdrx_msd *m);
+size_t sdrx_msd_m(const sdrx_msd *m);                                                   /* msd.hpp:71 */
+int    sdrx_msd_decimate(sdrx_msd *m, const float *in, size_t in_len, float *out, size_t *out_len); /* :75 */
+
+typedef struct sdrx_agc_state {   /* agc.hpp:72-79 / :134-142 */
+    float attack, decay, reference, min_gain, max_gain, alpha, gain, power;
+    int   active;                 /* LfAGC only */
+} sdrx_agc_state;
+int sdrx_agc_adjust(int device, sdrx_agc_state *s, const float *in, unsigned n, float *out);    /* agc.hpp:48  */
+int sdrx_lfagc_adjust(int device, sdrx_agc_state *s, const float *in, unsigned n, float *out);  /* agc.hpp:106 */
+
+typedef struct sdrx_fir sdrx_fir;
+/* kind 1 FIR (fir.hpp:78), 2 FIR2 (fir.hpp:130), 3 FIR3<iqsample_t> (fir.hpp:28) */
+int  sdrx_fir_create(int kind, const float *c, int n, int device, sdrx_fir **out);
+void sdrx_fir_destroy(sdrx_fir *f);
+int  sdrx_fir_set_gain(sdrx_fir *f, float gain_db);                                     /* fir.hpp:51  */
+int  sdrx_fir_filter(sdrx_fir *f, const float *in, unsigned in_len, float *out);        /* fir.hpp:34  */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDRX_B200_H */

@@ -1,0 +1,135 @@
+// sdrx_b200 -- generic channelizer kernels: any stage list, any block length, exact arithmetic.
+//
+// These restate MSD::decimate (msd.hpp:75-159) stage by stage.  Instead of the reference's
+// per-sample delay-line walk, stage output k is computed directly from its input window
+// (SURVEY.md §3.4): it is emitted after the stage's input index first + k*m and equals
+//   sum_{t<H} h[t] * x[first + k*m - (H-1) + t]
+// with the stage's last H-1 inputs of the previous call kept as a history prefix of the input
+// buffer (zeros before the stream start, msd.hpp:167).  The summation itself follows the
+// reference's portable folded loop (msd.hpp:308-331) add for add, so results are bit-identical.
+#pragma once
+
+#include "common.cuh"
+
+namespace sdrx {
+
+// Stage 0: raw -> float, NCO mix (msd.hpp:134-135) and the first decimating FIR, all channels.
+//   raw          [hist + n_in] samples in wire format; raw[hist + i] is call-relative input i
+//   table        [N][Cpad] translator, transposed so that a warp of 32 channels reads 256 B
+//   has_tr[c]    0 -> the reference's no-translator path (msd.hpp:79-101), no multiply at all
+//   pos0         trans_pos_ of call-relative input 0
+// grid (ceil(n_out/8), Cpad/32), block (32, 8): lane = channel, threadIdx.y = output.
+template <int FMT>
+static __global__ void __launch_bounds__(256)
+k_mix_fir_generic(const void *__restrict__ raw, int hist, const float2 *__restrict__ table, int Cpad, int C,
+                  int N, int pos0, const uint8_t *__restrict__ has_tr, const float *__restrict__ h, int H, int m,
+                  int first, int n_out, float2 *__restrict__ out, long out_stride, int out_off) {
+    const int c = blockIdx.y * 32 + threadIdx.x;
+    const int k = blockIdx.x * 8 + threadIdx.y;
+    if (k >= n_out || c >= C) return;
+    const int half = (H - 1) >> 1;
+    const long i0 = (long)first + (long)k * m - (H - 1);     // call-relative index of window tap 0
+    const bool tr_on = has_tr[c] != 0;
+    int idx_lo = (int)(((long)pos0 + i0) % N);
+    if (idx_lo < 0) idx_lo += N;
+    int idx_hi = (int)(((long)pos0 + i0 + (H - 1)) % N);
+    if (idx_hi < 0) idx_hi += N;
+    const long p_lo = hist + i0;
+
+    float re = 0.0f, im = 0.0f;
+    for (int i = 0; i < half; ++i) {
+        float2 a = load_iq<FMT>(raw, p_lo + i);
+        float2 b = load_iq<FMT>(raw, p_lo + (H - 1) - i);
+        if (tr_on) {
+            a = cmul_exact(a, __ldg(table + (long)idx_lo * Cpad + c));
+            b = cmul_exact(b, __ldg(table + (long)idx_hi * Cpad + c));
+        }
+        const float hv = __ldg(h + i);
+        re = __fadd_rn(re, __fmul_rn(__fadd_rn(a.x, b.x), hv));
+        im = __fadd_rn(im, __fmul_rn(__fadd_rn(a.y, b.y), hv));
+        if (++idx_lo == N) idx_lo = 0;
+        if (--idx_hi < 0) idx_hi = N - 1;
+    }
+    {
+        float2 a = load_iq<FMT>(raw, p_lo + half);
+        if (tr_on) a = cmul_exact(a, __ldg(table + (long)idx_lo * Cpad + c));
+        const float hv = __ldg(h + half);
+        re = __fadd_rn(re, __fmul_rn(a.x, hv));
+        im = __fadd_rn(im, __fmul_rn(a.y, hv));
+    }
+    out[(long)c * out_stride + out_off + k] = make_float2(re, im);
+}
+
+// Stage s >= 1: decimating symmetric FIR on a per-channel stream.
+//   in  [C][in_stride], in[c][in_hist + i] is call-relative input i (in_hist == H-1)
+// grid (ceil(n_out/128), C), block 128: lane = output.
+static __global__ void __launch_bounds__(128)
+k_fir_generic(const float2 *__restrict__ in, long in_stride, int in_hist, const float *__restrict__ h, int H, int m,
+              int first, int n_out, float2 *__restrict__ out, long out_stride, int out_off) {
+    const int c = blockIdx.y;
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_out) return;
+    const int half = (H - 1) >> 1;
+    const float2 *d = in + (long)c * in_stride + in_hist + (long)first + (long)k * m - (H - 1);
+    float re = 0.0f, im = 0.0f;
+    for (int i = 0; i < half; ++i) {
+        const float2 a = d[i], b = d[H - 1 - i];
+        const float hv = __ldg(h + i);
+        re = __fadd_rn(re, __fmul_rn(__fadd_rn(a.x, b.x), hv));
+        im = __fadd_rn(im, __fmul_rn(__fadd_rn(a.y, b.y), hv));
+    }
+    const float2 a = d[half];
+    const float hv = __ldg(h + half);
+    re = __fadd_rn(re, __fmul_rn(a.x, hv));
+    im = __fadd_rn(im, __fmul_rn(a.y, hv));
+    out[(long)c * out_stride + out_off + k] = make_float2(re, im);
+}
+
+// Carry the last `hist` entries of [hist | n_in new] to the front of the same per-channel buffer
+// (the reference's delay line, msd.hpp:228-247, seen as a sliding prefix).  One CTA per channel;
+// reads complete before any write, so n_in < hist (overlap) is safe.  hist <= 1024.
+static __global__ void __launch_bounds__(256)
+k_carry_hist(float2 *__restrict__ buf, long stride, int hist, int n_in) {
+    float2 *b = buf + (long)blockIdx.x * stride;
+    float2 v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int i = threadIdx.x + j * 256;
+        if (i < hist) v[j] = b[n_in + i];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int i = threadIdx.x + j * 256;
+        if (i < hist) b[i] = v[j];
+    }
+}
+
+// Raw history between the two ping-pong input buffers: dst[0..hist) = src[n_in .. n_in+hist),
+// byte granular (bps bytes per complex sample).  src already holds [hist | n_in].
+static __global__ void k_carry_raw(uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, long n_in_bytes, int hist_bytes) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < hist_bytes) dst[i] = src[n_in_bytes + i];
+}
+
+// Block power, pass 1: deterministic per-CTA partial sums of re^2+im^2 (rtl_dev.cpp:333-337).
+// The final mean / 10*log10f - 3 is taken by the mix kernel from the partials in fixed order.
+template <int FMT>
+static __global__ void __launch_bounds__(256)
+k_power_partial(const void *__restrict__ raw, int hist, int n, float *__restrict__ partial) {
+    __shared__ float sh[256];
+    float acc = 0.0f;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+        const float2 v = load_iq<FMT>(raw, (long)hist + i);
+        acc += v.x * v.x + v.y * v.y;
+    }
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) sh[threadIdx.x] += sh[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) partial[blockIdx.x] = sh[0];
+}
+
+}  // namespace sdrx

@@ -1,0 +1,799 @@
+// sdrx_b200 -- the C ABI (include/sdrx_b200.h) over the CUDA kernels.  Host side only orchestrates:
+// pinned double-buffered ingest, stream/event plumbing, block-to-block carries, state save/load.
+// There is no CPU compute path: every sample is touched by a kernel in bank_*.cuh / demod.cuh.
+#include <algorithm>
+#include <cmath>
+#include <complex>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "host_common.h"
+#include "bank_generic.cuh"
+#include "bank_fast.cuh"
+#include "demod.cuh"
+
+using namespace sdrx;
+
+namespace {
+
+constexpr int kNBuf = 2;          // ping-pong depth of raw input and of the output sets
+constexpr int kPwrPartials = 64;
+constexpr uint32_t kStateMagic = 0x58524453u;  // "SDRX"
+
+struct OutSet {                   // device-side results of one block
+    float2  *ch_iq = nullptr;     // [C][512]
+    float   *audio = nullptr;     // [C][512]
+    float   *snr = nullptr;       // [C]
+    float   *mix_pre = nullptr, *mix = nullptr;   // [1024]
+    int16_t *pcm = nullptr;       // [1024]
+    float   *pwr = nullptr;       // [1]
+    uint8_t *sql = nullptr;       // [C] snapshot of the state after the decision
+    float   *agc_gain = nullptr, *lf_gain = nullptr;   // [C] snapshots
+};
+
+}  // namespace
+
+struct sdrx_engine {
+    int dev = 0;
+    unsigned flags = 0;
+    int C = 0, Cpad = 0, N = 0, S = 0;
+    int m[SDRX_MAX_STAGES] = {0}, H[SDRX_MAX_STAGES] = {0}, tap_off[SDRX_MAX_STAGES] = {0};
+    std::vector<float> taps;
+    unsigned block_len = 0;
+    int raw_hist = 0;                    // history samples kept in front of each raw block
+    long stage_stride[SDRX_MAX_STAGES] = {0};   // per-channel stride of stage s input buffer (s >= 1)
+    long chiq_stride = kChunk;           // per-channel stride of the chain output
+    AgcParams agc{}, lf{};
+    float agc_power0 = 0.25f, lf_power0 = 0.0625f;
+    int lf_active = 0;
+    int fir2_ntaps = 0;
+
+    cudaStream_t s_main = nullptr, s_copy = nullptr;
+    cudaEvent_t ev_copied[kNBuf] = {nullptr, nullptr};
+    cudaEvent_t ev_raw_free[kNBuf] = {nullptr, nullptr};   // last reader of d_raw[b] has been queued
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr, ev_t2 = nullptr;
+    bool timing = false, timing_valid = false;
+
+    // device memory
+    uint8_t *d_raw[kNBuf] = {nullptr, nullptr};
+    size_t raw_buf_bytes = 0;
+    float2 *d_table_t = nullptr;         // [N][Cpad]
+    uint8_t *d_has_tr = nullptr;
+    float *d_taps = nullptr;
+    float2 *d_stage_in[SDRX_MAX_STAGES] = {nullptr};
+    float *d_pwr_partial = nullptr;
+    OutSet out[kNBuf];
+    // boundary B
+    ChannelState st{};
+    DemodTables tb{};
+    float *d_window = nullptr, *d_shape = nullptr, *d_ramp_up = nullptr, *d_ramp_down = nullptr;
+    float2 *d_twiddle = nullptr;
+    uint16_t *d_bitrev = nullptr;
+    float *d_sql_level = nullptr;
+    int *d_pos = nullptr;
+    float *d_c_adj = nullptr, *d_fir_hist = nullptr;
+    FastBank fast;                        // specialised channel bank (bank_fast.cuh)
+    bool use_fast = false;
+
+    // pinned staging for pageable callers
+    uint8_t *h_stage[kNBuf] = {nullptr, nullptr};
+    bool stage_busy[kNBuf] = {false, false};
+
+    // carried host-side state
+    long trans_pos = 0;                  // MSD::trans_pos_ (msd.hpp:440), same for every channel
+    int phase[SDRX_MAX_STAGES] = {0};    // inputs seen since the stage's last output (m - isn_)
+    int fmt = -1;                        // wire format of the stream so far
+    uint64_t blocks = 0;
+    unsigned prev_n = 0;                 // samples of the previous block (for the raw carry)
+    unsigned last_out_len = 0;
+    bool last_demod = false;
+    uint64_t launches = 0;
+};
+
+// ------------------------------------------------------------------------------------------------
+namespace sdrx {
+std::string &last_error_ref() {
+    static thread_local std::string err;
+    return err;
+}
+}  // namespace sdrx
+
+extern "C" const char *sdrx_last_error(void) { return last_error_ref().c_str(); }
+extern "C" const char *sdrx_version(void) { return "sdrx_b200 0.1 (sm_100a)"; }
+extern "C" int sdrx_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+// sdrx.cpp:1682-1690: the expression is evaluated in double (M_PI), narrowed to float by the
+// std::complex<float> constructor, then std::exp(std::complex<float>) of this host's libm.
+extern "C" void sdrx_make_translator(int N, int z, int ch_offset, float *out) {
+    if (ch_offset == 0) return;
+    for (int n = 0; n < N; n++) {
+        std::complex<float> e(0.0f, -2.0f * M_PI * n * ch_offset * (float)z / (float)N);
+        std::complex<float> v = std::exp(e);
+        out[2 * n] = v.real();
+        out[2 * n + 1] = v.imag();
+    }
+}
+
+// sdrx.cpp:898-900
+extern "C" void sdrx_make_window(float *out) {
+    for (unsigned n = 0; n < (unsigned)kChunk; n++) out[n] = 0.54f - 0.46f * std::cos((2.0f * M_PI * n) / kChunk);
+}
+
+extern "C" void *sdrx_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes) != cudaSuccess) { last_error_ref() = "cudaMallocHost failed"; cudaGetLastError(); return nullptr; }
+    return p;
+}
+extern "C" void sdrx_host_free(void *p) { if (p) cudaFreeHost(p); }
+extern "C" void *sdrx_device_alloc(int device, size_t bytes) {
+    DevGuard g(device);
+    void *p = nullptr;
+    if (!g.ok || cudaMalloc(&p, bytes) != cudaSuccess) { last_error_ref() = "cudaMalloc failed"; cudaGetLastError(); return nullptr; }
+    return p;
+}
+extern "C" void sdrx_device_free(int device, void *p) { DevGuard g(device); if (p) cudaFree(p); }
+extern "C" int sdrx_device_upload(int device, void *d_dst, const void *h_src, size_t bytes) {
+    DevGuard g(device);
+    CU(cudaMemcpy(d_dst, h_src, bytes, cudaMemcpyHostToDevice));
+    return SDRX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+template <typename T>
+int dalloc(T **p, size_t count) {
+    CU(cudaMalloc((void **)p, std::max<size_t>(count, 1) * sizeof(T)));
+    CU(cudaMemset(*p, 0, std::max<size_t>(count, 1) * sizeof(T)));
+    return SDRX_OK;
+}
+template <typename T>
+int upload(T *d, const T *h, size_t count) {
+    CU(cudaMemcpy(d, h, count * sizeof(T), cudaMemcpyHostToDevice));
+    return SDRX_OK;
+}
+
+void agc_defaults(AgcParams &p, float attack, float decay, float reference, float max_gain, float alpha,
+                  float d_max_gain, float d_alpha) {
+    // zero fields take what sdrx.cpp:1702-1710 sets (reference 1, attack 1, decay 0.01)
+    p.attack = attack != 0.0f ? attack : 1.0f;
+    p.decay = decay != 0.0f ? decay : 0.01f;
+    p.reference = reference != 0.0f ? reference : 1.0f;
+    p.max_gain = max_gain != 0.0f ? max_gain : d_max_gain;
+    p.alpha = alpha != 0.0f ? alpha : d_alpha;
+    p.min_gain = (p.max_gain > 0.0f) ? 1.0f / p.max_gain : 1.0f / 200.0f;   // agc.hpp:34-35, :41-44
+}
+
+int reset_state(sdrx_engine *e) {
+    const size_t C = (size_t)e->C;
+    for (int b = 0; b < kNBuf; ++b) CU(cudaMemsetAsync(e->d_raw[b], 0, e->raw_buf_bytes, e->s_main));
+    for (int s = 1; s < e->S; ++s)
+        CU(cudaMemsetAsync(e->d_stage_in[s], 0, sizeof(float2) * (size_t)e->stage_stride[s] * C, e->s_main));
+    if (!(e->flags & SDRX_FLAG_NO_DEMOD)) {
+        std::vector<float> ones(C, 1.0f), p0(C, e->agc_power0), p1(C, e->lf_power0);
+        CU(cudaMemcpyAsync(e->st.agc_gain, ones.data(), C * 4, cudaMemcpyHostToDevice, e->s_main));
+        CU(cudaMemcpyAsync(e->st.lf_gain, ones.data(), C * 4, cudaMemcpyHostToDevice, e->s_main));
+        CU(cudaMemcpyAsync(e->st.agc_power, p0.data(), C * 4, cudaMemcpyHostToDevice, e->s_main));
+        CU(cudaMemcpyAsync(e->st.lf_power, p1.data(), C * 4, cudaMemcpyHostToDevice, e->s_main));
+        CU(cudaMemsetAsync(e->st.sql_state, 0, C, e->s_main));
+        CU(cudaMemsetAsync(e->st.sql_prev, 0, C, e->s_main));
+        CU(cudaMemsetAsync(e->st.mixed, 0, C, e->s_main));
+        CU(cudaMemsetAsync(e->d_fir_hist, 0, sizeof(float) * 2 * (size_t)std::max(e->fir2_ntaps - 1, 1), e->s_main));
+        CU(cudaStreamSynchronize(e->s_main));   // the host vectors above die here
+    }
+    CU(cudaStreamSynchronize(e->s_main));
+    e->trans_pos = 0;
+    for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = 0;
+    e->fmt = -1;
+    e->blocks = 0;
+    e->prev_n = 0;
+    e->last_out_len = 0;
+    e->last_demod = false;
+    e->timing_valid = false;
+    return SDRX_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
+    if (!e) return;
+    DevGuard g(e->dev);
+    cudaDeviceSynchronize();
+    for (int b = 0; b < kNBuf; ++b) {
+        cudaFree(e->d_raw[b]);
+        if (e->h_stage[b]) cudaFreeHost(e->h_stage[b]);
+        OutSet &o = e->out[b];
+        cudaFree(o.ch_iq); cudaFree(o.audio); cudaFree(o.snr); cudaFree(o.mix_pre); cudaFree(o.mix);
+        cudaFree(o.pcm); cudaFree(o.pwr); cudaFree(o.sql); cudaFree(o.agc_gain); cudaFree(o.lf_gain);
+        if (e->ev_copied[b]) cudaEventDestroy(e->ev_copied[b]);
+        if (e->ev_raw_free[b]) cudaEventDestroy(e->ev_raw_free[b]);
+    }
+    for (int s = 0; s < SDRX_MAX_STAGES; ++s) cudaFree(e->d_stage_in[s]);
+    cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps); cudaFree(e->d_pwr_partial);
+    cudaFree(e->st.agc_gain); cudaFree(e->st.agc_power); cudaFree(e->st.lf_gain); cudaFree(e->st.lf_power);
+    cudaFree(e->st.sql_state); cudaFree(e->st.sql_prev); cudaFree(e->st.mixed);
+    cudaFree(e->d_window); cudaFree(e->d_shape); cudaFree(e->d_ramp_up); cudaFree(e->d_ramp_down);
+    cudaFree(e->d_twiddle); cudaFree(e->d_bitrev); cudaFree(e->d_sql_level); cudaFree(e->d_pos);
+    cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist);
+    e->fast.destroy();
+    if (e->ev_t0) cudaEventDestroy(e->ev_t0);
+    if (e->ev_t1) cudaEventDestroy(e->ev_t1);
+    if (e->ev_t2) cudaEventDestroy(e->ev_t2);
+    if (e->s_main) cudaStreamDestroy(e->s_main);
+    if (e->s_copy) cudaStreamDestroy(e->s_copy);
+    delete e;
+}
+
+namespace {
+
+int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
+    const int C = cfg->n_channels, S = cfg->n_stages;
+    e->dev = cfg->device;
+    e->flags = cfg->flags;
+    e->C = C;
+    e->Cpad = (C + 31) / 32 * 32;
+    e->N = std::max(cfg->translator_len, 1);
+    e->S = S;
+    e->block_len = cfg->block_len;
+    int off = 0;
+    for (int s = 0; s < S; ++s) {
+        e->m[s] = cfg->m[s];
+        e->H[s] = cfg->ntaps[s];
+        e->tap_off[s] = off;
+        off += cfg->ntaps[s];
+    }
+    e->taps.assign(cfg->taps, cfg->taps + off);
+    e->raw_hist = std::max((e->H[0] - 1 + 7) / 8 * 8, 128);
+
+    CU(cudaStreamCreateWithFlags(&e->s_main, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
+    for (int b = 0; b < kNBuf; ++b) {
+        CU(cudaEventCreateWithFlags(&e->ev_copied[b], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&e->ev_raw_free[b], cudaEventDisableTiming));
+    }
+    CU(cudaEventCreate(&e->ev_t0));
+    CU(cudaEventCreate(&e->ev_t1));
+    CU(cudaEventCreate(&e->ev_t2));
+
+    // raw ping-pong: [raw_hist | block_len] samples at the widest wire format
+    e->raw_buf_bytes = ((size_t)e->raw_hist + e->block_len) * 8 + 64;
+    for (int b = 0; b < kNBuf; ++b) {
+        int rc = dalloc(&e->d_raw[b], e->raw_buf_bytes);
+        if (rc) return rc;
+    }
+
+    // translator, transposed to [N][Cpad]; (1,0) rows are never read (has_tr == 0 skips the multiply)
+    {
+        std::vector<float2> t((size_t)e->N * e->Cpad, make_float2(1.0f, 0.0f));
+        std::vector<uint8_t> has(e->Cpad, 0);
+        for (int c = 0; c < C; ++c) {
+            const bool on = cfg->translators && cfg->translator_len > 0 &&
+                            (cfg->has_translator ? cfg->has_translator[c] != 0 : true);
+            has[c] = on ? 1 : 0;
+            if (!on) continue;
+            const float *row = cfg->translators + (size_t)c * cfg->translator_len * 2;
+            for (int n = 0; n < e->N; ++n) t[(size_t)n * e->Cpad + c] = make_float2(row[2 * n], row[2 * n + 1]);
+        }
+        int rc = dalloc(&e->d_table_t, t.size());
+        if (rc) return rc;
+        if ((rc = upload(e->d_table_t, t.data(), t.size()))) return rc;
+        if ((rc = dalloc(&e->d_has_tr, has.size()))) return rc;
+        if ((rc = upload(e->d_has_tr, has.data(), has.size()))) return rc;
+    }
+    {
+        int rc = dalloc(&e->d_taps, e->taps.size());
+        if (rc) return rc;
+        if ((rc = upload(e->d_taps, e->taps.data(), e->taps.size()))) return rc;
+    }
+    // stage input buffers for s >= 1: [C][H-1 + cap], cap = most inputs one call can deliver
+    {
+        size_t cap = e->block_len;
+        for (int s = 1; s < S; ++s) {
+            cap = cap / (size_t)e->m[s - 1] + 1;
+            e->stage_stride[s] = (long)((e->H[s] - 1) + cap + 3) / 4 * 4;
+            int rc = dalloc(&e->d_stage_in[s], (size_t)e->stage_stride[s] * C);
+            if (rc) return rc;
+        }
+    }
+    {
+        // the chain's output: 512 per channel for the reference's block sizes, more if a caller pushes
+        // a longer block through the channelizer alone
+        size_t cap = e->block_len;
+        for (int s = 0; s < S; ++s) cap = cap / (size_t)e->m[s] + 1;
+        e->chiq_stride = (long)std::max<size_t>(kChunk, (cap + 3) / 4 * 4);
+        int rc = dalloc(&e->d_pwr_partial, kPwrPartials);
+        if (rc) return rc;
+    }
+    for (int b = 0; b < kNBuf; ++b) {
+        OutSet &o = e->out[b];
+        int rc;
+        if ((rc = dalloc(&o.ch_iq, (size_t)C * e->chiq_stride))) return rc;
+        if (e->flags & SDRX_FLAG_NO_DEMOD) continue;
+        if ((rc = dalloc(&o.audio, (size_t)C * kChunk))) return rc;
+        if ((rc = dalloc(&o.snr, C))) return rc;
+        if ((rc = dalloc(&o.mix_pre, 2 * kChunk))) return rc;
+        if ((rc = dalloc(&o.mix, 2 * kChunk))) return rc;
+        if ((rc = dalloc(&o.pcm, 2 * kChunk))) return rc;
+        if ((rc = dalloc(&o.pwr, 1))) return rc;
+        if ((rc = dalloc(&o.sql, C))) return rc;
+        if ((rc = dalloc(&o.agc_gain, C))) return rc;
+        if ((rc = dalloc(&o.lf_gain, C))) return rc;
+    }
+
+    if (!(e->flags & SDRX_FLAG_NO_DEMOD)) {
+        if (!cfg->fir2_taps || cfg->fir2_ntaps < 1 || !cfg->passband_shape || !cfg->ramp_up || !cfg->ramp_down)
+            return fail(SDRX_ERR_ARG, "demod tables (fir2_taps, passband_shape, ramp_up, ramp_down) are required");
+        if (cfg->fir2_ntaps > 2048) return fail(SDRX_ERR_UNSUPPORTED, "fir2_ntaps > 2048");
+        agc_defaults(e->agc, cfg->agc_attack, cfg->agc_decay, cfg->agc_reference, cfg->agc_max_gain, cfg->agc_alpha,
+                     300.0f, 0.01f);
+        agc_defaults(e->lf, cfg->lf_attack, cfg->lf_decay, cfg->lf_reference, cfg->lf_max_gain, cfg->lf_alpha,
+                     200.0f, 0.005f);
+        e->agc_power0 = 0.25f;              // AGC(): power_(reference_) with the ctor default, agc.hpp:30-32
+        e->lf_power0 = 0.25f * 0.25f;       // LfAGC(): power_(reference_*reference_), agc.hpp:86-89
+        e->lf_active = cfg->use_lf_agc ? 1 : 0;
+        e->fir2_ntaps = cfg->fir2_ntaps;
+        int rc;
+        if ((rc = dalloc(&e->st.agc_gain, C)) || (rc = dalloc(&e->st.agc_power, C)) ||
+            (rc = dalloc(&e->st.lf_gain, C)) || (rc = dalloc(&e->st.lf_power, C)) ||
+            (rc = dalloc(&e->st.sql_state, C)) || (rc = dalloc(&e->st.sql_prev, C)) ||
+            (rc = dalloc(&e->st.mixed, C)))
+            return rc;
+        std::vector<float> win(kChunk);
+        sdrx_make_window(win.data());
+        std::vector<float2> tw(kChunk / 2);
+        for (int k = 0; k < kChunk / 2; ++k) {      // oracle/fft512.c: double, rounded once
+            const double a = -2.0 * M_PI * (double)k / (double)kChunk;
+            tw[k] = make_float2((float)cos(a), (float)sin(a));
+        }
+        std::vector<uint16_t> rev(kChunk);
+        for (int i = 0; i < kChunk; ++i) {
+            unsigned r = 0;
+            for (int b = 0; b < 9; ++b) if (i & (1 << b)) r |= 1u << (8 - b);
+            rev[i] = (uint16_t)r;
+        }
+        std::vector<float> sql(C, 9.0f);
+        std::vector<int> pos(C, 0);
+        if (cfg->sql_level) sql.assign(cfg->sql_level, cfg->sql_level + C);
+        if (cfg->pos) pos.assign(cfg->pos, cfg->pos + C);
+        std::vector<float> c_adj(cfg->fir2_taps, cfg->fir2_taps + cfg->fir2_ntaps);
+        if (cfg->lf_gain_db != 0.0f)            // FIR2::setGain, fir.hpp:160-170 (the ctor leaves c_adj_ = c_)
+            for (auto &c : c_adj) c = c * std::pow(10.0f, cfg->lf_gain_db / 20.0f);
+        if ((rc = dalloc(&e->d_window, kChunk)) || (rc = upload(e->d_window, win.data(), kChunk)) ||
+            (rc = dalloc(&e->d_twiddle, kChunk / 2)) || (rc = upload(e->d_twiddle, tw.data(), kChunk / 2)) ||
+            (rc = dalloc(&e->d_bitrev, kChunk)) || (rc = upload(e->d_bitrev, rev.data(), kChunk)) ||
+            (rc = dalloc(&e->d_shape, kChunk)) || (rc = upload(e->d_shape, cfg->passband_shape, kChunk)) ||
+            (rc = dalloc(&e->d_ramp_up, kChunk)) || (rc = upload(e->d_ramp_up, cfg->ramp_up, kChunk)) ||
+            (rc = dalloc(&e->d_ramp_down, kChunk)) || (rc = upload(e->d_ramp_down, cfg->ramp_down, kChunk)) ||
+            (rc = dalloc(&e->d_sql_level, C)) || (rc = upload(e->d_sql_level, sql.data(), C)) ||
+            (rc = dalloc(&e->d_pos, C)) || (rc = upload(e->d_pos, pos.data(), C)) ||
+            (rc = dalloc(&e->d_c_adj, c_adj.size())) || (rc = upload(e->d_c_adj, c_adj.data(), c_adj.size())) ||
+            (rc = dalloc(&e->d_fir_hist, 2 * (size_t)std::max(cfg->fir2_ntaps - 1, 1))))
+            return rc;
+        e->tb = DemodTables{e->d_window, e->d_twiddle, e->d_bitrev, e->d_shape, e->d_ramp_up, e->d_ramp_down};
+        CU(cudaFuncSetAttribute(k_mix_fir2_pcm, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)(sizeof(float) * 2 * (size_t)(cfg->fir2_ntaps - 1 + kChunk))));
+    }
+    return reset_state(e);
+}
+
+}  // namespace
+
+extern "C" int sdrx_engine_create(const sdrx_engine_config *cfg, sdrx_engine **out) {
+    if (!cfg || !out) return fail(SDRX_ERR_ARG, "null argument");
+    *out = nullptr;
+    if (cfg->n_channels < 1) return fail(SDRX_ERR_ARG, "n_channels < 1");
+    if (cfg->n_stages < 1 || cfg->n_stages > SDRX_MAX_STAGES) return fail(SDRX_ERR_ARG, "n_stages out of range");
+    if (!cfg->m || !cfg->ntaps || !cfg->taps) return fail(SDRX_ERR_ARG, "stage list missing");
+    if (cfg->block_len < 1) return fail(SDRX_ERR_ARG, "block_len < 1");
+    for (int s = 0; s < cfg->n_stages; ++s) {
+        if (cfg->m[s] < 1) return fail(SDRX_ERR_ARG, "stage m < 1");
+        // msd.hpp:169-170 asserts a non-empty, odd-length (folded FIR) coefficient vector
+        if (cfg->ntaps[s] < 1 || (cfg->ntaps[s] & 1) == 0) return fail(SDRX_ERR_ARG, "stage taps must be odd in number");
+        if (cfg->ntaps[s] > 1025) return fail(SDRX_ERR_UNSUPPORTED, "more than 1025 taps in a stage");
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+        cudaGetLastError();
+        return fail(SDRX_ERR_CUDA, "no CUDA device: sdrx_b200 has no CPU path");
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(SDRX_ERR_ARG, "device ordinal out of range");
+    DevGuard g(cfg->device);
+    if (!g.ok) return fail(SDRX_ERR_CUDA, "cudaSetDevice failed");
+    sdrx_engine *e = new sdrx_engine();
+    int rc = create_impl(cfg, e);
+    if (rc != SDRX_OK) {
+        std::string keep = last_error_ref();
+        sdrx_engine_destroy(e);
+        last_error_ref() = keep;
+        return rc;
+    }
+    *out = e;
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_engine_reset(sdrx_engine *e) {
+    if (!e) return fail(SDRX_ERR_ARG, "null engine");
+    DevGuard g(e->dev);
+    CU(cudaStreamSynchronize(e->s_copy));
+    return reset_state(e);
+}
+
+// ------------------------------------------------------------------------------------------------
+// One block through the chain.
+namespace {
+
+enum SrcKind { SRC_HOST, SRC_DEVICE, SRC_NONE };
+
+template <int FMT>
+int launch_bank_generic(sdrx_engine *e, const uint8_t *raw, unsigned n, const int *first, const int *n_out, OutSet &o) {
+    const int S = e->S;
+    for (int s = 0; s < S; ++s) {
+        float2 *dst;
+        long dst_stride;
+        int dst_off;
+        if (s + 1 < S) { dst = e->d_stage_in[s + 1]; dst_stride = e->stage_stride[s + 1]; dst_off = e->H[s + 1] - 1; }
+        else           { dst = o.ch_iq;              dst_stride = e->chiq_stride;         dst_off = 0; }
+        if (n_out[s] > 0) {
+            if (s == 0) {
+                dim3 grid(div_up(n_out[0], 8), e->Cpad / 32), block(32, 8);
+                k_mix_fir_generic<FMT><<<grid, block, 0, e->s_main>>>(
+                    raw, e->raw_hist, e->d_table_t, e->Cpad, e->C, e->N, (int)e->trans_pos, e->d_has_tr,
+                    e->d_taps + e->tap_off[0], e->H[0], e->m[0], first[0], n_out[0], dst, dst_stride, dst_off);
+            } else {
+                dim3 grid(div_up(n_out[s], 128), e->C);
+                k_fir_generic<<<grid, 128, 0, e->s_main>>>(e->d_stage_in[s], e->stage_stride[s], e->H[s] - 1,
+                                                           e->d_taps + e->tap_off[s], e->H[s], e->m[s], first[s],
+                                                           n_out[s], dst, dst_stride, dst_off);
+            }
+            ++e->launches;
+        }
+        // slide the delay line of stage s (s >= 1; stage 0's is the raw ping-pong prefix)
+        if (s >= 1 && e->H[s] > 1) {
+            const int n_in = n_out[s - 1];
+            if (n_in > 0) {
+                k_carry_hist<<<e->C, 256, 0, e->s_main>>>(e->d_stage_in[s], e->stage_stride[s], e->H[s] - 1, n_in);
+                ++e->launches;
+            }
+        }
+    }
+    (void)n;
+    CU(cudaGetLastError());
+    return SDRX_OK;
+}
+
+int launch_bank_generic_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, unsigned n, const int *first,
+                            const int *n_out, OutSet &o) {
+    switch (fmt) {
+        case SDRX_FMT_U8:  return launch_bank_generic<SDRX_FMT_U8>(e, raw, n, first, n_out, o);
+        case SDRX_FMT_S16: return launch_bank_generic<SDRX_FMT_S16>(e, raw, n, first, n_out, o);
+        default:           return launch_bank_generic<SDRX_FMT_F32>(e, raw, n, first, n_out, o);
+    }
+}
+
+int launch_power(sdrx_engine *e, int fmt, const uint8_t *raw, unsigned n) {
+    switch (fmt) {
+        case SDRX_FMT_U8:  k_power_partial<SDRX_FMT_U8><<<kPwrPartials, 256, 0, e->s_main>>>(raw, e->raw_hist, (int)n, e->d_pwr_partial); break;
+        case SDRX_FMT_S16: k_power_partial<SDRX_FMT_S16><<<kPwrPartials, 256, 0, e->s_main>>>(raw, e->raw_hist, (int)n, e->d_pwr_partial); break;
+        default:           k_power_partial<SDRX_FMT_F32><<<kPwrPartials, 256, 0, e->s_main>>>(raw, e->raw_hist, (int)n, e->d_pwr_partial); break;
+    }
+    ++e->launches;
+    CU(cudaGetLastError());
+    return SDRX_OK;
+}
+
+// boundary B on the chunk in o.ch_iq
+int launch_demod(sdrx_engine *e, OutSet &o, bool have_power, unsigned n_samples) {
+    k_demod_squelch<<<e->C, 256, 0, e->s_main>>>(o.ch_iq, e->chiq_stride, e->st, e->tb, e->agc, e->lf, e->lf_active,
+                                                 e->d_sql_level, o.audio, o.snr);
+    const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk);
+    k_mix_fir2_pcm<<<1, 1024, smem, e->s_main>>>(o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps,
+                                                 e->d_fir_hist, o.mix_pre, o.mix, o.pcm, e->d_pwr_partial,
+                                                 have_power ? kPwrPartials : 0, n_samples, have_power ? o.pwr : nullptr);
+    e->launches += 2;
+    CU(cudaGetLastError());
+    // snapshots, so that a later block cannot overwrite what get_outputs returns for this one
+    CU(cudaMemcpyAsync(o.sql, e->st.sql_state, e->C, cudaMemcpyDeviceToDevice, e->s_main));
+    CU(cudaMemcpyAsync(o.agc_gain, e->st.agc_gain, sizeof(float) * e->C, cudaMemcpyDeviceToDevice, e->s_main));
+    CU(cudaMemcpyAsync(o.lf_gain, e->st.lf_gain, sizeof(float) * e->C, cudaMemcpyDeviceToDevice, e->s_main));
+    return SDRX_OK;
+}
+
+int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out) {
+    const size_t C = (size_t)e->C;
+    auto d2h = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
+        return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, e->s_main) : cudaSuccess;
+    };
+    CU(d2h(out->audio, o.audio, C * kChunk * sizeof(float)));
+    CU(d2h(out->sql_state, o.sql, C));
+    CU(d2h(out->snr, o.snr, C * sizeof(float)));
+    CU(d2h(out->mix_pre, o.mix_pre, 2 * kChunk * sizeof(float)));
+    CU(d2h(out->mix, o.mix, 2 * kChunk * sizeof(float)));
+    CU(d2h(out->pcm, o.pcm, 2 * kChunk * sizeof(int16_t)));
+    CU(d2h(out->pwr_dbfs, o.pwr, sizeof(float)));
+    CU(d2h(out->agc_gain, o.agc_gain, C * sizeof(float)));
+    CU(d2h(out->lf_gain, o.lf_gain, C * sizeof(float)));
+    return SDRX_OK;
+}
+
+int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsigned n) {
+    if (fmt != SDRX_FMT_U8 && fmt != SDRX_FMT_S16 && fmt != SDRX_FMT_F32) return fail(SDRX_ERR_ARG, "unknown IQ format");
+    if (n > e->block_len) return fail(SDRX_ERR_ARG, "block longer than block_len");
+    if (e->fmt >= 0 && e->fmt != fmt && e->blocks > 0)
+        return fail(SDRX_ERR_STATE, "wire format changed mid-stream (the carried raw history is format specific); reset first");
+    e->fmt = fmt;
+    const int bps = raw_bytes_per_sample(fmt);
+    const int cur = (int)(e->blocks & 1), prv = cur ^ 1;
+    uint8_t *buf = e->d_raw[cur];
+    const size_t hist_bytes = (size_t)e->raw_hist * bps;
+
+    // ---- ingest: pinned, double buffered, on the copy stream
+    if (n > 0) {
+        // buffer `cur` was last read by block b-1's raw carry (and before that by block b-2's kernels)
+        CU(cudaStreamWaitEvent(e->s_copy, e->ev_raw_free[cur], 0));
+        if (kind == SRC_DEVICE) {
+            CU(cudaMemcpyAsync(buf + hist_bytes, src, (size_t)n * bps, cudaMemcpyDeviceToDevice, e->s_copy));
+        } else {
+            cudaPointerAttributes attr{};
+            bool pinned = cudaPointerGetAttributes(&attr, src) == cudaSuccess &&
+                          (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged);
+            cudaGetLastError();
+            const void *from = src;
+            if (!pinned) {
+                if (!e->h_stage[cur]) CU(cudaMallocHost((void **)&e->h_stage[cur], (size_t)e->block_len * 8));
+                if (e->stage_busy[cur]) CU(cudaEventSynchronize(e->ev_copied[cur]));
+                memcpy(e->h_stage[cur], src, (size_t)n * bps);
+                e->stage_busy[cur] = true;
+                from = e->h_stage[cur];
+            }
+            CU(cudaMemcpyAsync(buf + hist_bytes, from, (size_t)n * bps, cudaMemcpyHostToDevice, e->s_copy));
+        }
+        CU(cudaEventRecord(e->ev_copied[cur], e->s_copy));
+        CU(cudaStreamWaitEvent(e->s_main, e->ev_copied[cur], 0));
+    }
+    if (e->timing) CU(cudaEventRecord(e->ev_t0, e->s_main));
+
+    // ---- raw delay line: last raw_hist samples of the previous [hist | block] move in front of this block
+    {
+        const int hb = (int)hist_bytes;
+        k_carry_raw<<<div_up(hb, 256), 256, 0, e->s_main>>>(buf, e->d_raw[prv], (long)e->prev_n * bps, hb);
+        ++e->launches;
+        CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));
+    }
+
+    // ---- stage bookkeeping (MSD::S::isn_, msd.hpp:240-244): which inputs complete an output
+    int first[SDRX_MAX_STAGES], n_out[SDRX_MAX_STAGES];
+    long n_in = n;
+    for (int s = 0; s < e->S; ++s) {
+        first[s] = e->m[s] - 1 - e->phase[s];
+        n_out[s] = (int)((e->phase[s] + n_in) / e->m[s]);
+        e->phase[s] = (int)((e->phase[s] + n_in) % e->m[s]);
+        n_in = n_out[s];
+    }
+    const unsigned out_len = (unsigned)n_in;
+    OutSet &o = e->out[cur];
+    const bool demod = !(e->flags & SDRX_FLAG_NO_DEMOD) && out_len == (unsigned)kChunk;
+    if (demod && n > 0) { int rc = launch_power(e, fmt, buf, n); if (rc) return rc; }
+
+    int rc = launch_bank_generic_fmt(e, fmt, buf, n, first, n_out, o);
+    if (rc) return rc;
+    if (e->timing) CU(cudaEventRecord(e->ev_t1, e->s_main));
+
+    if (demod) { rc = launch_demod(e, o, n > 0, n); if (rc) return rc; }
+    if (e->timing) { CU(cudaEventRecord(e->ev_t2, e->s_main)); e->timing_valid = true; }
+
+    e->trans_pos = (e->trans_pos + n) % e->N;
+    e->prev_n = n;
+    e->last_out_len = out_len;
+    e->last_demod = demod;
+    ++e->blocks;
+    return SDRX_OK;
+}
+
+}  // namespace
+
+extern "C" int sdrx_engine_push_block(sdrx_engine *e, const void *raw, int fmt, unsigned n_samples) {
+    if (!e || (!raw && n_samples)) return fail(SDRX_ERR_ARG, "null argument");
+    DevGuard g(e->dev);
+    return enqueue_block(e, raw, SRC_HOST, fmt, n_samples);
+}
+
+extern "C" int sdrx_engine_push_block_device(sdrx_engine *e, const void *d_raw, int fmt, unsigned n_samples) {
+    if (!e || (!d_raw && n_samples)) return fail(SDRX_ERR_ARG, "null argument");
+    DevGuard g(e->dev);
+    return enqueue_block(e, d_raw, SRC_DEVICE, fmt, n_samples);
+}
+
+extern "C" int sdrx_engine_last_out_len(sdrx_engine *e, unsigned *out_len) {
+    if (!e || !out_len) return fail(SDRX_ERR_ARG, "null argument");
+    *out_len = e->last_out_len;
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_engine_sync(sdrx_engine *e) {
+    if (!e) return fail(SDRX_ERR_ARG, "null engine");
+    DevGuard g(e->dev);
+    CU(cudaStreamSynchronize(e->s_copy));
+    CU(cudaStreamSynchronize(e->s_main));
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_engine_get_channel_iq(sdrx_engine *e, float *ch_iq) {
+    if (!e || !ch_iq) return fail(SDRX_ERR_ARG, "null argument");
+    if (e->blocks == 0) return fail(SDRX_ERR_STATE, "no block pushed yet");
+    DevGuard g(e->dev);
+    const OutSet &o = e->out[(e->blocks - 1) & 1];
+    if (e->last_out_len > 0)
+        CU(cudaMemcpy2DAsync(ch_iq, (size_t)e->last_out_len * sizeof(float2), o.ch_iq, (size_t)e->chiq_stride * sizeof(float2),
+                             (size_t)e->last_out_len * sizeof(float2), (size_t)e->C, cudaMemcpyDeviceToHost, e->s_main));
+    CU(cudaStreamSynchronize(e->s_main));
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs *out) {
+    if (!e || !out) return fail(SDRX_ERR_ARG, "null argument");
+    if (e->blocks == 0) return fail(SDRX_ERR_STATE, "no block pushed yet");
+    if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
+    if (!e->last_demod) return fail(SDRX_ERR_STATE, "the last block did not yield 512 samples per channel; boundary B did not run");
+    DevGuard g(e->dev);
+    int rc = copy_outputs(e, e->out[(e->blocks - 1) & 1], out);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(e->s_main));
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_engine_demod_block(sdrx_engine *e, const float *ch_iq, float pwr_dbfs) {
+    if (!e || !ch_iq) return fail(SDRX_ERR_ARG, "null argument");
+    if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
+    DevGuard g(e->dev);
+    OutSet &o = e->out[e->blocks & 1];
+    CU(cudaMemcpy2DAsync(o.ch_iq, (size_t)e->chiq_stride * sizeof(float2), ch_iq, (size_t)kChunk * sizeof(float2),
+                         (size_t)kChunk * sizeof(float2), (size_t)e->C, cudaMemcpyHostToDevice, e->s_main));
+    CU(cudaMemcpyAsync(o.pwr, &pwr_dbfs, sizeof(float), cudaMemcpyHostToDevice, e->s_main));
+    CU(cudaStreamSynchronize(e->s_main));     // pwr_dbfs lives on this stack frame
+    int rc = launch_demod(e, o, false, 0);
+    if (rc) return rc;
+    e->last_out_len = kChunk;
+    e->last_demod = true;
+    ++e->blocks;      // the output set alternates like a pushed block's; the channelizer state is untouched
+    return SDRX_OK;
+}
+
+extern "C" void *sdrx_engine_stream(sdrx_engine *e) { return e ? (void *)e->s_main : nullptr; }
+extern "C" uint64_t sdrx_engine_launch_count(sdrx_engine *e) { return e ? e->launches : 0; }
+extern "C" int sdrx_engine_uses_fast_path(sdrx_engine *e) { return e && e->use_fast ? 1 : 0; }
+extern "C" int sdrx_engine_set_timing(sdrx_engine *e, int enable) {
+    if (!e) return fail(SDRX_ERR_ARG, "null engine");
+    e->timing = enable != 0;
+    e->timing_valid = false;
+    return SDRX_OK;
+}
+extern "C" int sdrx_engine_last_timing(sdrx_engine *e, float *bank_ms, float *block_ms) {
+    if (!e) return fail(SDRX_ERR_ARG, "null engine");
+    if (!e->timing_valid) return fail(SDRX_ERR_STATE, "timing not enabled or no block pushed since");
+    DevGuard g(e->dev);
+    CU(cudaEventSynchronize(e->ev_t2));
+    float a = 0, b = 0;
+    CU(cudaEventElapsedTime(&a, e->ev_t0, e->ev_t1));
+    CU(cudaEventElapsedTime(&b, e->ev_t0, e->ev_t2));
+    if (bank_ms) *bank_ms = a;
+    if (block_ms) *block_ms = b;
+    return SDRX_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Carried state.  Layout: StateHeader, raw history (raw_hist * 8 bytes, wire format `fmt`), then for
+// each stage s >= 1 its [C][H-1] delay line, then AGC gain/power, LfAGC gain/power (float[C] each),
+// sql_state, sql_state_prev (u8[C] each) and the FIR2 ring as (ntaps-1) stereo frames, oldest first.
+namespace {
+
+struct StateHeader {
+    uint32_t magic, version;
+    int32_t  C, S, fmt, raw_hist, fir2_ntaps, demod;
+    int64_t  trans_pos;
+    uint64_t blocks;
+    int32_t  phase[SDRX_MAX_STAGES];
+    int32_t  H[SDRX_MAX_STAGES];
+};
+
+size_t state_bytes(const sdrx_engine *e) {
+    size_t n = sizeof(StateHeader) + (size_t)e->raw_hist * 8;
+    for (int s = 1; s < e->S; ++s) n += sizeof(float2) * (size_t)(e->H[s] - 1) * e->C;
+    if (!(e->flags & SDRX_FLAG_NO_DEMOD))
+        n += (size_t)e->C * (4 * sizeof(float) + 2) + sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1);
+    return n;
+}
+
+}  // namespace
+
+extern "C" size_t sdrx_engine_state_size(sdrx_engine *e) { return e ? state_bytes(e) : 0; }
+
+extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
+    if (!e || !buf) return fail(SDRX_ERR_ARG, "null argument");
+    if (size < state_bytes(e)) return fail(SDRX_ERR_ARG, "state buffer too small");
+    DevGuard g(e->dev);
+    CU(cudaStreamSynchronize(e->s_copy));
+    CU(cudaStreamSynchronize(e->s_main));
+    uint8_t *p = (uint8_t *)buf;
+    StateHeader h{};
+    h.magic = kStateMagic; h.version = 1;
+    h.C = e->C; h.S = e->S; h.fmt = e->fmt; h.raw_hist = e->raw_hist; h.fir2_ntaps = e->fir2_ntaps;
+    h.demod = (e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1;
+    h.trans_pos = e->trans_pos; h.blocks = e->blocks;
+    for (int s = 0; s < SDRX_MAX_STAGES; ++s) { h.phase[s] = e->phase[s]; h.H[s] = e->H[s]; }
+    memcpy(p, &h, sizeof(h)); p += sizeof(h);
+    const int bps = e->fmt >= 0 ? raw_bytes_per_sample(e->fmt) : 8;
+    const int last = (int)((e->blocks & 1) ^ 1);
+    memset(p, 0, (size_t)e->raw_hist * 8);
+    CU(cudaMemcpy(p, e->d_raw[last] + (size_t)e->prev_n * bps, (size_t)e->raw_hist * bps, cudaMemcpyDeviceToHost));
+    p += (size_t)e->raw_hist * 8;
+    for (int s = 1; s < e->S; ++s) {
+        const size_t row = sizeof(float2) * (size_t)(e->H[s] - 1);
+        if (row) CU(cudaMemcpy2D(p, row, e->d_stage_in[s], sizeof(float2) * (size_t)e->stage_stride[s], row, e->C, cudaMemcpyDeviceToHost));
+        p += row * e->C;
+    }
+    if (h.demod) {
+        const size_t C = (size_t)e->C;
+        CU(cudaMemcpy(p, e->st.agc_gain, C * 4, cudaMemcpyDeviceToHost)); p += C * 4;
+        CU(cudaMemcpy(p, e->st.agc_power, C * 4, cudaMemcpyDeviceToHost)); p += C * 4;
+        CU(cudaMemcpy(p, e->st.lf_gain, C * 4, cudaMemcpyDeviceToHost)); p += C * 4;
+        CU(cudaMemcpy(p, e->st.lf_power, C * 4, cudaMemcpyDeviceToHost)); p += C * 4;
+        CU(cudaMemcpy(p, e->st.sql_state, C, cudaMemcpyDeviceToHost)); p += C;
+        CU(cudaMemcpy(p, e->st.sql_prev, C, cudaMemcpyDeviceToHost)); p += C;
+        const size_t fb = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1);
+        if (fb) CU(cudaMemcpy(p, e->d_fir_hist, fb, cudaMemcpyDeviceToHost));
+        p += fb;
+    }
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t size) {
+    if (!e || !buf) return fail(SDRX_ERR_ARG, "null argument");
+    if (size < sizeof(StateHeader)) return fail(SDRX_ERR_ARG, "state buffer too small");
+    StateHeader h;
+    memcpy(&h, buf, sizeof(h));
+    if (h.magic != kStateMagic || h.version != 1) return fail(SDRX_ERR_ARG, "not an sdrx_b200 state blob");
+    if (h.C != e->C || h.S != e->S || h.raw_hist != e->raw_hist || h.fir2_ntaps != e->fir2_ntaps ||
+        h.demod != ((e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1))
+        return fail(SDRX_ERR_ARG, "state blob was saved by a differently configured engine");
+    for (int s = 0; s < e->S; ++s)
+        if (h.H[s] != e->H[s]) return fail(SDRX_ERR_ARG, "state blob stage layout differs");
+    if (size < state_bytes(e)) return fail(SDRX_ERR_ARG, "state buffer too small");
+    DevGuard g(e->dev);
+    CU(cudaStreamSynchronize(e->s_copy));
+    CU(cudaStreamSynchronize(e->s_main));
+    const uint8_t *p = (const uint8_t *)buf + sizeof(h);
+    e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = h.blocks;
+    for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = h.phase[s];
+    e->prev_n = 0;          // the history is parked at the very front of the "previous" buffer
+    e->last_out_len = 0; e->last_demod = false; e->timing_valid = false;
+    const int last = (int)((e->blocks & 1) ^ 1);
+    CU(cudaMemcpy(e->d_raw[last], p, (size_t)e->raw_hist * 8, cudaMemcpyHostToDevice));
+    p += (size_t)e->raw_hist * 8;
+    for (int s = 1; s < e->S; ++s) {
+        const size_t row = sizeof(float2) * (size_t)(e->H[s] - 1);
+        if (row) CU(cudaMemcpy2D(e->d_stage_in[s], sizeof(float2) * (size_t)e->stage_stride[s], p, row, row, e->C, cudaMemcpyHostToDevice));
+        p += row * e->C;
+    }
+    if (h.demod) {
+        const size_t C = (size_t)e->C;
+        CU(cudaMemcpy(e->st.agc_gain, p, C * 4, cudaMemcpyHostToDevice)); p += C * 4;
+        CU(cudaMemcpy(e->st.agc_power, p, C * 4, cudaMemcpyHostToDevice)); p += C * 4;
+        CU(cudaMemcpy(e->st.lf_gain, p, C * 4, cudaMemcpyHostToDevice)); p += C * 4;
+        CU(cudaMemcpy(e->st.lf_power, p, C * 4, cudaMemcpyHostToDevice)); p += C * 4;
+        CU(cudaMemcpy(e->st.sql_state, p, C, cudaMemcpyHostToDevice)); p += C;
+        CU(cudaMemcpy(e->st.sql_prev, p, C, cudaMemcpyHostToDevice)); p += C;
+        const size_t fb = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1);
+        if (fb) CU(cudaMemcpy(e->d_fir_hist, p, fb, cudaMemcpyHostToDevice));
+        p += fb;
+    }
+    return SDRX_OK;
+}

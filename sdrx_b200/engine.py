@@ -1,0 +1,227 @@
+"""Python host side of the B200 engine: a thin mirror of include/sdrx_b200.h.
+
+:class:`Engine` is the receiver chain of one GPU -- what ``data_cb`` (sdrx.cpp:306) plus
+``alsa_write_cb`` (sdrx.cpp:420) do per 32 ms block for every listened channel.  All compute happens
+in the CUDA library; numpy arrays only carry bytes across the boundary.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import FMT_F32, FMT_S16, FMT_U8, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, CHUNK, SdrxError, check
+from .config import ChannelPlan, make_translator, tables
+
+
+def fmt_of(raw: np.ndarray) -> int:
+    if raw.dtype == np.uint8:
+        return FMT_U8
+    if raw.dtype == np.int16:
+        return FMT_S16
+    if raw.dtype in (np.float32, np.complex64):
+        return FMT_F32
+    raise TypeError(f"unsupported IQ dtype {raw.dtype}: use uint8, int16, float32 or complex64")
+
+
+def n_samples_of(raw: np.ndarray) -> int:
+    return raw.size if raw.dtype == np.complex64 else raw.size // 2
+
+
+@dataclass
+class BlockOut:
+    pwr_dbfs: float
+    ch_iq: Optional[np.ndarray]
+    audio: np.ndarray
+    sql: np.ndarray
+    snr: np.ndarray
+    mix_pre: np.ndarray
+    mix: np.ndarray
+    pcm: np.ndarray
+    agc_gain: np.ndarray
+    lf_gain: np.ndarray
+
+
+class PinnedBuffer:
+    """cudaMallocHost-backed numpy array (sdrx_host_alloc)."""
+
+    def __init__(self, nbytes: int):
+        self._lib = _lib.load()
+        self.ptr = self._lib.sdrx_host_alloc(nbytes)
+        if not self.ptr:
+            raise SdrxError("sdrx_host_alloc failed: " + self._lib.sdrx_last_error().decode())
+        self.nbytes = nbytes
+        self.u8 = np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(self.ptr))
+
+    def view(self, dtype, count: Optional[int] = None) -> np.ndarray:
+        a = self.u8.view(dtype)
+        return a if count is None else a[:count]
+
+    def free(self):
+        if self.ptr:
+            self._lib.sdrx_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Engine:
+    def __init__(self, plan: ChannelPlan, device: int = 0, use_lf_agc: bool = False, lf_gain_db: float = 0.0,
+                 block_len: Optional[int] = None, force_generic: bool = False, demod: bool = True,
+                 translators: Optional[np.ndarray] = None):
+        self.lib = _lib.load()
+        self.plan = plan
+        self.device = device
+        self.C = len(plan.offsets)
+        rc_ = plan.rate
+        self.N = rc_.N
+        self.block_len = int(block_len or rc_.block_len)
+        t = tables()
+        if translators is None:
+            tr = np.zeros((self.C, self.N), dtype=np.complex64)
+            for c, off in enumerate(plan.offsets):
+                if off != 0:
+                    tr[c] = make_translator(rc_.N, rc_.z, off)
+        else:
+            tr = np.ascontiguousarray(translators, dtype=np.complex64)
+        has = np.asarray([1 if o != 0 else 0 for o in plan.offsets], dtype=np.uint8)
+        m = np.asarray([s[0] for s in rc_.stages], dtype=np.int32)
+        nt = np.asarray([len(s[1]) for s in rc_.stages], dtype=np.int32)
+        taps = np.concatenate([s[1] for s in rc_.stages]).astype(np.float32)
+        sql = np.asarray(plan.sql_levels, dtype=np.float32)
+        pos = np.asarray(plan.pos, dtype=np.int32)
+        fir2 = np.ascontiguousarray(t["coeff_bp4am_channel"], dtype=np.float32)
+        shape = np.ascontiguousarray(t["passband_shape"], dtype=np.float32)
+        rup = np.ascontiguousarray(t["ramp_up"], dtype=np.float32)
+        rdn = np.ascontiguousarray(t["ramp_down"], dtype=np.float32)
+        fp = lambda a: a.ctypes.data_as(_lib.c_float_p)   # noqa: E731
+        cfg = _lib.EngineConfig()
+        cfg.device = device
+        cfg.n_channels = self.C
+        cfg.translator_len = self.N
+        cfg.translators = tr.view(np.float32).ctypes.data_as(_lib.c_float_p)
+        cfg.has_translator = has.ctypes.data_as(_lib.c_u8_p)
+        cfg.n_stages = len(rc_.stages)
+        cfg.m = m.ctypes.data_as(_lib.c_int_p)
+        cfg.ntaps = nt.ctypes.data_as(_lib.c_int_p)
+        cfg.taps = fp(taps)
+        cfg.block_len = self.block_len
+        cfg.sql_level = fp(sql)
+        cfg.pos = pos.ctypes.data_as(_lib.c_int_p)
+        cfg.use_lf_agc = 1 if use_lf_agc else 0
+        cfg.lf_gain_db = lf_gain_db
+        cfg.fir2_taps, cfg.fir2_ntaps = fp(fir2), fir2.size
+        cfg.passband_shape, cfg.ramp_up, cfg.ramp_down = fp(shape), fp(rup), fp(rdn)
+        cfg.flags = (FLAG_FORCE_GENERIC if force_generic else 0) | (0 if demod else FLAG_NO_DEMOD)
+        self.demod = demod
+        h = C.c_void_p()
+        check(self.lib.sdrx_engine_create(C.byref(cfg), C.byref(h)))
+        self.h = h
+
+    # ---- block interface
+    def push(self, raw: np.ndarray, fmt: Optional[int] = None) -> None:
+        """Queue one block (host array; pinned arrays from :class:`PinnedBuffer` avoid the staging copy)."""
+        raw = np.ascontiguousarray(raw)
+        check(self.lib.sdrx_engine_push_block(self.h, raw.ctypes.data_as(C.c_void_p),
+                                              fmt_of(raw) if fmt is None else fmt, n_samples_of(raw)))
+        self._keep = raw      # a pinned source must stay alive until the copy has run
+
+    def push_device(self, d_ptr: int, fmt: int, n_samples: int) -> None:
+        check(self.lib.sdrx_engine_push_block_device(self.h, C.c_void_p(d_ptr), fmt, n_samples))
+
+    def out_len(self) -> int:
+        n = C.c_uint()
+        check(self.lib.sdrx_engine_last_out_len(self.h, C.byref(n)))
+        return n.value
+
+    def channel_iq(self) -> np.ndarray:
+        n = self.out_len()
+        out = np.empty((self.C, n), dtype=np.complex64)
+        check(self.lib.sdrx_engine_get_channel_iq(self.h, out.view(np.float32).ctypes.data_as(_lib.c_float_p)))
+        return out
+
+    def outputs(self, with_iq: bool = True) -> BlockOut:
+        C_ = self.C
+        audio = np.empty((C_, CHUNK), np.float32)
+        sql = np.empty(C_, np.uint8)
+        snr = np.empty(C_, np.float32)
+        mix_pre = np.empty(2 * CHUNK, np.float32)
+        mix = np.empty(2 * CHUNK, np.float32)
+        pcm = np.empty(2 * CHUNK, np.int16)
+        pwr = np.empty(1, np.float32)
+        ag = np.empty(C_, np.float32)
+        lg = np.empty(C_, np.float32)
+        o = _lib.BlockOutputs()
+        fp = lambda a: a.ctypes.data_as(_lib.c_float_p)   # noqa: E731
+        o.audio, o.sql_state, o.snr = fp(audio), sql.ctypes.data_as(_lib.c_u8_p), fp(snr)
+        o.mix_pre, o.mix, o.pcm, o.pwr_dbfs = fp(mix_pre), fp(mix), pcm.ctypes.data_as(_lib.c_i16_p), fp(pwr)
+        o.agc_gain, o.lf_gain = fp(ag), fp(lg)
+        check(self.lib.sdrx_engine_get_outputs(self.h, C.byref(o)))
+        return BlockOut(float(pwr[0]), self.channel_iq() if with_iq else None, audio, sql, snr, mix_pre, mix, pcm, ag, lg)
+
+    def process(self, raw: np.ndarray, fmt: Optional[int] = None) -> BlockOut:
+        self.push(raw, fmt)
+        return self.outputs()
+
+    def demod_block(self, ch_iq: np.ndarray, pwr_dbfs: float = 0.0) -> BlockOut:
+        """Boundary B alone on caller-supplied channel IQ [C,512]."""
+        x = np.ascontiguousarray(ch_iq, dtype=np.complex64)
+        assert x.shape == (self.C, CHUNK)
+        check(self.lib.sdrx_engine_demod_block(self.h, x.view(np.float32).ctypes.data_as(_lib.c_float_p), pwr_dbfs))
+        return self.outputs(with_iq=False)
+
+    def sync(self) -> None:
+        check(self.lib.sdrx_engine_sync(self.h))
+
+    def reset(self) -> None:
+        check(self.lib.sdrx_engine_reset(self.h))
+
+    # ---- carried state
+    def save_state(self) -> bytes:
+        n = self.lib.sdrx_engine_state_size(self.h)
+        buf = (C.c_uint8 * n)()
+        check(self.lib.sdrx_engine_save_state(self.h, buf, n))
+        return bytes(buf)
+
+    def load_state(self, blob: bytes) -> None:
+        buf = (C.c_uint8 * len(blob)).from_buffer_copy(blob)
+        check(self.lib.sdrx_engine_load_state(self.h, buf, len(blob)))
+
+    # ---- introspection
+    @property
+    def stream(self) -> int:
+        return int(self.lib.sdrx_engine_stream(self.h) or 0)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.sdrx_engine_launch_count(self.h))
+
+    @property
+    def uses_fast_path(self) -> bool:
+        return bool(self.lib.sdrx_engine_uses_fast_path(self.h))
+
+    def set_timing(self, on: bool) -> None:
+        check(self.lib.sdrx_engine_set_timing(self.h, 1 if on else 0))
+
+    def last_timing(self):
+        a, b = C.c_float(), C.c_float()
+        check(self.lib.sdrx_engine_last_timing(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def close(self) -> None:
+        if getattr(self, "h", None):
+            self.lib.sdrx_engine_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,96 @@
+"""Seeded test scenarios shared by the oracle tests, the golden-vector generator and the GPU parity
+tests (scaled so the CPU oracle finishes in seconds)."""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Callable, List, Optional, Sequence
+
+import numpy as np
+
+from sdrx_b200 import FMT_F32, FMT_S16, FMT_U8, Carrier, ChannelPlan, SyntheticSource
+
+
+@dataclass
+class Scenario:
+    name: str
+    rate: int
+    offsets: List[int]
+    carriers: List[Carrier]
+    fmt: int = FMT_F32
+    n_blocks: int = 8
+    noise_sigma: float = 0.01
+    seed: int = 12345
+    sql_levels: Optional[List[float]] = None
+    use_lf_agc: bool = False
+    lf_gain_db: float = 0.0
+
+    def plan(self) -> ChannelPlan:
+        return ChannelPlan.from_offsets(self.rate, self.offsets, self.sql_levels)
+
+    def source(self) -> SyntheticSource:
+        return SyntheticSource(self.rate, self.carriers, self.noise_sigma, self.seed, self.fmt, self.n_blocks)
+
+
+def _window(lo: int, hi: int) -> Callable[[int], bool]:
+    return lambda b: lo <= b < hi
+
+
+def config1() -> Scenario:
+    """RTL-SDR 2.4 MS/s uint8, one channel on a 25 kHz designator (118.275 -> tuner 118.3 MHz, offset -3),
+    AM 1 kHz tone keyed on for blocks 8..27: closed -> open (ramp up) -> closed (ramp down)."""
+    return Scenario("config1_rtl_2400_u8", 2400000, [-3],
+                    [Carrier(-3, 0.5, 1000.0, 0.5, _window(8, 28))], fmt=FMT_U8, n_blocks=40)
+
+
+def config2(fmt: int = FMT_F32, n_blocks: int = 12) -> Scenario:
+    """Airspy 10 MS/s, 8 channels spread over +-3 MHz with their own tones and keying schedules."""
+    offs = [-360, -121, -37, -1, 2, 40, 250, 479]
+    tones = [300.0, 700.0, 1000.0, 1300.0, 1700.0, 2100.0, 2600.0, 2400.0]
+    amps = [0.05, 0.02, 0.1, 0.008, 0.2, 0.03, 0.012, 0.06]
+    sched = [_window(1, 7), _window(0, 99), _window(3, 5), _window(2, 9), _window(4, 10), _window(0, 3),
+             _window(6, 99), _window(2, 4)]
+    return Scenario(f"config2_airspy_10000_{['u8', 's16', 'f32'][fmt]}", 10000000, offs,
+                    [Carrier(o, a, t, 0.5, s) for o, a, t, s in zip(offs, amps, tones, sched)],
+                    fmt=fmt, n_blocks=n_blocks, noise_sigma=0.002)
+
+
+def config2_variants() -> List[Scenario]:
+    a = config2()
+    a.name += "_lfagc_vol"
+    a.use_lf_agc, a.lf_gain_db, a.n_blocks = True, 6.0, 6
+    b = config2()
+    b.name += "_sql"
+    b.sql_levels, b.n_blocks = [0.0, 20.0, 9.0, 3.0, 9.0, 12.0, 0.0, 30.0], 6
+    return [a, b]
+
+
+def centre_channel() -> Scenario:
+    """A channel at the tuner centre takes the reference's no-translator path (msd.hpp:79-101)."""
+    return Scenario("centre_10000", 10000000, [0, 5], [Carrier(0, 0.1, 800.0), Carrier(5, 0.05, 1200.0)],
+                    n_blocks=3, noise_sigma=0.002)
+
+
+def other_rates() -> List[Scenario]:
+    """Every other sample rate the reference supports, two channels, three blocks (generic kernels)."""
+    out = []
+    for rate, span in ((960000, 40), (1200000, 50), (1440000, 60), (1600000, 70), (1920000, 90), (2560000, 120),
+                       (6000000, 280)):
+        offs = [-span, span // 3]
+        out.append(Scenario(f"rate_{rate}", rate, offs,
+                            [Carrier(offs[0], 0.2, 900.0), Carrier(offs[1], 0.1, 1500.0, 0.5, _window(1, 99))],
+                            fmt=FMT_U8 if rate < 3000000 else FMT_S16, n_blocks=3, noise_sigma=0.005))
+    return out
+
+
+def config3(n_blocks: int = 3, n_channels: int = 960) -> Scenario:
+    """Airspy 10 MS/s, the whole 8 MHz band: offsets -480..479, ~10 % of the channels keyed, amplitudes
+    log-uniform so that in-channel SNRs span roughly 15..45 dB."""
+    offs = list(range(-n_channels // 2, n_channels // 2))
+    rng = np.random.Generator(np.random.PCG64(777))
+    active = sorted(rng.choice(len(offs), size=max(1, len(offs) // 10), replace=False).tolist())
+    carriers = []
+    for i, k in enumerate(active):
+        amp = float(10 ** rng.uniform(-2.6, -1.3))
+        start = int(rng.integers(0, 2))
+        carriers.append(Carrier(offs[k], amp, float(rng.uniform(300, 3000)), 0.5, _window(start, 99)))
+    return Scenario(f"config3_band_{n_channels}", 10000000, offs, carriers, n_blocks=n_blocks, noise_sigma=0.0008)
