@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""Headline benchmark: channel-MS/s of the sdrx per-channel DSP chain at 10 MS/s IQ.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload config3|config2]
+
+One *step* = one 32 ms IQ block (320 000 complex samples @10 MS/s) through the whole chain for every
+channel: raw->float ingest, block power, NCO translate + 4-stage decimating FIR (channel bank), AGC,
+AM envelope, SNR squelch (window + 512-pt FFT), pan mix, FIR2, s16.  channel-MS/s = channels x input
+samples / time / 1e6; divide by 10 for the number of real-time 8.33 kHz channels.
+
+Arms
+  value      device-resident IQ (a ring of blocks larger than L2), whole block timed with CUDA events
+             on the engine's stream, max over ranks.
+  e2e        the same chain through the C-ABI call a host makes (sdrx_engine_push_block from pinned
+             host memory + sdrx_engine_get_outputs into pinned host memory): H2D and D2H inside the
+             timed region every step.
+  reference  (--impl reference) the reference's own msd.hpp/agc.hpp/fir.hpp, Release flags, its
+             thread-per-channel DS mode (ds.hpp) on all host cores, same workload and metric.
+
+N > 1: one process per GPU (torchrun); every rank runs an independent 10 MS/s stream with the full
+channel set (stream-sharded, SURVEY.md §8e "replicas only", no data-path collective) -> weak scaling.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+RATE = 10_000_000
+# algorithmic flops per (channel, input complex sample) as the reference computes it:
+# mix 6 + folded FIR stages 52/5 + 58/25 + 64/125 (+ 202/625 in the stage-4 kernel)
+FLOP_BANK = 6.0 + 52.0 / 5 + 58.0 / 25 + 64.0 / 125
+FLOP_CHAIN = FLOP_BANK + 202.0 / 625
+NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12
+
+
+def workload(name: str):
+    from sdrx_b200 import Carrier, ChannelPlan
+    if name == "config3":
+        offs = list(range(-480, 480))
+        desc = "config3: Airspy 10 MS/s f32 IQ, full 8 MHz band, 960 channels at 8.33 kHz spacing, squelch+panorama"
+    elif name == "config2":
+        offs = [-360, -121, -37, -1, 2, 40, 250, 479]
+        desc = "config2: Airspy 10 MS/s f32 IQ, 8 channels at 8.33 kHz designators, squelch+panorama"
+    else:
+        raise SystemExit(f"unknown workload {name}")
+    rng = np.random.Generator(np.random.PCG64(777))
+    act = sorted(rng.choice(len(offs), size=min(len(offs), 24), replace=False).tolist())
+    carriers = [Carrier(offs[k], float(10 ** rng.uniform(-2.4, -1.3)), float(rng.uniform(300, 3000)), 0.5,
+                        (lambda b, k=k: (b + k) % 4 != 0)) for k in act]
+    return ChannelPlan.from_offsets(RATE, offs), carriers, desc
+
+
+def synth_blocks(carriers, n: int, seed: int):
+    from sdrx_b200 import SyntheticSource
+    src = SyntheticSource(RATE, carriers, noise_sigma=0.0008, seed=seed, n_blocks=n)
+    return [src.block(b) for b in range(n)]
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self) -> dict:
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().splitlines():
+            p = [x.strip() for x in line.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def fp32_peak():
+    """FP32 CUDA-core peak for the roofline: the FMA micro-benchmark measured on this pool's B200
+    (profiles/fp32_peak.json, tools/microbench/fp32_peak.cu) or, failing that, the nominal figure."""
+    p = os.path.join(ROOT, "profiles", "fp32_peak.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["fp32_tflops"]), "measured (profiles/fp32_peak.json: " + d.get("how", "FFMA micro-benchmark") + ")"
+    return NOMINAL_FP32_TFLOPS, "nominal 148 SM x 128 lanes x 2 x 1.965 GHz (MEASURED_PEAKS.json has no FP32 entry)"
+
+
+# ------------------------------------------------------------------------------------------------
+def time_reference(plan, blocks, steps: int, warmup: int, n_channels: int, threaded: bool = True):
+    """The reference's own classes (oracle/_ref/libsdrx_ref_avx2.so: msd.hpp AVX2 path, Release flags)
+    through the restated sdrx.cpp glue; thread-per-channel DS mode when `threaded`."""
+    from oracle import bindings as ob
+    backend = "ref_avx2" if ob.backend_available("ref_avx2") else ("ref" if ob.backend_available("ref") else None)
+    offs = plan.offsets[:n_channels]
+    if backend is not None:
+        rx = ob.RefRx(RATE, offs, None, threaded=threaded, backend=backend)
+        kind = "reference"
+    else:       # the reference build did not travel: time the plain-C port instead
+        from tests.harness import product_tables
+        rx = ob.OracleRx(product_tables(RATE), offs)
+        kind, threaded = "port", False
+    nb = len(blocks)
+    for i in range(warmup):
+        rx.process(blocks[i % nb], 2)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        rx.ingest(blocks[i % nb], 2)
+        rx.channelize_discard()
+        rx.demod()
+    dt = time.perf_counter() - t0
+    cores = os.cpu_count() or 1
+    used = min(cores, len(offs)) if threaded else 1
+    return dt / steps, kind, backend or "oracle", used
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    plan, carriers, desc = workload(args.workload)
+    blocks = synth_blocks(carriers, 2, 1)
+    C_ = len(plan.offsets)
+    L = plan.rate.block_len
+    per_step, kind, backend, used = time_reference(plan, blocks, args.steps, max(args.warmup, 1), C_)
+    val = C_ * L / per_step / 1e6
+    sample = f"all {C_} channels, one 32 ms block per step, {args.steps} steps, reference -t mode (one DS thread per channel)"
+    line = {
+        "impl": "reference", "metric": "channel-MS/s", "value": val, "unit": "channel-MS/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc, "channels": C_, "block_len": L, "sample_rate": RATE, "wire_format": "f32"},
+        "cpu_baseline": {"value": val, "unit": "channel-MS/s", "cores": used, "kind": kind, "sample": sample,
+                         "build": backend},
+        "e2e": {"value": val, "unit": "channel-MS/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "realtime_channels": val / (RATE / 1e6),
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from sdrx_b200 import Engine, PinnedBuffer, _lib
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (sdrx_b200 has no CPU path)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    plan, carriers, desc = workload(args.workload)
+    C_ = len(plan.offsets)
+    L = plan.rate.block_len
+    lib = _lib.load()
+    eng = Engine(plan, device=local)
+    stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
+
+    # ---- synthetic IQ: a few distinct blocks, laid out as a device ring larger than L2 (126 MB)
+    n_distinct = 4
+    blocks = synth_blocks(carriers, n_distinct, 1 + rank)
+    blk_bytes = blocks[0].nbytes
+    ring = max(8, int(np.ceil(140e6 / blk_bytes)))          # 55 x 2.56 MB = 141 MB of f32 IQ
+    d_ring = lib.sdrx_device_alloc(local, ring * blk_bytes)
+    if not d_ring:
+        raise SystemExit("device ring allocation failed")
+    for i in range(ring):
+        b = blocks[i % n_distinct]
+        _lib.check(lib.sdrx_device_upload(local, C.c_void_p(d_ring + i * blk_bytes), b.ctypes.data_as(C.c_void_p), blk_bytes))
+
+    def step_device(i):
+        eng.push_device(d_ring + (i % ring) * blk_bytes, 2, L)
+
+    # ---- value leg
+    for i in range(max(args.warmup, 3)):
+        step_device(i)
+    eng.sync()
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    l0 = eng.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for i in range(args.steps):
+        step_device(args.warmup + i)
+    ev1.record(stream)
+    eng.sync()
+    barrier()
+    launches = eng.launch_count - l0
+    clocks = sampler.stop()
+    ms = ev0.elapsed_time(ev1)
+    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    per_step_ms = ms_total / args.steps
+    value = world * C_ * L / (per_step_ms * 1e-3) / 1e6
+
+    # ---- per-kernel time of the dominant kernel (channel bank), CUDA events around it on its stream
+    eng.set_timing(True)
+    bank, whole = [], []
+    for i in range(min(args.steps, 20)):
+        step_device(i)
+        eng.sync()
+        a, b = eng.last_timing()
+        bank.append(a)
+        whole.append(b)
+    eng.set_timing(False)
+    bank_ms = statistics.mean(bank)
+    peak, peak_how = fp32_peak()
+    flop_bank = FLOP_BANK if eng.uses_fast_path else FLOP_CHAIN
+    achieved = flop_bank * C_ * L / (bank_ms * 1e-3) / 1e12
+    roofline = {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "channel bank (mix + decimating FIR stages)" if eng.uses_fast_path
+                else "generic channelizer kernels (all stages)",
+                "kernel_ms": bank_ms, "block_ms_serialised": statistics.mean(whole), "share_of_step": bank_ms / statistics.mean(whole),
+                "algorithmic_flop_per_channel_sample": flop_bank, "peak_source": peak_how}
+    prof = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(prof):
+        with open(prof) as f:
+            roofline["traffic"] = json.load(f).get("bank_dram_bytes_per_launch")
+
+    # ---- e2e leg: pinned host IQ in, pinned host results out, through the C ABI, every step
+    pins = [PinnedBuffer(blk_bytes) for _ in range(n_distinct)]
+    for p, b in zip(pins, blocks):
+        p.view(np.complex64, L)[:] = b
+    hviews = [p.view(np.complex64, L) for p in pins]
+    ostruct, oarr, d2h = eng.make_output_buffers(pinned=True)
+    for i in range(3):
+        eng.push(hviews[i % n_distinct])
+        eng.outputs_into(ostruct)
+    barrier()
+    t0 = time.perf_counter()
+    ev0.record(stream)
+    for i in range(args.steps):
+        eng.push(hviews[i % n_distinct])
+        eng.outputs_into(ostruct)
+    ev1.record(stream)
+    eng.sync()
+    wall = (time.perf_counter() - t0) * 1e3
+    barrier()
+    e2e_ms = max(ev0.elapsed_time(ev1), wall)       # host-inclusive: the later of device span and wall clock
+    t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_val = world * C_ * L / (float(t.item()) / args.steps * 1e-3) / 1e6
+    e2e = {"value": e2e_val, "unit": "channel-MS/s", "h2d_bytes_per_step": blk_bytes, "d2h_bytes_per_step": d2h,
+           "ms_per_step": float(t.item()) / args.steps}
+
+    # ---- CPU baseline on this box's host cores (rank 0, N = 1 only): bounded sample of the same workload
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cs = min(C_, 4 * (os.cpu_count() or 1), 256)
+        per_step, kind, backend, used = time_reference(plan, blocks, 4, 1, cs)
+        cpu = {"value": cs * L / per_step / 1e6, "unit": "channel-MS/s", "cores": used, "kind": kind,
+               "sample": f"first {cs} of {C_} channels, 4 blocks of 32 ms, reference -t mode (one DS thread per channel), build {backend}",
+               "host_cpus": os.cpu_count()}
+        per1, _, _, _ = time_reference(plan, blocks, 2, 1, min(C_, 8), threaded=False)
+        cpu["single_core_value"] = min(C_, 8) * L / per1 / 1e6
+
+    if rank == 0:
+        line = {
+            "metric": "channel-MS/s", "value": value, "unit": "channel-MS/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": per_step_ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "channels": C_, "block_len": L, "sample_rate": RATE, "wire_format": "f32",
+                       "parallelism": f"stream-sharded x{world} (one independent 10 MS/s stream per GPU, no collective)",
+                       "l2": f"inputs cycle through a {ring}-block device ring ({ring * blk_bytes / 1e6:.0f} MB > 126 MB L2)",
+                       "specialised_bank": bool(eng.uses_fast_path)},
+            "realtime_channels": value / (RATE / 1e6),
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        }
+        print(json.dumps(line))
+    eng.close()
+    lib.sdrx_device_free(local, C.c_void_p(d_ring))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="config3", choices=["config3", "config2"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    return run_reference(args) if args.impl == "reference" else run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -166,6 +166,34 @@ class Engine:
         check(self.lib.sdrx_engine_get_outputs(self.h, C.byref(o)))
         return BlockOut(float(pwr[0]), self.channel_iq() if with_iq else None, audio, sql, snr, mix_pre, mix, pcm, ag, lg)
 
+    def make_output_buffers(self, pinned: bool = True, want: Sequence[str] = ("audio", "sql_state", "snr", "mix", "pcm", "pwr_dbfs")):
+        """Reusable result buffers for :meth:`outputs_into` (pinned: D2H straight into them).  Returns
+        ``(struct, arrays, nbytes)``; only the fields named in ``want`` are fetched."""
+        C_ = self.C
+        spec = {"audio": (np.float32, C_ * CHUNK), "sql_state": (np.uint8, C_), "snr": (np.float32, C_),
+                "mix_pre": (np.float32, 2 * CHUNK), "mix": (np.float32, 2 * CHUNK), "pcm": (np.int16, 2 * CHUNK),
+                "pwr_dbfs": (np.float32, 1), "agc_gain": (np.float32, C_), "lf_gain": (np.float32, C_)}
+        o = _lib.BlockOutputs()
+        arrays, keep, total = {}, [], 0
+        for name in want:
+            dt, n = spec[name]
+            nbytes = n * np.dtype(dt).itemsize
+            if pinned:
+                pb = PinnedBuffer(nbytes)
+                keep.append(pb)
+                a = pb.view(dt, n)
+            else:
+                a = np.empty(n, dt)
+            arrays[name] = a
+            total += nbytes
+            ptr_t = {np.float32: _lib.c_float_p, np.uint8: _lib.c_u8_p, np.int16: _lib.c_i16_p}[dt]
+            setattr(o, name, a.ctypes.data_as(ptr_t))
+        arrays["_keep"] = keep
+        return o, arrays, total
+
+    def outputs_into(self, struct) -> None:
+        check(self.lib.sdrx_engine_get_outputs(self.h, C.byref(struct)))
+
     def process(self, raw: np.ndarray, fmt: Optional[int] = None) -> BlockOut:
         self.push(raw, fmt)
         return self.outputs()
