@@ -18,12 +18,15 @@ namespace sdrx {
 //   table        [N][Cpad] translator, transposed so that a warp of 32 channels reads 256 B
 //   has_tr[c]    0 -> the reference's no-translator path (msd.hpp:79-101), no multiply at all
 //   pos0         trans_pos_ of call-relative input 0
+//   valid_lo     buffer index of the first sample of the stream still in the history prefix; anything
+//                before it is the reference's zero-initialised delay line (msd.hpp:167) -- float 0, which
+//                a zero *byte* is not in the u8 wire format
 // grid (ceil(n_out/8), Cpad/32), block (32, 8): lane = channel, threadIdx.y = output.
 template <int FMT>
 static __global__ void __launch_bounds__(256)
 k_mix_fir_generic(const void *__restrict__ raw, int hist, const float2 *__restrict__ table, int Cpad, int C,
                   int N, int pos0, const uint8_t *__restrict__ has_tr, const float *__restrict__ h, int H, int m,
-                  int first, int n_out, float2 *__restrict__ out, long out_stride, int out_off) {
+                  int first, int n_out, float2 *__restrict__ out, long out_stride, int out_off, int valid_lo) {
     const int c = blockIdx.y * 32 + threadIdx.x;
     const int k = blockIdx.x * 8 + threadIdx.y;
     if (k >= n_out || c >= C) return;
@@ -38,8 +41,8 @@ k_mix_fir_generic(const void *__restrict__ raw, int hist, const float2 *__restri
 
     float re = 0.0f, im = 0.0f;
     for (int i = 0; i < half; ++i) {
-        float2 a = load_iq<FMT>(raw, p_lo + i);
-        float2 b = load_iq<FMT>(raw, p_lo + (H - 1) - i);
+        float2 a = load_iq_from<FMT>(raw, p_lo + i, valid_lo);
+        float2 b = load_iq_from<FMT>(raw, p_lo + (H - 1) - i, valid_lo);
         if (tr_on) {
             a = cmul_exact(a, __ldg(table + (long)idx_lo * Cpad + c));
             b = cmul_exact(b, __ldg(table + (long)idx_hi * Cpad + c));
@@ -51,7 +54,7 @@ k_mix_fir_generic(const void *__restrict__ raw, int hist, const float2 *__restri
         if (--idx_hi < 0) idx_hi = N - 1;
     }
     {
-        float2 a = load_iq<FMT>(raw, p_lo + half);
+        float2 a = load_iq_from<FMT>(raw, p_lo + half, valid_lo);
         if (tr_on) a = cmul_exact(a, __ldg(table + (long)idx_lo * Cpad + c));
         const float hv = __ldg(h + half);
         re = __fadd_rn(re, __fmul_rn(a.x, hv));

@@ -47,6 +47,11 @@ __device__ __forceinline__ float2 load_iq(const void *raw, long idx) {
     return convert_iq<FMT>(__ldg(reinterpret_cast<const V *>(raw) + idx));
 }
 
+template <int FMT>
+__device__ __forceinline__ float2 load_iq_from(const void *raw, long idx, int valid_lo) {
+    return idx >= valid_lo ? load_iq<FMT>(raw, idx) : make_float2(0.0f, 0.0f);
+}
+
 // ---- exact complex helpers (std::complex<float> as gcc evaluates it, no contraction) --------
 __device__ __forceinline__ float2 cmul_exact(float2 a, float2 b) {   // msd.hpp:134
     return make_float2(__fsub_rn(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y)),
@@ -59,6 +64,61 @@ __device__ __forceinline__ float norm_exact(float2 a) {               // std::no
 __device__ __forceinline__ float abs_exact(float2 a) {
     double x = (double)a.x, y = (double)a.y;
     return __double2float_rn(__dsqrt_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y))));
+}
+
+// ---- log10f exactly as the host libm computes it -------------------------------------------------
+// The squelch SNR (sdrx.cpp:566) goes through glibc's log10f, which is not correctly rounded, so a
+// generic device log10f differs from it in the last bit for ~5 % of arguments.  This restates glibc
+// 2.39's algorithm: sysdeps/ieee754/flt-32/e_log10f.c (fdlibm split y*log10_2lo + ivln10*logf(x) +
+// y*log10_2hi in float) over the table-driven logf of sysdeps/ieee754/flt-32/e_logf.c (16-entry
+// table, degree-3 polynomial, double arithmetic).  tests/test_log10f.py checks the same restatement
+// in C against the host's log10f over every positive float.
+__device__ const double kLogfTab[16][2] = {
+    {0x1.661ec79f8f3bep+0, -0x1.57bf7808caadep-2}, {0x1.571ed4aaf883dp+0, -0x1.2bef0a7c06ddbp-2},
+    {0x1.49539f0f010bp+0, -0x1.01eae7f513a67p-2},  {0x1.3c995b0b80385p+0, -0x1.b31d8a68224e9p-3},
+    {0x1.30d190c8864a5p+0, -0x1.6574f0ac07758p-3}, {0x1.25e227b0b8eap+0, -0x1.1aa2bc79c81p-3},
+    {0x1.1bb4a4a1a343fp+0, -0x1.a4e76ce8c0e5ep-4}, {0x1.12358f08ae5bap+0, -0x1.1973c5a611cccp-4},
+    {0x1.0953f419900a7p+0, -0x1.252f438e10c1ep-5}, {0x1p+0, 0x0p+0},
+    {0x1.e608cfd9a47acp-1, 0x1.aa5aa5df25984p-5},  {0x1.ca4b31f026aap-1, 0x1.c5e53aa362eb4p-4},
+    {0x1.b2036576afce6p-1, 0x1.526e57720db08p-3},  {0x1.9c2d163a1aa2dp-1, 0x1.bc2860d22477p-3},
+    {0x1.886e6037841edp-1, 0x1.1058bc8a07ee1p-2},  {0x1.767dcf5534862p-1, 0x1.4043057b6ee09p-2}};
+
+__device__ __forceinline__ float logf_glibc_normal(float x) {     // x finite, normal, > 0
+    const uint32_t ix = __float_as_uint(x);
+    if (ix == 0x3f800000u) return 0.0f;
+    const uint32_t tmp = ix - 0x3f330000u;
+    const int i = (int)((tmp >> 19) & 15u);
+    const int k = (int)tmp >> 23;
+    const uint32_t iz = ix - (tmp & 0xff800000u);
+    const double invc = kLogfTab[i][0], logc = kLogfTab[i][1];
+    const double z = (double)__uint_as_float(iz);
+    const double r = __dadd_rn(__dmul_rn(z, invc), -1.0);
+    const double y0 = __dadd_rn(logc, __dmul_rn((double)k, 0x1.62e42fefa39efp-1));
+    const double r2 = __dmul_rn(r, r);
+    double y = __dadd_rn(__dmul_rn(0x1.5575b0be00b6ap-2, r), -0x1.ffffef20a4123p-2);
+    y = __dadd_rn(__dmul_rn(-0x1.00ea348b88334p-2, r2), y);
+    y = __dadd_rn(__dmul_rn(y, r2), __dadd_rn(y0, r));
+    return __double2float_rn(y);
+}
+
+__device__ __forceinline__ float log10f_glibc(float x) {
+    int32_t hx = (int32_t)__float_as_uint(x);
+    int32_t k = 0;
+    if (hx < 0x00800000) {
+        if ((hx & 0x7fffffff) == 0) return __fdiv_rn(-3.3554432000e+07f, fabsf(x));   // log(+-0) = -inf
+        if (hx < 0) return __fdiv_rn(__fsub_rn(x, x), __fsub_rn(x, x));               // log(-#) = NaN
+        k -= 25;
+        x = __fmul_rn(x, 3.3554432000e+07f);
+        hx = (int32_t)__float_as_uint(x);
+    }
+    if (hx >= 0x7f800000) return __fadd_rn(x, x);
+    k += (hx >> 23) - 127;
+    const int32_t i = (int32_t)(((uint32_t)k & 0x80000000u) >> 31);
+    hx = (hx & 0x007fffff) | ((0x7f - i) << 23);
+    const float y = (float)(k + i);
+    const float lx = logf_glibc_normal(__uint_as_float((uint32_t)hx));
+    const float z = __fadd_rn(__fmul_rn(y, 7.9034151668e-07f), __fmul_rn(4.3429449201e-01f, lx));
+    return __fadd_rn(z, __fmul_rn(y, 3.0102920532e-01f));
 }
 
 __host__ __device__ inline int div_up(long a, long b) { return (int)((a + b - 1) / b); }

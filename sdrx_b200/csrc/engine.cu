@@ -89,6 +89,7 @@ struct sdrx_engine {
     int fmt = -1;                        // wire format of the stream so far
     uint64_t blocks = 0;
     unsigned prev_n = 0;                 // samples of the previous block (for the raw carry)
+    int hist_valid = 0;                  // how many samples of the raw history prefix belong to the stream
     unsigned last_out_len = 0;
     bool last_demod = false;
     uint64_t launches = 0;
@@ -195,6 +196,7 @@ int reset_state(sdrx_engine *e) {
     e->fmt = -1;
     e->blocks = 0;
     e->prev_n = 0;
+    e->hist_valid = 0;
     e->last_out_len = 0;
     e->last_demod = false;
     e->timing_valid = false;
@@ -447,7 +449,8 @@ int launch_bank_generic(sdrx_engine *e, const uint8_t *raw, unsigned n, const in
                 dim3 grid(div_up(n_out[0], 8), e->Cpad / 32), block(32, 8);
                 k_mix_fir_generic<FMT><<<grid, block, 0, e->s_main>>>(
                     raw, e->raw_hist, e->d_table_t, e->Cpad, e->C, e->N, (int)e->trans_pos, e->d_has_tr,
-                    e->d_taps + e->tap_off[0], e->H[0], e->m[0], first[0], n_out[0], dst, dst_stride, dst_off);
+                    e->d_taps + e->tap_off[0], e->H[0], e->m[0], first[0], n_out[0], dst, dst_stride, dst_off,
+                    e->raw_hist - e->hist_valid);
             } else {
                 dim3 grid(div_up(n_out[s], 128), e->C);
                 k_fir_generic<<<grid, 128, 0, e->s_main>>>(e->d_stage_in[s], e->stage_stride[s], e->H[s] - 1,
@@ -591,6 +594,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     if (e->timing) { CU(cudaEventRecord(e->ev_t2, e->s_main)); e->timing_valid = true; }
 
     e->trans_pos = (e->trans_pos + n) % e->N;
+    e->hist_valid = (int)std::min<long>((long)e->raw_hist, (long)e->hist_valid + (long)n);
     e->prev_n = n;
     e->last_out_len = out_len;
     e->last_demod = demod;
@@ -697,7 +701,7 @@ namespace {
 
 struct StateHeader {
     uint32_t magic, version;
-    int32_t  C, S, fmt, raw_hist, fir2_ntaps, demod;
+    int32_t  C, S, fmt, raw_hist, hist_valid, fir2_ntaps, demod;
     int64_t  trans_pos;
     uint64_t blocks;
     int32_t  phase[SDRX_MAX_STAGES];
@@ -725,7 +729,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     uint8_t *p = (uint8_t *)buf;
     StateHeader h{};
     h.magic = kStateMagic; h.version = 1;
-    h.C = e->C; h.S = e->S; h.fmt = e->fmt; h.raw_hist = e->raw_hist; h.fir2_ntaps = e->fir2_ntaps;
+    h.C = e->C; h.S = e->S; h.fmt = e->fmt; h.raw_hist = e->raw_hist; h.hist_valid = e->hist_valid; h.fir2_ntaps = e->fir2_ntaps;
     h.demod = (e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1;
     h.trans_pos = e->trans_pos; h.blocks = e->blocks;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) { h.phase[s] = e->phase[s]; h.H[s] = e->H[s]; }
@@ -771,7 +775,7 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     const uint8_t *p = (const uint8_t *)buf + sizeof(h);
-    e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = h.blocks;
+    e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = h.blocks; e->hist_valid = h.hist_valid;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = h.phase[s];
     e->prev_n = 0;          // the history is parked at the very front of the "previous" buffer
     e->last_out_len = 0; e->last_demod = false; e->timing_valid = false;
