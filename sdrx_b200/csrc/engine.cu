@@ -89,7 +89,8 @@ struct sdrx_engine {
     int fmt = -1;                        // wire format of the stream so far
     uint64_t blocks = 0;
     unsigned prev_n = 0;                 // samples of the previous block (for the raw carry)
-    int hist_valid = 0;                  // how many samples of the raw history prefix belong to the stream
+    uint64_t total = 0;                  // samples pushed so far (what of the raw history belongs to the stream)
+    bool generic_stale = false;          // stage 1-2 delay lines not maintained (the specialised bank ran last)
     unsigned last_out_len = 0;
     bool last_demod = false;
     uint64_t launches = 0;
@@ -196,7 +197,8 @@ int reset_state(sdrx_engine *e) {
     e->fmt = -1;
     e->blocks = 0;
     e->prev_n = 0;
-    e->hist_valid = 0;
+    e->total = 0;
+    e->generic_stale = false;
     e->last_out_len = 0;
     e->last_demod = false;
     e->timing_valid = false;
@@ -255,6 +257,9 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     }
     e->taps.assign(cfg->taps, cfg->taps + off);
     e->raw_hist = std::max((e->H[0] - 1 + 7) / 8 * 8, 128);
+    const bool eligible = fast_eligible(S, e->m, e->H, e->N);
+    const bool want_fast = !(cfg->flags & SDRX_FLAG_FORCE_GENERIC) && eligible;
+    if (eligible) e->raw_hist = std::max(e->raw_hist, kFastRawHist);   // also when forced generic: state blobs stay portable
 
     CU(cudaStreamCreateWithFlags(&e->s_main, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
@@ -314,6 +319,12 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         e->chiq_stride = (long)std::max<size_t>(kChunk, (cap + 3) / 4 * 4);
         int rc = dalloc(&e->d_pwr_partial, kPwrPartials);
         if (rc) return rc;
+    }
+    if (want_fast) {
+        int rc = fast_init(e->fast, C, e->N, e->taps.data() + e->tap_off[0], e->taps.data() + e->tap_off[1],
+                           e->taps.data() + e->tap_off[2]);
+        if (rc) return rc;
+        e->use_fast = true;
     }
     for (int b = 0; b < kNBuf; ++b) {
         OutSet &o = e->out[b];
@@ -435,10 +446,13 @@ namespace {
 
 enum SrcKind { SRC_HOST, SRC_DEVICE, SRC_NONE };
 
+// Stages [s_begin, s_end) of the chain.  `hist` = buffer index of call-relative input 0, `pos0` its
+// trans_pos_, `valid_lo` the first buffer index that holds stream samples.
 template <int FMT>
-int launch_bank_generic(sdrx_engine *e, const uint8_t *raw, unsigned n, const int *first, const int *n_out, OutSet &o) {
+int launch_bank_generic(sdrx_engine *e, const uint8_t *raw, int hist, int pos0, int valid_lo, const int *first,
+                        const int *n_out, OutSet &o, int s_begin, int s_end, bool carry_last = false) {
     const int S = e->S;
-    for (int s = 0; s < S; ++s) {
+    for (int s = s_begin; s < s_end; ++s) {
         float2 *dst;
         long dst_stride;
         int dst_off;
@@ -448,9 +462,9 @@ int launch_bank_generic(sdrx_engine *e, const uint8_t *raw, unsigned n, const in
             if (s == 0) {
                 dim3 grid(div_up(n_out[0], 8), e->Cpad / 32), block(32, 8);
                 k_mix_fir_generic<FMT><<<grid, block, 0, e->s_main>>>(
-                    raw, e->raw_hist, e->d_table_t, e->Cpad, e->C, e->N, (int)e->trans_pos, e->d_has_tr,
+                    raw, hist, e->d_table_t, e->Cpad, e->C, e->N, pos0, e->d_has_tr,
                     e->d_taps + e->tap_off[0], e->H[0], e->m[0], first[0], n_out[0], dst, dst_stride, dst_off,
-                    e->raw_hist - e->hist_valid);
+                    valid_lo);
             } else {
                 dim3 grid(div_up(n_out[s], 128), e->C);
                 k_fir_generic<<<grid, 128, 0, e->s_main>>>(e->d_stage_in[s], e->stage_stride[s], e->H[s] - 1,
@@ -468,17 +482,58 @@ int launch_bank_generic(sdrx_engine *e, const uint8_t *raw, unsigned n, const in
             }
         }
     }
-    (void)n;
+    // the delay line of the stage after the last one run (materialisation of stages 1-2 only)
+    if (carry_last && s_end < S && e->H[s_end] > 1 && n_out[s_end - 1] > 0) {
+        k_carry_hist<<<e->C, 256, 0, e->s_main>>>(e->d_stage_in[s_end], e->stage_stride[s_end], e->H[s_end] - 1, n_out[s_end - 1]);
+        ++e->launches;
+    }
     CU(cudaGetLastError());
     return SDRX_OK;
 }
 
-int launch_bank_generic_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, unsigned n, const int *first,
-                            const int *n_out, OutSet &o) {
+int launch_bank_generic_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int hist, int pos0, int valid_lo, const int *first,
+                            const int *n_out, OutSet &o, int s_begin, int s_end, bool carry_last = false) {
     switch (fmt) {
-        case SDRX_FMT_U8:  return launch_bank_generic<SDRX_FMT_U8>(e, raw, n, first, n_out, o);
-        case SDRX_FMT_S16: return launch_bank_generic<SDRX_FMT_S16>(e, raw, n, first, n_out, o);
-        default:           return launch_bank_generic<SDRX_FMT_F32>(e, raw, n, first, n_out, o);
+        case SDRX_FMT_U8:  return launch_bank_generic<SDRX_FMT_U8>(e, raw, hist, pos0, valid_lo, first, n_out, o, s_begin, s_end, carry_last);
+        case SDRX_FMT_S16: return launch_bank_generic<SDRX_FMT_S16>(e, raw, hist, pos0, valid_lo, first, n_out, o, s_begin, s_end, carry_last);
+        default:           return launch_bank_generic<SDRX_FMT_F32>(e, raw, hist, pos0, valid_lo, first, n_out, o, s_begin, s_end, carry_last);
+    }
+}
+
+// The specialised bank keeps no stage 1-2 delay lines (it recomputes from the raw history).  Before the
+// generic kernels take over (ragged block) or the state is saved, rebuild them by running generic
+// stages 0-1 over the last 625 samples in front of buffer index `end_idx`: the last 18 / 20 outputs of
+// stages 1 / 2 depend on nothing older.  Stage phases are zero whenever this is needed.
+constexpr int kMaterialize = 625;
+int materialize_generic(sdrx_engine *e, int fmt, const uint8_t *buf, long end_idx, uint64_t total_before_end) {
+    if (!e->generic_stale) return SDRX_OK;
+    const int hist = (int)(end_idx - kMaterialize);
+    const int valid_lo = (int)std::max<long>(0, end_idx - (long)std::min<uint64_t>(total_before_end, (uint64_t)end_idx));
+    long pos = ((long)e->trans_pos - kMaterialize) % e->N;
+    if (pos < 0) pos += e->N;
+    int first[SDRX_MAX_STAGES] = {0}, n_out[SDRX_MAX_STAGES] = {0};
+    long n_in = kMaterialize;
+    for (int s = 0; s < 2; ++s) { first[s] = e->m[s] - 1; n_out[s] = (int)(n_in / e->m[s]); n_in = n_out[s]; }
+    OutSet dummy{};
+    int rc = launch_bank_generic_fmt(e, fmt, buf, hist, (int)pos, valid_lo, first, n_out, dummy, 0, 2, true);
+    if (rc) return rc;
+    e->generic_stale = false;
+    return SDRX_OK;
+}
+
+template <int FMT>
+int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o) {
+    float2 *dst; long stride; int off;
+    if (e->S > 3) { dst = e->d_stage_in[3]; stride = e->stage_stride[3]; off = e->H[3] - 1; }
+    else          { dst = o.ch_iq;          stride = e->chiq_stride;     off = 0; }
+    return fast_launch<FMT>(e->fast, e->s_main, raw, e->raw_hist, valid_lo, e->d_table_t, e->Cpad, e->N, (int)e->trans_pos, n,
+                            dst, stride, off, &e->launches);
+}
+int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o) {
+    switch (fmt) {
+        case SDRX_FMT_U8:  return launch_bank_fast<SDRX_FMT_U8>(e, raw, valid_lo, n, o);
+        case SDRX_FMT_S16: return launch_bank_fast<SDRX_FMT_S16>(e, raw, valid_lo, n, o);
+        default:           return launch_bank_fast<SDRX_FMT_F32>(e, raw, valid_lo, n, o);
     }
 }
 
@@ -573,8 +628,9 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     }
 
     // ---- stage bookkeeping (MSD::S::isn_, msd.hpp:240-244): which inputs complete an output
-    int first[SDRX_MAX_STAGES], n_out[SDRX_MAX_STAGES];
+    int first[SDRX_MAX_STAGES], n_out[SDRX_MAX_STAGES], phase_in[SDRX_MAX_STAGES] = {0};
     long n_in = n;
+    for (int s = 0; s < e->S; ++s) phase_in[s] = e->phase[s];
     for (int s = 0; s < e->S; ++s) {
         first[s] = e->m[s] - 1 - e->phase[s];
         n_out[s] = (int)((e->phase[s] + n_in) / e->m[s]);
@@ -586,7 +642,17 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     const bool demod = !(e->flags & SDRX_FLAG_NO_DEMOD) && out_len == (unsigned)kChunk;
     if (demod && n > 0) { int rc = launch_power(e, fmt, buf, n); if (rc) return rc; }
 
-    int rc = launch_bank_generic_fmt(e, fmt, buf, n, first, n_out, o);
+    const int valid_lo = (int)std::max<long>(0, (long)e->raw_hist - (long)std::min<uint64_t>(e->total, (uint64_t)e->raw_hist));
+    const bool fast = e->use_fast && n > 0 && n % kUnit == 0 && phase_in[0] == 0 && phase_in[1] == 0 && phase_in[2] == 0;
+    int rc;
+    if (fast) {
+        rc = launch_bank_fast_fmt(e, fmt, buf, valid_lo, n, o);
+        if (!rc) rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 3, e->S);
+        e->generic_stale = true;
+    } else {
+        rc = materialize_generic(e, fmt, buf, e->raw_hist, e->total);
+        if (!rc) rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 0, e->S);
+    }
     if (rc) return rc;
     if (e->timing) CU(cudaEventRecord(e->ev_t1, e->s_main));
 
@@ -594,7 +660,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     if (e->timing) { CU(cudaEventRecord(e->ev_t2, e->s_main)); e->timing_valid = true; }
 
     e->trans_pos = (e->trans_pos + n) % e->N;
-    e->hist_valid = (int)std::min<long>((long)e->raw_hist, (long)e->hist_valid + (long)n);
+    e->total += n;
     e->prev_n = n;
     e->last_out_len = out_len;
     e->last_demod = demod;
@@ -701,7 +767,8 @@ namespace {
 
 struct StateHeader {
     uint32_t magic, version;
-    int32_t  C, S, fmt, raw_hist, hist_valid, fir2_ntaps, demod;
+    int32_t  C, S, fmt, raw_hist, fir2_ntaps, demod;
+    uint64_t total;
     int64_t  trans_pos;
     uint64_t blocks;
     int32_t  phase[SDRX_MAX_STAGES];
@@ -726,10 +793,16 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
+    if (e->generic_stale) {      // the blob always carries the stage delay lines (a generic engine can load it)
+        const int last_ = (int)((e->blocks & 1) ^ 1);
+        int rc = materialize_generic(e, e->fmt, e->d_raw[last_], (long)e->raw_hist + (long)e->prev_n, e->total);
+        if (rc) return rc;
+        CU(cudaStreamSynchronize(e->s_main));
+    }
     uint8_t *p = (uint8_t *)buf;
     StateHeader h{};
     h.magic = kStateMagic; h.version = 1;
-    h.C = e->C; h.S = e->S; h.fmt = e->fmt; h.raw_hist = e->raw_hist; h.hist_valid = e->hist_valid; h.fir2_ntaps = e->fir2_ntaps;
+    h.C = e->C; h.S = e->S; h.fmt = e->fmt; h.raw_hist = e->raw_hist; h.total = e->total; h.fir2_ntaps = e->fir2_ntaps;
     h.demod = (e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1;
     h.trans_pos = e->trans_pos; h.blocks = e->blocks;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) { h.phase[s] = e->phase[s]; h.H[s] = e->H[s]; }
@@ -775,7 +848,7 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     const uint8_t *p = (const uint8_t *)buf + sizeof(h);
-    e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = h.blocks; e->hist_valid = h.hist_valid;
+    e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = h.blocks; e->total = h.total; e->generic_stale = false;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = h.phase[s];
     e->prev_n = 0;          // the history is parked at the very front of the "previous" buffer
     e->last_out_len = 0; e->last_demod = false; e->timing_valid = false;

@@ -35,7 +35,7 @@ def _assert_exact(got, want):
         assert np.array_equal(x.mix_pre, y.mix_pre), f"block {i} mix_pre"
         assert np.array_equal(x.mix, y.mix), f"block {i} mix"
         assert np.array_equal(x.pcm, y.pcm), f"block {i} pcm"
-        assert abs(x.pwr_dbfs - y.pwr_dbfs) < 1e-3, f"block {i} power {x.pwr_dbfs} vs {y.pwr_dbfs}"
+        assert abs(x.pwr_dbfs - y.pwr_dbfs) < 2e-2, f"block {i} power {x.pwr_dbfs} vs {y.pwr_dbfs}"   # display value; tree sum vs the reference's sequential float sum
 
 
 def _assert_close(got, want, lvl):
@@ -154,7 +154,7 @@ def test_ragged_and_empty_blocks_through_the_channelizer():
     plan = cf.ChannelPlan.from_offsets(10000000, [7, 0, -333])
     rng = np.random.default_rng(5)
     x = (rng.standard_normal(60000) + 1j * rng.standard_normal(60000)).astype(np.complex64)
-    eng = Engine(plan, demod=False, block_len=40000)
+    eng = Engine(plan, demod=False, block_len=40000, force_generic=True)
     msd = [ob.OracleMSD(cf.make_translator(rc.N, rc.z, o) if o else None, rc.stages) for o in plan.offsets]
     pos = 0
     for n in [1, 3, 0, 17, 1000, 4096, 7, 20001, 625, 34250]:
@@ -167,6 +167,45 @@ def test_ragged_and_empty_blocks_through_the_channelizer():
         pos += n
     assert pos == x.size
     eng.close()
+
+
+def test_specialised_bank_hands_over_to_generic_kernels_mid_stream():
+    """Whole multiples of 125 samples take the specialised bank, anything else the generic kernels; the
+    hand-over (delay lines rebuilt from the raw history) and the way back must be seamless."""
+    from sdrx_b200 import Engine
+    rc = cf.rate_config(10000000)
+    plan = cf.ChannelPlan.from_offsets(10000000, [7, 0, -333, 479])
+    rng = np.random.default_rng(6)
+    x = (rng.standard_normal(200000) + 1j * rng.standard_normal(200000)).astype(np.complex64)
+    eng = Engine(plan, demod=False, block_len=80000)
+    assert eng.uses_fast_path
+    msd = [ob.OracleMSD(cf.make_translator(rc.N, rc.z, o) if o else None, rc.stages) for o in plan.offsets]
+    pos = 0
+    got, want = [], [[] for _ in msd]
+    for n in [40000, 625, 3, 17, 1605, 20000, 80000, 1250, 7, 618, 55875]:
+        eng.push(x[pos:pos + n])
+        if eng.out_len():
+            got.append(eng.channel_iq())
+        for c, m in enumerate(msd):
+            want[c].append(m.decimate(x[pos:pos + n]))
+        pos += n
+    assert pos == x.size
+    got = np.concatenate(got, axis=1)
+    for c in range(len(msd)):
+        w = np.concatenate(want[c])
+        assert got[c].size == w.size
+        assert rel_rms(got[c], w) < 2e-6, (c, rel_rms(got[c], w))
+    blob = eng.save_state()          # saved right after a specialised block
+    more = (rng.standard_normal(40000) + 1j * rng.standard_normal(40000)).astype(np.complex64)
+    eng.push(more)
+    a = eng.channel_iq()
+    g = Engine(plan, demod=False, block_len=80000, force_generic=True)
+    g.load_state(blob)               # ... and continued by a generic engine
+    g.push(more)
+    b = g.channel_iq()
+    assert rel_rms(a, b) < 2e-6
+    eng.close()
+    g.close()
 
 
 def test_pinned_and_device_resident_ingest_agree():
