@@ -10,7 +10,7 @@
 //     full period N, 9.6 KB per channel at N=1200) sit in shared memory for the CTA's whole life; the
 //     16 lanes of a half warp are the 16 channels, so one table row is one conflict-free 128 B read.
 //   * Time is cut into per-thread segments that are multiples of 125 samples (one stage-3 output).  The
-//     two half warps of a warp are two segments; the 16 segments of a CTA stream their input through a
+//     two half warps of a warp are two segments; the 32 segments of a CTA stream their input through a
 //     double-buffered shared-memory window (global loads for step t+1 are in flight while step t is
 //     computed), every sample being fetched from L2 once per 16 channels.
 //   * Each thread runs the three stages in transposed form (one accumulator per output in flight), so
@@ -27,12 +27,13 @@
 namespace sdrx {
 
 constexpr int kFastCh = 16;        // channels per group
-constexpr int kFastSegs = 16;      // time segments per CTA
+constexpr int kFastSegs = 32;      // time segments per CTA (512 threads: 4 warps per scheduler)
 constexpr int kFastThreads = kFastCh * kFastSegs;
 constexpr int kUnit = 125;         // raw samples per stage-3 output
 constexpr int kBody = 25;          // raw samples per stage-2 output
-constexpr int kXStride = 126;      // float2 per staged segment chunk (125 + 1: 1008 B keeps the two
-                                   // segments of a warp on different banks)
+constexpr int kXBody = 26;         // float2 per staged 25-sample body (+1: every body starts 16 B aligned)
+constexpr int kXSeg = 5 * kXBody;  // float2 per staged segment chunk; 1040 B puts the two segments of a warp
+                                   // 4 banks apart, so their 16 B broadcast reads never collide
 constexpr int kWrap = 24;          // table rows replicated past N so a 25-sample body never wraps
 constexpr int kFastMinSeg = 8;     // units; segments shorter than 4 would overlap their fix-ups
 constexpr int kFastWarmStart = 4;  // warm-up units of a segment at the start of the block
@@ -46,17 +47,24 @@ struct FastTaps {                  // kernel parameter: lives in the constant ba
     float2 h3[24];                 // 21 used
 };
 
-struct FastPiece {                 // one (group, unit range) run of one CTA
-    int group, u_begin, u_end, nseg, slot_base;
+// One (group, unit range) run of one CTA.  The range is cut into two halves A = [u_begin, u_begin+H) and
+// B = [u_begin+H, u_end); warp w takes the w-th segment (seg_len units) of A on lanes 0-15 and the w-th
+// segment of B on lanes 16-31.  The scheduler makes H a whole number of translator periods whenever that
+// keeps the halves balanced, so both half warps read the SAME table row: one broadcast wavefront.
+struct FastPiece {
+    int group, u_begin, u_end, H, seg_len, slot_base;
 };
 struct FastCta { int piece_begin, piece_end; };
-struct FastBound { int group, u0, slot; };      // stage-3 outputs u0..u0+3 of `group` need tails[slot]
+struct FastFix { int group, u, n, src[4]; };    // stage-3 output u of `group` += tails[src[0..n)]
+constexpr int kFastSlotsPerPiece = 2 * (kFastSegs / 2);
 
-// the segment split of a piece; shared by the kernel and the host-side schedule builder
-__host__ __device__ inline void fast_segment(int u_begin, int u_end, int nseg, int s, int *u0, int *u1) {
-    const int len = u_end - u_begin, base = len / nseg, rem = len % nseg;
-    *u0 = u_begin + s * base + (s < rem ? s : rem);
-    *u1 = *u0 + base + (s < rem ? 1 : 0);
+// the segment of (warp w, half) in a piece; shared by the kernel and the host-side schedule builder
+__host__ __device__ inline bool fast_segment(const FastPiece &p, int w, int half, int *u0, int *u1) {
+    const int lo = half ? p.u_begin + p.H : p.u_begin;
+    const int hi = half ? p.u_end : p.u_begin + p.H;
+    *u0 = lo + w * p.seg_len;
+    *u1 = *u0 + p.seg_len < hi ? *u0 + p.seg_len : hi;
+    return *u0 < hi;
 }
 
 __device__ __forceinline__ u64 pack2(float x, float y) { u64 d; asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(x), "f"(y)); return d; }
@@ -73,9 +81,16 @@ __device__ __forceinline__ u64 tap2(const float2 &h) { return pack2(h.x, h.y); }
 // Stage-1 output 5B+q covers raw 25B + [5q-12, 5q+4]; stage-2 output B+q2 covers stage-1 5B + [5q2-14, 5q2+4].
 __device__ __forceinline__ void fast_body(const float2 *__restrict__ xp, const float2 *__restrict__ tp,
                                           const FastTaps &tp_, u64 (&a)[8], u64 (&b)[4]) {
+    float2 xv[kBody + 1];
+#pragma unroll
+    for (int i = 0; i < kBody + 1; i += 2) {                   // 13 x LDS.128 (the 26th slot is padding)
+        const float4 v = *reinterpret_cast<const float4 *>(xp + i);
+        xv[i] = make_float2(v.x, v.y);
+        xv[i + 1] = make_float2(v.z, v.w);
+    }
 #pragma unroll
     for (int i = 0; i < kBody; ++i) {
-        const float2 x = xp[i];
+        const float2 x = xv[i];
         const float2 w = tp[i * kFastCh];
         const float sr = fmaf(x.x, w.x, -(x.y * w.y));          // msd.hpp:134  in[i] * translator_[pos]
         const float si = fmaf(x.x, w.y, x.y * w.x);
@@ -99,7 +114,7 @@ __device__ __forceinline__ void fast_body(const float2 *__restrict__ xp, const f
     }
 }
 
-// grid = number of CTAs in the schedule, block = 256, dynamic smem = fast_smem_bytes(N).
+// grid = number of CTAs in the schedule, block = kFastThreads, dynamic smem = fast_smem_bytes(N).
 template <int FMT>
 static __global__ void __launch_bounds__(kFastThreads, 1)
 k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *__restrict__ table, int Cpad, int C,
@@ -107,19 +122,19 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
             int U, float2 *__restrict__ s3, long s3_stride, int s3_off, float2 *__restrict__ tails, int n_slots) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2 *tb = reinterpret_cast<float2 *>(smem_raw);                       // [(N + kWrap)][16]
-    float2 *xs = tb + (size_t)(N + kWrap) * kFastCh;                         // [2][16][kXStride]
-    int *seg_start = reinterpret_cast<int *>(xs + 2 * kFastSegs * kXStride); // [16] first unit staged (may be < 0)
-    int *seg_steps = seg_start + kFastSegs;                                  // [16] steps (units) to stage
+    float2 *xs = tb + (size_t)(N + kWrap) * kFastCh;                         // [2][kFastSegs][kXSeg]
 
     const int tid = threadIdx.x;
     const int ch = tid & (kFastCh - 1);
-    const int seg = tid >> 4;
+    const int half = (tid >> 4) & 1;
+    const int w = tid >> 5;
+    const int seg = tid >> 4;                               // == 2*w + half: slot of the staged chunk
     const FastCta me = ctas[blockIdx.x];
     int cur_group = -1;
 
     for (int pi = me.piece_begin; pi < me.piece_end; ++pi) {
         const FastPiece pc = pieces[pi];
-        __syncthreads();                                   // previous piece is done with tb / xs / seg_*
+        __syncthreads();                                   // previous piece is done with tb / xs
         if (pc.group != cur_group) {
             cur_group = pc.group;
             const float2 *src = table + pc.group * kFastCh;
@@ -129,44 +144,58 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
             }
         }
         // my segment
-        int u0 = 0, u1 = 0, warm = 0;
-        const bool have = seg < pc.nseg;
-        if (have) {
-            fast_segment(pc.u_begin, pc.u_end, pc.nseg, seg, &u0, &u1);
-            warm = (u0 == 0) ? kFastWarmStart : 1;
-        }
+        int u0 = 0, u1 = 0;
+        const bool have = fast_segment(pc, w, half, &u0, &u1);
+        const int warm = (u0 == 0) ? kFastWarmStart : 1;
         const int my_steps = have ? warm + (u1 - u0) : 0;
-        if (ch == 0) { seg_start[seg] = u0 - warm; seg_steps[seg] = my_steps; }
-        int nsteps;
-        {
-            int a0, a1;
-            fast_segment(pc.u_begin, pc.u_end, pc.nseg, 0, &a0, &a1);
-            nsteps = ((pc.u_begin == 0) ? kFastWarmStart : 1) + (a1 - a0);   // segment 0 is never the shorter one
-        }
-        __syncthreads();
+        const int nsteps = ((pc.u_begin == 0) ? kFastWarmStart : 1) + pc.seg_len;   // the longest segment's
 
-        // stage the first chunk
-        float2 pre[8];
-        auto fetch = [&](int t) {
+        // Staging: the 16 threads of a segment fetch that segment's next 125 samples (8 coalesced rows of
+        // 128 B) while the current chunk is computed.  F32 goes global->shared with cp.async; u8/s16 are
+        // loaded early into registers, converted and stored after the compute.
+        const long my_raw0 = (long)hist + (long)kUnit * (u0 - warm) + ch;
+        float2 *my_xs = xs + seg * kXSeg;
+        typename RawTraits<FMT>::vec pre[8];
+        auto fetch = [&](int t, int buf) {
+            if (t >= my_steps) return;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                const int e = tid + j * kFastThreads;
-                const int s = e / kUnit, i = e - s * kUnit;
-                pre[j] = make_float2(0.0f, 0.0f);
-                if (e < kFastSegs * kUnit && t < seg_steps[s])
-                    pre[j] = load_iq_from<FMT>(raw, (long)hist + (long)kUnit * (seg_start[s] + t) + i, valid_lo);
+                const int i = ch + 16 * j;
+                if (i < kUnit) {
+                    const long idx = my_raw0 + (long)kUnit * t + 16 * j;
+                    if constexpr (FMT == SDRX_FMT_F32) {
+                        const unsigned dst = (unsigned)__cvta_generic_to_shared(my_xs + buf * kFastSegs * kXSeg + (i / kBody) * kXBody + i % kBody);
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(reinterpret_cast<const float2 *>(raw) + idx) : "memory");
+                    } else if constexpr (FMT == SDRX_FMT_S16) {
+                        unsigned v;
+                        asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(v) : "l"(reinterpret_cast<const short2 *>(raw) + idx));
+                        pre[j] = make_short2((short)(v & 0xffff), (short)(v >> 16));
+                    } else {
+                        unsigned short v;
+                        asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(v) : "l"(reinterpret_cast<const uchar2 *>(raw) + idx));
+                        pre[j] = make_uchar2((unsigned char)(v & 0xff), (unsigned char)(v >> 8));
+                    }
+                }
             }
         };
-        auto stash = [&](int buf) {
+        auto land = [&](int t, int buf) {                  // make chunk t visible in xs[buf] (before the barrier)
+            if constexpr (FMT == SDRX_FMT_F32) {
+                asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+            } else {
+                if (t >= my_steps) return;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int e = tid + j * kFastThreads;
-                const int s = e / kUnit, i = e - s * kUnit;
-                if (e < kFastSegs * kUnit) xs[(buf * kFastSegs + s) * kXStride + i] = pre[j];
+                for (int j = 0; j < 8; ++j) {
+                    const int i = ch + 16 * j;
+                    if (i < kUnit) {
+                        float2 v = convert_iq<FMT>(pre[j]);
+                        if (my_raw0 + (long)kUnit * t + 16 * j < valid_lo) v = make_float2(0.0f, 0.0f);   // before the stream
+                        my_xs[buf * kFastSegs * kXSeg + (i / kBody) * kXBody + i % kBody] = v;
+                    }
+                }
             }
         };
-        fetch(0);
-        stash(0);
+        fetch(0, 0);
+        land(0, 0);
         __syncthreads();
 
         // per-thread filter state
@@ -183,12 +212,12 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
         const bool ch_ok = pc.group * kFastCh + ch < C;
 
         for (int t = 0; t < nsteps; ++t) {
-            if (t + 1 < nsteps) fetch(t + 1);
+            if (t + 1 < nsteps) fetch(t + 1, (t + 1) & 1);
             if (t < my_steps) {
-                const float2 *xseg = xs + ((t & 1) * kFastSegs + seg) * kXStride;
+                const float2 *xseg = my_xs + (t & 1) * kFastSegs * kXSeg;
 #pragma unroll 1
                 for (int p = 0; p < 5; ++p) {
-                    fast_body(xseg + p * kBody, tb + row * kFastCh + ch, taps, a, b);
+                    fast_body(xseg + p * kXBody, tb + row * kFastCh + ch, taps, a, b);
                     row += kBody;
                     if (row >= N) row -= N;
                     const u64 z = b[0];                                  // stage-2 output of this body
@@ -206,46 +235,49 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
                 if (t >= warm && ch_ok) s3[out_base + (u0 + t - warm)] = unpack2(c3[0]);
                 c3[0] = c3[1]; c3[1] = c3[2]; c3[2] = c3[3]; c3[3] = c3[4]; c3[4] = 0ull;
             }
-            if (t + 1 < nsteps) stash((t + 1) & 1);
+            if (t + 1 < nsteps) land(t + 1, (t + 1) & 1);
             __syncthreads();
         }
-        // what this segment contributes to the first four outputs of the next one
+        // what this segment contributes to the (up to four) outputs that follow it
         if (have && u1 < U && ch_ok) {
-            float2 *tl = tails + ((long)(pc.group * kFastCh + ch) * n_slots + pc.slot_base + seg) * 4;
+            float2 *tl = tails + ((long)(pc.group * kFastCh + ch) * n_slots + pc.slot_base + half * (kFastSegs / 2) + w) * 4;
 #pragma unroll
             for (int q = 0; q < 4; ++q) tl[q] = unpack2(c3[q]);
         }
     }
 }
 
-// s3[c][u0 + i] += tails[c][slot][i]: completes the stage-3 outputs that straddle a segment boundary.
+// Completes the stage-3 outputs that straddle segment boundaries: s3[c][u] += sum of the tails that reach u,
+// added in a fixed order by one thread per (output, channel).
 static __global__ void k_fix_tails(float2 *__restrict__ s3, long s3_stride, int s3_off, const float2 *__restrict__ tails,
-                                   int n_slots, const FastBound *__restrict__ bounds, int n_bounds, int C) {
+                                   int n_slots, const FastFix *__restrict__ fixes, int n_fixes, int C) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= n_bounds * kFastCh * 4) return;
-    const int i = idx & 3, c16 = (idx >> 2) & 15, bi = idx >> 6;
-    const FastBound bd = bounds[bi];
-    const int c = bd.group * kFastCh + c16;
+    if (idx >= n_fixes * kFastCh) return;
+    const int c16 = idx & 15, fi = idx >> 4;
+    const FastFix fx = fixes[fi];
+    const int c = fx.group * kFastCh + c16;
     if (c >= C) return;
-    const float2 t = tails[((long)c * n_slots + bd.slot) * 4 + i];
-    float2 *p = s3 + (long)c * s3_stride + s3_off + bd.u0 + i;
+    float2 *p = s3 + (long)c * s3_stride + s3_off + fx.u;
     float2 v = *p;
-    v.x += t.x; v.y += t.y;
+    for (int k = 0; k < fx.n; ++k) {
+        const float2 t = tails[(long)c * n_slots * 4 + fx.src[k]];
+        v.x += t.x; v.y += t.y;
+    }
     *p = v;
 }
 
 inline size_t fast_smem_bytes(int N) {
-    return sizeof(float2) * ((size_t)(N + kWrap) * kFastCh + 2 * kFastSegs * kXStride) + sizeof(int) * 2 * kFastSegs;
+    return sizeof(float2) * ((size_t)(N + kWrap) * kFastCh + 2 * kFastSegs * kXSeg);
 }
 
 // ------------------------------------------------------------------------------------------------
 // Host side: the static schedule (depends only on C, the block length and the SM count) and launch.
 struct FastSchedule {
     int U = 0;                         // units (stage-3 outputs per channel) of the block length it was built for
-    int n_ctas = 0, n_slots = 0, n_bounds = 0;
+    int n_ctas = 0, n_slots = 0, n_fixes = 0;
     FastCta *d_ctas = nullptr;
     FastPiece *d_pieces = nullptr;
-    FastBound *d_bounds = nullptr;
+    FastFix *d_fixes = nullptr;
 };
 
 struct FastBank {
@@ -253,6 +285,7 @@ struct FastBank {
     int stages_fused = 0;              // leading MSD stages the kernel covers (3)
     int n_sms = 148;
     int groups = 0;
+    int period_units = 1;              // units after which the translator phase repeats: N / gcd(N, 125)
     FastTaps taps{};
     FastSchedule sched[2];             // small cache keyed by U (block length / 125)
     float2 *d_tails = nullptr;
@@ -260,7 +293,7 @@ struct FastBank {
     int C = 0;
 
     void free_schedule(FastSchedule &s) {
-        cudaFree(s.d_ctas); cudaFree(s.d_pieces); cudaFree(s.d_bounds);
+        cudaFree(s.d_ctas); cudaFree(s.d_pieces); cudaFree(s.d_fixes);
         s = FastSchedule{};
     }
     void destroy() {
@@ -281,14 +314,14 @@ inline bool fast_eligible(int S, const int *m, const int *H, int N) {
 }
 
 // Linearise (group, unit) work, cut it into one contiguous range per CTA, snap cuts that fall close to
-// a group boundary onto it, split ranges at group boundaries into pieces, and number the segment-end
-// boundaries whose stage-3 partial sums k_fix_tails has to add.
+// a group boundary onto it, split ranges at group boundaries into pieces, lay the two halves of every
+// piece out, and list the stage-3 outputs that need tails added (k_fix_tails).
 inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
     std::vector<FastCta> ctas;
     std::vector<FastPiece> pieces;
-    std::vector<FastBound> bounds;
+    const int half_segs = kFastSegs / 2;
     const long total = (long)fb.groups * U;
-    const long min_range = (long)kFastSegs * kFastMinSeg;                // 128 units: every segment >= 8 units
+    const long min_range = (long)kFastSegs * kFastMinSeg;                // every segment >= 8 units when possible
     long n_ctas = std::min<long>(fb.n_sms, std::max<long>(1, total / min_range));
     const int snap = std::min(4 * kFastMinSeg, std::max(1, U / 2));
     std::vector<long> cuts;
@@ -304,44 +337,70 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
     int slot = 0, slot_group = -1, max_slots = 0;     // slots are numbered per group (pieces of a group are consecutive)
     for (size_t i = 0; i + 1 < cuts.size(); ++i) {
         FastCta cta{(int)pieces.size(), 0};
-        long w = cuts[i];
-        while (w < cuts[i + 1]) {
-            const int g = (int)(w / U), ub = (int)(w % U);
-            const int ue = (int)std::min<long>(U, ub + (cuts[i + 1] - w));
+        long wk = cuts[i];
+        while (wk < cuts[i + 1]) {
+            const int g = (int)(wk / U), ub = (int)(wk % U);
+            const int ue = (int)std::min<long>(U, ub + (cuts[i + 1] - wk));
+            const int L = ue - ub;
             if (g != slot_group) { slot_group = g; slot = 0; }
-            FastPiece p{g, ub, ue, 0, slot};
-            p.nseg = std::max(1, std::min(kFastSegs, (ue - ub) / kFastMinSeg));
-            for (int s = 0; s < p.nseg; ++s) {
-                int u0, u1;
-                fast_segment(ub, ue, p.nseg, s, &u0, &u1);
-                if (u1 < U) bounds.push_back(FastBound{g, u1, slot + s});
+            FastPiece p{g, ub, ue, L, 0, slot};
+            if (L >= 2 * kFastMinSeg) {
+                const int P = fb.period_units;
+                const int h_min = (L + 1) / 2;
+                const int h_al = (h_min + P - 1) / P * P;            // phase-aligned halves: shared table rows
+                p.H = (h_al < L && h_al - h_min <= L / 8) ? h_al : h_min;
             }
-            slot += p.nseg;
+            const int ns = std::max(1, std::min(half_segs, p.H / kFastMinSeg));
+            p.seg_len = (p.H + ns - 1) / ns;
+            slot += kFastSlotsPerPiece;
             max_slots = std::max(max_slots, slot);
             pieces.push_back(p);
-            w += ue - ub;
+            wk += L;
         }
         cta.piece_end = (int)pieces.size();
         ctas.push_back(cta);
     }
+    // fix list: every segment end inside the block hands its four partial sums to the outputs after it
+    std::vector<FastFix> fixes;
+    {
+        std::vector<std::vector<int>> src((size_t)fb.groups * U);
+        for (const FastPiece &p : pieces)
+            for (int half = 0; half < 2; ++half)
+                for (int w = 0; w < half_segs; ++w) {
+                    int u0, u1;
+                    if (!fast_segment(p, w, half, &u0, &u1) || u1 >= U) continue;
+                    for (int q = 0; q < 4 && u1 + q < U; ++q)
+                        src[(size_t)p.group * U + u1 + q].push_back((p.slot_base + half * half_segs + w) * 4 + q);
+                }
+        for (int g = 0; g < fb.groups; ++g)
+            for (int u = 0; u < U; ++u) {
+                const std::vector<int> &v = src[(size_t)g * U + u];
+                if (v.empty()) continue;
+                if (v.size() > 4) return fail(SDRX_ERR_STATE, "internal: more than four tails reach one stage-3 output");
+                FastFix f{g, u, (int)v.size(), {0, 0, 0, 0}};
+                for (size_t k = 0; k < v.size(); ++k) f.src[k] = v[k];
+                fixes.push_back(f);
+            }
+    }
     out.U = U;
     out.n_ctas = (int)ctas.size();
     out.n_slots = max_slots;           // tails are indexed [channel][slot][4]
-    out.n_bounds = (int)bounds.size();
+    out.n_fixes = (int)fixes.size();
     CU(cudaMalloc((void **)&out.d_ctas, sizeof(FastCta) * ctas.size()));
     CU(cudaMalloc((void **)&out.d_pieces, sizeof(FastPiece) * pieces.size()));
-    CU(cudaMalloc((void **)&out.d_bounds, sizeof(FastBound) * std::max<size_t>(1, bounds.size())));
+    CU(cudaMalloc((void **)&out.d_fixes, sizeof(FastFix) * std::max<size_t>(1, fixes.size())));
     CU(cudaMemcpy(out.d_ctas, ctas.data(), sizeof(FastCta) * ctas.size(), cudaMemcpyHostToDevice));
     CU(cudaMemcpy(out.d_pieces, pieces.data(), sizeof(FastPiece) * pieces.size(), cudaMemcpyHostToDevice));
-    if (!bounds.empty())
-        CU(cudaMemcpy(out.d_bounds, bounds.data(), sizeof(FastBound) * bounds.size(), cudaMemcpyHostToDevice));
+    if (!fixes.empty())
+        CU(cudaMemcpy(out.d_fixes, fixes.data(), sizeof(FastFix) * fixes.size(), cudaMemcpyHostToDevice));
     return SDRX_OK;
 }
 
 // Launch the bank for one block of n = 125*U samples (all stage phases zero), then the tail fix-up.
 template <int FMT>
 int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int valid_lo, const float2 *table, int Cpad,
-                int N, int pos0, unsigned n, float2 *s3, long s3_stride, int s3_off, uint64_t *launches) {
+                int N, int pos0, unsigned n, float2 *s3, long s3_stride, int s3_off, uint64_t *launches,
+                cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr) {
     const int U = (int)(n / kUnit);
     FastSchedule *sc = nullptr;
     for (auto &s : fb.sched) if (s.U == U) sc = &s;
@@ -360,14 +419,16 @@ int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int va
         CU(cudaMalloc((void **)&fb.d_tails, sizeof(float2) * 4 * (size_t)sc->n_slots * fb.C));
         fb.tails_slots = sc->n_slots;
     }
+    if (ev0) CU(cudaEventRecord(ev0, st));
     k_bank_fast<FMT><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
         raw, hist, valid_lo, table, Cpad, fb.C, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U, s3, s3_stride, s3_off,
         fb.d_tails, fb.tails_slots);
+    if (ev1) CU(cudaEventRecord(ev1, st));
     ++*launches;
-    if (sc->n_bounds > 0) {
-        const int threads = sc->n_bounds * kFastCh * 4;
-        k_fix_tails<<<div_up(threads, 256), 256, 0, st>>>(s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots, sc->d_bounds,
-                                                          sc->n_bounds, fb.C);
+    if (sc->n_fixes > 0) {
+        const int threads = sc->n_fixes * kFastCh;
+        k_fix_tails<<<div_up(threads, 256), 256, 0, st>>>(s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots, sc->d_fixes,
+                                                          sc->n_fixes, fb.C);
         ++*launches;
     }
     CU(cudaGetLastError());
@@ -378,6 +439,11 @@ inline int fast_init(FastBank &fb, int C, int N, const float *h1, const float *h
     fb.C = C;
     fb.groups = (C + kFastCh - 1) / kFastCh;
     fb.stages_fused = 3;
+    {
+        int a = N, b = kUnit;
+        while (b) { const int t = a % b; a = b; b = t; }
+        fb.period_units = N / a;
+    }
     for (int i = 0; i < 17; ++i) fb.taps.h1[i] = make_float2(h1[i], h1[i]);
     for (int i = 0; i < 19; ++i) fb.taps.h2[i] = make_float2(h2[i], h2[i]);
     for (int i = 0; i < 24; ++i) fb.taps.h3[i] = i < 21 ? make_float2(h3[i], h3[i]) : make_float2(0.0f, 0.0f);
