@@ -55,7 +55,7 @@ struct FastPiece {
     int group, u_begin, u_end, H, seg_len, slot_base;
 };
 struct FastCta { int piece_begin, piece_end; };
-struct FastFix { int group, u, n, src[4]; };    // stage-3 output u of `group` += tails[src[0..n)]
+typedef TailFix FastFix;                        // stage-3 output u of `group` += tails[src[0..n)]
 constexpr int kFastSlotsPerPiece = 2 * (kFastSegs / 2);
 
 // the segment of (warp w, half) in a piece; shared by the kernel and the host-side schedule builder
@@ -278,6 +278,7 @@ struct FastSchedule {
     FastCta *d_ctas = nullptr;
     FastPiece *d_pieces = nullptr;
     FastFix *d_fixes = nullptr;
+    int2 *d_fix_range = nullptr;       // [groups] -> [begin, end) into d_fixes (the list is sorted by group)
 };
 
 struct FastBank {
@@ -293,7 +294,7 @@ struct FastBank {
     int C = 0;
 
     void free_schedule(FastSchedule &s) {
-        cudaFree(s.d_ctas); cudaFree(s.d_pieces); cudaFree(s.d_fixes);
+        cudaFree(s.d_ctas); cudaFree(s.d_pieces); cudaFree(s.d_fixes); cudaFree(s.d_fix_range);
         s = FastSchedule{};
     }
     void destroy() {
@@ -362,6 +363,7 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
     }
     // fix list: every segment end inside the block hands its four partial sums to the outputs after it
     std::vector<FastFix> fixes;
+    std::vector<int2> fix_range((size_t)fb.groups, make_int2(0, 0));
     {
         std::vector<std::vector<int>> src((size_t)fb.groups * U);
         for (const FastPiece &p : pieces)
@@ -372,7 +374,8 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
                     for (int q = 0; q < 4 && u1 + q < U; ++q)
                         src[(size_t)p.group * U + u1 + q].push_back((p.slot_base + half * half_segs + w) * 4 + q);
                 }
-        for (int g = 0; g < fb.groups; ++g)
+        for (int g = 0; g < fb.groups; ++g) {
+            fix_range[g].x = (int)fixes.size();
             for (int u = 0; u < U; ++u) {
                 const std::vector<int> &v = src[(size_t)g * U + u];
                 if (v.empty()) continue;
@@ -381,6 +384,8 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
                 for (size_t k = 0; k < v.size(); ++k) f.src[k] = v[k];
                 fixes.push_back(f);
             }
+            fix_range[g].y = (int)fixes.size();
+        }
     }
     out.U = U;
     out.n_ctas = (int)ctas.size();
@@ -393,6 +398,8 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
     CU(cudaMemcpy(out.d_pieces, pieces.data(), sizeof(FastPiece) * pieces.size(), cudaMemcpyHostToDevice));
     if (!fixes.empty())
         CU(cudaMemcpy(out.d_fixes, fixes.data(), sizeof(FastFix) * fixes.size(), cudaMemcpyHostToDevice));
+    CU(cudaMalloc((void **)&out.d_fix_range, sizeof(int2) * fix_range.size()));
+    CU(cudaMemcpy(out.d_fix_range, fix_range.data(), sizeof(int2) * fix_range.size(), cudaMemcpyHostToDevice));
     return SDRX_OK;
 }
 
@@ -400,7 +407,7 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
 template <int FMT>
 int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int valid_lo, const float2 *table, int Cpad,
                 int N, int pos0, unsigned n, float2 *s3, long s3_stride, int s3_off, uint64_t *launches,
-                cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr) {
+                cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr, const FastSchedule **deferred_fix = nullptr) {
     const int U = (int)(n / kUnit);
     FastSchedule *sc = nullptr;
     for (auto &s : fb.sched) if (s.U == U) sc = &s;
@@ -425,7 +432,8 @@ int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int va
         fb.d_tails, fb.tails_slots);
     if (ev1) CU(cudaEventRecord(ev1, st));
     ++*launches;
-    if (sc->n_fixes > 0) {
+    if (deferred_fix) *deferred_fix = sc;           // the caller's next kernel applies the fix list itself
+    else if (sc->n_fixes > 0) {
         const int threads = sc->n_fixes * kFastCh;
         k_fix_tails<<<div_up(threads, 256), 256, 0, st>>>(s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots, sc->d_fixes,
                                                           sc->n_fixes, fb.C);

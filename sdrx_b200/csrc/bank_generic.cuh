@@ -108,21 +108,25 @@ k_carry_hist(float2 *__restrict__ buf, long stride, int hist, int n_in) {
     }
 }
 
-// Raw history between the two ping-pong input buffers: dst[0..hist) = src[n_in .. n_in+hist),
-// byte granular (bps bytes per complex sample).  src already holds [hist | n_in].
-static __global__ void k_carry_raw(uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, long n_in_bytes, int hist_bytes) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < hist_bytes) dst[i] = src[n_in_bytes + i];
-}
-
-// Block power, pass 1: deterministic per-CTA partial sums of re^2+im^2 (rtl_dev.cpp:333-337).
-// The final mean / 10*log10f - 3 is taken by the mix kernel from the partials in fixed order.
+// Block preparation, one launch:
+//   CTAs [0, n_power): block power pass 1 -- deterministic per-CTA partial sums of re^2+im^2
+//                      (rtl_dev.cpp:333-337, airspy_dev.cpp:366-405); the mean / 10*log10f - 3 is taken
+//                      by the mix kernel from the partials in a fixed order.
+//   CTAs [n_power, ..): the raw delay line between the two ping-pong input buffers:
+//                      dst[0..hist) = src[n_in .. n_in+hist), byte granular (src holds [hist | n_in]).
+// The power CTAs only read dst[hist..], the carry CTAs only write dst[0..hist): no hazard.
 template <int FMT>
 static __global__ void __launch_bounds__(256)
-k_power_partial(const void *__restrict__ raw, int hist, int n, float *__restrict__ partial) {
+k_prep(const void *__restrict__ raw, int hist, int n, float *__restrict__ partial, int n_power,
+       uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, long n_in_bytes, int hist_bytes) {
+    if ((int)blockIdx.x >= n_power) {
+        const int i = ((int)blockIdx.x - n_power) * 256 + threadIdx.x;
+        if (i < hist_bytes) dst[i] = src[n_in_bytes + i];
+        return;
+    }
     __shared__ float sh[256];
     float acc = 0.0f;
-    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += gridDim.x * 256) {
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < n; i += n_power * 256) {
         const float2 v = load_iq<FMT>(raw, (long)hist + i);
         acc += v.x * v.x + v.y * v.y;
     }

@@ -121,6 +121,10 @@ __device__ __forceinline__ float log10f_glibc(float x) {
     return __fadd_rn(z, __fmul_rn(y, 3.0102920532e-01f));
 }
 
+// Tail fix-ups of the specialised channel bank (bank_fast.cuh): stage-3 output u of a 16-channel group
+// gets up to four partial sums added, in list order.
+struct TailFix { int group, u, n, src[4]; };
+
 __host__ __device__ inline int div_up(long a, long b) { return (int)((a + b - 1) / b); }
 
 }  // namespace sdrx

@@ -21,7 +21,7 @@ using namespace sdrx;
 namespace {
 
 constexpr int kNBuf = 2;          // ping-pong depth of raw input and of the output sets
-constexpr int kPwrPartials = 64;
+constexpr int kPwrPartials = 296;     // power CTAs of k_prep: two per SM
 constexpr uint32_t kStateMagic = 0x58524453u;  // "SDRX"
 
 struct OutSet {                   // device-side results of one block
@@ -79,6 +79,7 @@ struct sdrx_engine {
     float *d_c_adj = nullptr, *d_fir_hist = nullptr;
     FastBank fast;                        // specialised channel bank (bank_fast.cuh)
     bool use_fast = false;
+    bool tail_fusable = false;            // last stage + boundary B in one per-channel kernel (k_chan_tail<true>)
 
     // pinned staging for pageable callers
     uint8_t *h_stage[kNBuf] = {nullptr, nullptr};
@@ -397,8 +398,16 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             (rc = dalloc(&e->d_fir_hist, 2 * (size_t)std::max(cfg->fir2_ntaps - 1, 1))))
             return rc;
         e->tb = DemodTables{e->d_window, e->d_twiddle, e->d_bitrev, e->d_shape, e->d_ramp_up, e->d_ramp_down};
+        if ((size_t)C * 4 > 160 * 1024) return fail(SDRX_ERR_UNSUPPORTED, "more than 40960 channels per engine");
         CU(cudaFuncSetAttribute(k_mix_fir2_pcm, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)(sizeof(float) * 2 * (size_t)(cfg->fir2_ntaps - 1 + kChunk))));
+                                (int)(sizeof(float) * 2 * (size_t)(cfg->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad)));
+        if (S >= 1) {       // the per-channel tail kernel stages the last stage's input row in shared memory when fused
+            size_t row = (size_t)(e->H[S - 1] - 1) + (size_t)kChunk * e->m[S - 1];
+            e->tail_fusable = row * sizeof(float2) <= 100 * 1024;
+            if (e->tail_fusable)
+                CU(cudaFuncSetAttribute(k_chan_tail<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)(sizeof(float2) * std::max<size_t>(row, 768))));
+        }
     }
     return reset_state(e);
 }
@@ -527,27 +536,32 @@ int materialize_generic(sdrx_engine *e, int fmt, const uint8_t *buf, long end_id
 }
 
 template <int FMT>
-int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o) {
+int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o, const FastSchedule **deferred) {
     float2 *dst; long stride; int off;
     if (e->S > 3) { dst = e->d_stage_in[3]; stride = e->stage_stride[3]; off = e->H[3] - 1; }
     else          { dst = o.ch_iq;          stride = e->chiq_stride;     off = 0; }
     return fast_launch<FMT>(e->fast, e->s_main, raw, e->raw_hist, valid_lo, e->d_table_t, e->Cpad, e->N, (int)e->trans_pos, n,
                             dst, stride, off, &e->launches,
-                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr);
+                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred);
 }
-int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o) {
+int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o,
+                         const FastSchedule **deferred = nullptr) {
     switch (fmt) {
-        case SDRX_FMT_U8:  return launch_bank_fast<SDRX_FMT_U8>(e, raw, valid_lo, n, o);
-        case SDRX_FMT_S16: return launch_bank_fast<SDRX_FMT_S16>(e, raw, valid_lo, n, o);
-        default:           return launch_bank_fast<SDRX_FMT_F32>(e, raw, valid_lo, n, o);
+        case SDRX_FMT_U8:  return launch_bank_fast<SDRX_FMT_U8>(e, raw, valid_lo, n, o, deferred);
+        case SDRX_FMT_S16: return launch_bank_fast<SDRX_FMT_S16>(e, raw, valid_lo, n, o, deferred);
+        default:           return launch_bank_fast<SDRX_FMT_F32>(e, raw, valid_lo, n, o, deferred);
     }
 }
 
-int launch_power(sdrx_engine *e, int fmt, const uint8_t *raw, unsigned n) {
+// power partials of the new block (when boundary B will run) + the raw delay line, one launch
+int launch_prep(sdrx_engine *e, int fmt, uint8_t *buf, const uint8_t *prev, unsigned n, bool power, int hist_bytes, long prev_bytes) {
+    const int np = power ? kPwrPartials : 0;
+    const int grid = np + div_up(hist_bytes, 256);
+    if (grid == 0) return SDRX_OK;
     switch (fmt) {
-        case SDRX_FMT_U8:  k_power_partial<SDRX_FMT_U8><<<kPwrPartials, 256, 0, e->s_main>>>(raw, e->raw_hist, (int)n, e->d_pwr_partial); break;
-        case SDRX_FMT_S16: k_power_partial<SDRX_FMT_S16><<<kPwrPartials, 256, 0, e->s_main>>>(raw, e->raw_hist, (int)n, e->d_pwr_partial); break;
-        default:           k_power_partial<SDRX_FMT_F32><<<kPwrPartials, 256, 0, e->s_main>>>(raw, e->raw_hist, (int)n, e->d_pwr_partial); break;
+        case SDRX_FMT_U8:  k_prep<SDRX_FMT_U8><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, e->d_pwr_partial, np, buf, prev, prev_bytes, hist_bytes); break;
+        case SDRX_FMT_S16: k_prep<SDRX_FMT_S16><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, e->d_pwr_partial, np, buf, prev, prev_bytes, hist_bytes); break;
+        default:           k_prep<SDRX_FMT_F32><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, e->d_pwr_partial, np, buf, prev, prev_bytes, hist_bytes); break;
     }
     ++e->launches;
     CU(cudaGetLastError());
@@ -555,19 +569,24 @@ int launch_power(sdrx_engine *e, int fmt, const uint8_t *raw, unsigned n) {
 }
 
 // boundary B on the chunk in o.ch_iq
-int launch_demod(sdrx_engine *e, OutSet &o, bool have_power, unsigned n_samples) {
-    k_demod_squelch<<<e->C, 256, 0, e->s_main>>>(o.ch_iq, e->chiq_stride, e->st, e->tb, e->agc, e->lf, e->lf_active,
-                                                 e->d_sql_level, o.audio, o.snr);
-    const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk);
+// `fused`: the last MSD stage (and the specialised bank's tail fix-ups) run inside the per-channel kernel.
+int launch_demod(sdrx_engine *e, OutSet &o, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr) {
+    const TailSnap snap{o.sql, o.agc_gain, o.lf_gain};
+    if (fused) {
+        const size_t dyn = sizeof(float2) * (size_t)std::max(fused->H - 1 + fused->n_in, 768);
+        k_chan_tail<true><<<e->C, kTailThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->agc, e->lf,
+                                                                  e->lf_active, e->d_sql_level, o.audio, o.snr, snap);
+    } else {
+        k_chan_tail<false><<<e->C, kTailThreads, sizeof(float2) * 768, e->s_main>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
+                                                                                  e->agc, e->lf, e->lf_active, e->d_sql_level,
+                                                                                  o.audio, o.snr, snap);
+    }
+    const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad;
     k_mix_fir2_pcm<<<1, 1024, smem, e->s_main>>>(o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps,
                                                  e->d_fir_hist, o.mix_pre, o.mix, o.pcm, e->d_pwr_partial,
                                                  have_power ? kPwrPartials : 0, n_samples, have_power ? o.pwr : nullptr);
     e->launches += 2;
     CU(cudaGetLastError());
-    // snapshots, so that a later block cannot overwrite what get_outputs returns for this one
-    CU(cudaMemcpyAsync(o.sql, e->st.sql_state, e->C, cudaMemcpyDeviceToDevice, e->s_main));
-    CU(cudaMemcpyAsync(o.agc_gain, e->st.agc_gain, sizeof(float) * e->C, cudaMemcpyDeviceToDevice, e->s_main));
-    CU(cudaMemcpyAsync(o.lf_gain, e->st.lf_gain, sizeof(float) * e->C, cudaMemcpyDeviceToDevice, e->s_main));
     return SDRX_OK;
 }
 
@@ -625,13 +644,6 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     }
     if (e->timing) CU(cudaEventRecord(e->ev_t0, e->s_main));
 
-    // ---- raw delay line: last raw_hist samples of the previous [hist | block] move in front of this block
-    {
-        const int hb = (int)hist_bytes;
-        k_carry_raw<<<div_up(hb, 256), 256, 0, e->s_main>>>(buf, e->d_raw[prv], (long)e->prev_n * bps, hb);
-        ++e->launches;
-        CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));
-    }
 
     // ---- stage bookkeeping (MSD::S::isn_, msd.hpp:240-244): which inputs complete an output
     int first[SDRX_MAX_STAGES], n_out[SDRX_MAX_STAGES], phase_in[SDRX_MAX_STAGES] = {0};
@@ -646,14 +658,30 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     const unsigned out_len = (unsigned)n_in;
     OutSet &o = e->out[cur];
     const bool demod = !(e->flags & SDRX_FLAG_NO_DEMOD) && out_len == (unsigned)kChunk;
-    if (demod && n > 0) { int rc = launch_power(e, fmt, buf, n); if (rc) return rc; }
+    // ---- raw delay line (last raw_hist samples of the previous [hist | block] move in front of this block)
+    //      and, when boundary B will run, the block power partials
+    {
+        int rc = launch_prep(e, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps);
+        if (rc) return rc;
+        CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));
+    }
 
     const int valid_lo = (int)std::max<long>(0, (long)e->raw_hist - (long)std::min<uint64_t>(e->total, (uint64_t)e->raw_hist));
     const bool fast = e->use_fast && n > 0 && n % kUnit == 0 && phase_in[0] == 0 && phase_in[1] == 0 && phase_in[2] == 0;
     int rc;
+    const bool fuse_tail = fast && demod && e->tail_fusable && e->S == e->fast.stages_fused + 1;
+    TailFirArgs tail{};
     if (fast) {
-        rc = launch_bank_fast_fmt(e, fmt, buf, valid_lo, n, o);
-        if (!rc) rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 3, e->S);
+        const FastSchedule *sc = nullptr;
+        rc = launch_bank_fast_fmt(e, fmt, buf, valid_lo, n, o, fuse_tail ? &sc : nullptr);
+        if (!rc && fuse_tail) {
+            const int s = e->S - 1;
+            tail = TailFirArgs{e->d_stage_in[s], e->stage_stride[s], n_out[s - 1], e->H[s], e->m[s], first[s],
+                               e->d_taps + e->tap_off[s], sc->n_fixes > 0 ? e->fast.d_tails : nullptr, e->fast.tails_slots,
+                               sc->d_fixes, sc->d_fix_range};
+        } else if (!rc) {
+            rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 3, e->S);
+        }
         e->generic_stale = true;
         e->bank_timed = e->timing;
     } else {
@@ -664,7 +692,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     if (rc) return rc;
     if (e->timing) CU(cudaEventRecord(e->ev_t1, e->s_main));
 
-    if (demod) { rc = launch_demod(e, o, n > 0, n); if (rc) return rc; }
+    if (demod) { rc = launch_demod(e, o, n > 0, n, fuse_tail ? &tail : nullptr); if (rc) return rc; }
     if (e->timing) { CU(cudaEventRecord(e->ev_t2, e->s_main)); e->timing_valid = true; }
 
     e->trans_pos = (e->trans_pos + n) % e->N;
