@@ -1,4 +1,4 @@
-// sdrx_b200 -- single-object C ABI behind the drop-in C++ classes (dropin/msd.hpp, agc.hpp, fir.hpp).
+// sdrx_b200 -- single-object C ABI behind the drop-in C++ classes (include/sdrx_b200/msd.hpp, ds.hpp, agc.hpp, fir.hpp).
 // An MSD object is a one-channel channelizer engine; AGC/LfAGC/FIR objects run their exact
 // sequential kernels on caller-supplied arrays.  Same numerics as the batched engine.
 #include <algorithm>

@@ -7,7 +7,7 @@ Same names, argument meaning and defaults as the reference's classes:
 * :class:`LfAGC` -- agc.hpp:86-131
 * :class:`FIR` / :class:`FIR2` / :class:`FIR3` -- fir.hpp:78, :130, :28
 
-The C++ drop-in headers with the identical surface are under ``dropin/``; these classes exist so the
+The C++ drop-in headers with the identical surface are under ``include/sdrx_b200/``; these classes exist so the
 parity tests read like tests of the reference's own classes.  All compute is on the GPU.
 """
 from __future__ import annotations
