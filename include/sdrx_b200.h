@@ -52,6 +52,8 @@ typedef enum { SDRX_FMT_U8 = 0, SDRX_FMT_S16 = 1, SDRX_FMT_F32 = 2 } sdrx_iq_for
 /* flags for sdrx_engine_config.flags */
 #define SDRX_FLAG_FORCE_GENERIC 0x1u  /* never take the specialised channel-bank kernel         */
 #define SDRX_FLAG_NO_DEMOD      0x2u  /* channelizer only (boundary A); skip boundary B kernels  */
+#define SDRX_FLAG_PARTIAL_MIX   0x4u  /* channel-sharded run: stop at mix_pre (this GPU's share of the pan
+                                         mix); FIR2 + s16 run once, in sdrx_engine_finish_mix              */
 
 typedef struct sdrx_engine sdrx_engine;
 
@@ -123,6 +125,15 @@ int  sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
 /* Boundary B on caller-supplied channel IQ (host, [C][512][2]) instead of the channelizer's. */
 int  sdrx_engine_demod_block(sdrx_engine *e, const float *ch_iq, float pwr_dbfs);
 int  sdrx_engine_sync(sdrx_engine *e);
+/* The recurrences and the mix of a block run on a side stream (they overlap the next block's channel bank).
+ * sdrx_engine_join orders sdrx_engine_stream() behind everything queued there so far, so that an event a caller
+ * records on that stream afterwards covers all of every pushed block.  get_* / sync do this implicitly.     */
+int  sdrx_engine_join(sdrx_engine *e);
+/* Channel-sharded runs: the stereo mix is a sum over channels (sdrx.cpp:471-532), so each GPU
+ * returns its partial mix_pre[1024] and ONE engine finishes the block: adds the n_parts partials (host,
+ * [n_parts][1024]) in the order given, then FIR2 (sdrx.cpp:646) with this engine's carried ring and float->s16
+ * (sdrx.cpp:649-656).  mix_pre / mix / pcm (host, 1024 each) may be NULL.                                  */
+int  sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_parts, float *mix_pre, float *mix, int16_t *pcm);
 
 /* Carried state (MSD delay lines + trans_pos, AGC/LfAGC gain+power, squelch states, FIR2 ring):
  * what the reference keeps in its objects between blocks (SURVEY.md §5 checkpoint/resume). */

@@ -13,7 +13,7 @@ c_u8_p = C.POINTER(C.c_uint8)
 c_i16_p = C.POINTER(C.c_int16)
 
 FMT_U8, FMT_S16, FMT_F32 = 0, 1, 2
-FLAG_FORCE_GENERIC, FLAG_NO_DEMOD = 0x1, 0x2
+FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX = 0x1, 0x2, 0x4
 CHUNK = 512
 
 
@@ -62,6 +62,8 @@ PROTOTYPES = [
     ("sdrx_engine_get_outputs", C.c_int, [C.c_void_p, C.POINTER(BlockOutputs)]),
     ("sdrx_engine_demod_block", C.c_int, [C.c_void_p, c_float_p, C.c_float]),
     ("sdrx_engine_sync", C.c_int, [C.c_void_p]),
+    ("sdrx_engine_join", C.c_int, [C.c_void_p]),
+    ("sdrx_engine_finish_mix", C.c_int, [C.c_void_p, c_float_p, C.c_int, c_float_p, c_float_p, c_i16_p]),
     ("sdrx_engine_state_size", C.c_size_t, [C.c_void_p]),
     ("sdrx_engine_save_state", C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     ("sdrx_engine_load_state", C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),

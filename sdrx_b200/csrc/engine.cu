@@ -53,6 +53,11 @@ struct sdrx_engine {
     int fir2_ntaps = 0;
 
     cudaStream_t s_main = nullptr, s_copy = nullptr;
+    cudaStream_t s_side = nullptr;        // latency-bound tail of boundary B (k_chan_recur, k_mix_fir2_pcm): overlaps the next bank
+    cudaEvent_t ev_head_done = nullptr;   // k_chan_head of the current block has been queued behind this point (main -> side)
+    cudaEvent_t ev_side_done[kNBuf] = {nullptr, nullptr};   // side-stream work that reads / writes output set b is complete
+    bool side_pending[kNBuf] = {false, false};
+    uint8_t *d_gate[kNBuf] = {nullptr, nullptr};             // [C] squelch state entering the block (k_chan_head -> k_chan_recur)
     cudaEvent_t ev_copied[kNBuf] = {nullptr, nullptr};
     cudaEvent_t ev_raw_free[kNBuf] = {nullptr, nullptr};   // last reader of d_raw[b] has been queued
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr, ev_t2 = nullptr, ev_b0 = nullptr, ev_b1 = nullptr;
@@ -66,7 +71,7 @@ struct sdrx_engine {
     uint8_t *d_has_tr = nullptr;
     float *d_taps = nullptr;
     float2 *d_stage_in[SDRX_MAX_STAGES] = {nullptr};
-    float *d_pwr_partial = nullptr;
+    float *d_pwr_partial[kNBuf] = {nullptr, nullptr};       // per parity: k_prep of block b+1 runs while block b's mix kernel reads its own
     OutSet out[kNBuf];
     // boundary B
     ChannelState st{};
@@ -77,9 +82,11 @@ struct sdrx_engine {
     float *d_sql_level = nullptr;
     int *d_pos = nullptr;
     float *d_c_adj = nullptr, *d_fir_hist = nullptr;
+    float *d_parts = nullptr;             // staging of the per-GPU partial mixes (sdrx_engine_finish_mix)
+    size_t parts_cap = 0;
     FastBank fast;                        // specialised channel bank (bank_fast.cuh)
     bool use_fast = false;
-    bool tail_fusable = false;            // last stage + boundary B in one per-channel kernel (k_chan_tail<true>)
+    bool tail_fusable = false;            // last stage inside the per-channel head kernel (k_chan_head<true>)
 
     // pinned staging for pageable callers
     uint8_t *h_stage[kNBuf] = {nullptr, nullptr};
@@ -178,6 +185,8 @@ void agc_defaults(AgcParams &p, float attack, float decay, float reference, floa
 
 int reset_state(sdrx_engine *e) {
     const size_t C = (size_t)e->C;
+    CU(cudaStreamSynchronize(e->s_side));
+    e->side_pending[0] = e->side_pending[1] = false;
     for (int b = 0; b < kNBuf; ++b) CU(cudaMemsetAsync(e->d_raw[b], 0, e->raw_buf_bytes, e->s_main));
     for (int s = 1; s < e->S; ++s)
         CU(cudaMemsetAsync(e->d_stage_in[s], 0, sizeof(float2) * (size_t)e->stage_stride[s] * C, e->s_main));
@@ -222,14 +231,17 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
         cudaFree(o.pcm); cudaFree(o.pwr); cudaFree(o.sql); cudaFree(o.agc_gain); cudaFree(o.lf_gain);
         if (e->ev_copied[b]) cudaEventDestroy(e->ev_copied[b]);
         if (e->ev_raw_free[b]) cudaEventDestroy(e->ev_raw_free[b]);
+        if (e->ev_side_done[b]) cudaEventDestroy(e->ev_side_done[b]);
+        cudaFree(e->d_gate[b]); cudaFree(e->d_pwr_partial[b]);
     }
+    if (e->ev_head_done) cudaEventDestroy(e->ev_head_done);
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) cudaFree(e->d_stage_in[s]);
-    cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps); cudaFree(e->d_pwr_partial);
+    cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps);
     cudaFree(e->st.agc_gain); cudaFree(e->st.agc_power); cudaFree(e->st.lf_gain); cudaFree(e->st.lf_power);
     cudaFree(e->st.sql_state); cudaFree(e->st.sql_prev); cudaFree(e->st.mixed);
     cudaFree(e->d_window); cudaFree(e->d_shape); cudaFree(e->d_ramp_up); cudaFree(e->d_ramp_down);
     cudaFree(e->d_twiddle); cudaFree(e->d_bitrev); cudaFree(e->d_sql_level); cudaFree(e->d_pos);
-    cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist);
+    cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist); cudaFree(e->d_parts);
     e->fast.destroy();
     if (e->ev_t0) cudaEventDestroy(e->ev_t0);
     if (e->ev_t1) cudaEventDestroy(e->ev_t1);
@@ -238,6 +250,7 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     if (e->ev_b1) cudaEventDestroy(e->ev_b1);
     if (e->s_main) cudaStreamDestroy(e->s_main);
     if (e->s_copy) cudaStreamDestroy(e->s_copy);
+    if (e->s_side) cudaStreamDestroy(e->s_side);
     delete e;
 }
 
@@ -267,7 +280,10 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
 
     CU(cudaStreamCreateWithFlags(&e->s_main, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&e->s_side, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&e->ev_head_done, cudaEventDisableTiming));
     for (int b = 0; b < kNBuf; ++b) {
+        CU(cudaEventCreateWithFlags(&e->ev_side_done[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_copied[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_raw_free[b], cudaEventDisableTiming));
     }
@@ -323,8 +339,11 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         size_t cap = e->block_len;
         for (int s = 0; s < S; ++s) cap = cap / (size_t)e->m[s] + 1;
         e->chiq_stride = (long)std::max<size_t>(kChunk, (cap + 3) / 4 * 4);
-        int rc = dalloc(&e->d_pwr_partial, kPwrPartials);
-        if (rc) return rc;
+        for (int b = 0; b < kNBuf; ++b) {
+            int rc = dalloc(&e->d_pwr_partial[b], kPwrPartials);
+            if (rc) return rc;
+            if ((rc = dalloc(&e->d_gate[b], C))) return rc;
+        }
     }
     if (want_fast) {
         int rc = fast_init(e->fast, C, e->N, e->taps.data() + e->tap_off[0], e->taps.data() + e->tap_off[1],
@@ -403,10 +422,10 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
                                 (int)(sizeof(float) * 2 * (size_t)(cfg->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad)));
         if (S >= 1) {       // the per-channel tail kernel stages the last stage's input row in shared memory when fused
             size_t row = (size_t)(e->H[S - 1] - 1) + (size_t)kChunk * e->m[S - 1];
-            e->tail_fusable = row * sizeof(float2) <= 100 * 1024;
+            e->tail_fusable = row * sizeof(float2) <= 100 * 1024 && (e->H[S - 1] - 1) / 2 + 1 <= kTailMaxHalf;
             if (e->tail_fusable)
-                CU(cudaFuncSetAttribute(k_chan_tail<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)(sizeof(float2) * std::max<size_t>(row, 768))));
+                CU(cudaFuncSetAttribute(k_chan_head<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)(sizeof(float2) * row)));
         }
     }
     return reset_state(e);
@@ -554,39 +573,55 @@ int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_
 }
 
 // power partials of the new block (when boundary B will run) + the raw delay line, one launch
-int launch_prep(sdrx_engine *e, int fmt, uint8_t *buf, const uint8_t *prev, unsigned n, bool power, int hist_bytes, long prev_bytes) {
+int launch_prep(sdrx_engine *e, int fmt, uint8_t *buf, const uint8_t *prev, unsigned n, bool power, int hist_bytes, long prev_bytes, float *partial) {
     const int np = power ? kPwrPartials : 0;
     const int grid = np + div_up(hist_bytes, 256);
     if (grid == 0) return SDRX_OK;
     switch (fmt) {
-        case SDRX_FMT_U8:  k_prep<SDRX_FMT_U8><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, e->d_pwr_partial, np, buf, prev, prev_bytes, hist_bytes); break;
-        case SDRX_FMT_S16: k_prep<SDRX_FMT_S16><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, e->d_pwr_partial, np, buf, prev, prev_bytes, hist_bytes); break;
-        default:           k_prep<SDRX_FMT_F32><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, e->d_pwr_partial, np, buf, prev, prev_bytes, hist_bytes); break;
+        case SDRX_FMT_U8:  k_prep<SDRX_FMT_U8><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
+        case SDRX_FMT_S16: k_prep<SDRX_FMT_S16><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
+        default:           k_prep<SDRX_FMT_F32><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
     }
     ++e->launches;
     CU(cudaGetLastError());
     return SDRX_OK;
 }
 
-// boundary B on the chunk in o.ch_iq
-// `fused`: the last MSD stage (and the specialised bank's tail fix-ups) run inside the per-channel kernel.
-int launch_demod(sdrx_engine *e, OutSet &o, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr) {
+// Boundary B on the chunk in o.ch_iq (output set `idx`).  The head kernel (last MSD stage when `fused`, squelch
+// detector) runs on the main stream; the recurrences and the mix follow on the side stream, where they overlap
+// the next block's channel bank.
+int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr) {
+    OutSet &o = e->out[idx];
     const TailSnap snap{o.sql, o.agc_gain, o.lf_gain};
     if (fused) {
-        const size_t dyn = sizeof(float2) * (size_t)std::max(fused->H - 1 + fused->n_in, 768);
-        k_chan_tail<true><<<e->C, kTailThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->agc, e->lf,
-                                                                  e->lf_active, e->d_sql_level, o.audio, o.snr, snap);
+        const size_t dyn = sizeof(float2) * (size_t)(fused->H - 1 + fused->n_in);
+        k_chan_head<true><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
+                                                                  o.snr, e->d_gate[idx], snap);
     } else {
-        k_chan_tail<false><<<e->C, kTailThreads, sizeof(float2) * 768, e->s_main>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
-                                                                                  e->agc, e->lf, e->lf_active, e->d_sql_level,
-                                                                                  o.audio, o.snr, snap);
+        k_chan_head<false><<<e->C, kHeadThreads, 0, e->s_main>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
+                                                                 e->d_sql_level, o.snr, e->d_gate[idx], snap);
     }
-    const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad;
-    k_mix_fir2_pcm<<<1, 1024, smem, e->s_main>>>(o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps,
-                                                 e->d_fir_hist, o.mix_pre, o.mix, o.pcm, e->d_pwr_partial,
-                                                 have_power ? kPwrPartials : 0, n_samples, have_power ? o.pwr : nullptr);
-    e->launches += 2;
     CU(cudaGetLastError());
+    CU(cudaEventRecord(e->ev_head_done, e->s_main));
+    CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
+    k_chan_recur<<<e->C, 32, 0, e->s_side>>>(o.ch_iq, e->chiq_stride, e->st, e->d_gate[idx], e->tb, e->agc, e->lf, e->lf_active,
+                                             o.audio, snap);
+    const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad;
+    k_mix_fir2_pcm<<<1, 1024, smem, e->s_side>>>(o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps,
+                                                 e->d_fir_hist, o.mix_pre, o.mix, o.pcm, e->d_pwr_partial[idx],
+                                                 have_power ? kPwrPartials : 0, n_samples, have_power ? o.pwr : nullptr,
+                                                 nullptr, 0, (e->flags & SDRX_FLAG_PARTIAL_MIX) ? 0 : 1);
+    e->launches += 3;
+    CU(cudaGetLastError());
+    if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_side));
+    CU(cudaEventRecord(e->ev_side_done[idx], e->s_side));
+    e->side_pending[idx] = true;
+    return SDRX_OK;
+}
+
+// the main stream may not touch output set `idx` (or its power partials / gate) before the side stream is done with it
+int wait_side(sdrx_engine *e, int idx) {
+    if (e->side_pending[idx]) CU(cudaStreamWaitEvent(e->s_main, e->ev_side_done[idx], 0));
     return SDRX_OK;
 }
 
@@ -642,6 +677,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         CU(cudaEventRecord(e->ev_copied[cur], e->s_copy));
         CU(cudaStreamWaitEvent(e->s_main, e->ev_copied[cur], 0));
     }
+    { int rc = wait_side(e, cur); if (rc) return rc; }      // block b-2's recurrences / mix read this output set
     if (e->timing) CU(cudaEventRecord(e->ev_t0, e->s_main));
 
 
@@ -661,7 +697,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     // ---- raw delay line (last raw_hist samples of the previous [hist | block] move in front of this block)
     //      and, when boundary B will run, the block power partials
     {
-        int rc = launch_prep(e, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps);
+        int rc = launch_prep(e, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps, e->d_pwr_partial[cur]);
         if (rc) return rc;
         CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));
     }
@@ -692,8 +728,9 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     if (rc) return rc;
     if (e->timing) CU(cudaEventRecord(e->ev_t1, e->s_main));
 
-    if (demod) { rc = launch_demod(e, o, n > 0, n, fuse_tail ? &tail : nullptr); if (rc) return rc; }
-    if (e->timing) { CU(cudaEventRecord(e->ev_t2, e->s_main)); e->timing_valid = true; }
+    if (demod) { rc = launch_demod(e, cur, n > 0, n, fuse_tail ? &tail : nullptr); if (rc) return rc; }
+    else if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_main));
+    if (e->timing) e->timing_valid = true;
 
     e->trans_pos = (e->trans_pos + n) % e->N;
     e->total += n;
@@ -729,6 +766,16 @@ extern "C" int sdrx_engine_sync(sdrx_engine *e) {
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
+    CU(cudaStreamSynchronize(e->s_side));
+    return SDRX_OK;
+}
+
+// Orders the main stream behind everything queued so far on the side stream, so that an event recorded on
+// sdrx_engine_stream() afterwards covers the whole of every pushed block (bench timing).
+extern "C" int sdrx_engine_join(sdrx_engine *e) {
+    if (!e) return fail(SDRX_ERR_ARG, "null engine");
+    DevGuard g(e->dev);
+    for (int b = 0; b < kNBuf; ++b) { int rc = wait_side(e, b); if (rc) return rc; }
     return SDRX_OK;
 }
 
@@ -750,7 +797,8 @@ extern "C" int sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs 
     if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
     if (!e->last_demod) return fail(SDRX_ERR_STATE, "the last block did not yield 512 samples per channel; boundary B did not run");
     DevGuard g(e->dev);
-    int rc = copy_outputs(e, e->out[(e->blocks - 1) & 1], out);
+    int rc = wait_side(e, (int)((e->blocks - 1) & 1));
+    if (!rc) rc = copy_outputs(e, e->out[(e->blocks - 1) & 1], out);
     if (rc) return rc;
     CU(cudaStreamSynchronize(e->s_main));
     return SDRX_OK;
@@ -760,16 +808,46 @@ extern "C" int sdrx_engine_demod_block(sdrx_engine *e, const float *ch_iq, float
     if (!e || !ch_iq) return fail(SDRX_ERR_ARG, "null argument");
     if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
     DevGuard g(e->dev);
-    OutSet &o = e->out[e->blocks & 1];
+    const int idx = (int)(e->blocks & 1);
+    OutSet &o = e->out[idx];
+    { int rc = wait_side(e, idx); if (rc) return rc; }
     CU(cudaMemcpy2DAsync(o.ch_iq, (size_t)e->chiq_stride * sizeof(float2), ch_iq, (size_t)kChunk * sizeof(float2),
                          (size_t)kChunk * sizeof(float2), (size_t)e->C, cudaMemcpyHostToDevice, e->s_main));
     CU(cudaMemcpyAsync(o.pwr, &pwr_dbfs, sizeof(float), cudaMemcpyHostToDevice, e->s_main));
     CU(cudaStreamSynchronize(e->s_main));     // pwr_dbfs lives on this stack frame
-    int rc = launch_demod(e, o, false, 0);
+    int rc = launch_demod(e, idx, false, 0);
     if (rc) return rc;
     e->last_out_len = kChunk;
     e->last_demod = true;
     ++e->blocks;      // the output set alternates like a pushed block's; the channelizer state is untouched
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_parts, float *mix_pre, float *mix, int16_t *pcm) {
+    if (!e || !parts || n_parts < 1) return fail(SDRX_ERR_ARG, "null argument");
+    if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
+    DevGuard g(e->dev);
+    const size_t bytes = sizeof(float) * 2 * kChunk * (size_t)n_parts;
+    if ((size_t)n_parts > e->parts_cap) {
+        CU(cudaStreamSynchronize(e->s_main));
+        cudaFree(e->d_parts);
+        e->d_parts = nullptr;
+        CU(cudaMalloc((void **)&e->d_parts, bytes));
+        e->parts_cap = (size_t)n_parts;
+    }
+    const int idx = e->blocks ? (int)((e->blocks - 1) & 1) : 0;
+    OutSet &o = e->out[idx];
+    { int rc = wait_side(e, idx); if (rc) return rc; }
+    CU(cudaMemcpyAsync(e->d_parts, parts, bytes, cudaMemcpyHostToDevice, e->s_main));
+    const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad;
+    k_mix_fir2_pcm<<<1, 1024, smem, e->s_main>>>(o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps, e->d_fir_hist,
+                                                 o.mix_pre, o.mix, o.pcm, nullptr, 0, 0, nullptr, e->d_parts, n_parts, 1);
+    ++e->launches;
+    CU(cudaGetLastError());
+    if (mix_pre) CU(cudaMemcpyAsync(mix_pre, o.mix_pre, sizeof(float) * 2 * kChunk, cudaMemcpyDeviceToHost, e->s_main));
+    if (mix) CU(cudaMemcpyAsync(mix, o.mix, sizeof(float) * 2 * kChunk, cudaMemcpyDeviceToHost, e->s_main));
+    if (pcm) CU(cudaMemcpyAsync(pcm, o.pcm, sizeof(int16_t) * 2 * kChunk, cudaMemcpyDeviceToHost, e->s_main));
+    CU(cudaStreamSynchronize(e->s_main));
     return SDRX_OK;
 }
 
@@ -830,6 +908,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
+    CU(cudaStreamSynchronize(e->s_side));
     if (e->generic_stale) {      // the blob always carries the stage delay lines (a generic engine can load it)
         const int last_ = (int)((e->blocks & 1) ^ 1);
         int rc = materialize_generic(e, e->fmt, e->d_raw[last_], (long)e->raw_hist + (long)e->prev_n, e->total);
@@ -884,6 +963,8 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
+    CU(cudaStreamSynchronize(e->s_side));
+    e->side_pending[0] = e->side_pending[1] = false;
     const uint8_t *p = (const uint8_t *)buf + sizeof(h);
     e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = h.blocks; e->total = h.total; e->generic_stale = false;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = h.phase[s];

@@ -13,7 +13,8 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import FMT_F32, FMT_S16, FMT_U8, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, CHUNK, SdrxError, check
+from ._lib import (FMT_F32, FMT_S16, FMT_U8, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, CHUNK, SdrxError,
+                   check)
 from .config import ChannelPlan, make_translator, tables
 
 
@@ -75,7 +76,7 @@ class PinnedBuffer:
 class Engine:
     def __init__(self, plan: ChannelPlan, device: int = 0, use_lf_agc: bool = False, lf_gain_db: float = 0.0,
                  block_len: Optional[int] = None, force_generic: bool = False, demod: bool = True,
-                 translators: Optional[np.ndarray] = None):
+                 translators: Optional[np.ndarray] = None, partial_mix: bool = False):
         self.lib = _lib.load()
         self.plan = plan
         self.device = device
@@ -119,7 +120,8 @@ class Engine:
         cfg.lf_gain_db = lf_gain_db
         cfg.fir2_taps, cfg.fir2_ntaps = fp(fir2), fir2.size
         cfg.passband_shape, cfg.ramp_up, cfg.ramp_down = fp(shape), fp(rup), fp(rdn)
-        cfg.flags = (FLAG_FORCE_GENERIC if force_generic else 0) | (0 if demod else FLAG_NO_DEMOD)
+        cfg.flags = ((FLAG_FORCE_GENERIC if force_generic else 0) | (0 if demod else FLAG_NO_DEMOD)
+                     | (FLAG_PARTIAL_MIX if partial_mix else 0))
         self.demod = demod
         h = C.c_void_p()
         check(self.lib.sdrx_engine_create(C.byref(cfg), C.byref(h)))
@@ -205,8 +207,24 @@ class Engine:
         check(self.lib.sdrx_engine_demod_block(self.h, x.view(np.float32).ctypes.data_as(_lib.c_float_p), pwr_dbfs))
         return self.outputs(with_iq=False)
 
+    def finish_mix(self, parts: np.ndarray):
+        """Channel-sharded runs: add the per-GPU partial mixes ``parts[n][1024]`` in order, then FIR2 + s16 with
+        this engine's carried FIR2 ring.  Returns ``(mix_pre, mix, pcm)``."""
+        parts = np.ascontiguousarray(parts, np.float32).reshape(-1, 2 * CHUNK)
+        mix_pre = np.empty(2 * CHUNK, np.float32)
+        mix = np.empty(2 * CHUNK, np.float32)
+        pcm = np.empty(2 * CHUNK, np.int16)
+        check(self.lib.sdrx_engine_finish_mix(self.h, parts.ctypes.data_as(_lib.c_float_p), parts.shape[0],
+                                              mix_pre.ctypes.data_as(_lib.c_float_p), mix.ctypes.data_as(_lib.c_float_p),
+                                              pcm.ctypes.data_as(_lib.c_i16_p)))
+        return mix_pre, mix, pcm
+
     def sync(self) -> None:
         check(self.lib.sdrx_engine_sync(self.h))
+
+    def join(self) -> None:
+        """Order :attr:`stream` behind the side stream's queued work (see sdrx_engine_join)."""
+        check(self.lib.sdrx_engine_join(self.h))
 
     def reset(self) -> None:
         check(self.lib.sdrx_engine_reset(self.h))
