@@ -196,7 +196,7 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
         };
         fetch(0, 0);
         land(0, 0);
-        __syncthreads();
+        __syncwarp();                                      // a segment's window is private to its half warp: no CTA barrier
 
         // per-thread filter state
         u64 a[8], b[4], c3[5];
@@ -236,7 +236,7 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
                 c3[0] = c3[1]; c3[1] = c3[2]; c3[2] = c3[3]; c3[3] = c3[4]; c3[4] = 0ull;
             }
             if (t + 1 < nsteps) land(t + 1, (t + 1) & 1);
-            __syncthreads();
+            __syncwarp();
         }
         // what this segment contributes to the (up to four) outputs that follow it
         if (have && u1 < U && ch_ok) {
