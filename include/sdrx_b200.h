@@ -52,6 +52,8 @@ typedef enum { SDRX_FMT_U8 = 0, SDRX_FMT_S16 = 1, SDRX_FMT_F32 = 2 } sdrx_iq_for
 /* flags for sdrx_engine_config.flags */
 #define SDRX_FLAG_FORCE_GENERIC 0x1u  /* never take the specialised channel-bank kernel         */
 #define SDRX_FLAG_NO_DEMOD      0x2u  /* channelizer only (boundary A); skip boundary B kernels  */
+#define SDRX_FLAG_NO_PAIRING    0x8u  /* specialised bank: one channel per lane slot even where +-offset channels
+                                         could share a translator table as conjugates                       */
 #define SDRX_FLAG_PARTIAL_MIX   0x4u  /* channel-sharded run: stop at mix_pre (this GPU's share of the pan
                                          mix); FIR2 + s16 run once, in sdrx_engine_finish_mix              */
 
@@ -146,6 +148,7 @@ int  sdrx_engine_reset(sdrx_engine *e);
 void    *sdrx_engine_stream(sdrx_engine *e);          /* cudaStream_t the hot kernels run on       */
 uint64_t sdrx_engine_launch_count(sdrx_engine *e);    /* kernels launched so far                   */
 int      sdrx_engine_uses_fast_path(sdrx_engine *e);  /* 1 when the specialised channel bank runs  */
+int      sdrx_engine_bank_pairs(sdrx_engine *e);      /* conjugate channel pairs sharing a lane slot */
 /* Device-timed duration (ms, CUDA events on the engine stream) of the channel-bank kernel(s) and of
  * the whole block for the last pushed block; valid after a sync. */
 int      sdrx_engine_last_timing(sdrx_engine *e, float *bank_ms, float *block_ms);

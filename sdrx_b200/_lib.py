@@ -13,7 +13,7 @@ c_u8_p = C.POINTER(C.c_uint8)
 c_i16_p = C.POINTER(C.c_int16)
 
 FMT_U8, FMT_S16, FMT_F32 = 0, 1, 2
-FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX = 0x1, 0x2, 0x4
+FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING = 0x1, 0x2, 0x4, 0x8
 CHUNK = 512
 
 
@@ -71,6 +71,7 @@ PROTOTYPES = [
     ("sdrx_engine_stream", C.c_void_p, [C.c_void_p]),
     ("sdrx_engine_launch_count", C.c_uint64, [C.c_void_p]),
     ("sdrx_engine_uses_fast_path", C.c_int, [C.c_void_p]),
+    ("sdrx_engine_bank_pairs", C.c_int, [C.c_void_p]),
     ("sdrx_engine_last_timing", C.c_int, [C.c_void_p, c_float_p, c_float_p]),
     ("sdrx_engine_set_timing", C.c_int, [C.c_void_p, C.c_int]),
     ("sdrx_host_alloc", C.c_void_p, [C.c_size_t]),

@@ -1,32 +1,45 @@
 // sdrx_b200 -- specialised channel bank for sm_100a: raw->float ingest, NCO mix (msd.hpp:134-135) and
 // the first three decimating FIR stages (msd.hpp:251-335) of every channel in ONE kernel, for chains
-// whose first three stages all decimate by 5 (the 10 MS/s and 6 MS/s Airspy chains, sdrx.cpp:1646-1668).
+// whose first three stages all decimate by 5 (the 10 MS/s Airspy chain, sdrx.cpp:1660-1668).
 //
 // Mapping (DESIGN.md "channel bank"):
 //   * FP32 CUDA-core bound (19.2 flop per channel-sample against 8 B of *shared* input), so the job is
 //     to keep the FMA pipe issuing: accumulations are packed FFMA2 (fma.rn.f32x2 on (re,im) pairs with
 //     the tap duplicated), which halves their issue slots and leaves room for the shared-memory loads.
-//   * A CTA owns a group of 16 channels.  Their translator tables (the reference's own FP32 tables,
-//     full period N, 9.6 KB per channel at N=1200) sit in shared memory for the CTA's whole life; the
-//     16 lanes of a half warp are the 16 channels, so one table row is one conflict-free 128 B read.
+//   * A CTA owns a group of 16 lane slots.  Their translator tables (the reference's own FP32 tables,
+//     full period N, 9.6 KB per slot at N=1200) sit in shared memory for the CTA's whole life; the
+//     16 lanes of a half warp are the 16 slots, so one table row is one conflict-free 128 B read.
+//   * NCH = 2 ("conjugate pairs"): the table of channel offset -k is, bit for bit, the complex conjugate of
+//     the table of +k (the float-rounded angle is sign symmetric, cosf is even, sinf odd), so one thread
+//     carries BOTH channels of a +-k pair off one table word and one input word: the shared-memory traffic per
+//     channel-sample halves and the two mixes share their four products (6 instead of 8 FMA-pipe slots).
+//     The host pairs channels by comparing the tables it was given (never by assuming offsets); channels
+//     without a partner ride alone in a slot.  NCH = 1 is the same kernel with one channel per slot and is
+//     used when too few channels pair up.
 //   * Time is cut into per-thread segments that are multiples of 125 samples (one stage-3 output).  The
-//     two half warps of a warp are two segments; the 32 segments of a CTA stream their input through a
+//     two half warps of a warp are two segments; each segment streams its input through its own
 //     double-buffered shared-memory window (global loads for step t+1 are in flight while step t is
-//     computed), every sample being fetched from L2 once per 16 channels.
+//     computed; the window is private to the half warp, so only warp-level syncs are needed), every
+//     sample being fetched from L2 once per slot group.
 //   * Each thread runs the three stages in transposed form (one accumulator per output in flight), so
-//     there are no delay lines: a segment warms up on the 125 samples before it (stages 1-2 recomputed,
-//     1.5 % extra work), and stage-3 outputs that straddle a segment boundary are produced as two
-//     partial sums (the tail of one segment, the head of the next) that k_fix_tails adds.  At the start
+//     there are no delay lines: a segment warms up on the 125 samples before it (stages 1-2 recomputed),
+//     and stage-3 outputs that straddle a segment boundary are produced as two partial sums (the tail of
+//     one segment, the head of the next) that the next kernel adds in a fixed order.  At the start
 //     of a block the warm-up is 500 samples of the carried raw history and the heads are complete, so
 //     the only state carried between blocks is that raw history.
-//   * Work is (channel group x time) linearised and cut into one contiguous range per SM, so all 148
+//   * Work is (slot group x time) linearised and cut into one contiguous range per SM, so all 148
 //     SMs finish together whatever the channel count.
 #pragma once
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <vector>
+
 #include "common.cuh"
 
 namespace sdrx {
 
-constexpr int kFastCh = 16;        // channels per group
+constexpr int kFastCh = 16;        // lane slots per group
 constexpr int kFastSegs = 32;      // time segments per CTA (512 threads: 4 warps per scheduler)
 constexpr int kFastThreads = kFastCh * kFastSegs;
 constexpr int kUnit = 125;         // raw samples per stage-3 output
@@ -49,8 +62,7 @@ struct FastTaps {                  // kernel parameter: lives in the constant ba
 
 // One (group, unit range) run of one CTA.  The range is cut into two halves A = [u_begin, u_begin+H) and
 // B = [u_begin+H, u_end); warp w takes the w-th segment (seg_len units) of A on lanes 0-15 and the w-th
-// segment of B on lanes 16-31.  The scheduler makes H a whole number of translator periods whenever that
-// keeps the halves balanced, so both half warps read the SAME table row: one broadcast wavefront.
+// segment of B on lanes 16-31.
 struct FastPiece {
     int group, u_begin, u_end, H, seg_len, slot_base;
 };
@@ -73,14 +85,16 @@ __device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 d; asm("fma.rn.f3
 __device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 __device__ __forceinline__ u64 tap2(const float2 &h) { return pack2(h.x, h.y); }
 
-// One 25-sample body of one thread: mixes 25 samples and advances the three stages by 5 / 1 / 0.2 outputs.
+// One 25-sample body of one thread: mixes 25 samples and advances the three stages by 5 / 1 / 0.2 outputs, for
+// the NCH channels of its slot (channel 1 mixes with the conjugate of the table word).
 //   xp   the thread's 25 staged input samples (shared memory, broadcast within the half warp)
-//   tp   table row of the first sample, already offset to the thread's channel (row stride 16 float2)
+//   tp   table row of the first sample, already offset to the thread's slot (row stride 16 float2)
 //   a    stage-1 accumulators: a[0..2] enter in flight, a[5..7] leave in flight (renamed by the caller)
 //   b    stage-2 accumulators: b[0..2] enter in flight, b[0] completes here, b[3] starts here
 // Stage-1 output 5B+q covers raw 25B + [5q-12, 5q+4]; stage-2 output B+q2 covers stage-1 5B + [5q2-14, 5q2+4].
+template <int NCH>
 __device__ __forceinline__ void fast_body(const float2 *__restrict__ xp, const float2 *__restrict__ tp,
-                                          const FastTaps &tp_, u64 (&a)[8], u64 (&b)[4]) {
+                                          const FastTaps &tp_, u64 (&a)[NCH][8], u64 (&b)[NCH][4]) {
     float2 xv[kBody + 1];
 #pragma unroll
     for (int i = 0; i < kBody + 1; i += 2) {                   // 13 x LDS.128 (the 26th slot is padding)
@@ -92,34 +106,42 @@ __device__ __forceinline__ void fast_body(const float2 *__restrict__ xp, const f
     for (int i = 0; i < kBody; ++i) {
         const float2 x = xv[i];
         const float2 w = tp[i * kFastCh];
-        const float sr = fmaf(x.x, w.x, -(x.y * w.y));          // msd.hpp:134  in[i] * translator_[pos]
-        const float si = fmaf(x.x, w.y, x.y * w.x);
-        const u64 s = pack2(sr, si);
+        // msd.hpp:134  in[i] * translator_[pos]; the conjugate channel reuses the same four products
+        const float m1 = x.y * w.y, m2 = x.y * w.x;
+        u64 s[NCH];
+        s[0] = pack2(fmaf(x.x, w.x, -m1), fmaf(x.x, w.y, m2));
+        if (NCH == 2) s[1] = pack2(fmaf(x.x, w.x, m1), fmaf(-x.x, w.y, m2));
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const int t = i - 5 * q + 12;                         // tap index of this sample in output q
-            if (t == 0) a[q] = mul2(s, tap2(tp_.h1[0]));
-            else if (t > 0 && t <= 16) a[q] = fma2(s, tap2(tp_.h1[t]), a[q]);
-        }
-        if (i % 5 == 4) {                                         // stage-1 output q1 = i/5 is complete
-            const int q1 = i / 5;
-            const u64 y = a[q1];
+        for (int c = 0; c < NCH; ++c) {
 #pragma unroll
-            for (int q2 = 0; q2 < 4; ++q2) {
-                const int t2 = q1 - 5 * q2 + 14;
-                if (t2 == 0) b[q2] = mul2(y, tap2(tp_.h2[0]));
-                else if (t2 > 0 && t2 <= 18) b[q2] = fma2(y, tap2(tp_.h2[t2]), b[q2]);
+            for (int q = 0; q < 8; ++q) {
+                const int t = i - 5 * q + 12;                     // tap index of this sample in output q
+                if (t == 0) a[c][q] = mul2(s[c], tap2(tp_.h1[0]));
+                else if (t > 0 && t <= 16) a[c][q] = fma2(s[c], tap2(tp_.h1[t]), a[c][q]);
+            }
+            if (i % 5 == 4) {                                     // stage-1 output q1 = i/5 is complete
+                const int q1 = i / 5;
+                const u64 y = a[c][q1];
+#pragma unroll
+                for (int q2 = 0; q2 < 4; ++q2) {
+                    const int t2 = q1 - 5 * q2 + 14;
+                    if (t2 == 0) b[c][q2] = mul2(y, tap2(tp_.h2[0]));
+                    else if (t2 > 0 && t2 <= 18) b[c][q2] = fma2(y, tap2(tp_.h2[t2]), b[c][q2]);
+                }
             }
         }
     }
 }
 
 // grid = number of CTAs in the schedule, block = kFastThreads, dynamic smem = fast_smem_bytes(N).
-template <int FMT>
+//   table      [N][tstride] float2, one column per lane slot (slot = group * 16 + lane)
+//   slot_chan  [slots][NCH] channel index carried by the slot (-1: none); channel 1 of a slot is the conjugate partner
+template <int FMT, int NCH>
 static __global__ void __launch_bounds__(kFastThreads, 1)
-k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *__restrict__ table, int Cpad, int C,
-            int N, int pos0, const FastTaps taps, const FastCta *__restrict__ ctas, const FastPiece *__restrict__ pieces,
-            int U, float2 *__restrict__ s3, long s3_stride, int s3_off, float2 *__restrict__ tails, int n_slots) {
+k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *__restrict__ table, int tstride,
+            const int *__restrict__ slot_chan, int N, int pos0, const FastTaps taps, const FastCta *__restrict__ ctas,
+            const FastPiece *__restrict__ pieces, int U, float2 *__restrict__ s3, long s3_stride, int s3_off,
+            float2 *__restrict__ tails, int n_slots) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2 *tb = reinterpret_cast<float2 *>(smem_raw);                       // [(N + kWrap)][16]
     float2 *xs = tb + (size_t)(N + kWrap) * kFastCh;                         // [2][kFastSegs][kXSeg]
@@ -134,14 +156,15 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
 
     for (int pi = me.piece_begin; pi < me.piece_end; ++pi) {
         const FastPiece pc = pieces[pi];
-        __syncthreads();                                   // previous piece is done with tb / xs
         if (pc.group != cur_group) {
+            __syncthreads();                               // every warp is done with the previous group's table
             cur_group = pc.group;
             const float2 *src = table + pc.group * kFastCh;
             for (int idx = tid; idx < (N + kWrap) * kFastCh; idx += kFastThreads) {
                 const int row = idx >> 4, c16 = idx & 15;
-                tb[idx] = __ldg(src + (long)(row < N ? row : row - N) * Cpad + c16);
+                tb[idx] = __ldg(src + (long)(row < N ? row : row - N) * tstride + c16);
             }
+            __syncthreads();
         }
         // my segment
         int u0 = 0, u1 = 0;
@@ -178,7 +201,7 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
                 }
             }
         };
-        auto land = [&](int t, int buf) {                  // make chunk t visible in xs[buf] (before the barrier)
+        auto land = [&](int t, int buf) {                  // make chunk t visible in xs[buf] (before the warp sync)
             if constexpr (FMT == SDRX_FMT_F32) {
                 asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
             } else {
@@ -194,22 +217,31 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
                 }
             }
         };
+        __syncwarp();                                      // the warp is done with its previous piece's window
         fetch(0, 0);
         land(0, 0);
         __syncwarp();                                      // a segment's window is private to its half warp: no CTA barrier
 
         // per-thread filter state
-        u64 a[8], b[4], c3[5];
+        u64 a[NCH][8], b[NCH][4], c3[NCH][5];
 #pragma unroll
-        for (int q = 0; q < 8; ++q) a[q] = 0ull;
+        for (int c = 0; c < NCH; ++c) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) b[q] = 0ull;
+            for (int q = 0; q < 8; ++q) a[c][q] = 0ull;
 #pragma unroll
-        for (int q = 0; q < 5; ++q) c3[q] = 0ull;
+            for (int q = 0; q < 4; ++q) b[c][q] = 0ull;
+#pragma unroll
+            for (int q = 0; q < 5; ++q) c3[c][q] = 0ull;
+        }
         int row = (int)((((long)pos0 + (long)kUnit * (u0 - warm)) % N + N) % N);
         const int feed_from = (u0 == 0) ? 4 : 5 * warm;      // first local body whose stage-2 output feeds stage 3
-        const long out_base = (long)(pc.group * kFastCh + ch) * s3_stride + s3_off;
-        const bool ch_ok = pc.group * kFastCh + ch < C;
+        int chan[NCH];
+        long out_base[NCH];
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+            chan[c] = slot_chan[(pc.group * kFastCh + ch) * NCH + c];
+            out_base[c] = (long)chan[c] * s3_stride + s3_off;
+        }
 
         for (int t = 0; t < nsteps; ++t) {
             if (t + 1 < nsteps) fetch(t + 1, (t + 1) & 1);
@@ -217,46 +249,57 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
                 const float2 *xseg = my_xs + (t & 1) * kFastSegs * kXSeg;
 #pragma unroll 1
                 for (int p = 0; p < 5; ++p) {
-                    fast_body(xseg + p * kXBody, tb + row * kFastCh + ch, taps, a, b);
+                    fast_body<NCH>(xseg + p * kXBody, tb + row * kFastCh + ch, taps, a, b);
                     row += kBody;
                     if (row >= N) row -= N;
-                    const u64 z = b[0];                                  // stage-2 output of this body
-                    b[0] = b[1]; b[1] = b[2]; b[2] = b[3];
-                    a[0] = a[5]; a[1] = a[6]; a[2] = a[7];
-                    // stage 3: output U_+q3 covers stage-2 5U_ + [5q3-16, 5q3+4]
-                    if (t * 5 + p >= feed_from) {
-                        c3[0] = fma2(z, tap2(taps.h3[p + 16]), c3[0]);
-                        c3[1] = fma2(z, tap2(taps.h3[p + 11]), c3[1]);
-                        c3[2] = fma2(z, tap2(taps.h3[p + 6]), c3[2]);
-                        c3[3] = fma2(z, tap2(taps.h3[p + 1]), c3[3]);
-                        if (p == 4) c3[4] = mul2(z, tap2(taps.h3[0]));
+#pragma unroll
+                    for (int c = 0; c < NCH; ++c) {
+                        const u64 z = b[c][0];                               // stage-2 output of this body
+                        b[c][0] = b[c][1]; b[c][1] = b[c][2]; b[c][2] = b[c][3];
+                        a[c][0] = a[c][5]; a[c][1] = a[c][6]; a[c][2] = a[c][7];
+                        // stage 3: output U_+q3 covers stage-2 5U_ + [5q3-16, 5q3+4]
+                        if (t * 5 + p >= feed_from) {
+                            c3[c][0] = fma2(z, tap2(taps.h3[p + 16]), c3[c][0]);
+                            c3[c][1] = fma2(z, tap2(taps.h3[p + 11]), c3[c][1]);
+                            c3[c][2] = fma2(z, tap2(taps.h3[p + 6]), c3[c][2]);
+                            c3[c][3] = fma2(z, tap2(taps.h3[p + 1]), c3[c][3]);
+                            if (p == 4) c3[c][4] = mul2(z, tap2(taps.h3[0]));
+                        }
                     }
                 }
-                if (t >= warm && ch_ok) s3[out_base + (u0 + t - warm)] = unpack2(c3[0]);
-                c3[0] = c3[1]; c3[1] = c3[2]; c3[2] = c3[3]; c3[3] = c3[4]; c3[4] = 0ull;
+#pragma unroll
+                for (int c = 0; c < NCH; ++c) {
+                    if (t >= warm && chan[c] >= 0) s3[out_base[c] + (u0 + t - warm)] = unpack2(c3[c][0]);
+                    c3[c][0] = c3[c][1]; c3[c][1] = c3[c][2]; c3[c][2] = c3[c][3]; c3[c][3] = c3[c][4]; c3[c][4] = 0ull;
+                }
             }
             if (t + 1 < nsteps) land(t + 1, (t + 1) & 1);
             __syncwarp();
         }
         // what this segment contributes to the (up to four) outputs that follow it
-        if (have && u1 < U && ch_ok) {
-            float2 *tl = tails + ((long)(pc.group * kFastCh + ch) * n_slots + pc.slot_base + half * (kFastSegs / 2) + w) * 4;
+        if (have && u1 < U) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) tl[q] = unpack2(c3[q]);
+            for (int c = 0; c < NCH; ++c) {
+                if (chan[c] < 0) continue;
+                float2 *tl = tails + ((long)chan[c] * n_slots + pc.slot_base + half * (kFastSegs / 2) + w) * 4;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) tl[q] = unpack2(c3[c][q]);
+            }
         }
     }
 }
 
-// Completes the stage-3 outputs that straddle segment boundaries: s3[c][u] += sum of the tails that reach u,
-// added in a fixed order by one thread per (output, channel).
+// Completes the stage-3 outputs that straddle segment boundaries (only when the next kernel does not do it itself):
+// s3[c][u] += sum of the tails that reach u, added in a fixed order by one thread per (output, channel of the group).
 static __global__ void k_fix_tails(float2 *__restrict__ s3, long s3_stride, int s3_off, const float2 *__restrict__ tails,
-                                   int n_slots, const FastFix *__restrict__ fixes, int n_fixes, int C) {
+                                   int n_slots, const FastFix *__restrict__ fixes, int n_fixes,
+                                   const int *__restrict__ slot_chan, int per_group /* 16 * NCH */) {
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= n_fixes * kFastCh) return;
-    const int c16 = idx & 15, fi = idx >> 4;
+    if (idx >= n_fixes * per_group) return;
+    const int j = idx % per_group, fi = idx / per_group;
     const FastFix fx = fixes[fi];
-    const int c = fx.group * kFastCh + c16;
-    if (c >= C) return;
+    const int c = slot_chan[fx.group * per_group + j];
+    if (c < 0) return;
     float2 *p = s3 + (long)c * s3_stride + s3_off + fx.u;
     float2 v = *p;
     for (int k = 0; k < fx.n; ++k) {
@@ -271,7 +314,8 @@ inline size_t fast_smem_bytes(int N) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// Host side: the static schedule (depends only on C, the block length and the SM count) and launch.
+// Host side: slot assignment (conjugate pairing), the static schedule (depends only on the slot count,
+// the block length and the SM count) and launch.
 struct FastSchedule {
     int U = 0;                         // units (stage-3 outputs per channel) of the block length it was built for
     int n_ctas = 0, n_slots = 0, n_fixes = 0;
@@ -285,13 +329,19 @@ struct FastBank {
     bool enabled = false;
     int stages_fused = 0;              // leading MSD stages the kernel covers (3)
     int n_sms = 148;
-    int groups = 0;
+    int nch = 1;                       // channels per lane slot: 2 when conjugate pairing pays
+    int groups = 0;                    // ceil(slots / 16)
+    int n_pairs = 0;
     int period_units = 1;              // units after which the translator phase repeats: N / gcd(N, 125)
     FastTaps taps{};
     FastSchedule sched[2];             // small cache keyed by U (block length / 125)
     float2 *d_tails = nullptr;
     int tails_slots = 0;               // capacity of d_tails in slots per channel
     int C = 0;
+    float2 *d_table_slot = nullptr;    // [N][groups*16] one column per slot (own copy only when paired)
+    int tstride = 0;
+    int *d_slot_chan = nullptr;        // [groups*16][nch]
+    int *d_chan_group = nullptr;       // [C] group whose fix list covers the channel
 
     void free_schedule(FastSchedule &s) {
         cudaFree(s.d_ctas); cudaFree(s.d_pieces); cudaFree(s.d_fixes); cudaFree(s.d_fix_range);
@@ -299,8 +349,8 @@ struct FastBank {
     }
     void destroy() {
         for (auto &s : sched) free_schedule(s);
-        cudaFree(d_tails);
-        d_tails = nullptr;
+        cudaFree(d_tails); cudaFree(d_table_slot); cudaFree(d_slot_chan); cudaFree(d_chan_group);
+        d_tails = nullptr; d_table_slot = nullptr; d_slot_chan = nullptr; d_chan_group = nullptr;
         enabled = false;
     }
 };
@@ -314,9 +364,41 @@ inline bool fast_eligible(int S, const int *m, const int *H, int N) {
     return true;
 }
 
+// Conjugate partners among the translator tables the caller supplied ([C][N] float2, row ignored where has[c] == 0):
+// partner[c] = d when table[d][n] == conj(table[c][n]) for every n (compared as numbers), else -1.
+inline std::vector<int> fast_find_partners(const float *tables, const uint8_t *has, int C, int N) {
+    std::vector<int> partner((size_t)C, -1);
+    if (!tables) return partner;
+    auto bits = [](float f) { uint32_t u; memcpy(&u, &f, 4); return (u << 1) == 0 ? 0u : u; };   // +-0 alike
+    auto key = [&](int c, bool conj) {
+        uint64_t h = 1469598103934665603ull;
+        const float *r = tables + (size_t)c * N * 2;
+        for (int n = 0; n < N; ++n) {
+            h = (h ^ bits(r[2 * n])) * 1099511628211ull;
+            h = (h ^ bits(conj ? -r[2 * n + 1] : r[2 * n + 1])) * 1099511628211ull;
+        }
+        return h;
+    };
+    std::multimap<uint64_t, int> by_key;
+    for (int c = 0; c < C; ++c) if (has[c]) by_key.insert({key(c, false), c});
+    for (int c = 0; c < C; ++c) {
+        if (!has[c] || partner[c] >= 0) continue;
+        auto range = by_key.equal_range(key(c, true));
+        for (auto it = range.first; it != range.second; ++it) {
+            const int d = it->second;
+            if (d == c || partner[d] >= 0) continue;
+            const float *a = tables + (size_t)c * N * 2, *b = tables + (size_t)d * N * 2;
+            bool ok = true;
+            for (int n = 0; n < N && ok; ++n) ok = a[2 * n] == b[2 * n] && a[2 * n + 1] == -b[2 * n + 1];
+            if (ok) { partner[c] = d; partner[d] = c; break; }
+        }
+    }
+    return partner;
+}
+
 // Linearise (group, unit) work, cut it into one contiguous range per CTA, snap cuts that fall close to
 // a group boundary onto it, split ranges at group boundaries into pieces, lay the two halves of every
-// piece out, and list the stage-3 outputs that need tails added (k_fix_tails).
+// piece out, and list the stage-3 outputs that need tails added.
 inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
     std::vector<FastCta> ctas;
     std::vector<FastPiece> pieces;
@@ -345,12 +427,7 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
             const int L = ue - ub;
             if (g != slot_group) { slot_group = g; slot = 0; }
             FastPiece p{g, ub, ue, L, 0, slot};
-            if (L >= 2 * kFastMinSeg) {
-                const int P = fb.period_units;
-                const int h_min = (L + 1) / 2;
-                const int h_al = (h_min + P - 1) / P * P;            // phase-aligned halves: shared table rows
-                p.H = (h_al < L && h_al - h_min <= L / 8) ? h_al : h_min;
-            }
+            if (L >= 2 * kFastMinSeg) p.H = (L + 1) / 2;
             const int ns = std::max(1, std::min(half_segs, p.H / kFastMinSeg));
             p.seg_len = (p.H + ns - 1) / ns;
             slot += kFastSlotsPerPiece;
@@ -403,49 +480,58 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
     return SDRX_OK;
 }
 
-// Launch the bank for one block of n = 125*U samples (all stage phases zero), then the tail fix-up.
+// Launch the bank for one block of n = 125*U samples (all stage phases zero), then -- unless the caller's next
+// kernel applies the fix list itself (`deferred_fix`) -- the tail fix-up.
 template <int FMT>
-int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int valid_lo, const float2 *table, int Cpad,
-                int N, int pos0, unsigned n, float2 *s3, long s3_stride, int s3_off, uint64_t *launches,
-                cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr, const FastSchedule **deferred_fix = nullptr) {
+int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int valid_lo, int N, int pos0, unsigned n,
+                float2 *s3, long s3_stride, int s3_off, uint64_t *launches, cudaEvent_t ev0 = nullptr,
+                cudaEvent_t ev1 = nullptr, const FastSchedule **deferred_fix = nullptr) {
     const int U = (int)(n / kUnit);
     FastSchedule *sc = nullptr;
     for (auto &s : fb.sched) if (s.U == U) sc = &s;
     if (!sc) {
         FastSchedule &victim = fb.sched[0].U == 0 ? fb.sched[0] : fb.sched[1];
-        CU(cudaStreamSynchronize(st));          // a launch may still be reading the evicted schedule
+        CU(cudaDeviceSynchronize());            // a launch (or a side-stream reader) may still use the evicted schedule
         fb.free_schedule(victim);
         int rc = fast_build_schedule(fb, victim, U);
         if (rc) return rc;
         sc = &victim;
     }
     if (sc->n_slots > fb.tails_slots) {
-        CU(cudaStreamSynchronize(st));
+        CU(cudaDeviceSynchronize());
         cudaFree(fb.d_tails);
         fb.d_tails = nullptr;
         CU(cudaMalloc((void **)&fb.d_tails, sizeof(float2) * 4 * (size_t)sc->n_slots * fb.C));
         fb.tails_slots = sc->n_slots;
     }
     if (ev0) CU(cudaEventRecord(ev0, st));
-    k_bank_fast<FMT><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
-        raw, hist, valid_lo, table, Cpad, fb.C, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U, s3, s3_stride, s3_off,
-        fb.d_tails, fb.tails_slots);
+    if (fb.nch == 2)
+        k_bank_fast<FMT, 2><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
+            raw, hist, valid_lo, fb.d_table_slot, fb.tstride, fb.d_slot_chan, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U,
+            s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots);
+    else
+        k_bank_fast<FMT, 1><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
+            raw, hist, valid_lo, fb.d_table_slot, fb.tstride, fb.d_slot_chan, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U,
+            s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots);
     if (ev1) CU(cudaEventRecord(ev1, st));
     ++*launches;
     if (deferred_fix) *deferred_fix = sc;           // the caller's next kernel applies the fix list itself
     else if (sc->n_fixes > 0) {
-        const int threads = sc->n_fixes * kFastCh;
+        const int per_group = kFastCh * fb.nch;
+        const int threads = sc->n_fixes * per_group;
         k_fix_tails<<<div_up(threads, 256), 256, 0, st>>>(s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots, sc->d_fixes,
-                                                          sc->n_fixes, fb.C);
+                                                          sc->n_fixes, fb.d_slot_chan, per_group);
         ++*launches;
     }
     CU(cudaGetLastError());
     return SDRX_OK;
 }
 
-inline int fast_init(FastBank &fb, int C, int N, const float *h1, const float *h2, const float *h3) {
+// tables: the caller's translator tables [C][N] float2 (host) or nullptr; has[c] == 0 -> no translator (the slot's
+// table column is (1, 0): multiplying by it is exact).
+inline int fast_init(FastBank &fb, int C, int N, const float *h1, const float *h2, const float *h3, const float *tables,
+                     const uint8_t *has, bool allow_pairs) {
     fb.C = C;
-    fb.groups = (C + kFastCh - 1) / kFastCh;
     fb.stages_fused = 3;
     {
         int a = N, b = kUnit;
@@ -458,10 +544,55 @@ inline int fast_init(FastBank &fb, int C, int N, const float *h1, const float *h
     int dev = 0;
     CU(cudaGetDevice(&dev));
     CU(cudaDeviceGetAttribute(&fb.n_sms, cudaDevAttrMultiProcessorCount, dev));
+
+    // ---- slots: conjugate pairs share a slot when enough channels pair up to shrink the work
+    std::vector<uint8_t> has_v((size_t)C, 0);
+    for (int c = 0; c < C; ++c) has_v[c] = (tables && (has ? has[c] != 0 : true)) ? 1 : 0;
+    std::vector<int> partner = allow_pairs ? fast_find_partners(tables, has_v.data(), C, N) : std::vector<int>((size_t)C, -1);
+    int n_pairs = 0;
+    for (int c = 0; c < C; ++c) if (partner[c] > c) ++n_pairs;
+    fb.nch = (n_pairs * 4 >= C) ? 2 : 1;            // pairing costs a second accumulator set for every slot
+    fb.n_pairs = fb.nch == 2 ? n_pairs : 0;
+    std::vector<int> slot_chan;
+    for (int c = 0; c < C; ++c) {
+        if (fb.nch == 2) {
+            if (partner[c] >= 0 && partner[c] < c) continue;          // rides in its partner's slot
+            slot_chan.push_back(c);
+            slot_chan.push_back(partner[c]);
+        } else {
+            slot_chan.push_back(c);
+        }
+    }
+    const int slots = (int)slot_chan.size() / fb.nch;
+    fb.groups = (slots + kFastCh - 1) / kFastCh;
+    slot_chan.resize((size_t)fb.groups * kFastCh * fb.nch, -1);
+    fb.tstride = fb.groups * kFastCh;
+    std::vector<float2> tslot((size_t)N * fb.tstride, make_float2(1.0f, 0.0f));
+    std::vector<int> chan_group((size_t)C, 0);
+    for (int s = 0; s < fb.groups * kFastCh; ++s) {
+        for (int q = 0; q < fb.nch; ++q) {
+            const int c = slot_chan[(size_t)s * fb.nch + q];
+            if (c >= 0) chan_group[c] = s / kFastCh;
+        }
+        const int c0 = slot_chan[(size_t)s * fb.nch];
+        if (c0 < 0 || !has_v[c0]) continue;
+        const float *r = tables + (size_t)c0 * N * 2;
+        for (int n = 0; n < N; ++n) tslot[(size_t)n * fb.tstride + s] = make_float2(r[2 * n], r[2 * n + 1]);
+    }
+    CU(cudaMalloc((void **)&fb.d_table_slot, sizeof(float2) * tslot.size()));
+    CU(cudaMemcpy(fb.d_table_slot, tslot.data(), sizeof(float2) * tslot.size(), cudaMemcpyHostToDevice));
+    CU(cudaMalloc((void **)&fb.d_slot_chan, sizeof(int) * slot_chan.size()));
+    CU(cudaMemcpy(fb.d_slot_chan, slot_chan.data(), sizeof(int) * slot_chan.size(), cudaMemcpyHostToDevice));
+    CU(cudaMalloc((void **)&fb.d_chan_group, sizeof(int) * chan_group.size()));
+    CU(cudaMemcpy(fb.d_chan_group, chan_group.data(), sizeof(int) * chan_group.size(), cudaMemcpyHostToDevice));
+
     const int smem = (int)fast_smem_bytes(N);
-    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_U8>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_S16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_F32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_U8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_S16, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_F32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_U8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_S16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_F32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     fb.enabled = true;
     return SDRX_OK;
 }

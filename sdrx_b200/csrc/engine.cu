@@ -347,7 +347,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     }
     if (want_fast) {
         int rc = fast_init(e->fast, C, e->N, e->taps.data() + e->tap_off[0], e->taps.data() + e->tap_off[1],
-                           e->taps.data() + e->tap_off[2]);
+                           e->taps.data() + e->tap_off[2], cfg->translator_len > 0 ? cfg->translators : nullptr,
+                           cfg->has_translator, !(cfg->flags & SDRX_FLAG_NO_PAIRING));
         if (rc) return rc;
         e->use_fast = true;
     }
@@ -559,7 +560,7 @@ int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned 
     float2 *dst; long stride; int off;
     if (e->S > 3) { dst = e->d_stage_in[3]; stride = e->stage_stride[3]; off = e->H[3] - 1; }
     else          { dst = o.ch_iq;          stride = e->chiq_stride;     off = 0; }
-    return fast_launch<FMT>(e->fast, e->s_main, raw, e->raw_hist, valid_lo, e->d_table_t, e->Cpad, e->N, (int)e->trans_pos, n,
+    return fast_launch<FMT>(e->fast, e->s_main, raw, e->raw_hist, valid_lo, e->N, (int)e->trans_pos, n,
                             dst, stride, off, &e->launches,
                             e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred);
 }
@@ -714,7 +715,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
             const int s = e->S - 1;
             tail = TailFirArgs{e->d_stage_in[s], e->stage_stride[s], n_out[s - 1], e->H[s], e->m[s], first[s],
                                e->d_taps + e->tap_off[s], sc->n_fixes > 0 ? e->fast.d_tails : nullptr, e->fast.tails_slots,
-                               sc->d_fixes, sc->d_fix_range};
+                               sc->d_fixes, sc->d_fix_range, e->fast.d_chan_group};
         } else if (!rc) {
             rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 3, e->S);
         }
@@ -854,6 +855,7 @@ extern "C" int sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_
 extern "C" void *sdrx_engine_stream(sdrx_engine *e) { return e ? (void *)e->s_main : nullptr; }
 extern "C" uint64_t sdrx_engine_launch_count(sdrx_engine *e) { return e ? e->launches : 0; }
 extern "C" int sdrx_engine_uses_fast_path(sdrx_engine *e) { return e && e->use_fast ? 1 : 0; }
+extern "C" int sdrx_engine_bank_pairs(sdrx_engine *e) { return e && e->use_fast ? e->fast.n_pairs : 0; }
 extern "C" int sdrx_engine_set_timing(sdrx_engine *e, int enable) {
     if (!e) return fail(SDRX_ERR_ARG, "null engine");
     e->timing = enable != 0;

@@ -13,7 +13,8 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import (FMT_F32, FMT_S16, FMT_U8, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, CHUNK, SdrxError,
+from ._lib import (FMT_F32, FMT_S16, FMT_U8, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, CHUNK,
+                   SdrxError,
                    check)
 from .config import ChannelPlan, make_translator, tables
 
@@ -76,7 +77,7 @@ class PinnedBuffer:
 class Engine:
     def __init__(self, plan: ChannelPlan, device: int = 0, use_lf_agc: bool = False, lf_gain_db: float = 0.0,
                  block_len: Optional[int] = None, force_generic: bool = False, demod: bool = True,
-                 translators: Optional[np.ndarray] = None, partial_mix: bool = False):
+                 translators: Optional[np.ndarray] = None, partial_mix: bool = False, no_pairing: bool = False):
         self.lib = _lib.load()
         self.plan = plan
         self.device = device
@@ -121,7 +122,7 @@ class Engine:
         cfg.fir2_taps, cfg.fir2_ntaps = fp(fir2), fir2.size
         cfg.passband_shape, cfg.ramp_up, cfg.ramp_down = fp(shape), fp(rup), fp(rdn)
         cfg.flags = ((FLAG_FORCE_GENERIC if force_generic else 0) | (0 if demod else FLAG_NO_DEMOD)
-                     | (FLAG_PARTIAL_MIX if partial_mix else 0))
+                     | (FLAG_PARTIAL_MIX if partial_mix else 0) | (FLAG_NO_PAIRING if no_pairing else 0))
         self.demod = demod
         h = C.c_void_p()
         check(self.lib.sdrx_engine_create(C.byref(cfg), C.byref(h)))
@@ -252,6 +253,11 @@ class Engine:
     @property
     def uses_fast_path(self) -> bool:
         return bool(self.lib.sdrx_engine_uses_fast_path(self.h))
+
+    @property
+    def bank_pairs(self) -> int:
+        """Conjugate (+-offset) channel pairs that share a lane slot of the specialised bank."""
+        return int(self.lib.sdrx_engine_bank_pairs(self.h))
 
     def set_timing(self, on: bool) -> None:
         check(self.lib.sdrx_engine_set_timing(self.h, 1 if on else 0))

@@ -64,6 +64,19 @@ def config2_variants() -> List[Scenario]:
     return [a, b]
 
 
+def paired_channels(fmt: int = FMT_F32) -> Scenario:
+    """+-offset channels whose translator tables are complex conjugates of each other share a lane slot of the
+    specialised bank (bank_fast.cuh, NCH = 2); mixed here with a centre channel and unpaired ones."""
+    offs = [-37, 37, -1, 1, 0, 250, -250, 5, -479, 479, 33]
+    tones = [400.0, 900.0, 1300.0, 700.0, 1000.0, 2100.0, 1700.0, 500.0, 2600.0, 1500.0, 800.0]
+    amps = [0.05, 0.02, 0.1, 0.03, 0.08, 0.04, 0.012, 0.06, 0.02, 0.09, 0.015]
+    sched = [_window(1, 5), _window(0, 99), _window(2, 4), _window(0, 3), _window(1, 99), _window(3, 6), _window(0, 99),
+             _window(2, 99), _window(0, 2), _window(1, 4), _window(4, 99)]
+    return Scenario(f"paired_10000_{['u8', 's16', 'f32'][fmt]}", 10000000, offs,
+                    [Carrier(o, a, t, 0.5, s) for o, a, t, s in zip(offs, amps, tones, sched)],
+                    fmt=fmt, n_blocks=6, noise_sigma=0.002)
+
+
 def centre_channel() -> Scenario:
     """A channel at the tuner centre takes the reference's no-translator path (msd.hpp:79-101)."""
     return Scenario("centre_10000", 10000000, [0, 5], [Carrier(0, 0.1, 800.0), Carrier(5, 0.05, 1200.0)],

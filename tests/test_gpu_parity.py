@@ -114,6 +114,26 @@ def test_engine_reproduces_reference_golden_vectors(name, scn):
         assert rel_rms(got2[b].mix, z["mix"][j]) < AUDIO_TOL or not np.any(z["mix"][j])
 
 
+@pytest.mark.parametrize("fmt", [sc.FMT_F32, sc.FMT_S16, sc.FMT_U8], ids=["f32", "s16", "u8"])
+def test_conjugate_paired_bank_meets_the_parity_bar(fmt):
+    """+-offset channels share a lane slot (NCH = 2 kernel); the same scenario with pairing disabled must agree."""
+    from sdrx_b200 import Engine
+    scn = sc.paired_channels(fmt)
+    blocks = _blocks(scn)
+    want = run_cpu(scn, "oracle", blocks)
+    eng = Engine(scn.plan())
+    assert eng.uses_fast_path and eng.bank_pairs == 4
+    eng.close()
+    got, _ = run_engine(scn, blocks=blocks)
+    lvl = np.full(len(scn.offsets), 9.0)
+    _assert_close(got, want, lvl)
+    single, _ = run_engine(scn, blocks=blocks, no_pairing=True)
+    _assert_close(single, want, lvl)
+    # the first channel of a pair runs the identical instruction sequence in both kernels
+    for a, b in zip(got, single):
+        assert np.array_equal(a.ch_iq[0], b.ch_iq[0]) and np.array_equal(a.sql, b.sql)
+
+
 def test_full_band_960_channels_against_oracle():
     """SURVEY.md §8d config 3 at full width (960 channels), three blocks."""
     scn = sc.config3(n_blocks=3)
@@ -122,6 +142,10 @@ def test_full_band_960_channels_against_oracle():
     got, fast = run_engine(scn, blocks=blocks)
     _assert_close(got, want, np.full(len(scn.offsets), 9.0))
     assert any(o.sql.any() for o in want), "scenario opens no squelch"
+    from sdrx_b200 import Engine
+    eng = Engine(scn.plan())
+    assert eng.bank_pairs == 479          # offsets -479..479 pair up; -480 and 0 ride alone
+    eng.close()
 
 
 def test_state_save_load_and_reset_round_trip():
