@@ -154,6 +154,10 @@ int      sdrx_engine_bank_pairs(sdrx_engine *e);      /* conjugate channel pairs
 int      sdrx_engine_last_timing(sdrx_engine *e, float *bank_ms, float *block_ms);
 int      sdrx_engine_set_timing(sdrx_engine *e, int enable);
 
+/* Host-only self-check of the channel-bank work schedule (no GPU needed): plans `groups` slot groups x U units of
+ * 125 samples over n_sms SMs; returns the number of tiling violations (0 = every output produced exactly once).  */
+int      sdrx_debug_bank_plan_check(int groups, int U, int n_sms, int *n_ctas, int *n_pieces, int *max_steps);
+
 /* Pinned host memory for zero-staging push_block / get_*.  */
 void *sdrx_host_alloc(size_t bytes);
 void  sdrx_host_free(void *p);

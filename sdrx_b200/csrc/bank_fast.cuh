@@ -48,7 +48,8 @@ constexpr int kXBody = 26;         // float2 per staged 25-sample body (+1: ever
 constexpr int kXSeg = 5 * kXBody;  // float2 per staged segment chunk; 1040 B puts the two segments of a warp
                                    // 4 banks apart, so their 16 B broadcast reads never collide
 constexpr int kWrap = 24;          // table rows replicated past N so a 25-sample body never wraps
-constexpr int kFastMinSeg = 8;     // units; segments shorter than 4 would overlap their fix-ups
+constexpr int kFastMinSeg = 8;     // units per segment when sizing the grid: shorter ones mostly warm up
+constexpr int kFastMinSegPiece = 2;// ... but a small piece (a CTA range that straddles a group) still spreads over all warps
 constexpr int kFastWarmStart = 4;  // warm-up units of a segment at the start of the block
 constexpr int kFastRawHist = 768;  // raw history samples the engine keeps for this path
 
@@ -70,12 +71,19 @@ struct FastCta { int piece_begin, piece_end; };
 typedef TailFix FastFix;                        // stage-3 output u of `group` += tails[src[0..n)]
 constexpr int kFastSlotsPerPiece = 2 * (kFastSegs / 2);
 
+// The segment that starts a block warms up on kFastWarmStart units of raw history instead of one; it is made
+// that much shorter so that every segment of the piece runs the same number of steps.
+__host__ __device__ inline int fast_cut(const FastPiece &p) {
+    return (p.u_begin == 0 && p.seg_len > 2 * (kFastWarmStart - 1)) ? kFastWarmStart - 1 : 0;
+}
 // the segment of (warp w, half) in a piece; shared by the kernel and the host-side schedule builder
 __host__ __device__ inline bool fast_segment(const FastPiece &p, int w, int half, int *u0, int *u1) {
     const int lo = half ? p.u_begin + p.H : p.u_begin;
     const int hi = half ? p.u_end : p.u_begin + p.H;
-    *u0 = lo + w * p.seg_len;
-    *u1 = *u0 + p.seg_len < hi ? *u0 + p.seg_len : hi;
+    const int cut = half ? 0 : fast_cut(p);
+    *u0 = lo + w * p.seg_len - (w > 0 ? cut : 0);
+    const int e = *u0 + p.seg_len - (w == 0 ? cut : 0);
+    *u1 = e < hi ? e : hi;
     return *u0 < hi;
 }
 
@@ -159,11 +167,13 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
         if (pc.group != cur_group) {
             __syncthreads();                               // every warp is done with the previous group's table
             cur_group = pc.group;
-            const float2 *src = table + pc.group * kFastCh;
-            for (int idx = tid; idx < (N + kWrap) * kFastCh; idx += kFastThreads) {
-                const int row = idx >> 4, c16 = idx & 15;
-                tb[idx] = __ldg(src + (long)(row < N ? row : row - N) * tstride + c16);
+            const float2 *src = table + pc.group * kFastCh;           // 16 B aligned: tstride and the group base are multiples of 16
+            for (int idx = tid; idx < (N + kWrap) * (kFastCh / 2); idx += kFastThreads) {   // all copies in flight at once
+                const int row = idx >> 3, c8 = idx & 7;
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(tb + row * kFastCh + 2 * c8);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src + (long)(row < N ? row : row - N) * tstride + 2 * c8) : "memory");
             }
+            asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
             __syncthreads();
         }
         // my segment
@@ -171,7 +181,7 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
         const bool have = fast_segment(pc, w, half, &u0, &u1);
         const int warm = (u0 == 0) ? kFastWarmStart : 1;
         const int my_steps = have ? warm + (u1 - u0) : 0;
-        const int nsteps = ((pc.u_begin == 0) ? kFastWarmStart : 1) + pc.seg_len;   // the longest segment's
+        const int nsteps = ((pc.u_begin == 0 && !fast_cut(pc)) ? kFastWarmStart : 1) + pc.seg_len;   // the longest segment's
 
         // Staging: the 16 threads of a segment fetch that segment's next 125 samples (8 coalesced rows of
         // 128 B) while the current chunk is computed.  F32 goes global->shared with cp.async; u8/s16 are
@@ -399,50 +409,96 @@ inline std::vector<int> fast_find_partners(const float *tables, const uint8_t *h
 // Linearise (group, unit) work, cut it into one contiguous range per CTA, snap cuts that fall close to
 // a group boundary onto it, split ranges at group boundaries into pieces, lay the two halves of every
 // piece out, and list the stage-3 outputs that need tails added.
-inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
+struct FastPlan {                      // the host-side result, before upload
     std::vector<FastCta> ctas;
     std::vector<FastPiece> pieces;
-    const int half_segs = kFastSegs / 2;
-    const long total = (long)fb.groups * U;
-    const long min_range = (long)kFastSegs * kFastMinSeg;                // every segment >= 8 units when possible
-    long n_ctas = std::min<long>(fb.n_sms, std::max<long>(1, total / min_range));
-    const int snap = std::min(4 * kFastMinSeg, std::max(1, U / 2));
-    std::vector<long> cuts;
-    cuts.push_back(0);
-    for (long i = 1; i < n_ctas; ++i) {
-        long c = (total * i) / n_ctas;
-        const long g = c / U, u = c % U;
-        if (u < snap) c = g * U;
-        else if (U - u < snap) c = (g + 1) * U;
-        if (c > cuts.back() && c < total) cuts.push_back(c);
-    }
-    cuts.push_back(total);
-    int slot = 0, slot_group = -1, max_slots = 0;     // slots are numbered per group (pieces of a group are consecutive)
-    for (size_t i = 0; i + 1 < cuts.size(); ++i) {
-        FastCta cta{(int)pieces.size(), 0};
-        long wk = cuts[i];
-        while (wk < cuts[i + 1]) {
-            const int g = (int)(wk / U), ub = (int)(wk % U);
-            const int ue = (int)std::min<long>(U, ub + (cuts[i + 1] - wk));
-            const int L = ue - ub;
-            if (g != slot_group) { slot_group = g; slot = 0; }
-            FastPiece p{g, ub, ue, L, 0, slot};
-            if (L >= 2 * kFastMinSeg) p.H = (L + 1) / 2;
-            const int ns = std::max(1, std::min(half_segs, p.H / kFastMinSeg));
-            p.seg_len = (p.H + ns - 1) / ns;
-            slot += kFastSlotsPerPiece;
-            max_slots = std::max(max_slots, slot);
-            pieces.push_back(p);
-            wk += L;
-        }
-        cta.piece_end = (int)pieces.size();
-        ctas.push_back(cta);
-    }
-    // fix list: every segment end inside the block hands its four partial sums to the outputs after it
     std::vector<FastFix> fixes;
-    std::vector<int2> fix_range((size_t)fb.groups, make_int2(0, 0));
+    std::vector<int2> fix_range;
+    int max_slots = 0;
+};
+
+// One piece [ub, ub+L) of a group: halves, segment length (see fast_segment / fast_cut).
+inline FastPiece fast_make_piece(int g, int ub, int L, int slot) {
+    const int half_segs = kFastSegs / 2;
+    FastPiece p{g, ub, ub + L, L, 0, slot};
+    const int cut = ub == 0 ? kFastWarmStart - 1 : 0;            // see fast_cut
+    if (L >= 2 * kFastMinSegPiece) p.H = (L - cut + 1) / 2;
+    if (p.H < 1) p.H = L;
+    int ns = std::max(1, std::min(half_segs, p.H / kFastMinSegPiece));
+    if (cut) ns = std::max(1, std::min(ns, (p.H + cut) / (2 * cut + 1)));   // keep the segments long enough to shift the first one
+    p.seg_len = std::max((p.H + cut + ns - 1) / ns, (L - p.H + ns - 1) / ns);
+    if (p.seg_len <= 2 * cut) p.seg_len = std::max((p.H + ns - 1) / ns, (L - p.H + ns - 1) / ns);   // too short to shift
+    return p;
+}
+// steps (125-sample units per thread, warm-up included) a CTA spends on a piece: every warp runs the longest segment's
+inline int fast_piece_steps(const FastPiece &p) {
+    return ((p.u_begin == 0 && !fast_cut(p)) ? kFastWarmStart : 1) + p.seg_len;
+}
+
+// Linearise (group, unit) work and hand every CTA a contiguous range that costs at most T steps, for the smallest
+// T that needs no more CTAs than there are SMs: a range that crosses a group boundary is two pieces (the table
+// in shared memory belongs to one group), each paying its own warm-up step, so ranges are sized by cost, not
+// by length -- all SMs finish together.  Then lay the two halves of every piece out and list the stage-3
+// outputs that need tails added.
+inline int fast_plan_schedule(int groups, int U, int n_sms, FastPlan &plan) {
+    const int half_segs = kFastSegs / 2;
+    const long total = (long)groups * U;
+    auto max_len = [&](int ub, int rem, int budget) {            // largest L <= rem whose piece fits the budget (0: none)
+        int lo = 0, hi = rem;
+        while (lo < hi) {
+            const int mid = (lo + hi + 1) / 2;
+            if (fast_piece_steps(fast_make_piece(0, ub, mid, 0)) <= budget) lo = mid; else hi = mid - 1;
+        }
+        return lo;
+    };
+    auto simulate = [&](int T, std::vector<FastCta> *ctas, std::vector<FastPiece> *pieces, int *max_slots) -> long {
+        long wk = 0, n = 0;
+        int slot = 0, slot_group = -1;                           // slots are numbered per group (pieces of a group are consecutive)
+        while (wk < total) {
+            int budget = T;
+            FastCta cta{pieces ? (int)pieces->size() : 0, 0};
+            bool took = false;
+            while (wk < total && budget >= (took ? 3 : 2)) {
+                const int g = (int)(wk / U), ub = (int)(wk % U);
+                int L = max_len(ub, U - ub, budget);
+                if (L == 0) break;
+                if (U - ub - L > 0 && U - ub - L < 2 * kFastMinSegPiece) {       // do not leave a sliver of the group behind
+                    const int all = U - ub;
+                    if (fast_piece_steps(fast_make_piece(0, ub, all, 0)) <= budget + 1) L = all;
+                }
+                if (g != slot_group) { slot_group = g; slot = 0; }
+                const FastPiece p = fast_make_piece(g, ub, L, slot);
+                budget -= fast_piece_steps(p);
+                slot += kFastSlotsPerPiece;
+                if (pieces) { pieces->push_back(p); *max_slots = std::max(*max_slots, slot); }
+                wk += L;
+                took = true;
+            }
+            if (!took) return -1;                                // T too small to make progress
+            if (ctas) { cta.piece_end = (int)pieces->size(); ctas->push_back(cta); }
+            ++n;
+        }
+        return n;
+    };
+    int lo = 2, hi = kFastWarmStart + 2 + U;                     // a whole group fits one CTA at hi
+    while (simulate(hi, nullptr, nullptr, nullptr) < 0 || simulate(hi, nullptr, nullptr, nullptr) > n_sms) hi *= 2;
+    while (lo < hi) {
+        const int mid = (lo + hi) / 2;
+        const long n = simulate(mid, nullptr, nullptr, nullptr);
+        if (n > 0 && n <= n_sms) hi = mid; else lo = mid + 1;
+    }
+    // small jobs: do not shred the block into segments that mostly warm up when there are SMs to spare anyway
+    const int T = std::max(lo, std::min(1 + kFastMinSeg, (int)std::max<long>(2, 1 + (total + kFastSegs - 1) / kFastSegs)));
+    std::vector<FastCta> &ctas = plan.ctas;
+    std::vector<FastPiece> &pieces = plan.pieces;
+    int max_slots = 0;
+    if (simulate(T, &ctas, &pieces, &max_slots) < 0) return fail(SDRX_ERR_STATE, "internal: channel-bank schedule");
+    // fix list: every segment end inside the block hands its four partial sums to the outputs after it
+    std::vector<FastFix> &fixes = plan.fixes;
+    std::vector<int2> &fix_range = plan.fix_range;
+    fix_range.assign((size_t)groups, make_int2(0, 0));
     {
-        std::vector<std::vector<int>> src((size_t)fb.groups * U);
+        std::vector<std::vector<int>> src((size_t)groups * U);
         for (const FastPiece &p : pieces)
             for (int half = 0; half < 2; ++half)
                 for (int w = 0; w < half_segs; ++w) {
@@ -451,7 +507,7 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
                     for (int q = 0; q < 4 && u1 + q < U; ++q)
                         src[(size_t)p.group * U + u1 + q].push_back((p.slot_base + half * half_segs + w) * 4 + q);
                 }
-        for (int g = 0; g < fb.groups; ++g) {
+        for (int g = 0; g < groups; ++g) {
             fix_range[g].x = (int)fixes.size();
             for (int u = 0; u < U; ++u) {
                 const std::vector<int> &v = src[(size_t)g * U + u];
@@ -464,6 +520,41 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
             fix_range[g].y = (int)fixes.size();
         }
     }
+    plan.max_slots = max_slots;
+    return SDRX_OK;
+}
+
+// Self-check of a plan (also exported for the CPU tests): every (group, unit) is produced by exactly one segment
+// and no output receives more than four tails (a stage-2 output of unit v feeds stage-3 outputs v..v+4, so the
+// segment that owns v reaches at most the four outputs after its end, whatever its length).  Returns the number
+// of violations.
+inline int fast_check_plan(int groups, int U, const FastPlan &plan) {
+    int bad = 0;
+    std::vector<int> cover((size_t)groups * U, 0);
+    for (const FastPiece &p : plan.pieces)
+        for (int half = 0; half < 2; ++half)
+            for (int w = 0; w < kFastSegs / 2; ++w) {
+                int u0, u1;
+                if (!fast_segment(p, w, half, &u0, &u1)) continue;
+                if (u1 <= u0 || u0 < p.u_begin || u1 > p.u_end) { ++bad; continue; }
+                for (int u = u0; u < u1; ++u) ++cover[(size_t)p.group * U + u];
+            }
+    for (int v : cover) if (v != 1) ++bad;
+    for (const FastFix &f : plan.fixes) if (f.n < 1 || f.n > 4) ++bad;
+    for (const FastCta &c : plan.ctas) if (c.piece_end <= c.piece_begin) ++bad;
+    return bad;
+}
+
+inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
+    FastPlan plan;
+    int rc = fast_plan_schedule(fb.groups, U, fb.n_sms, plan);
+    if (rc) return rc;
+    if (fast_check_plan(fb.groups, U, plan) != 0) return fail(SDRX_ERR_STATE, "internal: channel-bank schedule does not tile the block");
+    const std::vector<FastCta> &ctas = plan.ctas;
+    const std::vector<FastPiece> &pieces = plan.pieces;
+    const std::vector<FastFix> &fixes = plan.fixes;
+    const std::vector<int2> &fix_range = plan.fix_range;
+    const int max_slots = plan.max_slots;
     out.U = U;
     out.n_ctas = (int)ctas.size();
     out.n_slots = max_slots;           // tails are indexed [channel][slot][4]

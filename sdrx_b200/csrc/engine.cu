@@ -854,6 +854,26 @@ extern "C" int sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_
 
 extern "C" void *sdrx_engine_stream(sdrx_engine *e) { return e ? (void *)e->s_main : nullptr; }
 extern "C" uint64_t sdrx_engine_launch_count(sdrx_engine *e) { return e ? e->launches : 0; }
+// host-only: plans the channel-bank schedule for `groups` slot groups x U units on n_sms SMs and self-checks it
+extern "C" int sdrx_debug_bank_plan_check(int groups, int U, int n_sms, int *n_ctas, int *n_pieces, int *max_steps) {
+    FastPlan plan;
+    if (groups < 1 || U < 1 || n_sms < 1) return -1;
+    if (fast_plan_schedule(groups, U, n_sms, plan) != SDRX_OK) return -1;
+    if (n_ctas) *n_ctas = (int)plan.ctas.size();
+    if (n_pieces) *n_pieces = (int)plan.pieces.size();
+    if (max_steps) {                 // steps (125-sample units incl. warm-up) of the busiest CTA: the kernel's critical path
+        int worst = 0;
+        for (const FastCta &c : plan.ctas) {
+            int steps = 0;
+            for (int i = c.piece_begin; i < c.piece_end; ++i)
+                steps += ((plan.pieces[i].u_begin == 0 && !fast_cut(plan.pieces[i])) ? kFastWarmStart : 1) + plan.pieces[i].seg_len;
+            worst = std::max(worst, steps);
+        }
+        *max_steps = worst;
+    }
+    return fast_check_plan(groups, U, plan);
+}
+
 extern "C" int sdrx_engine_uses_fast_path(sdrx_engine *e) { return e && e->use_fast ? 1 : 0; }
 extern "C" int sdrx_engine_bank_pairs(sdrx_engine *e) { return e && e->use_fast ? e->fast.n_pairs : 0; }
 extern "C" int sdrx_engine_set_timing(sdrx_engine *e, int enable) {
