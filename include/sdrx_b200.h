@@ -124,6 +124,11 @@ int  sdrx_engine_last_out_len(sdrx_engine *e, unsigned *out_len);
 int  sdrx_engine_get_channel_iq(sdrx_engine *e, float *ch_iq);
 /* Boundary B results. Waits for the block. */
 int  sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
+/* Streaming form: queue the read-back of the last pushed block and return; push the next block at once (its H2D
+ * and kernels overlap this read-back); the host buffers (pinned) are valid after sdrx_engine_wait_outputs(e, back),
+ * back = number of blocks pushed since the fetch (0 or 1).                                                  */
+int  sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
+int  sdrx_engine_wait_outputs(sdrx_engine *e, int back);
 /* Boundary B on caller-supplied channel IQ (host, [C][512][2]) instead of the channelizer's. */
 int  sdrx_engine_demod_block(sdrx_engine *e, const float *ch_iq, float pwr_dbfs);
 int  sdrx_engine_sync(sdrx_engine *e);

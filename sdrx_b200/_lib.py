@@ -60,6 +60,8 @@ PROTOTYPES = [
     ("sdrx_engine_last_out_len", C.c_int, [C.c_void_p, C.POINTER(C.c_uint)]),
     ("sdrx_engine_get_channel_iq", C.c_int, [C.c_void_p, c_float_p]),
     ("sdrx_engine_get_outputs", C.c_int, [C.c_void_p, C.POINTER(BlockOutputs)]),
+    ("sdrx_engine_fetch_outputs", C.c_int, [C.c_void_p, C.POINTER(BlockOutputs)]),
+    ("sdrx_engine_wait_outputs", C.c_int, [C.c_void_p, C.c_int]),
     ("sdrx_engine_demod_block", C.c_int, [C.c_void_p, c_float_p, C.c_float]),
     ("sdrx_engine_sync", C.c_int, [C.c_void_p]),
     ("sdrx_engine_join", C.c_int, [C.c_void_p]),

@@ -57,6 +57,9 @@ struct sdrx_engine {
     cudaEvent_t ev_head_done = nullptr;   // k_chan_head of the current block has been queued behind this point (main -> side)
     cudaEvent_t ev_side_done[kNBuf] = {nullptr, nullptr};   // side-stream work that reads / writes output set b is complete
     bool side_pending[kNBuf] = {false, false};
+    cudaStream_t s_out = nullptr;         // asynchronous result fetch (sdrx_engine_fetch_outputs): D2H overlaps the next block
+    cudaEvent_t ev_fetch_done[kNBuf] = {nullptr, nullptr};
+    bool fetch_pending[kNBuf] = {false, false};
     uint8_t *d_gate[kNBuf] = {nullptr, nullptr};             // [C] squelch state entering the block (k_chan_head -> k_chan_recur)
     cudaEvent_t ev_copied[kNBuf] = {nullptr, nullptr};
     cudaEvent_t ev_raw_free[kNBuf] = {nullptr, nullptr};   // last reader of d_raw[b] has been queued
@@ -186,7 +189,9 @@ void agc_defaults(AgcParams &p, float attack, float decay, float reference, floa
 int reset_state(sdrx_engine *e) {
     const size_t C = (size_t)e->C;
     CU(cudaStreamSynchronize(e->s_side));
+    CU(cudaStreamSynchronize(e->s_out));
     e->side_pending[0] = e->side_pending[1] = false;
+    e->fetch_pending[0] = e->fetch_pending[1] = false;
     for (int b = 0; b < kNBuf; ++b) CU(cudaMemsetAsync(e->d_raw[b], 0, e->raw_buf_bytes, e->s_main));
     for (int s = 1; s < e->S; ++s)
         CU(cudaMemsetAsync(e->d_stage_in[s], 0, sizeof(float2) * (size_t)e->stage_stride[s] * C, e->s_main));
@@ -232,6 +237,7 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
         if (e->ev_copied[b]) cudaEventDestroy(e->ev_copied[b]);
         if (e->ev_raw_free[b]) cudaEventDestroy(e->ev_raw_free[b]);
         if (e->ev_side_done[b]) cudaEventDestroy(e->ev_side_done[b]);
+        if (e->ev_fetch_done[b]) cudaEventDestroy(e->ev_fetch_done[b]);
         cudaFree(e->d_gate[b]); cudaFree(e->d_pwr_partial[b]);
     }
     if (e->ev_head_done) cudaEventDestroy(e->ev_head_done);
@@ -251,6 +257,7 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     if (e->s_main) cudaStreamDestroy(e->s_main);
     if (e->s_copy) cudaStreamDestroy(e->s_copy);
     if (e->s_side) cudaStreamDestroy(e->s_side);
+    if (e->s_out) cudaStreamDestroy(e->s_out);
     delete e;
 }
 
@@ -281,9 +288,11 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     CU(cudaStreamCreateWithFlags(&e->s_main, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_side, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->ev_head_done, cudaEventDisableTiming));
     for (int b = 0; b < kNBuf; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_side_done[b], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&e->ev_fetch_done[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_copied[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_raw_free[b], cudaEventDisableTiming));
     }
@@ -623,13 +632,14 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
 // the main stream may not touch output set `idx` (or its power partials / gate) before the side stream is done with it
 int wait_side(sdrx_engine *e, int idx) {
     if (e->side_pending[idx]) CU(cudaStreamWaitEvent(e->s_main, e->ev_side_done[idx], 0));
+    if (e->fetch_pending[idx]) CU(cudaStreamWaitEvent(e->s_main, e->ev_fetch_done[idx], 0));
     return SDRX_OK;
 }
 
-int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out) {
+int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out, cudaStream_t st) {
     const size_t C = (size_t)e->C;
     auto d2h = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
-        return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, e->s_main) : cudaSuccess;
+        return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
     };
     CU(d2h(out->audio, o.audio, C * kChunk * sizeof(float)));
     CU(d2h(out->sql_state, o.sql, C));
@@ -768,6 +778,7 @@ extern "C" int sdrx_engine_sync(sdrx_engine *e) {
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
+    CU(cudaStreamSynchronize(e->s_out));
     return SDRX_OK;
 }
 
@@ -799,9 +810,38 @@ extern "C" int sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs 
     if (!e->last_demod) return fail(SDRX_ERR_STATE, "the last block did not yield 512 samples per channel; boundary B did not run");
     DevGuard g(e->dev);
     int rc = wait_side(e, (int)((e->blocks - 1) & 1));
-    if (!rc) rc = copy_outputs(e, e->out[(e->blocks - 1) & 1], out);
+    if (!rc) rc = copy_outputs(e, e->out[(e->blocks - 1) & 1], out, e->s_main);
     if (rc) return rc;
     CU(cudaStreamSynchronize(e->s_main));
+    return SDRX_OK;
+}
+
+// Asynchronous form of get_outputs for streaming callers: the D2H copies of the LAST pushed block are queued on
+// their own stream behind that block's kernels and the call returns; the next push_block may follow at once, so
+// its H2D and kernels overlap this block's read-back.  The (pinned) host buffers are valid after
+// sdrx_engine_wait_outputs(e, back) with back = how many blocks have been pushed since.
+extern "C" int sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_outputs *out) {
+    if (!e || !out) return fail(SDRX_ERR_ARG, "null argument");
+    if (e->blocks == 0) return fail(SDRX_ERR_STATE, "no block pushed yet");
+    if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
+    if (!e->last_demod) return fail(SDRX_ERR_STATE, "the last block did not yield 512 samples per channel; boundary B did not run");
+    DevGuard g(e->dev);
+    const int idx = (int)((e->blocks - 1) & 1);
+    if (e->side_pending[idx]) CU(cudaStreamWaitEvent(e->s_out, e->ev_side_done[idx], 0));
+    int rc = copy_outputs(e, e->out[idx], out, e->s_out);
+    if (rc) return rc;
+    CU(cudaEventRecord(e->ev_fetch_done[idx], e->s_out));
+    e->fetch_pending[idx] = true;
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_engine_wait_outputs(sdrx_engine *e, int back) {
+    if (!e || back < 0 || back > 1) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) or 1 (the one before)");
+    if (e->blocks < (uint64_t)back + 1) return fail(SDRX_ERR_STATE, "no such block");
+    DevGuard g(e->dev);
+    const int idx = (int)((e->blocks - 1 - back) & 1);
+    if (!e->fetch_pending[idx]) return fail(SDRX_ERR_STATE, "no fetch was queued for that block");
+    CU(cudaEventSynchronize(e->ev_fetch_done[idx]));
     return SDRX_OK;
 }
 

@@ -197,6 +197,14 @@ class Engine:
     def outputs_into(self, struct) -> None:
         check(self.lib.sdrx_engine_get_outputs(self.h, C.byref(struct)))
 
+    def fetch_outputs(self, struct) -> None:
+        """Queue the read-back of the last pushed block into (pinned) buffers and return at once."""
+        check(self.lib.sdrx_engine_fetch_outputs(self.h, C.byref(struct)))
+
+    def wait_outputs(self, back: int = 0) -> None:
+        """Block until the fetch queued ``back`` pushes ago has landed in host memory."""
+        check(self.lib.sdrx_engine_wait_outputs(self.h, back))
+
     def process(self, raw: np.ndarray, fmt: Optional[int] = None) -> BlockOut:
         self.push(raw, fmt)
         return self.outputs()

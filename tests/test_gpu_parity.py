@@ -258,6 +258,36 @@ def test_pinned_and_device_resident_ingest_agree():
     pin.free()
 
 
+def test_streaming_fetch_equals_blocking_get_outputs():
+    """push / fetch_outputs / wait_outputs (read-back overlapping the next block) returns what get_outputs returns."""
+    from sdrx_b200 import Engine
+    scn = sc.config2(n_blocks=7)
+    blocks = _blocks(scn)
+    ref, _ = run_engine(scn, blocks=blocks)
+    eng = Engine(scn.plan())
+    sets = [eng.make_output_buffers(pinned=True, want=("audio", "sql_state", "snr", "mix", "pcm", "pwr_dbfs", "agc_gain")) for _ in range(2)]
+    got = []
+
+    def keep(k):
+        a = sets[k & 1][1]
+        got.append({n: a[n].copy() for n in ("audio", "sql_state", "snr", "mix", "pcm", "agc_gain")})
+    for i, blk in enumerate(blocks):
+        eng.push(blk)
+        eng.fetch_outputs(sets[i & 1][0])
+        if i > 0:
+            eng.wait_outputs(1)
+            keep(i - 1)
+    eng.wait_outputs(0)
+    keep(len(blocks) - 1)
+    for g, r in zip(got, ref):
+        assert np.array_equal(g["audio"].reshape(r.audio.shape), r.audio) and np.array_equal(g["sql_state"], r.sql)
+        assert np.array_equal(g["snr"], r.snr, equal_nan=True) and np.array_equal(g["mix"], r.mix)
+        assert np.array_equal(g["pcm"], r.pcm) and np.array_equal(g["agc_gain"], r.agc_gain)
+    with pytest.raises(Exception):
+        eng.wait_outputs(2)
+    eng.close()
+
+
 def test_demod_block_alone_matches_oracle_boundary_b():
     """Boundary B on caller-supplied channel IQ (sdrx.cpp:454-656), bit-exact."""
     from sdrx_b200 import Engine
