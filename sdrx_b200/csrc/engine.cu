@@ -438,6 +438,19 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
                                         (int)(sizeof(float2) * row)));
         }
     }
+    // Every kernel of the block asks for the same (maximum) shared-memory carve-out: an SM only co-schedules CTAs of
+    // different kernels when they agree on the L1/shared split, and the side-stream kernels are meant to run next to
+    // the channel bank, which needs all of it.
+    {
+        const int mx = (int)cudaSharedmemCarveoutMaxShared;
+        CU(cudaFuncSetAttribute(k_chan_recur, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_mix_fir2_pcm, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_chan_head<true>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_chan_head<false>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_U8>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_S16>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_F32>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+    }
     return reset_state(e);
 }
 
@@ -583,14 +596,14 @@ int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_
 }
 
 // power partials of the new block (when boundary B will run) + the raw delay line, one launch
-int launch_prep(sdrx_engine *e, int fmt, uint8_t *buf, const uint8_t *prev, unsigned n, bool power, int hist_bytes, long prev_bytes, float *partial) {
+int launch_prep(sdrx_engine *e, cudaStream_t st, int fmt, uint8_t *buf, const uint8_t *prev, unsigned n, bool power, int hist_bytes, long prev_bytes, float *partial) {
     const int np = power ? kPwrPartials : 0;
     const int grid = np + div_up(hist_bytes, 256);
     if (grid == 0) return SDRX_OK;
     switch (fmt) {
-        case SDRX_FMT_U8:  k_prep<SDRX_FMT_U8><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
-        case SDRX_FMT_S16: k_prep<SDRX_FMT_S16><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
-        default:           k_prep<SDRX_FMT_F32><<<grid, 256, 0, e->s_main>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
+        case SDRX_FMT_U8:  k_prep<SDRX_FMT_U8><<<grid, 256, 0, st>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
+        case SDRX_FMT_S16: k_prep<SDRX_FMT_S16><<<grid, 256, 0, st>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
+        default:           k_prep<SDRX_FMT_F32><<<grid, 256, 0, st>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
     }
     ++e->launches;
     CU(cudaGetLastError());
@@ -614,8 +627,8 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
     CU(cudaGetLastError());
     CU(cudaEventRecord(e->ev_head_done, e->s_main));
     CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
-    k_chan_recur<<<e->C, 32, 0, e->s_side>>>(o.ch_iq, e->chiq_stride, e->st, e->d_gate[idx], e->tb, e->agc, e->lf, e->lf_active,
-                                             o.audio, snap);
+    k_chan_recur<<<div_up(e->C, kRecurCh), 32, 0, e->s_side>>>(o.ch_iq, e->chiq_stride, e->st, e->d_gate[idx], e->tb, e->agc, e->lf, e->lf_active,
+                                             o.audio, snap, e->C);
     const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad;
     k_mix_fir2_pcm<<<1, 1024, smem, e->s_side>>>(o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps,
                                                  e->d_fir_hist, o.mix_pre, o.mix, o.pcm, e->d_pwr_partial[idx],
@@ -664,10 +677,24 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     uint8_t *buf = e->d_raw[cur];
     const size_t hist_bytes = (size_t)e->raw_hist * bps;
 
+
+    // ---- stage bookkeeping (MSD::S::isn_, msd.hpp:240-244): which inputs complete an output
+    int first[SDRX_MAX_STAGES], n_out[SDRX_MAX_STAGES], phase_in[SDRX_MAX_STAGES] = {0};
+    long n_in = n;
+    for (int s = 0; s < e->S; ++s) phase_in[s] = e->phase[s];
+    for (int s = 0; s < e->S; ++s) {
+        first[s] = e->m[s] - 1 - e->phase[s];
+        n_out[s] = (int)((e->phase[s] + n_in) / e->m[s]);
+        e->phase[s] = (int)((e->phase[s] + n_in) % e->m[s]);
+        n_in = n_out[s];
+    }
+    const unsigned out_len = (unsigned)n_in;
+    OutSet &o = e->out[cur];
+    const bool demod = !(e->flags & SDRX_FLAG_NO_DEMOD) && out_len == (unsigned)kChunk;
     // ---- ingest: pinned, double buffered, on the copy stream
+    // buffer `cur` was last read by block b-1's raw carry (and before that by block b-2's kernels)
+    CU(cudaStreamWaitEvent(e->s_copy, e->ev_raw_free[cur], 0));
     if (n > 0) {
-        // buffer `cur` was last read by block b-1's raw carry (and before that by block b-2's kernels)
-        CU(cudaStreamWaitEvent(e->s_copy, e->ev_raw_free[cur], 0));
         if (kind == SRC_DEVICE) {
             CU(cudaMemcpyAsync(buf + hist_bytes, src, (size_t)n * bps, cudaMemcpyDeviceToDevice, e->s_copy));
         } else {
@@ -685,33 +712,21 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
             }
             CU(cudaMemcpyAsync(buf + hist_bytes, from, (size_t)n * bps, cudaMemcpyHostToDevice, e->s_copy));
         }
+    }
+    // ---- still on the copy stream, off the compute stream's critical path: the raw delay line (last raw_hist
+    //      samples of the previous [hist | block] move in front of this block) and, when boundary B will run,
+    //      the block power partials.  The partials of parity `cur` were last read by block b-2's mix kernel.
+    {
+        if (e->side_pending[cur]) CU(cudaStreamWaitEvent(e->s_copy, e->ev_side_done[cur], 0));
+        int rc = launch_prep(e, e->s_copy, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps,
+                             e->d_pwr_partial[cur]);
+        if (rc) return rc;
         CU(cudaEventRecord(e->ev_copied[cur], e->s_copy));
         CU(cudaStreamWaitEvent(e->s_main, e->ev_copied[cur], 0));
+        CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));   // every kernel that read buffer `prv` is queued before this point
     }
     { int rc = wait_side(e, cur); if (rc) return rc; }      // block b-2's recurrences / mix read this output set
     if (e->timing) CU(cudaEventRecord(e->ev_t0, e->s_main));
-
-
-    // ---- stage bookkeeping (MSD::S::isn_, msd.hpp:240-244): which inputs complete an output
-    int first[SDRX_MAX_STAGES], n_out[SDRX_MAX_STAGES], phase_in[SDRX_MAX_STAGES] = {0};
-    long n_in = n;
-    for (int s = 0; s < e->S; ++s) phase_in[s] = e->phase[s];
-    for (int s = 0; s < e->S; ++s) {
-        first[s] = e->m[s] - 1 - e->phase[s];
-        n_out[s] = (int)((e->phase[s] + n_in) / e->m[s]);
-        e->phase[s] = (int)((e->phase[s] + n_in) % e->m[s]);
-        n_in = n_out[s];
-    }
-    const unsigned out_len = (unsigned)n_in;
-    OutSet &o = e->out[cur];
-    const bool demod = !(e->flags & SDRX_FLAG_NO_DEMOD) && out_len == (unsigned)kChunk;
-    // ---- raw delay line (last raw_hist samples of the previous [hist | block] move in front of this block)
-    //      and, when boundary B will run, the block power partials
-    {
-        int rc = launch_prep(e, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps, e->d_pwr_partial[cur]);
-        if (rc) return rc;
-        CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));
-    }
 
     const int valid_lo = (int)std::max<long>(0, (long)e->raw_hist - (long)std::min<uint64_t>(e->total, (uint64_t)e->raw_hist));
     const bool fast = e->use_fast && n > 0 && n % kUnit == 0 && phase_in[0] == 0 && phase_in[1] == 0 && phase_in[2] == 0;
