@@ -54,6 +54,8 @@ typedef enum { SDRX_FMT_U8 = 0, SDRX_FMT_S16 = 1, SDRX_FMT_F32 = 2 } sdrx_iq_for
 #define SDRX_FLAG_NO_DEMOD      0x2u  /* channelizer only (boundary A); skip boundary B kernels  */
 #define SDRX_FLAG_NO_PAIRING    0x8u  /* specialised bank: one channel per lane slot even where +-offset channels
                                          could share a translator table as conjugates                       */
+#define SDRX_FLAG_FTFIR         0x10u /* --ftfir (sdrx.cpp:1199,:1692): the first stage is the frequency-translating FIR,
+                                         msd.hpp:104-131 + calculateOutputTranslated :341-423, instead of mix + FIR      */
 #define SDRX_FLAG_PARTIAL_MIX   0x4u  /* channel-sharded run: stop at mix_pre (this GPU's share of the pan
                                          mix); FIR2 + s16 run once, in sdrx_engine_finish_mix              */
 
@@ -124,9 +126,11 @@ int  sdrx_engine_last_out_len(sdrx_engine *e, unsigned *out_len);
 int  sdrx_engine_get_channel_iq(sdrx_engine *e, float *ch_iq);
 /* Boundary B results. Waits for the block. */
 int  sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
-/* Streaming form: queue the read-back of the last pushed block and return; push the next block at once (its H2D
- * and kernels overlap this read-back); the host buffers (pinned) are valid after sdrx_engine_wait_outputs(e, back),
- * back = number of blocks pushed since the fetch (0 or 1).                                                  */
+/* Streaming form: queue the read-back of the last pushed block and return; push the next block(s) at once (their
+ * H2D and kernels overlap this read-back); the host buffers (pinned) are valid after
+ * sdrx_engine_wait_outputs(e, back), back = number of blocks pushed since the fetch (0..2: the engine keeps a ring
+ * of four output sets, so a caller may run two blocks ahead of the results it reads -- enough to take the
+ * device->host->device round trip off the critical path).                                                   */
 int  sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
 int  sdrx_engine_wait_outputs(sdrx_engine *e, int back);
 /* Boundary B on caller-supplied channel IQ (host, [C][512][2]) instead of the channelizer's. */

@@ -114,11 +114,18 @@ __device__ __forceinline__ void fast_body(const float2 *__restrict__ xp, const f
     for (int i = 0; i < kBody; ++i) {
         const float2 x = xv[i];
         const float2 w = tp[i * kFastCh];
-        // msd.hpp:134  in[i] * translator_[pos]; the conjugate channel reuses the same four products
-        const float m1 = x.y * w.y, m2 = x.y * w.x;
+        // msd.hpp:134  in[i] * translator_[pos].  A conjugate pair does not form the two mixed samples at all: the
+        // stages are linear, so the four real product streams P = xr wr, S = xi wr, R = xr wi, Q = xi wi are
+        // filtered as the packed pairs (P,S) and (R,Q) -- 4 multiplies per sample for both channels -- and
+        // x w = (P - Q, R + S), x conj(w) = (P + Q, S - R) are taken on the stage-3 results (fast_unmix).
         u64 s[NCH];
-        s[0] = pack2(fmaf(x.x, w.x, -m1), fmaf(x.x, w.y, m2));
-        if (NCH == 2) s[1] = pack2(fmaf(x.x, w.x, m1), fmaf(-x.x, w.y, m2));
+        if (NCH == 2) {
+            s[0] = pack2(x.x * w.x, x.y * w.x);
+            s[1] = pack2(x.x * w.y, x.y * w.y);
+        } else {
+            const float m1 = x.y * w.y, m2 = x.y * w.x;
+            s[0] = pack2(fmaf(x.x, w.x, -m1), fmaf(x.x, w.y, m2));
+        }
 #pragma unroll
         for (int c = 0; c < NCH; ++c) {
 #pragma unroll
@@ -139,6 +146,13 @@ __device__ __forceinline__ void fast_body(const float2 *__restrict__ xp, const f
             }
         }
     }
+}
+
+// Stage-3 sums of the product streams (P,S) and (R,Q) of a conjugate pair -> the pair's two channel samples.
+__device__ __forceinline__ void fast_unmix(u64 ps, u64 rq, float2 &plus, float2 &minus) {
+    const float2 a = unpack2(ps), b = unpack2(rq);
+    plus = make_float2(a.x - b.y, b.x + a.y);
+    minus = make_float2(a.x + b.y, a.y - b.x);
 }
 
 // grid = number of CTAs in the schedule, block = kFastThreads, dynamic smem = fast_smem_bytes(N).
@@ -277,9 +291,16 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
                         }
                     }
                 }
+                if (t >= warm) {
+                    float2 y[2];
+                    if (NCH == 2) fast_unmix(c3[0][0], c3[NCH - 1][0], y[0], y[1]);
+                    else y[0] = unpack2(c3[0][0]);
+#pragma unroll
+                    for (int c = 0; c < NCH; ++c)
+                        if (chan[c] >= 0) s3[out_base[c] + (u0 + t - warm)] = y[c];
+                }
 #pragma unroll
                 for (int c = 0; c < NCH; ++c) {
-                    if (t >= warm && chan[c] >= 0) s3[out_base[c] + (u0 + t - warm)] = unpack2(c3[c][0]);
                     c3[c][0] = c3[c][1]; c3[c][1] = c3[c][2]; c3[c][2] = c3[c][3]; c3[c][3] = c3[c][4]; c3[c][4] = 0ull;
                 }
             }
@@ -288,12 +309,18 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
         }
         // what this segment contributes to the (up to four) outputs that follow it
         if (have && u1 < U) {
+            float2 y[4][2];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (NCH == 2) fast_unmix(c3[0][q], c3[NCH - 1][q], y[q][0], y[q][1]);
+                else y[q][0] = unpack2(c3[0][q]);
+            }
 #pragma unroll
             for (int c = 0; c < NCH; ++c) {
                 if (chan[c] < 0) continue;
                 float2 *tl = tails + ((long)chan[c] * n_slots + pc.slot_base + half * (kFastSegs / 2) + w) * 4;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) tl[q] = unpack2(c3[c][q]);
+                for (int q = 0; q < 4; ++q) tl[q] = y[q][c];
             }
         }
     }
@@ -464,7 +491,7 @@ inline int fast_plan_schedule(int groups, int U, int n_sms, FastPlan &plan) {
                 if (L == 0) break;
                 if (U - ub - L > 0 && U - ub - L < 2 * kFastMinSegPiece) {       // do not leave a sliver of the group behind
                     const int all = U - ub;
-                    if (fast_piece_steps(fast_make_piece(0, ub, all, 0)) <= budget + 1) L = all;
+                    if (fast_piece_steps(fast_make_piece(0, ub, all, 0)) <= budget) L = all;
                 }
                 if (g != slot_group) { slot_group = g; slot = 0; }
                 const FastPiece p = fast_make_piece(g, ub, L, slot);

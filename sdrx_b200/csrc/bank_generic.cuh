@@ -63,6 +63,48 @@ k_mix_fir_generic(const void *__restrict__ raw, int hist, const float2 *__restri
     out[(long)c * out_stride + out_off + k] = make_float2(re, im);
 }
 
+// Stage 0 of the --ftfir path (msd.hpp:104-131): the raw samples enter the first stage's delay line unmixed and
+// its output is S::calculateOutputTranslated (msd.hpp:341-423, portable loop :398-416): a complex x complex dot
+// product with the coefficient set hk_[k_], k_ advancing by one per output and wrapping at N/m sets (:420).
+//   hk      [n_sets * H][Cpad] float2, hk[(set * H + i) * Cpad + c] = h[i] * tr_c[(j0 + set*m + i) % N] * 2  (msd.hpp:192-224)
+//   k0      k_ before the call's first output
+// Channels without a translator take the plain folded stage (msd.hpp:79-101), as in the reference.
+// grid (ceil(n_out/8), Cpad/32), block (32, 8): lane = channel, threadIdx.y = output.
+template <int FMT>
+static __global__ void __launch_bounds__(256)
+k_ftfir_generic(const void *__restrict__ raw, int hist, const float2 *__restrict__ hk, int n_sets, int k0, int Cpad, int C,
+                const uint8_t *__restrict__ has_tr, const float *__restrict__ h, int H, int m, int first, int n_out,
+                float2 *__restrict__ out, long out_stride, int out_off, int valid_lo) {
+    const int c = blockIdx.y * 32 + threadIdx.x;
+    const int k = blockIdx.x * 8 + threadIdx.y;
+    if (k >= n_out || c >= C) return;
+    const long p_lo = hist + (long)first + (long)k * m - (H - 1);
+    float re = 0.0f, im = 0.0f;
+    if (has_tr[c]) {
+        const float2 *hs = hk + ((long)((k0 + k) % n_sets) * H) * Cpad + c;
+        for (int i = 0; i < H; ++i) {
+            const float2 d = load_iq_from<FMT>(raw, p_lo + i, valid_lo);
+            const float2 g = __ldg(hs + (long)i * Cpad);
+            re = __fadd_rn(re, __fsub_rn(__fmul_rn(d.x, g.x), __fmul_rn(d.y, g.y)));
+            im = __fadd_rn(im, __fadd_rn(__fmul_rn(d.x, g.y), __fmul_rn(d.y, g.x)));
+        }
+    } else {
+        const int half = (H - 1) >> 1;
+        for (int i = 0; i < half; ++i) {
+            const float2 a = load_iq_from<FMT>(raw, p_lo + i, valid_lo);
+            const float2 b = load_iq_from<FMT>(raw, p_lo + (H - 1) - i, valid_lo);
+            const float hv = __ldg(h + i);
+            re = __fadd_rn(re, __fmul_rn(__fadd_rn(a.x, b.x), hv));
+            im = __fadd_rn(im, __fmul_rn(__fadd_rn(a.y, b.y), hv));
+        }
+        const float2 a = load_iq_from<FMT>(raw, p_lo + half, valid_lo);
+        const float hv = __ldg(h + half);
+        re = __fadd_rn(re, __fmul_rn(a.x, hv));
+        im = __fadd_rn(im, __fmul_rn(a.y, hv));
+    }
+    out[(long)c * out_stride + out_off + k] = make_float2(re, im);
+}
+
 // Stage s >= 1: decimating symmetric FIR on a per-channel stream.
 //   in  [C][in_stride], in[c][in_hist + i] is call-relative input i (in_hist == H-1)
 // grid (ceil(n_out/128), C), block 128: lane = output.

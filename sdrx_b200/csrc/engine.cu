@@ -20,7 +20,8 @@ using namespace sdrx;
 
 namespace {
 
-constexpr int kNBuf = 2;          // ping-pong depth of raw input and of the output sets
+constexpr int kNBuf = 2;          // ping-pong depth of raw input
+constexpr int kNOut = 4;          // ring of output sets: a streaming caller may run up to kNOut-1 blocks ahead of the results it reads
 constexpr int kPwrPartials = 296;     // power CTAs of k_prep: two per SM
 constexpr uint32_t kStateMagic = 0x58524453u;  // "SDRX"
 
@@ -55,12 +56,12 @@ struct sdrx_engine {
     cudaStream_t s_main = nullptr, s_copy = nullptr;
     cudaStream_t s_side = nullptr;        // latency-bound tail of boundary B (k_chan_recur, k_mix_fir2_pcm): overlaps the next bank
     cudaEvent_t ev_head_done = nullptr;   // k_chan_head of the current block has been queued behind this point (main -> side)
-    cudaEvent_t ev_side_done[kNBuf] = {nullptr, nullptr};   // side-stream work that reads / writes output set b is complete
-    bool side_pending[kNBuf] = {false, false};
+    cudaEvent_t ev_side_done[kNOut] = {};   // side-stream work that reads / writes output set b is complete
+    bool side_pending[kNOut] = {};
     cudaStream_t s_out = nullptr;         // asynchronous result fetch (sdrx_engine_fetch_outputs): D2H overlaps the next block
-    cudaEvent_t ev_fetch_done[kNBuf] = {nullptr, nullptr};
-    bool fetch_pending[kNBuf] = {false, false};
-    uint8_t *d_gate[kNBuf] = {nullptr, nullptr};             // [C] squelch state entering the block (k_chan_head -> k_chan_recur)
+    cudaEvent_t ev_fetch_done[kNOut] = {};
+    bool fetch_pending[kNOut] = {};
+    uint8_t *d_gate[kNOut] = {};            // [C] squelch state entering the block (k_chan_head -> k_chan_recur)
     cudaEvent_t ev_copied[kNBuf] = {nullptr, nullptr};
     cudaEvent_t ev_raw_free[kNBuf] = {nullptr, nullptr};   // last reader of d_raw[b] has been queued
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr, ev_t2 = nullptr, ev_b0 = nullptr, ev_b1 = nullptr;
@@ -74,8 +75,8 @@ struct sdrx_engine {
     uint8_t *d_has_tr = nullptr;
     float *d_taps = nullptr;
     float2 *d_stage_in[SDRX_MAX_STAGES] = {nullptr};
-    float *d_pwr_partial[kNBuf] = {nullptr, nullptr};       // per parity: k_prep of block b+1 runs while block b's mix kernel reads its own
-    OutSet out[kNBuf];
+    float *d_pwr_partial[kNOut] = {};      // per parity: k_prep of block b+1 runs while block b's mix kernel reads its own
+    OutSet out[kNOut];
     // boundary B
     ChannelState st{};
     DemodTables tb{};
@@ -90,6 +91,9 @@ struct sdrx_engine {
     FastBank fast;                        // specialised channel bank (bank_fast.cuh)
     bool use_fast = false;
     bool tail_fusable = false;            // last stage inside the per-channel head kernel (k_chan_head<true>)
+    bool ftfir = false;                   // --ftfir: stage 0 is the frequency-translating FIR (msd.hpp:104-131)
+    int ft_sets = 0;                      // coefficient sets, N / m[0] (msd.hpp:196)
+    float2 *d_hk = nullptr;               // [ft_sets * H0][Cpad]
 
     // pinned staging for pageable callers
     uint8_t *h_stage[kNBuf] = {nullptr, nullptr};
@@ -98,6 +102,7 @@ struct sdrx_engine {
     // carried host-side state
     long trans_pos = 0;                  // MSD::trans_pos_ (msd.hpp:440), same for every channel
     int phase[SDRX_MAX_STAGES] = {0};    // inputs seen since the stage's last output (m - isn_)
+    int ft_k = 0;                        // S::k_ of stage 0 (msd.hpp:434), same for every channel
     int fmt = -1;                        // wire format of the stream so far
     uint64_t blocks = 0;
     unsigned prev_n = 0;                 // samples of the previous block (for the raw carry)
@@ -190,8 +195,7 @@ int reset_state(sdrx_engine *e) {
     const size_t C = (size_t)e->C;
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_out));
-    e->side_pending[0] = e->side_pending[1] = false;
-    e->fetch_pending[0] = e->fetch_pending[1] = false;
+    for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
     for (int b = 0; b < kNBuf; ++b) CU(cudaMemsetAsync(e->d_raw[b], 0, e->raw_buf_bytes, e->s_main));
     for (int s = 1; s < e->S; ++s)
         CU(cudaMemsetAsync(e->d_stage_in[s], 0, sizeof(float2) * (size_t)e->stage_stride[s] * C, e->s_main));
@@ -209,6 +213,7 @@ int reset_state(sdrx_engine *e) {
     }
     CU(cudaStreamSynchronize(e->s_main));
     e->trans_pos = 0;
+    e->ft_k = 0;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = 0;
     e->fmt = -1;
     e->blocks = 0;
@@ -231,18 +236,20 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     for (int b = 0; b < kNBuf; ++b) {
         cudaFree(e->d_raw[b]);
         if (e->h_stage[b]) cudaFreeHost(e->h_stage[b]);
+        if (e->ev_copied[b]) cudaEventDestroy(e->ev_copied[b]);
+        if (e->ev_raw_free[b]) cudaEventDestroy(e->ev_raw_free[b]);
+    }
+    for (int b = 0; b < kNOut; ++b) {
         OutSet &o = e->out[b];
         cudaFree(o.ch_iq); cudaFree(o.audio); cudaFree(o.snr); cudaFree(o.mix_pre); cudaFree(o.mix);
         cudaFree(o.pcm); cudaFree(o.pwr); cudaFree(o.sql); cudaFree(o.agc_gain); cudaFree(o.lf_gain);
-        if (e->ev_copied[b]) cudaEventDestroy(e->ev_copied[b]);
-        if (e->ev_raw_free[b]) cudaEventDestroy(e->ev_raw_free[b]);
         if (e->ev_side_done[b]) cudaEventDestroy(e->ev_side_done[b]);
         if (e->ev_fetch_done[b]) cudaEventDestroy(e->ev_fetch_done[b]);
         cudaFree(e->d_gate[b]); cudaFree(e->d_pwr_partial[b]);
     }
     if (e->ev_head_done) cudaEventDestroy(e->ev_head_done);
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) cudaFree(e->d_stage_in[s]);
-    cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps);
+    cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps); cudaFree(e->d_hk);
     cudaFree(e->st.agc_gain); cudaFree(e->st.agc_power); cudaFree(e->st.lf_gain); cudaFree(e->st.lf_power);
     cudaFree(e->st.sql_state); cudaFree(e->st.sql_prev); cudaFree(e->st.mixed);
     cudaFree(e->d_window); cudaFree(e->d_shape); cudaFree(e->d_ramp_up); cudaFree(e->d_ramp_down);
@@ -282,7 +289,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     e->taps.assign(cfg->taps, cfg->taps + off);
     e->raw_hist = std::max((e->H[0] - 1 + 7) / 8 * 8, 128);
     const bool eligible = fast_eligible(S, e->m, e->H, e->N);
-    const bool want_fast = !(cfg->flags & SDRX_FLAG_FORCE_GENERIC) && eligible;
+    e->ftfir = (cfg->flags & SDRX_FLAG_FTFIR) && cfg->translators && cfg->translator_len > 0;
+    const bool want_fast = !(cfg->flags & SDRX_FLAG_FORCE_GENERIC) && eligible && !e->ftfir;
     if (eligible) e->raw_hist = std::max(e->raw_hist, kFastRawHist);   // also when forced generic: state blobs stay portable
 
     CU(cudaStreamCreateWithFlags(&e->s_main, cudaStreamNonBlocking));
@@ -290,9 +298,11 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     CU(cudaStreamCreateWithFlags(&e->s_side, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->ev_head_done, cudaEventDisableTiming));
-    for (int b = 0; b < kNBuf; ++b) {
+    for (int b = 0; b < kNOut; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_side_done[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_fetch_done[b], cudaEventDisableTiming));
+    }
+    for (int b = 0; b < kNBuf; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_copied[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_raw_free[b], cudaEventDisableTiming));
     }
@@ -327,6 +337,33 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if ((rc = dalloc(&e->d_has_tr, has.size()))) return rc;
         if ((rc = upload(e->d_has_tr, has.data(), has.size()))) return rc;
     }
+    if (e->ftfir) {
+        // msd.hpp:192-224: hk_[set][i] = h[i] * translator[(j + set*m + i) % N] * 2.0f  (float * complex, then
+        // complex * float: every product rounds once, the doubling is exact), j = (N - (H-1) % N) % N
+        const int N = e->N, H = e->H[0], m0 = e->m[0];
+        e->ft_sets = N / m0;
+        if (e->ft_sets < 1) return fail(SDRX_ERR_ARG, "ftfir: translator shorter than the first stage's decimation factor");
+        std::vector<float2> hk((size_t)e->ft_sets * H * e->Cpad, make_float2(0.0f, 0.0f));
+        const float *h = e->taps.data() + e->tap_off[0];
+        for (int c = 0; c < C; ++c) {
+            if (cfg->has_translator && !cfg->has_translator[c]) continue;
+            const float *row = cfg->translators + (size_t)c * N * 2;
+            size_t j = (size_t)((N - (H - 1) % N) % N);
+            for (int set = 0; set < e->ft_sets; ++set) {
+                size_t k = j;
+                for (int i = 0; i < H; ++i) {
+                    const float re = h[i] * row[2 * k], im = h[i] * row[2 * k + 1];
+                    hk[((size_t)set * H + i) * e->Cpad + c] = make_float2(re * 2.0f, im * 2.0f);
+                    if (++k == (size_t)N) k = 0;
+                }
+                j += (size_t)m0;
+                if (j >= (size_t)N) j -= (size_t)N;
+            }
+        }
+        int rc = dalloc(&e->d_hk, hk.size());
+        if (rc) return rc;
+        if ((rc = upload(e->d_hk, hk.data(), hk.size()))) return rc;
+    }
     {
         int rc = dalloc(&e->d_taps, e->taps.size());
         if (rc) return rc;
@@ -348,7 +385,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         size_t cap = e->block_len;
         for (int s = 0; s < S; ++s) cap = cap / (size_t)e->m[s] + 1;
         e->chiq_stride = (long)std::max<size_t>(kChunk, (cap + 3) / 4 * 4);
-        for (int b = 0; b < kNBuf; ++b) {
+        for (int b = 0; b < kNOut; ++b) {
             int rc = dalloc(&e->d_pwr_partial[b], kPwrPartials);
             if (rc) return rc;
             if ((rc = dalloc(&e->d_gate[b], C))) return rc;
@@ -361,7 +398,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if (rc) return rc;
         e->use_fast = true;
     }
-    for (int b = 0; b < kNBuf; ++b) {
+    for (int b = 0; b < kNOut; ++b) {
         OutSet &o = e->out[b];
         int rc;
         if ((rc = dalloc(&o.ch_iq, (size_t)C * e->chiq_stride))) return rc;
@@ -517,6 +554,11 @@ int launch_bank_generic(sdrx_engine *e, const uint8_t *raw, int hist, int pos0, 
         if (n_out[s] > 0) {
             if (s == 0) {
                 dim3 grid(div_up(n_out[0], 8), e->Cpad / 32), block(32, 8);
+                if (e->ftfir)
+                    k_ftfir_generic<FMT><<<grid, block, 0, e->s_main>>>(
+                        raw, hist, e->d_hk, e->ft_sets, e->ft_k, e->Cpad, e->C, e->d_has_tr, e->d_taps + e->tap_off[0],
+                        e->H[0], e->m[0], first[0], n_out[0], dst, dst_stride, dst_off, valid_lo);
+                else
                 k_mix_fir_generic<FMT><<<grid, block, 0, e->s_main>>>(
                     raw, hist, e->d_table_t, e->Cpad, e->C, e->N, pos0, e->d_has_tr,
                     e->d_taps + e->tap_off[0], e->H[0], e->m[0], first[0], n_out[0], dst, dst_stride, dst_off,
@@ -673,7 +715,8 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         return fail(SDRX_ERR_STATE, "wire format changed mid-stream (the carried raw history is format specific); reset first");
     e->fmt = fmt;
     const int bps = raw_bytes_per_sample(fmt);
-    const int cur = (int)(e->blocks & 1), prv = cur ^ 1;
+    const int cur = (int)(e->blocks & 1), prv = cur ^ 1;      // raw ping-pong
+    const int oc = (int)(e->blocks % kNOut);                 // output set of this block
     uint8_t *buf = e->d_raw[cur];
     const size_t hist_bytes = (size_t)e->raw_hist * bps;
 
@@ -689,7 +732,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         n_in = n_out[s];
     }
     const unsigned out_len = (unsigned)n_in;
-    OutSet &o = e->out[cur];
+    OutSet &o = e->out[oc];
     const bool demod = !(e->flags & SDRX_FLAG_NO_DEMOD) && out_len == (unsigned)kChunk;
     // ---- ingest: pinned, double buffered, on the copy stream
     // buffer `cur` was last read by block b-1's raw carry (and before that by block b-2's kernels)
@@ -715,17 +758,17 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     }
     // ---- still on the copy stream, off the compute stream's critical path: the raw delay line (last raw_hist
     //      samples of the previous [hist | block] move in front of this block) and, when boundary B will run,
-    //      the block power partials.  The partials of parity `cur` were last read by block b-2's mix kernel.
+    //      the block power partials.  The partials of set `oc` were last read by block b-kNOut's mix kernel.
     {
-        if (e->side_pending[cur]) CU(cudaStreamWaitEvent(e->s_copy, e->ev_side_done[cur], 0));
+        if (e->side_pending[oc]) CU(cudaStreamWaitEvent(e->s_copy, e->ev_side_done[oc], 0));
         int rc = launch_prep(e, e->s_copy, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps,
-                             e->d_pwr_partial[cur]);
+                             e->d_pwr_partial[oc]);
         if (rc) return rc;
         CU(cudaEventRecord(e->ev_copied[cur], e->s_copy));
         CU(cudaStreamWaitEvent(e->s_main, e->ev_copied[cur], 0));
         CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));   // every kernel that read buffer `prv` is queued before this point
     }
-    { int rc = wait_side(e, cur); if (rc) return rc; }      // block b-2's recurrences / mix read this output set
+    { int rc = wait_side(e, oc); if (rc) return rc; }       // block b-kNOut's recurrences / mix / read-back used this output set
     if (e->timing) CU(cudaEventRecord(e->ev_t0, e->s_main));
 
     const int valid_lo = (int)std::max<long>(0, (long)e->raw_hist - (long)std::min<uint64_t>(e->total, (uint64_t)e->raw_hist));
@@ -754,11 +797,12 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     if (rc) return rc;
     if (e->timing) CU(cudaEventRecord(e->ev_t1, e->s_main));
 
-    if (demod) { rc = launch_demod(e, cur, n > 0, n, fuse_tail ? &tail : nullptr); if (rc) return rc; }
+    if (demod) { rc = launch_demod(e, oc, n > 0, n, fuse_tail ? &tail : nullptr); if (rc) return rc; }
     else if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_main));
     if (e->timing) e->timing_valid = true;
 
     e->trans_pos = (e->trans_pos + n) % e->N;
+    if (e->ftfir) e->ft_k = (e->ft_k + n_out[0]) % e->ft_sets;
     e->total += n;
     e->prev_n = n;
     e->last_out_len = out_len;
@@ -802,7 +846,7 @@ extern "C" int sdrx_engine_sync(sdrx_engine *e) {
 extern "C" int sdrx_engine_join(sdrx_engine *e) {
     if (!e) return fail(SDRX_ERR_ARG, "null engine");
     DevGuard g(e->dev);
-    for (int b = 0; b < kNBuf; ++b) { int rc = wait_side(e, b); if (rc) return rc; }
+    for (int b = 0; b < kNOut; ++b) { int rc = wait_side(e, b); if (rc) return rc; }
     return SDRX_OK;
 }
 
@@ -810,7 +854,7 @@ extern "C" int sdrx_engine_get_channel_iq(sdrx_engine *e, float *ch_iq) {
     if (!e || !ch_iq) return fail(SDRX_ERR_ARG, "null argument");
     if (e->blocks == 0) return fail(SDRX_ERR_STATE, "no block pushed yet");
     DevGuard g(e->dev);
-    const OutSet &o = e->out[(e->blocks - 1) & 1];
+    const OutSet &o = e->out[(e->blocks - 1) % kNOut];
     if (e->last_out_len > 0)
         CU(cudaMemcpy2DAsync(ch_iq, (size_t)e->last_out_len * sizeof(float2), o.ch_iq, (size_t)e->chiq_stride * sizeof(float2),
                              (size_t)e->last_out_len * sizeof(float2), (size_t)e->C, cudaMemcpyDeviceToHost, e->s_main));
@@ -824,8 +868,8 @@ extern "C" int sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs 
     if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
     if (!e->last_demod) return fail(SDRX_ERR_STATE, "the last block did not yield 512 samples per channel; boundary B did not run");
     DevGuard g(e->dev);
-    int rc = wait_side(e, (int)((e->blocks - 1) & 1));
-    if (!rc) rc = copy_outputs(e, e->out[(e->blocks - 1) & 1], out, e->s_main);
+    int rc = wait_side(e, (int)((e->blocks - 1) % kNOut));
+    if (!rc) rc = copy_outputs(e, e->out[(e->blocks - 1) % kNOut], out, e->s_main);
     if (rc) return rc;
     CU(cudaStreamSynchronize(e->s_main));
     return SDRX_OK;
@@ -841,7 +885,7 @@ extern "C" int sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_output
     if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
     if (!e->last_demod) return fail(SDRX_ERR_STATE, "the last block did not yield 512 samples per channel; boundary B did not run");
     DevGuard g(e->dev);
-    const int idx = (int)((e->blocks - 1) & 1);
+    const int idx = (int)((e->blocks - 1) % kNOut);
     if (e->side_pending[idx]) CU(cudaStreamWaitEvent(e->s_out, e->ev_side_done[idx], 0));
     int rc = copy_outputs(e, e->out[idx], out, e->s_out);
     if (rc) return rc;
@@ -851,10 +895,10 @@ extern "C" int sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_output
 }
 
 extern "C" int sdrx_engine_wait_outputs(sdrx_engine *e, int back) {
-    if (!e || back < 0 || back > 1) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) or 1 (the one before)");
+    if (!e || back < 0 || back > kNOut - 2) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) .. 2");
     if (e->blocks < (uint64_t)back + 1) return fail(SDRX_ERR_STATE, "no such block");
     DevGuard g(e->dev);
-    const int idx = (int)((e->blocks - 1 - back) & 1);
+    const int idx = (int)((e->blocks - 1 - back) % kNOut);
     if (!e->fetch_pending[idx]) return fail(SDRX_ERR_STATE, "no fetch was queued for that block");
     CU(cudaEventSynchronize(e->ev_fetch_done[idx]));
     return SDRX_OK;
@@ -864,7 +908,7 @@ extern "C" int sdrx_engine_demod_block(sdrx_engine *e, const float *ch_iq, float
     if (!e || !ch_iq) return fail(SDRX_ERR_ARG, "null argument");
     if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
     DevGuard g(e->dev);
-    const int idx = (int)(e->blocks & 1);
+    const int idx = (int)(e->blocks % kNOut);
     OutSet &o = e->out[idx];
     { int rc = wait_side(e, idx); if (rc) return rc; }
     CU(cudaMemcpy2DAsync(o.ch_iq, (size_t)e->chiq_stride * sizeof(float2), ch_iq, (size_t)kChunk * sizeof(float2),
@@ -891,7 +935,7 @@ extern "C" int sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_
         CU(cudaMalloc((void **)&e->d_parts, bytes));
         e->parts_cap = (size_t)n_parts;
     }
-    const int idx = e->blocks ? (int)((e->blocks - 1) & 1) : 0;
+    const int idx = e->blocks ? (int)((e->blocks - 1) % kNOut) : 0;
     OutSet &o = e->out[idx];
     { int rc = wait_side(e, idx); if (rc) return rc; }
     CU(cudaMemcpyAsync(e->d_parts, parts, bytes, cudaMemcpyHostToDevice, e->s_main));
@@ -965,6 +1009,7 @@ struct StateHeader {
     uint64_t blocks;
     int32_t  phase[SDRX_MAX_STAGES];
     int32_t  H[SDRX_MAX_STAGES];
+    int32_t  ft_k, ftfir;
 };
 
 size_t state_bytes(const sdrx_engine *e) {
@@ -994,11 +1039,12 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     }
     uint8_t *p = (uint8_t *)buf;
     StateHeader h{};
-    h.magic = kStateMagic; h.version = 1;
+    h.magic = kStateMagic; h.version = 2;
     h.C = e->C; h.S = e->S; h.fmt = e->fmt; h.raw_hist = e->raw_hist; h.total = e->total; h.fir2_ntaps = e->fir2_ntaps;
     h.demod = (e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1;
     h.trans_pos = e->trans_pos; h.blocks = e->blocks;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) { h.phase[s] = e->phase[s]; h.H[s] = e->H[s]; }
+    h.ft_k = e->ft_k; h.ftfir = e->ftfir ? 1 : 0;
     memcpy(p, &h, sizeof(h)); p += sizeof(h);
     const int bps = e->fmt >= 0 ? raw_bytes_per_sample(e->fmt) : 8;
     const int last = (int)((e->blocks & 1) ^ 1);
@@ -1030,9 +1076,9 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     if (size < sizeof(StateHeader)) return fail(SDRX_ERR_ARG, "state buffer too small");
     StateHeader h;
     memcpy(&h, buf, sizeof(h));
-    if (h.magic != kStateMagic || h.version != 1) return fail(SDRX_ERR_ARG, "not an sdrx_b200 state blob");
+    if (h.magic != kStateMagic || h.version != 2) return fail(SDRX_ERR_ARG, "not an sdrx_b200 state blob");
     if (h.C != e->C || h.S != e->S || h.raw_hist != e->raw_hist || h.fir2_ntaps != e->fir2_ntaps ||
-        h.demod != ((e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1))
+        h.demod != ((e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1) || h.ftfir != (e->ftfir ? 1 : 0))
         return fail(SDRX_ERR_ARG, "state blob was saved by a differently configured engine");
     for (int s = 0; s < e->S; ++s)
         if (h.H[s] != e->H[s]) return fail(SDRX_ERR_ARG, "state blob stage layout differs");
@@ -1041,10 +1087,12 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
-    e->side_pending[0] = e->side_pending[1] = false;
+    CU(cudaStreamSynchronize(e->s_out));
+    for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
     const uint8_t *p = (const uint8_t *)buf + sizeof(h);
     e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = h.blocks; e->total = h.total; e->generic_stale = false;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = h.phase[s];
+    e->ft_k = h.ft_k;
     e->prev_n = 0;          // the history is parked at the very front of the "previous" buffer
     e->last_out_len = 0; e->last_demod = false; e->timing_valid = false;
     const int last = (int)((e->blocks & 1) ^ 1);

@@ -20,6 +20,7 @@ struct sdrx_msd {
     std::vector<int> m, ntaps;
     std::vector<float> taps;
     size_t m_total = 1;
+    bool use_ftfir = false;                 // msd.hpp:54 third argument
     unsigned cap = 0;                       // block_len of the current engine
     sdrx_engine *eng = nullptr;
 };
@@ -40,7 +41,7 @@ int msd_make_engine(sdrx_msd *q, unsigned cap, sdrx_engine **out) {
     cfg.ntaps = q->ntaps.data();
     cfg.taps = q->taps.data();
     cfg.block_len = cap;
-    cfg.flags = SDRX_FLAG_NO_DEMOD | SDRX_FLAG_FORCE_GENERIC;
+    cfg.flags = SDRX_FLAG_NO_DEMOD | SDRX_FLAG_FORCE_GENERIC | (q->use_ftfir ? SDRX_FLAG_FTFIR : 0u);
     return sdrx_engine_create(&cfg, out);
 }
 
@@ -69,11 +70,10 @@ extern "C" int sdrx_msd_create(const float *translator, int N, int n_stages, con
                                const float *taps, int use_ftfir, int device, sdrx_msd **out) {
     if (!out || !m || !ntaps || !taps || n_stages < 1) return fail(SDRX_ERR_ARG, "null or empty stage list");
     *out = nullptr;
-    if (use_ftfir && translator && N > 0)
-        return fail(SDRX_ERR_UNSUPPORTED, "use_ftfir (experimental msd.hpp:104-131 path) is not implemented; parity target is the default path");
     sdrx_msd *q = new sdrx_msd();
     q->device = device;
     q->S = n_stages;
+    q->use_ftfir = use_ftfir != 0;
     q->N = (translator && N > 0) ? N : 0;
     if (q->N) q->translator.assign(translator, translator + 2 * (size_t)N);
     int tot = 0;
@@ -97,6 +97,7 @@ extern "C" int sdrx_msd_clone(const sdrx_msd *src, sdrx_msd **out) {
     q->device = src->device; q->N = src->N; q->S = src->S;
     q->translator = src->translator; q->m = src->m; q->ntaps = src->ntaps; q->taps = src->taps;
     q->m_total = src->m_total;
+    q->use_ftfir = src->use_ftfir;
     int rc = msd_make_engine(q, src->cap, &q->eng);
     if (rc) { delete q; return rc; }
     q->cap = src->cap;

@@ -24,8 +24,9 @@ def product_tables(rate: int) -> dict:
 
 def make_cpu_rx(scn: Scenario, backend: str = "oracle", threaded: bool = False):
     if backend == "oracle":
-        return ob.OracleRx(product_tables(scn.rate), scn.offsets, scn.sql_levels, None, scn.use_lf_agc, scn.lf_gain_db)
-    return ob.RefRx(scn.rate, scn.offsets, scn.sql_levels, scn.use_lf_agc, scn.lf_gain_db, False, threaded, backend)
+        return ob.OracleRx(product_tables(scn.rate), scn.offsets, scn.sql_levels, None, scn.use_lf_agc, scn.lf_gain_db,
+                           scn.use_ftfir)
+    return ob.RefRx(scn.rate, scn.offsets, scn.sql_levels, scn.use_lf_agc, scn.lf_gain_db, scn.use_ftfir, threaded, backend)
 
 
 def run_cpu(scn: Scenario, backend: str = "oracle", blocks: Optional[List[np.ndarray]] = None) -> List[ob.BlockOut]:
@@ -42,7 +43,7 @@ def run_engine(scn: Scenario, force_generic: bool = False, blocks: Optional[List
                no_pairing: bool = False):
     from sdrx_b200 import Engine
     eng = Engine(scn.plan(), device=device, use_lf_agc=scn.use_lf_agc, lf_gain_db=scn.lf_gain_db,
-                 force_generic=force_generic, no_pairing=no_pairing)
+                 force_generic=force_generic, no_pairing=no_pairing, use_ftfir=scn.use_ftfir)
     src = scn.source()
     out = []
     for b in range(scn.n_blocks):

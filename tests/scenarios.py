@@ -23,6 +23,7 @@ class Scenario:
     sql_levels: Optional[List[float]] = None
     use_lf_agc: bool = False
     lf_gain_db: float = 0.0
+    use_ftfir: bool = False         # --ftfir (sdrx.cpp:1199): msd.hpp:104-131
 
     def plan(self) -> ChannelPlan:
         return ChannelPlan.from_offsets(self.rate, self.offsets, self.sql_levels)
@@ -62,6 +63,22 @@ def config2_variants() -> List[Scenario]:
     b.name += "_sql"
     b.sql_levels, b.n_blocks = [0.0, 20.0, 9.0, 3.0, 9.0, 12.0, 0.0, 30.0], 6
     return [a, b]
+
+
+def ftfir_scenarios() -> List[Scenario]:
+    """--ftfir (sdrx.cpp:1199, msd.hpp:104-131, :341-423): 10 MS/s f32 (incl. a centre channel, which keeps the
+    no-translator path), 2.4 MS/s u8 and 2.56 MS/s (the rate whose N is not a multiple of m, msd.hpp:173)."""
+    a = config2(n_blocks=5)
+    a.offsets = a.offsets + [0]
+    a.name += "_ftfir"
+    b = config1()
+    b.name += "_ftfir"
+    b.n_blocks = 14
+    c = [s for s in other_rates() if s.rate == 2560000][0]
+    c.name += "_ftfir"
+    for s in (a, b, c):
+        s.use_ftfir = True
+    return [a, b, c]
 
 
 def paired_channels(fmt: int = FMT_F32) -> Scenario:

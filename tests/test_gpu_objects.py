@@ -10,13 +10,15 @@ from sdrx_b200.objects import AGC, FIR, FIR2, FIR3, MSD, LfAGC
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("rate,off", [(2400000, -3), (10000000, 7), (10000000, 0), (2560000, 11)])
-def test_msd_any_chunking_and_copy(rate, off):
+@pytest.mark.parametrize("rate,off,ftfir", [(2400000, -3, False), (10000000, 7, False), (10000000, 0, False),
+                                            (2560000, 11, False), (10000000, -233, True), (2400000, 5, True),
+                                            (10000000, 0, True)])
+def test_msd_any_chunking_and_copy(rate, off, ftfir):
     rc = cf.rate_config(rate)
     rng = np.random.default_rng(5)
     x = (rng.standard_normal(50000) + 1j * rng.standard_normal(50000)).astype(np.complex64)
     tr = cf.make_translator(rc.N, rc.z, off) if off else None
-    a, o = MSD(tr, rc.stages), ob.OracleMSD(tr, rc.stages)
+    a, o = MSD(tr, rc.stages, use_ftfir=ftfir), ob.OracleMSD(tr, rc.stages, use_ftfir=ftfir)   # msd.hpp:54
     assert a.m() == o.m == rc.M
     pos = 0
     for n in [1, 3, 17, 1000, 4096, 7, 20001, 24875]:

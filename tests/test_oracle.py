@@ -29,7 +29,7 @@ def _assert_blocks_equal(a, b):
 
 @needs_ref
 @pytest.mark.parametrize("scn", [sc.config1(), sc.config2(n_blocks=6), sc.config2(sc.FMT_S16, 3), sc.centre_channel()]
-                         + sc.config2_variants() + sc.other_rates(), ids=lambda s: s.name)
+                         + sc.config2_variants() + sc.other_rates() + sc.ftfir_scenarios(), ids=lambda s: s.name)
 def test_restatement_is_bit_exact_with_reference_build(scn):
     src = scn.source()
     blocks = [src.block(b) for b in range(scn.n_blocks)]
