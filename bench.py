@@ -283,12 +283,12 @@ def run_ours(args):
         p.view(np.complex64, L)[:] = b
     hviews = [p.view(np.complex64, L) for p in pins]
     # Streaming use of the API: push block i (H2D from pinned memory), queue its read-back into pinned result
-    # buffers, and only then wait for block i-2's results -- so the copies of one block overlap the kernels of
+    # buffers, and only then wait for block i-3's results -- so the copies of one block overlap the kernels of
     # its neighbours and the device->host->device round trip is off the critical path.  Every step still moves its own input and its own results across PCIe inside the timed region.
-    LAG = 2                                  # the host reads block i-LAG's results while blocks i-1, i are in flight
+    LAG = 3                                  # the host reads block i-LAG's results while blocks i-LAG+1 .. i are in flight
     osets = [eng.make_output_buffers(pinned=True) for _ in range(LAG + 1)]
     d2h = osets[0][2]
-    for i in range(3):
+    for i in range(4):
         eng.push(hviews[i % n_distinct])
         eng.outputs_into(osets[i % (LAG + 1)][0])
     barrier()
@@ -319,7 +319,21 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_val = world * C_ * L / (float(t.item()) / args.steps * 1e-3) / 1e6
-    e2e = {"value": e2e_val, "unit": "channel-MS/s", "h2d_bytes_per_step": blk_bytes, "d2h_bytes_per_step": d2h,
+    # what the wire allows: one block's H2D and one block's D2H alone, pinned memory, CUDA events (diagnostic)
+    def _copy_gbs(dst, src, nbytes, reps=20):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dst.copy_(src, non_blocking=True)
+        torch.cuda.synchronize()
+        a.record()
+        for _ in range(reps):
+            dst.copy_(src, non_blocking=True)
+        b.record()
+        torch.cuda.synchronize()
+        return nbytes * reps / (a.elapsed_time(b) * 1e-3) / 1e9
+    hbuf = torch.empty(blk_bytes, dtype=torch.uint8, pin_memory=True)
+    dbuf = torch.empty(blk_bytes, dtype=torch.uint8, device="cuda")
+    pcie = {"h2d_gbs_block": _copy_gbs(dbuf, hbuf, blk_bytes), "d2h_gbs_block": _copy_gbs(hbuf, dbuf, blk_bytes)}
+    e2e = {"value": e2e_val, "unit": "channel-MS/s", "h2d_bytes_per_step": blk_bytes, "d2h_bytes_per_step": d2h, "pcie": pcie,
            "ms_per_step": float(t.item()) / args.steps,
            "host_us_per_step": {"push": host[0] / args.steps * 1e6, "fetch": host[1] / args.steps * 1e6,
                                 "wait": host[2] / args.steps * 1e6}}

@@ -128,9 +128,9 @@ int  sdrx_engine_get_channel_iq(sdrx_engine *e, float *ch_iq);
 int  sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
 /* Streaming form: queue the read-back of the last pushed block and return; push the next block(s) at once (their
  * H2D and kernels overlap this read-back); the host buffers (pinned) are valid after
- * sdrx_engine_wait_outputs(e, back), back = number of blocks pushed since the fetch (0..2: the engine keeps a ring
- * of four output sets, so a caller may run two blocks ahead of the results it reads -- enough to take the
- * device->host->device round trip off the critical path).                                                   */
+ * sdrx_engine_wait_outputs(e, back), back = number of blocks pushed since the fetch (0..4: the engine keeps a ring
+ * of six output sets, so a caller may run a few blocks ahead of the results it reads -- enough to take the
+ * side-stream kernels + device->host->device round trip off the critical path).                                                   */
 int  sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
 int  sdrx_engine_wait_outputs(sdrx_engine *e, int back);
 /* Boundary B on caller-supplied channel IQ (host, [C][512][2]) instead of the channelizer's. */

@@ -53,8 +53,6 @@ constexpr int kFastMinSegPiece = 2;// ... but a small piece (a CTA range that st
 constexpr int kFastWarmStart = 4;  // warm-up units of a segment at the start of the block
 constexpr int kFastRawHist = 768;  // raw history samples the engine keeps for this path
 
-typedef unsigned long long u64;
-
 struct FastTaps {                  // kernel parameter: lives in the constant bank
     float2 h1[17];                 // (h,h) pairs for FFMA2
     float2 h2[19];
@@ -87,10 +85,6 @@ __host__ __device__ inline bool fast_segment(const FastPiece &p, int w, int half
     return *u0 < hi;
 }
 
-__device__ __forceinline__ u64 pack2(float x, float y) { u64 d; asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(x), "f"(y)); return d; }
-__device__ __forceinline__ float2 unpack2(u64 v) { float2 d; asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(v)); return d; }
-__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
-__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
 __device__ __forceinline__ u64 tap2(const float2 &h) { return pack2(h.x, h.y); }
 
 // One 25-sample body of one thread: mixes 25 samples and advances the three stages by 5 / 1 / 0.2 outputs, for

@@ -52,6 +52,14 @@ __device__ __forceinline__ float2 load_iq_from(const void *raw, long idx, int va
     return idx >= valid_lo ? load_iq<FMT>(raw, idx) : make_float2(0.0f, 0.0f);
 }
 
+// ---- packed FP32 pairs (sm_100a fma.rn.f32x2 family): (re, im) in one 64-bit register ----------------
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pack2(float x, float y) { u64 d; asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "f"(x), "f"(y)); return d; }
+__device__ __forceinline__ float2 unpack2(u64 v) { float2 d; asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(v)); return d; }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 d; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c)); return d; }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ u64 add2(u64 a, u64 b) { u64 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+
 // ---- exact complex helpers (std::complex<float> as gcc evaluates it, no contraction) --------
 __device__ __forceinline__ float2 cmul_exact(float2 a, float2 b) {   // msd.hpp:134
     return make_float2(__fsub_rn(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y)),

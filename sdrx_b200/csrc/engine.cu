@@ -21,7 +21,7 @@ using namespace sdrx;
 namespace {
 
 constexpr int kNBuf = 2;          // ping-pong depth of raw input
-constexpr int kNOut = 4;          // ring of output sets: a streaming caller may run up to kNOut-1 blocks ahead of the results it reads
+constexpr int kNOut = 6;          // ring of output sets: a streaming caller may run up to kNOut-1 blocks ahead of the results it reads
 constexpr int kPwrPartials = 296;     // power CTAs of k_prep: two per SM
 constexpr uint32_t kStateMagic = 0x58524453u;  // "SDRX"
 
@@ -471,7 +471,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             size_t row = (size_t)(e->H[S - 1] - 1) + (size_t)kChunk * e->m[S - 1];
             e->tail_fusable = row * sizeof(float2) <= 100 * 1024 && (e->H[S - 1] - 1) / 2 + 1 <= kTailMaxHalf;
             if (e->tail_fusable)
-                CU(cudaFuncSetAttribute(k_chan_head<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                CU(cudaFuncSetAttribute(k_chan_head<kHeadFir>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)(sizeof(float2) * row)));
         }
     }
@@ -482,8 +482,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         const int mx = (int)cudaSharedmemCarveoutMaxShared;
         CU(cudaFuncSetAttribute(k_chan_recur, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
         CU(cudaFuncSetAttribute(k_mix_fir2_pcm, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
-        CU(cudaFuncSetAttribute(k_chan_head<true>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
-        CU(cudaFuncSetAttribute(k_chan_head<false>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_chan_head<kHeadFir>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_chan_head<kHeadDetect>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
         CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_U8>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
         CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_S16>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
         CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_F32>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
@@ -652,23 +652,23 @@ int launch_prep(sdrx_engine *e, cudaStream_t st, int fmt, uint8_t *buf, const ui
     return SDRX_OK;
 }
 
-// Boundary B on the chunk in o.ch_iq (output set `idx`).  The head kernel (last MSD stage when `fused`, squelch
-// detector) runs on the main stream; the recurrences and the mix follow on the side stream, where they overlap
-// the next block's channel bank.
+// Boundary B on the chunk in o.ch_iq (output set `idx`).  Only the last MSD stage (when `fused`) runs on the main
+// stream; the squelch detector, the recurrences and the mix follow on the side stream, where their CTAs sit next
+// to the next block's channel-bank CTAs (none of them needs more than the 9 KB of shared memory the bank leaves).
 int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr) {
     OutSet &o = e->out[idx];
     const TailSnap snap{o.sql, o.agc_gain, o.lf_gain};
     if (fused) {
         const size_t dyn = sizeof(float2) * (size_t)(fused->H - 1 + fused->n_in);
-        k_chan_head<true><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
-                                                                  o.snr, e->d_gate[idx], snap);
-    } else {
-        k_chan_head<false><<<e->C, kHeadThreads, 0, e->s_main>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
-                                                                 e->d_sql_level, o.snr, e->d_gate[idx], snap);
+        k_chan_head<kHeadFir><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
+                                                                      o.snr, e->d_gate[idx], snap);
+        ++e->launches;
     }
     CU(cudaGetLastError());
     CU(cudaEventRecord(e->ev_head_done, e->s_main));
     CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
+    k_chan_head<kHeadDetect><<<e->C, kHeadThreads, 0, e->s_side>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
+                                                                   e->d_sql_level, o.snr, e->d_gate[idx], snap);
     k_chan_recur<<<div_up(e->C, kRecurCh), 32, 0, e->s_side>>>(o.ch_iq, e->chiq_stride, e->st, e->d_gate[idx], e->tb, e->agc, e->lf, e->lf_active,
                                              o.audio, snap, e->C);
     const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad;
@@ -895,7 +895,7 @@ extern "C" int sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_output
 }
 
 extern "C" int sdrx_engine_wait_outputs(sdrx_engine *e, int back) {
-    if (!e || back < 0 || back > kNOut - 2) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) .. 2");
+    if (!e || back < 0 || back > kNOut - 2) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) .. 4");
     if (e->blocks < (uint64_t)back + 1) return fail(SDRX_ERR_STATE, "no such block");
     DevGuard g(e->dev);
     const int idx = (int)((e->blocks - 1 - back) % kNOut);

@@ -16,7 +16,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --c
     python bench.py --steps 2 --warmup 3 --no-cpu > $OUT/ncu_launches.log 2>&1; echo "ncu launches rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_bank_fast -s 3 -c 1 -o $OUT/bank_full -f \
     python bench.py --steps 2 --warmup 3 --no-cpu > $OUT/ncu_full.log 2>&1; echo "ncu full rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_chan_head -s 3 -c 1 -o $OUT/head_full -f \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_chan_head -s 6 -c 1 -o $OUT/head_full -f \
     python bench.py --steps 2 --warmup 3 --no-cpu > $OUT/ncu_full_demod.log 2>&1; echo "ncu full demod rc=$?"
 fi
 tail -5 $OUT/pytest_gpu.log
