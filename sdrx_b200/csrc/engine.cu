@@ -90,7 +90,9 @@ struct sdrx_engine {
     size_t parts_cap = 0;
     FastBank fast;                        // specialised channel bank (bank_fast.cuh)
     bool use_fast = false;
-    bool tail_fusable = false;            // last stage inside the per-channel head kernel (k_chan_head<true>)
+    bool tail_fusable = false;            // last stage as one per-channel kernel fed by the bank's rows + tail fix-ups
+    bool tail_fast = false;               // ... in its specialised form (67 taps, decimate by 5: k_chan_fir_fast)
+    FirTaps<67> tail_taps{};
     bool ftfir = false;                   // --ftfir: stage 0 is the frequency-translating FIR (msd.hpp:104-131)
     int ft_sets = 0;                      // coefficient sets, N / m[0] (msd.hpp:196)
     float2 *d_hk = nullptr;               // [ft_sets * H0][Cpad]
@@ -473,6 +475,15 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             if (e->tail_fusable)
                 CU(cudaFuncSetAttribute(k_chan_head<kHeadFir>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         (int)(sizeof(float2) * row)));
+            e->tail_fast = e->tail_fusable && e->H[S - 1] == 67 && e->m[S - 1] == 5 && e->chiq_stride % 2 == 0;
+            if (e->tail_fast) {
+                const float *h = e->taps.data() + e->tap_off[S - 1];
+                for (int i = 0; i < 67; ++i) e->tail_taps.h[i] = make_float2(h[i], h[i]);
+                CU(cudaFuncSetAttribute(k_chan_fir_fast<67, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)fir_fast_smem(67, 5, kChunk * 5)));
+                CU(cudaFuncSetAttribute(k_chan_fir_fast<67, 5>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        (int)cudaSharedmemCarveoutMaxShared));
+            }
         }
     }
     // Every kernel of the block asks for the same (maximum) shared-memory carve-out: an SM only co-schedules CTAs of
@@ -660,8 +671,12 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
     const TailSnap snap{o.sql, o.agc_gain, o.lf_gain};
     if (fused) {
         const size_t dyn = sizeof(float2) * (size_t)(fused->H - 1 + fused->n_in);
-        k_chan_head<kHeadFir><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
-                                                                      o.snr, e->d_gate[idx], snap);
+        if (e->tail_fast && fused->n_in == kChunk * 5 && fused->first >= 0 && fused->first < 5)
+            k_chan_fir_fast<67, 5><<<e->C, kHeadThreads, fir_fast_smem(67, 5, fused->n_in), e->s_main>>>(*fused, e->tail_taps, o.ch_iq,
+                                                                                                        e->chiq_stride);
+        else
+            k_chan_head<kHeadFir><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
+                                                                          o.snr, e->d_gate[idx], snap);
         ++e->launches;
     }
     CU(cudaGetLastError());
