@@ -203,6 +203,35 @@ void sdrx_fir_destroy(sdrx_fir *f);
 int  sdrx_fir_set_gain(sdrx_fir *f, float gain_db);                                     /* fir.hpp:51  */
 int  sdrx_fir_filter(sdrx_fir *f, const float *in, unsigned in_len, float *out);        /* fir.hpp:34  */
 
+/* ---- Airspy real -> IQ front end: what libairspy does on the host for
+ * AIRSPY_SAMPLE_FLOAT32_IQ -- unpack_samples (airspy.c:323-338), convert_samples_float (:311-321) and
+ * iqconverter_float_process (iqconverter_float.c:504-508: remove_dc, translate_fs_4, half-band FIR, delay) --
+ * so that the wire format can be the ADC's own 12-bit REAL samples at twice the IQ rate. ---- */
+typedef struct sdrx_airspy_fe sdrx_airspy_fe;
+#define SDRX_FE_PACKED12 0x1u   /* airspy_set_packing(1): 8 samples per three 32-bit words (airspy.c:323-338); else one
+                                   sample per uint16 (0..4095)                                                     */
+#define SDRX_FE_EXACT_DC 0x2u   /* run remove_dc (one recurrence over the whole stream) on a single thread: bit-exact by
+                                   construction, ~4 ms per 640 000 samples; the default is segment-parallel          */
+/* hb_kernel: HB_KERNEL_FLOAT (libairspy filters.h:28-30, 47 taps); max_samples: most REAL samples per call (multiple of 8) */
+int   sdrx_airspy_fe_create(int device, const float *hb_kernel, int hb_len, unsigned max_samples, unsigned flags,
+                            sdrx_airspy_fe **out);                                        /* iqconverter_float_create */
+void  sdrx_airspy_fe_destroy(sdrx_airspy_fe *f);                                          /* iqconverter_float_free   */
+int   sdrx_airspy_fe_reset(sdrx_airspy_fe *f);                                            /* iqconverter_float_reset  */
+/* One libairspy buffer: n_samples REAL samples in (host pointer, wire format per flags; multiple of 8), n_samples/2
+ * IQ pairs out.  Queued on the front end's stream; iq_host (may be NULL) receives the pairs and makes the call wait. */
+int   sdrx_airspy_fe_process(sdrx_airspy_fe *f, const void *raw, unsigned n_samples, float *iq_host);
+int   sdrx_airspy_fe_process_device(sdrx_airspy_fe *f, const void *d_raw, unsigned n_samples);
+/* Device pointer to the last call's IQ pairs (float re,im): feed it to sdrx_engine_push_block_device(SDRX_FMT_F32)
+ * after sdrx_engine_wait_event(e, sdrx_airspy_fe_done_event(f)) -- no host synchronisation in between.            */
+const float *sdrx_airspy_fe_output(sdrx_airspy_fe *f, unsigned *n_pairs);
+void *sdrx_airspy_fe_done_event(sdrx_airspy_fe *f);    /* cudaEvent_t */
+void *sdrx_airspy_fe_stream(sdrx_airspy_fe *f);        /* cudaStream_t */
+int   sdrx_airspy_fe_sync(sdrx_airspy_fe *f);
+int   sdrx_airspy_fe_avg(sdrx_airspy_fe *f, float *avg);                                  /* cnv->avg */
+uint64_t sdrx_airspy_fe_launch_count(sdrx_airspy_fe *f);
+/* Orders the engine's ingest stream behind a CUDA event recorded by another producer (e.g. the front end above). */
+int   sdrx_engine_wait_event(sdrx_engine *e, void *cuda_event);
+
 #ifdef __cplusplus
 }
 #endif

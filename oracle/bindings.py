@@ -679,3 +679,109 @@ def ref_tables(rate: int, backend: str = "ref") -> dict:
     return dict(N=N, z=z, stages=stages, fir2_taps=ref_table("coeff_bp4am_channel", backend),
                 passband_shape=ref_table("passband_shape", backend), ramp_up=ref_table("ramp_up", backend),
                 ramp_down=ref_table("ramp_down", backend))
+
+
+# ----------------------------------------------------------------------------- Airspy real -> IQ front end
+# (SURVEY.md 8f rank 1).  "oracle": oracle/airspy_fe_oracle.c inside liboracle.so; "ref": the reference's own
+# libairspy iqconverter_float.c + filters.h compiled into oracle/_ref/libairspy_ref.so.
+_AIRSPY_REF = os.path.join(HERE, "_ref", "libairspy_ref.so")
+_AIRSPY_LIB = {}
+
+
+def airspy_ref_available() -> bool:
+    return os.path.exists(_AIRSPY_REF)
+
+
+def _airspy_ref():
+    if "ref" not in _AIRSPY_LIB:
+        if not os.path.exists(_AIRSPY_REF) and os.path.isdir(REF_SRC):
+            build()
+        lib = C.CDLL(_AIRSPY_REF)
+        lib.sdrxref_hb_kernel_len.restype = C.c_int
+        lib.sdrxref_hb_kernel.argtypes = [c_float_p]
+        lib.sdrxref_iqconv_create.restype = C.c_void_p
+        lib.sdrxref_iqconv_free.argtypes = [C.c_void_p]
+        lib.sdrxref_iqconv_reset.argtypes = [C.c_void_p]
+        lib.sdrxref_iqconv_process.argtypes = [C.c_void_p, c_float_p, C.c_int]
+        _AIRSPY_LIB["ref"] = lib
+    return _AIRSPY_LIB["ref"]
+
+
+def _airspy_oracle():
+    if "oracle" not in _AIRSPY_LIB:
+        lib = load_backend("oracle").lib
+        lib.sdrxo_airspy_fe_create.restype = C.c_void_p
+        lib.sdrxo_airspy_fe_create.argtypes = [c_float_p, C.c_int]
+        lib.sdrxo_airspy_fe_destroy.argtypes = [C.c_void_p]
+        lib.sdrxo_airspy_fe_reset.argtypes = [C.c_void_p]
+        lib.sdrxo_airspy_unpack12.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        lib.sdrxo_airspy_fe_process.argtypes = [C.c_void_p, C.c_void_p, C.c_int, c_float_p]
+        lib.sdrxo_airspy_fe_avg.restype = C.c_float
+        lib.sdrxo_airspy_fe_avg.argtypes = [C.c_void_p]
+        _AIRSPY_LIB["oracle"] = lib
+    return _AIRSPY_LIB["oracle"]
+
+
+def ref_hb_kernel() -> np.ndarray:
+    """HB_KERNEL_FLOAT (libairspy filters.h:28-30) out of the compiled reference header."""
+    lib = _airspy_ref()
+    out = np.empty(lib.sdrxref_hb_kernel_len(), np.float32)
+    lib.sdrxref_hb_kernel(_fp(out))
+    return out
+
+
+def airspy_pack12(samples: np.ndarray) -> np.ndarray:
+    """Inverse of airspy.c:323-338 unpack_samples: 8 twelve-bit samples -> three uint32 (test input maker)."""
+    s = np.asarray(samples, np.uint32).reshape(-1, 8)
+    a = (s[:, 0] << 20) | (s[:, 1] << 8) | (s[:, 2] >> 4)
+    b = ((s[:, 2] & 0xf) << 28) | (s[:, 3] << 16) | (s[:, 4] << 4) | (s[:, 5] >> 8)
+    c = ((s[:, 5] & 0xff) << 24) | (s[:, 6] << 12) | s[:, 7]
+    return np.stack([a, b, c], axis=1).astype(np.uint32).ravel()
+
+
+class OracleAirspyFE:
+    """real uint16 ADC samples (0..4095) -> complex64 IQ at half the rate, state carried between calls."""
+
+    def __init__(self, hb_kernel: np.ndarray, backend: str = "oracle"):
+        self.backend = backend
+        self.hb = _f32(hb_kernel)
+        if backend == "ref":
+            self.lib = _airspy_ref()
+            assert np.array_equal(self.hb, ref_hb_kernel())
+            self.h = self.lib.sdrxref_iqconv_create()
+        else:
+            self.lib = _airspy_oracle()
+            self.h = self.lib.sdrxo_airspy_fe_create(_fp(self.hb), int(self.hb.size))
+
+    def unpack12(self, packed: np.ndarray) -> np.ndarray:
+        packed = np.ascontiguousarray(packed, np.uint32)
+        n = packed.size // 3 * 8
+        out = np.empty(n, np.uint16)
+        _airspy_oracle().sdrxo_airspy_unpack12(packed.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p), n)
+        return out
+
+    def process(self, raw_u16: np.ndarray) -> np.ndarray:
+        raw = np.ascontiguousarray(raw_u16, np.uint16)
+        assert raw.size % 4 == 0
+        if self.backend == "ref":
+            # airspy.c:311-321 convert_samples_float, then the converter in place
+            buf = ((raw.astype(np.int32) - 2048).astype(np.float32) * np.float32(1.0 / 2048.0)).astype(np.float32)
+            self.lib.sdrxref_iqconv_process(self.h, _fp(buf), int(buf.size))
+            return buf[:raw.size].view(np.complex64)[:raw.size // 2].copy()
+        out = np.empty(raw.size // 2, np.complex64)
+        self.lib.sdrxo_airspy_fe_process(self.h, raw.ctypes.data_as(C.c_void_p), int(raw.size), _cf(out))
+        return out
+
+    def reset(self):
+        (self.lib.sdrxref_iqconv_reset if self.backend == "ref" else self.lib.sdrxo_airspy_fe_reset)(self.h)
+
+    def close(self):
+        if self.h:
+            (self.lib.sdrxref_iqconv_free if self.backend == "ref" else self.lib.sdrxo_airspy_fe_destroy)(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -7,3 +7,4 @@ from ._lib import FMT_F32, FMT_S16, FMT_U8, SdrxError  # noqa: F401
 from .config import ChannelPlan, rate_config  # noqa: F401
 from .engine import BlockOut, Engine, PinnedBuffer  # noqa: F401
 from .source import Carrier, FileSource, SyntheticSource  # noqa: F401
+from .airspy_fe import AirspyFrontEnd  # noqa: F401,E402

@@ -96,7 +96,20 @@ PROTOTYPES = [
     ("sdrx_fir_destroy", None, [C.c_void_p]),
     ("sdrx_fir_set_gain", C.c_int, [C.c_void_p, C.c_float]),
     ("sdrx_fir_filter", C.c_int, [C.c_void_p, c_float_p, C.c_uint, c_float_p]),
+    ("sdrx_airspy_fe_create", C.c_int, [C.c_int, c_float_p, C.c_int, C.c_uint, C.c_uint, C.POINTER(C.c_void_p)]),
+    ("sdrx_airspy_fe_destroy", None, [C.c_void_p]),
+    ("sdrx_airspy_fe_reset", C.c_int, [C.c_void_p]),
+    ("sdrx_airspy_fe_process", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint, c_float_p]),
+    ("sdrx_airspy_fe_process_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint]),
+    ("sdrx_airspy_fe_output", C.c_void_p, [C.c_void_p, C.POINTER(C.c_uint)]),
+    ("sdrx_airspy_fe_done_event", C.c_void_p, [C.c_void_p]),
+    ("sdrx_airspy_fe_stream", C.c_void_p, [C.c_void_p]),
+    ("sdrx_airspy_fe_sync", C.c_int, [C.c_void_p]),
+    ("sdrx_airspy_fe_avg", C.c_int, [C.c_void_p, c_float_p]),
+    ("sdrx_airspy_fe_launch_count", C.c_uint64, [C.c_void_p]),
+    ("sdrx_engine_wait_event", C.c_int, [C.c_void_p, C.c_void_p]),
 ]
+FE_PACKED12, FE_EXACT_DC = 0x1, 0x2
 
 _LIB = None
 

@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsdrx_b200.so")
-SOURCES = ["engine.cu", "objects.cu"]
+SOURCES = ["engine.cu", "objects.cu", "airspy_fe.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "-Xcompiler", "-fPIC,-O2", "-shared", "-Xptxas", "-v",

@@ -1,0 +1,340 @@
+// sdrx_b200 -- Airspy real -> IQ front end on the GPU: the step libairspy runs on the host
+// in front of the sdrx hot path for AIRSPY_SAMPLE_FLOAT32_IQ (airspy.c:393-396).  Moving it here lets the wire format
+// be the ADC's own 12-bit samples (2 B, or 1.5 B packed, per REAL sample at 20 MS/s = 3-4 B per IQ sample instead
+// of 8) and hands the channel bank a device-resident float IQ block.
+//
+// Restated (paths under libairspy/libairspy/src of the reference):
+//   airspy.c:323-338  unpack_samples          -> load_adc8<true>
+//   airspy.c:311-321  convert_samples_float   -> (raw - 2048) * (1/2048)
+//   iqconverter_float.c:455-468 remove_dc     -> k_fe_dc: s -= avg; avg += 0.01f * s over ALL samples in order
+//   iqconverter_float.c:470-502 translate_fs_4, :191-230 fir_interleaved_24, :430-451 delay_interleaved -> k_fe_iq
+//
+// remove_dc is one sequential recurrence over the whole stream.  It is a contraction (pole 0.99), so a trajectory
+// started kFeWarm = 2048 samples early from any nearby value has forgotten its start (0.99^2048 = 1e-9) and has, in
+// practice, snapped onto the bit-exact sequence: k_fe_dc cuts the block into 128-sample segments, one thread each,
+// every thread warming up on the 2048 samples before its segment (carried raw history across blocks).  Segment 0
+// continues from the carried avg itself.  SDRX_FE_EXACT_DC runs the recurrence on one thread instead (tests).
+// Everything after remove_dc is a pure function of a short window and is evaluated in the reference's order,
+// un-contracted: bit-exact given bit-exact inputs.
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "common.cuh"
+#include "host_common.h"
+
+using namespace sdrx;
+
+namespace {
+
+constexpr int kFeSeg = 128;          // real samples per thread of k_fe_dc
+constexpr int kFeWarm = 2048;        // warm-up samples in front of a segment
+constexpr int kFeEvenHist = 24;      // >= len - 1 = 23 rotated even samples carried between blocks
+constexpr int kFeOddHist = 12;       // len / 2 delayed odd samples
+constexpr int kFeMaxLen = 64;
+
+// eight consecutive ADC samples starting at index `idx` (a multiple of 8) of a buffer in wire format
+template <bool PACKED>
+__device__ __forceinline__ void load_adc8(const void *__restrict__ raw, long idx, int (&v)[8]) {
+    if constexpr (PACKED) {                      // airspy.c:323-338
+        const uint32_t *in = reinterpret_cast<const uint32_t *>(raw) + (idx >> 3) * 3;
+        const uint32_t a = __ldg(in), b = __ldg(in + 1), c = __ldg(in + 2);
+        v[0] = (a >> 20) & 0xfff;
+        v[1] = (a >> 8) & 0xfff;
+        v[2] = ((a & 0xff) << 4) | ((b >> 28) & 0xf);
+        v[3] = (b >> 16) & 0xfff;
+        v[4] = (b >> 4) & 0xfff;
+        v[5] = ((b & 0xf) << 8) | ((c >> 24) & 0xff);
+        v[6] = (c >> 12) & 0xfff;
+        v[7] = c & 0xfff;
+    } else {
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const uint16_t *>(raw) + idx));
+        v[0] = q.x & 0xffff; v[1] = q.x >> 16; v[2] = q.y & 0xffff; v[3] = q.y >> 16;
+        v[4] = q.z & 0xffff; v[5] = q.z >> 16; v[6] = q.w & 0xffff; v[7] = q.w >> 16;
+    }
+}
+
+__device__ __forceinline__ float adc_to_float(int v) {            // airspy.c:311-321, SAMPLE_SCALE = 1/2048
+    return __fmul_rn((float)(v - 2048), 1.0f / 2048.0f);
+}
+
+// One remove_dc step (iqconverter_float.c:461-464).
+__device__ __forceinline__ float dc_step(float x, float &avg) {
+    const float s = __fsub_rn(x, avg);
+    avg = __fadd_rn(avg, __fmul_rn(0.01f, s));
+    return s;
+}
+
+// remove_dc + translate_fs_4's sign / hbc pattern, segment-parallel.
+//   raw        this block, wire format, n samples (n % 8 == 0)
+//   hist       the kFeWarm unpacked samples (uint16) in front of the block
+//   known      how many of them belong to the stream (the rest lie before its start)
+//   avg_io     [0] avg at the block start (in), [1] avg at the block end (out)
+//   ev / od    rotated even / odd samples of the block, behind their carried history prefixes
+template <bool PACKED>
+static __global__ void __launch_bounds__(128)
+k_fe_dc(const void *__restrict__ raw, const uint16_t *__restrict__ hist, int known, int n, float *__restrict__ avg_io,
+        float hbc, float *__restrict__ ev, float *__restrict__ od, int exact) {
+    const int seg = blockIdx.x * blockDim.x + threadIdx.x;
+    const long s0 = exact ? 0 : (long)seg * kFeSeg;
+    if (s0 >= n || (exact && seg != 0)) return;
+    const long s1 = exact ? n : (s0 + kFeSeg < n ? s0 + kFeSeg : n);
+    float avg = avg_io[0];
+    if (s0 > 0) {
+        long w0 = s0 - kFeWarm;
+        if (w0 < -(long)known) { w0 = -(long)known; avg = known < kFeWarm ? 0.0f : avg; }   // the stream starts inside the window: exact from avg = 0
+        for (long i = w0; i < s0; i += 8) {
+            int v[8];
+            if (i < 0) {
+                const uint4 q = __ldg(reinterpret_cast<const uint4 *>(hist + kFeWarm + i));
+                v[0] = q.x & 0xffff; v[1] = q.x >> 16; v[2] = q.y & 0xffff; v[3] = q.y >> 16;
+                v[4] = q.z & 0xffff; v[5] = q.z >> 16; v[6] = q.w & 0xffff; v[7] = q.w >> 16;
+            } else {
+                load_adc8<PACKED>(raw, i, v);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) dc_step(adc_to_float(v[j]), avg);
+        }
+    }
+    for (long i = s0; i < s1; i += 8) {
+        int v[8];
+        load_adc8<PACKED>(raw, i, v);
+        float s[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] = dc_step(adc_to_float(v[j]), avg);
+        // translate_fs_4 (iqconverter_float.c:489-498): [-s0, -s1*hbc, s2, s3*hbc] per group of four
+        const long p = i >> 1;
+        float4 e, o;
+        e.x = -s[0];               o.x = __fmul_rn(-s[1], hbc);
+        e.y = s[2];                o.y = __fmul_rn(s[3], hbc);
+        e.z = -s[4];               o.z = __fmul_rn(-s[5], hbc);
+        e.w = s[6];                o.w = __fmul_rn(s[7], hbc);
+        *reinterpret_cast<float4 *>(ev + kFeEvenHist + p) = e;
+        *reinterpret_cast<float4 *>(od + kFeOddHist + p) = o;
+    }
+    if (s1 == n) avg_io[1] = avg;
+}
+
+// Half-band FIR on the even samples (fir_interleaved_24's order: k[0]*(q0+q23) + k[1]*(q1+q22) + ... left to right),
+// the odd samples through their 12-deep delay line.  One thread per IQ pair.
+static __global__ void __launch_bounds__(256)
+k_fe_iq(const float *__restrict__ ev, const float *__restrict__ od, int npair, const float *__restrict__ k, int len,
+        float2 *__restrict__ out) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npair) return;
+    const int half = len >> 1;
+    const float *q = ev + kFeEvenHist + p;
+    float acc = __fmul_rn(__ldg(k), __fadd_rn(q[0], q[-(len - 1)]));
+    for (int i = 1; i < half; ++i) acc = __fadd_rn(acc, __fmul_rn(__ldg(k + i), __fadd_rn(q[-i], q[-(len - 1 - i)])));
+    out[p] = make_float2(acc, od[kFeOddHist + p - half]);
+}
+
+// Block-to-block carries: the last kFeWarm raw samples (unpacked) and the even / odd history prefixes.
+template <bool PACKED>
+static __global__ void __launch_bounds__(256)
+k_fe_carry(const void *__restrict__ raw, int n, const uint16_t *__restrict__ hist_in, uint16_t *__restrict__ hist_out,
+           float *__restrict__ ev, float *__restrict__ od, float *__restrict__ avg_io) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;          // group of 8 history samples
+    if (g < kFeWarm / 8) {
+        const long src = (long)n - kFeWarm + 8L * g;              // block-relative index of the group
+        int v[8];
+        if (src >= 0) load_adc8<PACKED>(raw, src, v);
+        else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = hist_in[kFeWarm + src + j];
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) hist_out[8 * g + j] = (uint16_t)v[j];
+    }
+    // the even / odd prefixes slide in place: every read below happens before the barrier, every write after
+    // (one CTA does it: kFeEvenHist + kFeOddHist <= 256)
+    if (blockIdx.x == 0) {
+        const int npair = n >> 1;
+        float keep = 0.0f;
+        const int t = threadIdx.x;
+        if (t < kFeEvenHist) keep = ev[npair + t];
+        else if (t < kFeEvenHist + kFeOddHist) keep = od[npair + (t - kFeEvenHist)];
+        __syncthreads();
+        if (t < kFeEvenHist) ev[t] = keep;
+        else if (t < kFeEvenHist + kFeOddHist) od[t - kFeEvenHist] = keep;
+        if (t == 0) avg_io[0] = avg_io[1];
+    }
+}
+
+}  // namespace
+
+struct sdrx_airspy_fe {
+    int dev = 0;
+    unsigned flags = 0;
+    unsigned cap = 0;                    // real samples per call at most
+    int len = 0;                         // hb_len / 2 + 1
+    float hbc = 0.0f;
+    cudaStream_t st = nullptr;
+    cudaEvent_t ev_done = nullptr;
+    uint8_t *d_raw = nullptr;            // wire-format staging of one call
+    uint8_t *h_stage = nullptr;          // pinned staging for pageable callers
+    uint16_t *d_hist[2] = {nullptr, nullptr};
+    float *d_ev = nullptr, *d_od = nullptr, *d_k = nullptr, *d_avg = nullptr;
+    float2 *d_iq = nullptr;
+    uint64_t total = 0;                  // real samples seen so far
+    uint64_t calls = 0;
+    unsigned last_pairs = 0;
+    uint64_t launches = 0;
+};
+
+extern "C" void sdrx_airspy_fe_destroy(sdrx_airspy_fe *f) {
+    if (!f) return;
+    DevGuard g(f->dev);
+    if (f->st) cudaStreamSynchronize(f->st);
+    cudaFree(f->d_raw); cudaFree(f->d_hist[0]); cudaFree(f->d_hist[1]); cudaFree(f->d_ev); cudaFree(f->d_od);
+    cudaFree(f->d_k); cudaFree(f->d_avg); cudaFree(f->d_iq);
+    if (f->h_stage) cudaFreeHost(f->h_stage);
+    if (f->ev_done) cudaEventDestroy(f->ev_done);
+    if (f->st) cudaStreamDestroy(f->st);
+    delete f;
+}
+
+extern "C" int sdrx_airspy_fe_reset(sdrx_airspy_fe *f) {
+    if (!f) return fail(SDRX_ERR_ARG, "null front end");
+    DevGuard g(f->dev);
+    CU(cudaStreamSynchronize(f->st));
+    CU(cudaMemsetAsync(f->d_hist[0], 0, sizeof(uint16_t) * kFeWarm, f->st));
+    CU(cudaMemsetAsync(f->d_hist[1], 0, sizeof(uint16_t) * kFeWarm, f->st));
+    CU(cudaMemsetAsync(f->d_ev, 0, sizeof(float) * (kFeEvenHist + f->cap / 2 + 8), f->st));     // iqconverter_float_reset
+    CU(cudaMemsetAsync(f->d_od, 0, sizeof(float) * (kFeOddHist + f->cap / 2 + 8), f->st));
+    CU(cudaMemsetAsync(f->d_avg, 0, sizeof(float) * 2, f->st));
+    CU(cudaStreamSynchronize(f->st));
+    f->total = 0;
+    f->calls = 0;
+    f->last_pairs = 0;
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_airspy_fe_create(int device, const float *hb_kernel, int hb_len, unsigned max_samples, unsigned flags,
+                                     sdrx_airspy_fe **out) {
+    if (!out || !hb_kernel) return fail(SDRX_ERR_ARG, "null argument");
+    *out = nullptr;
+    if (hb_len < 3 || (hb_len & 1) == 0) return fail(SDRX_ERR_ARG, "half-band kernel length must be odd");
+    const int len = hb_len / 2 + 1;
+    if ((len & 1) || len - 1 > kFeEvenHist || len / 2 > kFeOddHist || len > kFeMaxLen)
+        return fail(SDRX_ERR_UNSUPPORTED, "half-band kernels other than libairspy's 47-tap family (len/2+1 even, <= 24) are not implemented");
+    if (max_samples < 8 || max_samples % 8) return fail(SDRX_ERR_ARG, "max_samples must be a positive multiple of 8");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+        cudaGetLastError();
+        return fail(SDRX_ERR_CUDA, "no CUDA device: sdrx_b200 has no CPU path");
+    }
+    if (device < 0 || device >= ndev) return fail(SDRX_ERR_ARG, "device ordinal out of range");
+    DevGuard g(device);
+    if (!g.ok) return fail(SDRX_ERR_CUDA, "cudaSetDevice failed");
+    sdrx_airspy_fe *f = new sdrx_airspy_fe();
+    f->dev = device; f->flags = flags; f->cap = max_samples; f->len = len;
+    f->hbc = hb_kernel[hb_len / 2];                              // iqconverter_float.c:81
+    std::vector<float> k((size_t)len);
+    for (int i = 0, j = 0; i < len; ++i, j += 2) k[i] = hb_kernel[j];   // iqconverter_float.c:91-94
+    auto bail = [&](const char *what) { std::string keep = what; sdrx_airspy_fe_destroy(f); return fail(SDRX_ERR_CUDA, keep.c_str()); };
+    if (cudaStreamCreateWithFlags(&f->st, cudaStreamNonBlocking) != cudaSuccess) return bail("cudaStreamCreate");
+    if (cudaEventCreateWithFlags(&f->ev_done, cudaEventDisableTiming) != cudaSuccess) return bail("cudaEventCreate");
+    const size_t pairs = max_samples / 2;
+    if (cudaMalloc((void **)&f->d_raw, (size_t)max_samples * 2 + 64) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_hist[0], sizeof(uint16_t) * kFeWarm) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_hist[1], sizeof(uint16_t) * kFeWarm) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_ev, sizeof(float) * (kFeEvenHist + pairs + 8)) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_od, sizeof(float) * (kFeOddHist + pairs + 8)) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_k, sizeof(float) * len) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_avg, sizeof(float) * 2) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_iq, sizeof(float2) * pairs) != cudaSuccess)
+        return bail("cudaMalloc failed");
+    if (cudaMemcpy(f->d_k, k.data(), sizeof(float) * len, cudaMemcpyHostToDevice) != cudaSuccess) return bail("cudaMemcpy failed");
+    int rc = sdrx_airspy_fe_reset(f);
+    if (rc) { sdrx_airspy_fe_destroy(f); return rc; }
+    *out = f;
+    return SDRX_OK;
+}
+
+namespace {
+
+int fe_run(sdrx_airspy_fe *f, const void *d_raw, unsigned n) {
+    const bool packed = (f->flags & SDRX_FE_PACKED12) != 0;
+    const int exact = (f->flags & SDRX_FE_EXACT_DC) ? 1 : 0;
+    const int cur = (int)(f->calls & 1);
+    const int known = (int)std::min<uint64_t>(f->total, (uint64_t)kFeWarm);
+    const int segs = exact ? 1 : div_up(n, kFeSeg);
+    const int npair = (int)(n / 2);
+    if (packed) k_fe_dc<true><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_hist[cur], known, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
+    else        k_fe_dc<false><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_hist[cur], known, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
+    k_fe_iq<<<div_up(npair, 256), 256, 0, f->st>>>(f->d_ev, f->d_od, npair, f->d_k, f->len, f->d_iq);
+    if (packed) k_fe_carry<true><<<div_up(kFeWarm / 8, 256), 256, 0, f->st>>>(d_raw, (int)n, f->d_hist[cur], f->d_hist[cur ^ 1], f->d_ev, f->d_od, f->d_avg);
+    else        k_fe_carry<false><<<div_up(kFeWarm / 8, 256), 256, 0, f->st>>>(d_raw, (int)n, f->d_hist[cur], f->d_hist[cur ^ 1], f->d_ev, f->d_od, f->d_avg);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(f->ev_done, f->st));
+    f->launches += 3;
+    f->total += n;
+    ++f->calls;
+    f->last_pairs = (unsigned)npair;
+    return SDRX_OK;
+}
+
+int fe_check(sdrx_airspy_fe *f, const void *raw, unsigned n) {
+    if (!f || (!raw && n)) return fail(SDRX_ERR_ARG, "null argument");
+    if (n == 0 || n % 8) return fail(SDRX_ERR_ARG, "n_samples must be a positive multiple of 8 (libairspy buffers are)");
+    if (n > f->cap) return fail(SDRX_ERR_ARG, "more samples than max_samples");
+    return SDRX_OK;
+}
+
+}  // namespace
+
+extern "C" int sdrx_airspy_fe_process(sdrx_airspy_fe *f, const void *raw, unsigned n_samples, float *iq_host) {
+    int rc = fe_check(f, raw, n_samples);
+    if (rc) return rc;
+    DevGuard g(f->dev);
+    const size_t bytes = (f->flags & SDRX_FE_PACKED12) ? (size_t)n_samples / 8 * 12 : (size_t)n_samples * 2;
+    cudaPointerAttributes attr{};
+    const bool pinned = cudaPointerGetAttributes(&attr, raw) == cudaSuccess &&
+                        (attr.type == cudaMemoryTypeHost || attr.type == cudaMemoryTypeManaged);
+    cudaGetLastError();
+    const void *from = raw;
+    if (!pinned) {
+        if (!f->h_stage) CU(cudaMallocHost((void **)&f->h_stage, (size_t)f->cap * 2));
+        CU(cudaStreamSynchronize(f->st));           // the previous call's copy out of the staging buffer has run
+        memcpy(f->h_stage, raw, bytes);
+        from = f->h_stage;
+    }
+    CU(cudaMemcpyAsync(f->d_raw, from, bytes, cudaMemcpyHostToDevice, f->st));
+    rc = fe_run(f, f->d_raw, n_samples);
+    if (rc) return rc;
+    if (iq_host) {
+        CU(cudaMemcpyAsync(iq_host, f->d_iq, sizeof(float2) * (size_t)(n_samples / 2), cudaMemcpyDeviceToHost, f->st));
+        CU(cudaStreamSynchronize(f->st));
+    }
+    return SDRX_OK;
+}
+
+extern "C" int sdrx_airspy_fe_process_device(sdrx_airspy_fe *f, const void *d_raw, unsigned n_samples) {
+    int rc = fe_check(f, d_raw, n_samples);
+    if (rc) return rc;
+    DevGuard g(f->dev);
+    return fe_run(f, d_raw, n_samples);
+}
+
+extern "C" const float *sdrx_airspy_fe_output(sdrx_airspy_fe *f, unsigned *n_pairs) {
+    if (!f) return nullptr;
+    if (n_pairs) *n_pairs = f->last_pairs;
+    return reinterpret_cast<const float *>(f->d_iq);
+}
+extern "C" void *sdrx_airspy_fe_done_event(sdrx_airspy_fe *f) { return f ? (void *)f->ev_done : nullptr; }
+extern "C" void *sdrx_airspy_fe_stream(sdrx_airspy_fe *f) { return f ? (void *)f->st : nullptr; }
+extern "C" uint64_t sdrx_airspy_fe_launch_count(sdrx_airspy_fe *f) { return f ? f->launches : 0; }
+extern "C" int sdrx_airspy_fe_sync(sdrx_airspy_fe *f) {
+    if (!f) return fail(SDRX_ERR_ARG, "null front end");
+    DevGuard g(f->dev);
+    CU(cudaStreamSynchronize(f->st));
+    return SDRX_OK;
+}
+extern "C" int sdrx_airspy_fe_avg(sdrx_airspy_fe *f, float *avg) {
+    if (!f || !avg) return fail(SDRX_ERR_ARG, "null argument");
+    DevGuard g(f->dev);
+    CU(cudaStreamSynchronize(f->st));
+    CU(cudaMemcpy(avg, f->d_avg, sizeof(float), cudaMemcpyDeviceToHost));
+    return SDRX_OK;
+}

@@ -840,6 +840,13 @@ extern "C" int sdrx_engine_push_block_device(sdrx_engine *e, const void *d_raw, 
     return enqueue_block(e, d_raw, SRC_DEVICE, fmt, n_samples);
 }
 
+extern "C" int sdrx_engine_wait_event(sdrx_engine *e, void *cuda_event) {
+    if (!e || !cuda_event) return fail(SDRX_ERR_ARG, "null argument");
+    DevGuard g(e->dev);
+    CU(cudaStreamWaitEvent(e->s_copy, (cudaEvent_t)cuda_event, 0));
+    return SDRX_OK;
+}
+
 extern "C" int sdrx_engine_last_out_len(sdrx_engine *e, unsigned *out_len) {
     if (!e || !out_len) return fail(SDRX_ERR_ARG, "null argument");
     *out_len = e->last_out_len;

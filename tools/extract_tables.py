@@ -33,6 +33,8 @@ def main() -> None:
         out[f"rate_{rate}_taps"] = np.concatenate([s[1] for s in stages]).astype(np.float32)
     for name in ob.TABLE_NAMES:
         out[name] = ob.ref_table(name)
+    # libairspy/libairspy/src/filters.h:28-30 HB_KERNEL_FLOAT: the half-band kernel of the real -> IQ front end
+    out["airspy_hb_kernel"] = ob.ref_hb_kernel()
     path = os.path.join(ROOT, "sdrx_b200", "data", "tables.npz")
     np.savez_compressed(path, **out)
     print(f"wrote {path}: {len(out)} arrays, {os.path.getsize(path)} bytes")
