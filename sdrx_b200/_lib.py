@@ -108,6 +108,8 @@ PROTOTYPES = [
     ("sdrx_airspy_fe_avg", C.c_int, [C.c_void_p, c_float_p]),
     ("sdrx_airspy_fe_launch_count", C.c_uint64, [C.c_void_p]),
     ("sdrx_engine_wait_event", C.c_int, [C.c_void_p, C.c_void_p]),
+    ("sdrx_engine_ingest_event", C.c_void_p, [C.c_void_p]),
+    ("sdrx_airspy_fe_wait_event", C.c_int, [C.c_void_p, C.c_void_p]),
 ]
 FE_PACKED12, FE_EXACT_DC = 0x1, 0x2
 

@@ -50,6 +50,9 @@ class AirspyFrontEnd:
 
     def feed(self, engine, raw: np.ndarray) -> None:
         """One buffer through the front end and on into ``engine`` (push_block_device), without a host sync."""
+        ev = self.lib.sdrx_engine_ingest_event(engine.h)
+        if ev:          # the engine has read the output of the call before last: that ring slot is free again
+            check(self.lib.sdrx_airspy_fe_wait_event(self.h, C.c_void_p(ev)))
         self.process(raw, fetch=False)
         n = C.c_uint()
         d = self.lib.sdrx_airspy_fe_output(self.h, C.byref(n))

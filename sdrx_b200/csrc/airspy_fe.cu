@@ -9,11 +9,18 @@
 //   iqconverter_float.c:455-468 remove_dc     -> k_fe_dc: s -= avg; avg += 0.01f * s over ALL samples in order
 //   iqconverter_float.c:470-502 translate_fs_4, :191-230 fir_interleaved_24, :430-451 delay_interleaved -> k_fe_iq
 //
-// remove_dc is one sequential recurrence over the whole stream.  It is a contraction (pole 0.99), so a trajectory
-// started kFeWarm = 2048 samples early from any nearby value has forgotten its start (0.99^2048 = 1e-9) and has, in
-// practice, snapped onto the bit-exact sequence: k_fe_dc cuts the block into 128-sample segments, one thread each,
-// every thread warming up on the 2048 samples before its segment (carried raw history across blocks).  Segment 0
-// continues from the carried avg itself.  SDRX_FE_EXACT_DC runs the recurrence on one thread instead (tests).
+// remove_dc is one sequential recurrence over the whole stream: avg' = avg + 0.01f * (x - avg), i.e. the affine map
+// avg' = a * avg + 0.01f * x with a = 1 - 0.01f.  The block is cut into 128-sample segments, one thread each, and
+// the recurrence is run in three short passes instead of one long one:
+//   k_fe_partial  every segment from avg = 0: B[k], so that the segment maps avg_in -> a^128 * avg_in + B[k];
+//   k_fe_scan     one warp composes those maps (double precision) into the avg at every segment start, starting
+//                 from the carried block-start avg -- right to a few ulp, not yet the reference's rounded sequence;
+//   k_fe_dc       every thread starts kFeBack = 3 segments early from that estimate and runs the reference's own
+//                 float recurrence: it is a contraction (0.99^384 = 0.02), so the few-ulp error dies out and the
+//                 trajectory snaps onto the reference's rounded sequence before the thread's own segment begins
+//                 (segments 0..3 start from the exact carried avg).
+// A thread's dependent chain is 128 + 512 steps instead of 640 000.  SDRX_FE_EXACT_DC runs the recurrence on one
+// thread instead (tests): bit-exact by construction.
 // Everything after remove_dc is a pure function of a short window and is evaluated in the reference's order,
 // un-contracted: bit-exact given bit-exact inputs.
 #include <algorithm>
@@ -28,7 +35,7 @@ using namespace sdrx;
 namespace {
 
 constexpr int kFeSeg = 128;          // real samples per thread of k_fe_dc
-constexpr int kFeWarm = 2048;        // warm-up samples in front of a segment
+constexpr int kFeBack = 3;           // warm-up segments in front of a thread's own
 constexpr int kFeEvenHist = 24;      // >= len - 1 = 23 rotated even samples carried between blocks
 constexpr int kFeOddHist = 12;       // len / 2 delayed odd samples
 constexpr int kFeMaxLen = 64;
@@ -65,52 +72,123 @@ __device__ __forceinline__ float dc_step(float x, float &avg) {
     return s;
 }
 
-// remove_dc + translate_fs_4's sign / hbc pattern, segment-parallel.
+// Pass 1: the recurrence over one segment from avg = 0 (the additive term of the segment's affine map).
+template <bool PACKED>
+static __global__ void __launch_bounds__(128)
+k_fe_partial(const void *__restrict__ raw, int n, float *__restrict__ seg_b) {
+    const int seg = blockIdx.x * blockDim.x + threadIdx.x;
+    const long s0 = (long)seg * kFeSeg;
+    if (s0 + kFeSeg > n) return;                      // only whole segments feed the scan (the last start needs no successor)
+    float avg = 0.0f;
+    uint4 q[kFeSeg / 8];
+#pragma unroll
+    for (int j = 0; j < kFeSeg / 8; ++j) {
+        if constexpr (PACKED) {
+            int v[8];
+            load_adc8<true>(raw, s0 + 8 * j, v);
+            q[j] = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
+        } else {
+            q[j] = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const uint16_t *>(raw) + s0 + 8 * j));
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < kFeSeg / 8; ++j) {
+        const int v[8] = {(int)(q[j].x & 0xffff), (int)(q[j].x >> 16), (int)(q[j].y & 0xffff), (int)(q[j].y >> 16),
+                          (int)(q[j].z & 0xffff), (int)(q[j].z >> 16), (int)(q[j].w & 0xffff), (int)(q[j].w >> 16)};
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            dc_step(__fmul_rn(__fsub_rn(__int_as_float(0x4B000000 | v[k]), 8390656.0f), 1.0f / 2048.0f), avg);
+    }
+    seg_b[seg] = avg;
+}
+
+// Pass 2: avg at every segment start, start[0] = the carried avg, start[k+1] = A * start[k] + B[k] (A = a^128),
+// composed by one warp in double precision: each lane folds a contiguous chunk, lane 0 chains the 32 chunks, every
+// lane re-walks its chunk from its chunk start.
+static __global__ void __launch_bounds__(32)
+k_fe_scan(const float *__restrict__ seg_b, int nseg, const float *__restrict__ avg_io, double A, float *__restrict__ seg_start) {
+    __shared__ double sa[32], sb[32], st[32];
+    const int lane = threadIdx.x;
+    const int m = (nseg + 31) / 32;
+    const int k0 = lane * m, k1 = min(nseg, k0 + m);
+    double a = 1.0, b = 0.0;
+    for (int k = k0; k < k1; ++k) { b = A * b + (double)seg_b[k]; a *= A; }
+    sa[lane] = a; sb[lane] = b;
+    __syncwarp();
+    if (lane == 0) {
+        double v = (double)avg_io[0];
+        for (int l = 0; l < 32; ++l) { st[l] = v; v = sa[l] * v + sb[l]; }
+    }
+    __syncwarp();
+    double v = st[lane];
+    for (int k = k0; k < k1; ++k) { seg_start[k] = (float)v; v = A * v + (double)seg_b[k]; }
+}
+
+// Pass 3: remove_dc + translate_fs_4's sign / hbc pattern, segment-parallel.
 //   raw        this block, wire format, n samples (n % 8 == 0)
-//   hist       the kFeWarm unpacked samples (uint16) in front of the block
-//   known      how many of them belong to the stream (the rest lie before its start)
+//   seg_start  estimate of avg at every segment start (k_fe_scan)
 //   avg_io     [0] avg at the block start (in), [1] avg at the block end (out)
 //   ev / od    rotated even / odd samples of the block, behind their carried history prefixes
 template <bool PACKED>
 static __global__ void __launch_bounds__(128)
-k_fe_dc(const void *__restrict__ raw, const uint16_t *__restrict__ hist, int known, int n, float *__restrict__ avg_io,
+k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n, float *__restrict__ avg_io,
         float hbc, float *__restrict__ ev, float *__restrict__ od, int exact) {
     const int seg = blockIdx.x * blockDim.x + threadIdx.x;
     const long s0 = exact ? 0 : (long)seg * kFeSeg;
     if (s0 >= n || (exact && seg != 0)) return;
     const long s1 = exact ? n : (s0 + kFeSeg < n ? s0 + kFeSeg : n);
-    float avg = avg_io[0];
-    if (s0 > 0) {
-        long w0 = s0 - kFeWarm;
-        if (w0 < -(long)known) { w0 = -(long)known; avg = known < kFeWarm ? 0.0f : avg; }   // the stream starts inside the window: exact from avg = 0
-        for (long i = w0; i < s0; i += 8) {
+    const int kb = (exact || seg <= kFeBack) ? 0 : seg - kFeBack;      // segment the warm-up starts at
+    const long w0 = (long)kb * kFeSeg;
+    float avg = kb == 0 ? avg_io[0] : seg_start[kb];                   // from the block start the trajectory is the exact one
+    // Groups of eight samples travel through a ring of registers, fetched kFeAhead groups (64 samples, ~770 cycles of
+    // the recurrence) ahead of their use: the loads do not depend on the recurrence, so its dependent chain never
+    // waits for memory.  A ring slot holds the eight samples as four words of two uint16 each, whatever the wire format.
+    constexpr int kFeAhead = 8;
+    auto fetch = [&](long i) -> uint4 {
+        if (i >= s1) return make_uint4(0, 0, 0, 0);
+        if constexpr (PACKED) {
             int v[8];
-            if (i < 0) {
-                const uint4 q = __ldg(reinterpret_cast<const uint4 *>(hist + kFeWarm + i));
-                v[0] = q.x & 0xffff; v[1] = q.x >> 16; v[2] = q.y & 0xffff; v[3] = q.y >> 16;
-                v[4] = q.z & 0xffff; v[5] = q.z >> 16; v[6] = q.w & 0xffff; v[7] = q.w >> 16;
-            } else {
-                load_adc8<PACKED>(raw, i, v);
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) dc_step(adc_to_float(v[j]), avg);
+            load_adc8<true>(raw, i, v);
+            return make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
+        } else {
+            return __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const uint16_t *>(raw) + i));
         }
-    }
-    for (long i = s0; i < s1; i += 8) {
-        int v[8];
-        load_adc8<PACKED>(raw, i, v);
-        float s[8];
+    };
+    uint4 ring[kFeAhead];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) s[j] = dc_step(adc_to_float(v[j]), avg);
-        // translate_fs_4 (iqconverter_float.c:489-498): [-s0, -s1*hbc, s2, s3*hbc] per group of four
-        const long p = i >> 1;
-        float4 e, o;
-        e.x = -s[0];               o.x = __fmul_rn(-s[1], hbc);
-        e.y = s[2];                o.y = __fmul_rn(s[3], hbc);
-        e.z = -s[4];               o.z = __fmul_rn(-s[5], hbc);
-        e.w = s[6];                o.w = __fmul_rn(s[7], hbc);
-        *reinterpret_cast<float4 *>(ev + kFeEvenHist + p) = e;
-        *reinterpret_cast<float4 *>(od + kFeOddHist + p) = o;
+    for (int j = 0; j < kFeAhead; ++j) ring[j] = fetch(w0 + 8L * j);
+    const long ng = (s1 - w0) >> 3;
+    for (long g0 = 0; g0 < ng; g0 += kFeAhead) {
+#pragma unroll
+        for (int j = 0; j < kFeAhead; ++j) {
+            const long i = w0 + 8 * (g0 + j);
+            if (g0 + j < ng) {
+                const uint4 q = ring[j];
+                ring[j] = fetch(i + 8L * kFeAhead);
+                const int v[8] = {(int)(q.x & 0xffff), (int)(q.x >> 16), (int)(q.y & 0xffff), (int)(q.y >> 16),
+                                  (int)(q.z & 0xffff), (int)(q.z >> 16), (int)(q.w & 0xffff), (int)(q.w >> 16)};
+                // (raw - 2048) * (1/2048) without the integer->float converter on the way: 2^23 + v is the float whose
+                // low mantissa bits are v; subtracting 2^23 + 2048 and scaling by 2^-11 are both exact, so the value is
+                // bit for bit convert_samples_float's.  All eight conversions sit in front of the recurrence's chain.
+                float x[8], s[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    x[k] = __fmul_rn(__fsub_rn(__int_as_float(0x4B000000 | v[k]), 8390656.0f), 1.0f / 2048.0f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) s[k] = dc_step(x[k], avg);
+                if (i >= s0) {
+                    // translate_fs_4 (iqconverter_float.c:489-498): [-s0, -s1*hbc, s2, s3*hbc] per group of four
+                    const long p = i >> 1;
+                    float4 e, o;
+                    e.x = -s[0];               o.x = __fmul_rn(-s[1], hbc);
+                    e.y = s[2];                o.y = __fmul_rn(s[3], hbc);
+                    e.z = -s[4];               o.z = __fmul_rn(-s[5], hbc);
+                    e.w = s[6];                o.w = __fmul_rn(s[7], hbc);
+                    *reinterpret_cast<float4 *>(ev + kFeEvenHist + p) = e;
+                    *reinterpret_cast<float4 *>(od + kFeOddHist + p) = o;
+                }
+            }
+        }
     }
     if (s1 == n) avg_io[1] = avg;
 }
@@ -129,23 +207,9 @@ k_fe_iq(const float *__restrict__ ev, const float *__restrict__ od, int npair, c
     out[p] = make_float2(acc, od[kFeOddHist + p - half]);
 }
 
-// Block-to-block carries: the last kFeWarm raw samples (unpacked) and the even / odd history prefixes.
-template <bool PACKED>
-static __global__ void __launch_bounds__(256)
-k_fe_carry(const void *__restrict__ raw, int n, const uint16_t *__restrict__ hist_in, uint16_t *__restrict__ hist_out,
-           float *__restrict__ ev, float *__restrict__ od, float *__restrict__ avg_io) {
-    const int g = blockIdx.x * blockDim.x + threadIdx.x;          // group of 8 history samples
-    if (g < kFeWarm / 8) {
-        const long src = (long)n - kFeWarm + 8L * g;              // block-relative index of the group
-        int v[8];
-        if (src >= 0) load_adc8<PACKED>(raw, src, v);
-        else {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = hist_in[kFeWarm + src + j];
-        }
-#pragma unroll
-        for (int j = 0; j < 8; ++j) hist_out[8 * g + j] = (uint16_t)v[j];
-    }
+// Block-to-block carries: the even / odd history prefixes and avg.
+static __global__ void __launch_bounds__(64)
+k_fe_carry(int n, float *__restrict__ ev, float *__restrict__ od, float *__restrict__ avg_io) {
     // the even / odd prefixes slide in place: every read below happens before the barrier, every write after
     // (one CTA does it: kFeEvenHist + kFeOddHist <= 256)
     if (blockIdx.x == 0) {
@@ -173,9 +237,10 @@ struct sdrx_airspy_fe {
     cudaEvent_t ev_done = nullptr;
     uint8_t *d_raw = nullptr;            // wire-format staging of one call
     uint8_t *h_stage = nullptr;          // pinned staging for pageable callers
-    uint16_t *d_hist[2] = {nullptr, nullptr};
+    float *d_seg_b = nullptr, *d_seg_start = nullptr;   // per-segment affine terms / avg estimates (k_fe_partial, k_fe_scan)
+    double A = 0.0;                      // (1 - 0.01f)^kFeSeg
     float *d_ev = nullptr, *d_od = nullptr, *d_k = nullptr, *d_avg = nullptr;
-    float2 *d_iq = nullptr;
+    float2 *d_iq[2] = {nullptr, nullptr};    // ring: the consumer of call k may still read while call k+1 runs
     uint64_t total = 0;                  // real samples seen so far
     uint64_t calls = 0;
     unsigned last_pairs = 0;
@@ -186,8 +251,8 @@ extern "C" void sdrx_airspy_fe_destroy(sdrx_airspy_fe *f) {
     if (!f) return;
     DevGuard g(f->dev);
     if (f->st) cudaStreamSynchronize(f->st);
-    cudaFree(f->d_raw); cudaFree(f->d_hist[0]); cudaFree(f->d_hist[1]); cudaFree(f->d_ev); cudaFree(f->d_od);
-    cudaFree(f->d_k); cudaFree(f->d_avg); cudaFree(f->d_iq);
+    cudaFree(f->d_raw); cudaFree(f->d_seg_b); cudaFree(f->d_seg_start); cudaFree(f->d_ev); cudaFree(f->d_od);
+    cudaFree(f->d_k); cudaFree(f->d_avg); cudaFree(f->d_iq[0]); cudaFree(f->d_iq[1]);
     if (f->h_stage) cudaFreeHost(f->h_stage);
     if (f->ev_done) cudaEventDestroy(f->ev_done);
     if (f->st) cudaStreamDestroy(f->st);
@@ -198,8 +263,6 @@ extern "C" int sdrx_airspy_fe_reset(sdrx_airspy_fe *f) {
     if (!f) return fail(SDRX_ERR_ARG, "null front end");
     DevGuard g(f->dev);
     CU(cudaStreamSynchronize(f->st));
-    CU(cudaMemsetAsync(f->d_hist[0], 0, sizeof(uint16_t) * kFeWarm, f->st));
-    CU(cudaMemsetAsync(f->d_hist[1], 0, sizeof(uint16_t) * kFeWarm, f->st));
     CU(cudaMemsetAsync(f->d_ev, 0, sizeof(float) * (kFeEvenHist + f->cap / 2 + 8), f->st));     // iqconverter_float_reset
     CU(cudaMemsetAsync(f->d_od, 0, sizeof(float) * (kFeOddHist + f->cap / 2 + 8), f->st));
     CU(cudaMemsetAsync(f->d_avg, 0, sizeof(float) * 2, f->st));
@@ -230,6 +293,11 @@ extern "C" int sdrx_airspy_fe_create(int device, const float *hb_kernel, int hb_
     sdrx_airspy_fe *f = new sdrx_airspy_fe();
     f->dev = device; f->flags = flags; f->cap = max_samples; f->len = len;
     f->hbc = hb_kernel[hb_len / 2];                              // iqconverter_float.c:81
+    {
+        const double a = 1.0 - (double)0.01f;                    // avg' = a * avg + 0.01f * x (iqconverter_float.c:461-464)
+        f->A = 1.0;
+        for (int i = 0; i < kFeSeg; ++i) f->A *= a;
+    }
     std::vector<float> k((size_t)len);
     for (int i = 0, j = 0; i < len; ++i, j += 2) k[i] = hb_kernel[j];   // iqconverter_float.c:91-94
     auto bail = [&](const char *what) { std::string keep = what; sdrx_airspy_fe_destroy(f); return fail(SDRX_ERR_CUDA, keep.c_str()); };
@@ -237,15 +305,27 @@ extern "C" int sdrx_airspy_fe_create(int device, const float *hb_kernel, int hb_
     if (cudaEventCreateWithFlags(&f->ev_done, cudaEventDisableTiming) != cudaSuccess) return bail("cudaEventCreate");
     const size_t pairs = max_samples / 2;
     if (cudaMalloc((void **)&f->d_raw, (size_t)max_samples * 2 + 64) != cudaSuccess ||
-        cudaMalloc((void **)&f->d_hist[0], sizeof(uint16_t) * kFeWarm) != cudaSuccess ||
-        cudaMalloc((void **)&f->d_hist[1], sizeof(uint16_t) * kFeWarm) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_seg_b, sizeof(float) * (max_samples / kFeSeg + 2)) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_seg_start, sizeof(float) * (max_samples / kFeSeg + 2)) != cudaSuccess ||
         cudaMalloc((void **)&f->d_ev, sizeof(float) * (kFeEvenHist + pairs + 8)) != cudaSuccess ||
         cudaMalloc((void **)&f->d_od, sizeof(float) * (kFeOddHist + pairs + 8)) != cudaSuccess ||
         cudaMalloc((void **)&f->d_k, sizeof(float) * len) != cudaSuccess ||
         cudaMalloc((void **)&f->d_avg, sizeof(float) * 2) != cudaSuccess ||
-        cudaMalloc((void **)&f->d_iq, sizeof(float2) * pairs) != cudaSuccess)
+        cudaMalloc((void **)&f->d_iq[0], sizeof(float2) * pairs) != cudaSuccess ||
+        cudaMalloc((void **)&f->d_iq[1], sizeof(float2) * pairs) != cudaSuccess)
         return bail("cudaMalloc failed");
     if (cudaMemcpy(f->d_k, k.data(), sizeof(float) * len, cudaMemcpyHostToDevice) != cudaSuccess) return bail("cudaMemcpy failed");
+    {   // same (maximum) shared-memory carve-out as the channel bank: an SM only co-schedules kernels that agree on it
+        const int mx = (int)cudaSharedmemCarveoutMaxShared;
+        cudaFuncSetAttribute(k_fe_dc<true>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaFuncSetAttribute(k_fe_dc<false>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaFuncSetAttribute(k_fe_iq, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaFuncSetAttribute(k_fe_carry, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaFuncSetAttribute(k_fe_partial<true>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaFuncSetAttribute(k_fe_partial<false>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaFuncSetAttribute(k_fe_scan, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaGetLastError();
+    }
     int rc = sdrx_airspy_fe_reset(f);
     if (rc) { sdrx_airspy_fe_destroy(f); return rc; }
     *out = f;
@@ -258,14 +338,19 @@ int fe_run(sdrx_airspy_fe *f, const void *d_raw, unsigned n) {
     const bool packed = (f->flags & SDRX_FE_PACKED12) != 0;
     const int exact = (f->flags & SDRX_FE_EXACT_DC) ? 1 : 0;
     const int cur = (int)(f->calls & 1);
-    const int known = (int)std::min<uint64_t>(f->total, (uint64_t)kFeWarm);
     const int segs = exact ? 1 : div_up(n, kFeSeg);
     const int npair = (int)(n / 2);
-    if (packed) k_fe_dc<true><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_hist[cur], known, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
-    else        k_fe_dc<false><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_hist[cur], known, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
-    k_fe_iq<<<div_up(npair, 256), 256, 0, f->st>>>(f->d_ev, f->d_od, npair, f->d_k, f->len, f->d_iq);
-    if (packed) k_fe_carry<true><<<div_up(kFeWarm / 8, 256), 256, 0, f->st>>>(d_raw, (int)n, f->d_hist[cur], f->d_hist[cur ^ 1], f->d_ev, f->d_od, f->d_avg);
-    else        k_fe_carry<false><<<div_up(kFeWarm / 8, 256), 256, 0, f->st>>>(d_raw, (int)n, f->d_hist[cur], f->d_hist[cur ^ 1], f->d_ev, f->d_od, f->d_avg);
+    if (!exact && segs > kFeBack + 1) {
+        const int whole = (int)(n / kFeSeg);
+        if (packed) k_fe_partial<true><<<div_up(whole, 128), 128, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
+        else        k_fe_partial<false><<<div_up(whole, 128), 128, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
+        k_fe_scan<<<1, 32, 0, f->st>>>(f->d_seg_b, whole, f->d_avg, f->A, f->d_seg_start);
+        f->launches += 2;
+    }
+    if (packed) k_fe_dc<true><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
+    else        k_fe_dc<false><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
+    k_fe_iq<<<div_up(npair, 256), 256, 0, f->st>>>(f->d_ev, f->d_od, npair, f->d_k, f->len, f->d_iq[cur]);
+    k_fe_carry<<<1, 64, 0, f->st>>>((int)n, f->d_ev, f->d_od, f->d_avg);
     CU(cudaGetLastError());
     CU(cudaEventRecord(f->ev_done, f->st));
     f->launches += 3;
@@ -304,7 +389,7 @@ extern "C" int sdrx_airspy_fe_process(sdrx_airspy_fe *f, const void *raw, unsign
     rc = fe_run(f, f->d_raw, n_samples);
     if (rc) return rc;
     if (iq_host) {
-        CU(cudaMemcpyAsync(iq_host, f->d_iq, sizeof(float2) * (size_t)(n_samples / 2), cudaMemcpyDeviceToHost, f->st));
+        CU(cudaMemcpyAsync(iq_host, f->d_iq[(f->calls - 1) & 1], sizeof(float2) * (size_t)(n_samples / 2), cudaMemcpyDeviceToHost, f->st));
         CU(cudaStreamSynchronize(f->st));
     }
     return SDRX_OK;
@@ -320,7 +405,15 @@ extern "C" int sdrx_airspy_fe_process_device(sdrx_airspy_fe *f, const void *d_ra
 extern "C" const float *sdrx_airspy_fe_output(sdrx_airspy_fe *f, unsigned *n_pairs) {
     if (!f) return nullptr;
     if (n_pairs) *n_pairs = f->last_pairs;
-    return reinterpret_cast<const float *>(f->d_iq);
+    return reinterpret_cast<const float *>(f->d_iq[(f->calls + 1) & 1]);    // the buffer the last call wrote
+}
+// Orders the front end's stream behind an event of the consumer (e.g. sdrx_engine_ingest_event after the push that
+// read the previous output): the output ring is two deep, so waiting for the consumer of call k-1 frees call k+1's buffer.
+extern "C" int sdrx_airspy_fe_wait_event(sdrx_airspy_fe *f, void *cuda_event) {
+    if (!f || !cuda_event) return fail(SDRX_ERR_ARG, "null argument");
+    DevGuard g(f->dev);
+    CU(cudaStreamWaitEvent(f->st, (cudaEvent_t)cuda_event, 0));
+    return SDRX_OK;
 }
 extern "C" void *sdrx_airspy_fe_done_event(sdrx_airspy_fe *f) { return f ? (void *)f->ev_done : nullptr; }
 extern "C" void *sdrx_airspy_fe_stream(sdrx_airspy_fe *f) { return f ? (void *)f->st : nullptr; }

@@ -847,6 +847,13 @@ extern "C" int sdrx_engine_wait_event(sdrx_engine *e, void *cuda_event) {
     return SDRX_OK;
 }
 
+// The event that completes when the last pushed block's ingest copy (and raw carry) has run: a device-side producer
+// may overwrite the buffer it handed to push_block_device after this.
+extern "C" void *sdrx_engine_ingest_event(sdrx_engine *e) {
+    if (!e || e->blocks == 0) return nullptr;
+    return (void *)e->ev_copied[(e->blocks - 1) & 1];
+}
+
 extern "C" int sdrx_engine_last_out_len(sdrx_engine *e, unsigned *out_len) {
     if (!e || !out_len) return fail(SDRX_ERR_ARG, "null argument");
     *out_len = e->last_out_len;
