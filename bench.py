@@ -70,18 +70,64 @@ def synth_blocks(carriers, n: int, seed: int):
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    """SM clock and throttle reasons sampled DURING the timed region (B200_PROFILING.md).  The timed region of the
+    default run lasts milliseconds, so the sampler is an NVML polling thread (about one sample per millisecond,
+    nvidia_ml_py); `nvidia-smi -lms 100` is only the fallback where NVML cannot be loaded."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    BITS = (("sw_power_cap", 0x4), ("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40))
 
-    def __init__(self, index: int):
+    def __init__(self, index: int, uuid=None):
         self.index = index
-        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.nv = self.h = None
+        self.samples, self.bits = [], 0
+        self.stop_flag = False
+        self.thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = None
+            if uuid is not None:
+                for cand in (f"GPU-{uuid}", str(uuid)):
+                    try:
+                        h = pynvml.nvmlDeviceGetHandleByUUID(cand.encode() if isinstance(cand, str) else cand)
+                        break
+                    except Exception:
+                        try:
+                            h = pynvml.nvmlDeviceGetHandleByUUID(cand)
+                            break
+                        except Exception:
+                            h = None
+            self.h = h if h is not None else pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nv = pynvml
+        except Exception:
+            self.nv = None
+        self.f = None
         self.p = None
 
+    def _poll(self):
+        nv, h = self.nv, self.h
+        while not self.stop_flag:
+            try:
+                self.samples.append(float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                try:
+                    self.bits |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    self.bits |= int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+            except Exception:
+                pass
+            time.sleep(0.0005)
+
     def start(self):
+        if self.nv is not None:
+            import threading
+            self.stop_flag = False
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
         try:
+            self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
             self.p = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
                                        "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
@@ -89,6 +135,22 @@ class ClockSampler:
             self.p = None
 
     def stop(self) -> dict:
+        if self.nv is not None:
+            self.stop_flag = True
+            if self.thread is not None:
+                self.thread.join(timeout=2)
+            if not self.samples:          # the region ended before the first poll returned: read once, right behind it
+                try:
+                    self.samples.append(float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                except Exception:
+                    pass
+            try:
+                mx = float(self.nv.nvmlDeviceGetMaxClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+            except Exception:
+                mx = None
+            reasons = sorted(n for n, b in self.BITS if self.bits & b)
+            return {"sm_mhz": statistics.median(self.samples) if self.samples else None, "sm_max_mhz": mx,
+                    "samples": len(self.samples), "reasons": reasons, "how": "NVML polling thread inside the timed region"}
         if self.p is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
@@ -117,7 +179,7 @@ class ClockSampler:
         except OSError:
             pass
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "reasons": sorted(reasons), "how": "nvidia-smi -lms 100"}
 
 
 def fp32_peak():
@@ -231,7 +293,11 @@ def run_ours(args):
     for i in range(max(args.warmup, 3)):
         step_device(i)
     eng.sync()
-    sampler = ClockSampler(local)
+    try:
+        uuid = torch.cuda.get_device_properties(local).uuid
+    except Exception:
+        uuid = None
+    sampler = ClockSampler(local, uuid)
     barrier()
     sampler.start()
     l0 = eng.launch_count
