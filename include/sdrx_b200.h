@@ -56,6 +56,10 @@ typedef enum { SDRX_FMT_U8 = 0, SDRX_FMT_S16 = 1, SDRX_FMT_F32 = 2 } sdrx_iq_for
                                          could share a translator table as conjugates                       */
 #define SDRX_FLAG_FTFIR         0x10u /* --ftfir (sdrx.cpp:1199,:1692): the first stage is the frequency-translating FIR,
                                          msd.hpp:104-131 + calculateOutputTranslated :341-423, instead of mix + FIR      */
+#define SDRX_FLAG_TAIL_SIDE     0x20u /* specialised path, experimental: run the last MSD stage together with the detector under
+                                         the next block's bank (k_chan_tail_side, own stream, ping-pong stage rows) instead
+                                         of on the main stream (k_chan_fir_fast).  Measured slower on B200 (one 7 KB CTA per
+                                         SM next to a bank CTA, ~30 us of latency each): off by default.                  */
 #define SDRX_FLAG_PARTIAL_MIX   0x4u  /* channel-sharded run: stop at mix_pre (this GPU's share of the pan
                                          mix); FIR2 + s16 run once, in sdrx_engine_finish_mix              */
 

@@ -93,6 +93,14 @@ struct sdrx_engine {
     bool tail_fusable = false;            // last stage as one per-channel kernel fed by the bank's rows + tail fix-ups
     bool tail_fast = false;               // ... in its specialised form (67 taps, decimate by 5: k_chan_fir_fast)
     FirTaps<67> tail_taps{};
+    bool tail_side = false;               // ... and under the next bank on its own side stream (k_chan_tail_side)
+    cudaStream_t s_tail = nullptr;        // last stage + detector of block b (needs only the 9 KB a bank CTA leaves)
+    float2 *d_stage_alt = nullptr;        // ping-pong partner of d_stage_in[S-1]: block b+1's bank writes it while block b's tail kernel reads the other
+    cudaEvent_t ev_tail_done[2] = {nullptr, nullptr};   // tail kernel that read row / tails buffer `par` is complete
+    bool tail_pending[2] = {false, false};
+    int tail_par = 0;                     // row / tails buffer the next fused block uses
+    int last_tail_par = -1;               // buffer of the most recent side-stream tail kernel (-1: none outstanding)
+    bool prev_block_side_tail = false;
     bool ftfir = false;                   // --ftfir: stage 0 is the frequency-translating FIR (msd.hpp:104-131)
     int ft_sets = 0;                      // coefficient sets, N / m[0] (msd.hpp:196)
     float2 *d_hk = nullptr;               // [ft_sets * H0][Cpad]
@@ -195,9 +203,13 @@ void agc_defaults(AgcParams &p, float attack, float decay, float reference, floa
 
 int reset_state(sdrx_engine *e) {
     const size_t C = (size_t)e->C;
+    CU(cudaStreamSynchronize(e->s_tail));
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
+    e->tail_pending[0] = e->tail_pending[1] = false;
+    e->tail_par = 0; e->last_tail_par = -1; e->prev_block_side_tail = false;
+    if (e->d_stage_alt) CU(cudaMemsetAsync(e->d_stage_alt, 0, sizeof(float2) * (size_t)e->stage_stride[e->S - 1] * C, e->s_main));
     for (int b = 0; b < kNBuf; ++b) CU(cudaMemsetAsync(e->d_raw[b], 0, e->raw_buf_bytes, e->s_main));
     for (int s = 1; s < e->S; ++s)
         CU(cudaMemsetAsync(e->d_stage_in[s], 0, sizeof(float2) * (size_t)e->stage_stride[s] * C, e->s_main));
@@ -250,6 +262,9 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
         cudaFree(e->d_gate[b]); cudaFree(e->d_pwr_partial[b]);
     }
     if (e->ev_head_done) cudaEventDestroy(e->ev_head_done);
+    for (int b = 0; b < 2; ++b) if (e->ev_tail_done[b]) cudaEventDestroy(e->ev_tail_done[b]);
+    cudaFree(e->d_stage_alt);
+    if (e->s_tail) cudaStreamDestroy(e->s_tail);
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) cudaFree(e->d_stage_in[s]);
     cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps); cudaFree(e->d_hk);
     cudaFree(e->st.agc_gain); cudaFree(e->st.agc_power); cudaFree(e->st.lf_gain); cudaFree(e->st.lf_power);
@@ -300,6 +315,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     CU(cudaStreamCreateWithFlags(&e->s_side, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->ev_head_done, cudaEventDisableTiming));
+    CU(cudaStreamCreateWithFlags(&e->s_tail, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) CU(cudaEventCreateWithFlags(&e->ev_tail_done[b], cudaEventDisableTiming));
     for (int b = 0; b < kNOut; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_side_done[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_fetch_done[b], cudaEventDisableTiming));
@@ -483,6 +500,13 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
                                         (int)fir_fast_smem(67, 5, kChunk * 5)));
                 CU(cudaFuncSetAttribute(k_chan_fir_fast<67, 5>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                         (int)cudaSharedmemCarveoutMaxShared));
+                CU(cudaFuncSetAttribute(k_chan_tail_side<67, 5>, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        (int)cudaSharedmemCarveoutMaxShared));
+                e->tail_side = e->use_fast && (cfg->flags & SDRX_FLAG_TAIL_SIDE);
+                if (e->tail_side) {
+                    int rc2 = dalloc(&e->d_stage_alt, (size_t)e->stage_stride[S - 1] * C);
+                    if (rc2) return rc2;
+                }
             }
         }
     }
@@ -631,20 +655,21 @@ int materialize_generic(sdrx_engine *e, int fmt, const uint8_t *buf, long end_id
 }
 
 template <int FMT>
-int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o, const FastSchedule **deferred) {
+int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o, const FastSchedule **deferred,
+                     int tail_half) {
     float2 *dst; long stride; int off;
     if (e->S > 3) { dst = e->d_stage_in[3]; stride = e->stage_stride[3]; off = e->H[3] - 1; }
     else          { dst = o.ch_iq;          stride = e->chiq_stride;     off = 0; }
     return fast_launch<FMT>(e->fast, e->s_main, raw, e->raw_hist, valid_lo, e->N, (int)e->trans_pos, n,
                             dst, stride, off, &e->launches,
-                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred);
+                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred, tail_half);
 }
 int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o,
-                         const FastSchedule **deferred = nullptr) {
+                         const FastSchedule **deferred = nullptr, int tail_half = 0) {
     switch (fmt) {
-        case SDRX_FMT_U8:  return launch_bank_fast<SDRX_FMT_U8>(e, raw, valid_lo, n, o, deferred);
-        case SDRX_FMT_S16: return launch_bank_fast<SDRX_FMT_S16>(e, raw, valid_lo, n, o, deferred);
-        default:           return launch_bank_fast<SDRX_FMT_F32>(e, raw, valid_lo, n, o, deferred);
+        case SDRX_FMT_U8:  return launch_bank_fast<SDRX_FMT_U8>(e, raw, valid_lo, n, o, deferred, tail_half);
+        case SDRX_FMT_S16: return launch_bank_fast<SDRX_FMT_S16>(e, raw, valid_lo, n, o, deferred, tail_half);
+        default:           return launch_bank_fast<SDRX_FMT_F32>(e, raw, valid_lo, n, o, deferred, tail_half);
     }
 }
 
@@ -666,24 +691,49 @@ int launch_prep(sdrx_engine *e, cudaStream_t st, int fmt, uint8_t *buf, const ui
 // Boundary B on the chunk in o.ch_iq (output set `idx`).  Only the last MSD stage (when `fused`) runs on the main
 // stream; the squelch detector, the recurrences and the mix follow on the side stream, where their CTAs sit next
 // to the next block's channel-bank CTAs (none of them needs more than the 9 KB of shared memory the bank leaves).
-int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr) {
+int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr,
+                 int side_par = -1) {
     OutSet &o = e->out[idx];
     const TailSnap snap{o.sql, o.agc_gain, o.lf_gain};
-    if (fused) {
-        const size_t dyn = sizeof(float2) * (size_t)(fused->H - 1 + fused->n_in);
-        if (e->tail_fast && fused->n_in == kChunk * 5 && fused->first >= 0 && fused->first < 5)
-            k_chan_fir_fast<67, 5><<<e->C, kHeadThreads, fir_fast_smem(67, 5, fused->n_in), e->s_main>>>(*fused, e->tail_taps, o.ch_iq,
-                                                                                                        e->chiq_stride);
-        else
-            k_chan_head<kHeadFir><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
-                                                                          o.snr, e->d_gate[idx], snap);
+    if (fused && side_par >= 0) {
+        // last stage + detector under the next block's bank: main (bank done) -> s_tail -> s_side (recurrences, mix)
+        CU(cudaEventRecord(e->ev_head_done, e->s_main));
+        CU(cudaStreamWaitEvent(e->s_tail, e->ev_head_done, 0));
+        if (!e->prev_block_side_tail && e->blocks > 0) {       // the previous block's detector ran on s_side: order behind it
+            const int pidx = (int)((e->blocks - 1) % kNOut);
+            if (e->side_pending[pidx]) CU(cudaStreamWaitEvent(e->s_tail, e->ev_side_done[pidx], 0));
+        }
+        float2 *rows_next = (fused->stage_in == e->d_stage_alt) ? e->d_stage_in[e->S - 1] : e->d_stage_alt;
+        k_chan_tail_side<67, 5><<<e->C, kHeadThreads, 0, e->s_tail>>>(*fused, rows_next, e->tail_taps, o.ch_iq, e->chiq_stride, e->st,
+                                                                      e->tb, e->d_sql_level, o.snr, e->d_gate[idx], snap);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(e->ev_tail_done[side_par], e->s_tail));
+        e->tail_pending[side_par] = true;
+        e->last_tail_par = side_par;
+        CU(cudaStreamWaitEvent(e->s_side, e->ev_tail_done[side_par], 0));
         ++e->launches;
+        e->prev_block_side_tail = true;
+    } else {
+        if (fused) {
+            const size_t dyn = sizeof(float2) * (size_t)(fused->H - 1 + fused->n_in);
+            if (e->tail_fast && fused->n_in == kChunk * 5 && fused->first >= 0 && fused->first < 5)
+                k_chan_fir_fast<67, 5><<<e->C, kHeadThreads, fir_fast_smem(67, 5, fused->n_in), e->s_main>>>(*fused, e->tail_taps, o.ch_iq,
+                                                                                                            e->chiq_stride);
+            else
+                k_chan_head<kHeadFir><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
+                                                                              o.snr, e->d_gate[idx], snap);
+            ++e->launches;
+        }
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(e->ev_head_done, e->s_main));
+        CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
+        if (e->prev_block_side_tail && e->last_tail_par >= 0)  // the previous block's detector ran on s_tail: order behind it
+            CU(cudaStreamWaitEvent(e->s_side, e->ev_tail_done[e->last_tail_par], 0));
+        k_chan_head<kHeadDetect><<<e->C, kHeadThreads, 0, e->s_side>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
+                                                                       e->d_sql_level, o.snr, e->d_gate[idx], snap);
+        ++e->launches;
+        e->prev_block_side_tail = false;
     }
-    CU(cudaGetLastError());
-    CU(cudaEventRecord(e->ev_head_done, e->s_main));
-    CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
-    k_chan_head<kHeadDetect><<<e->C, kHeadThreads, 0, e->s_side>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
-                                                                   e->d_sql_level, o.snr, e->d_gate[idx], snap);
     k_chan_recur<<<div_up(e->C, kRecurCh), 32, 0, e->s_side>>>(o.ch_iq, e->chiq_stride, e->st, e->d_gate[idx], e->tb, e->agc, e->lf, e->lf_active,
                                              o.audio, snap, e->C);
     const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad;
@@ -691,7 +741,7 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
                                                  e->d_fir_hist, o.mix_pre, o.mix, o.pcm, e->d_pwr_partial[idx],
                                                  have_power ? kPwrPartials : 0, n_samples, have_power ? o.pwr : nullptr,
                                                  nullptr, 0, (e->flags & SDRX_FLAG_PARTIAL_MIX) ? 0 : 1);
-    e->launches += 3;
+    e->launches += 2;
     CU(cudaGetLastError());
     if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_side));
     CU(cudaEventRecord(e->ev_side_done[idx], e->s_side));
@@ -790,15 +840,35 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     const bool fast = e->use_fast && n > 0 && n % kUnit == 0 && phase_in[0] == 0 && phase_in[1] == 0 && phase_in[2] == 0;
     int rc;
     const bool fuse_tail = fast && demod && e->tail_fusable && e->S == e->fast.stages_fused + 1;
+    const int s_last = e->S - 1;
+    const bool side_tail = fuse_tail && e->tail_side && e->tail_fast && n_out[s_last - 1] == kChunk * 5 &&
+                           first[s_last] == 4;
+    int side_par = -1;
     TailFirArgs tail{};
     if (fast) {
         const FastSchedule *sc = nullptr;
-        rc = launch_bank_fast_fmt(e, fmt, buf, valid_lo, n, o, fuse_tail ? &sc : nullptr);
+        int tail_half = 0;
+        if (side_tail) {
+            // row / tails buffer `par` was last read by the tail kernel two fused blocks ago
+            side_par = e->tail_par;
+            tail_half = side_par;
+            if (e->tail_pending[side_par]) CU(cudaStreamWaitEvent(e->s_main, e->ev_tail_done[side_par], 0));
+        } else if (e->last_tail_par >= 0) {
+            // this block works in place on the row buffer whose delay line the last side-stream tail kernel writes
+            CU(cudaStreamWaitEvent(e->s_main, e->ev_tail_done[e->last_tail_par], 0));
+        }
+        rc = launch_bank_fast_fmt(e, fmt, buf, valid_lo, n, o, fuse_tail ? &sc : nullptr, tail_half);
         if (!rc && fuse_tail) {
-            const int s = e->S - 1;
+            const int s = s_last;
             tail = TailFirArgs{e->d_stage_in[s], e->stage_stride[s], n_out[s - 1], e->H[s], e->m[s], first[s],
-                               e->d_taps + e->tap_off[s], sc->n_fixes > 0 ? e->fast.d_tails : nullptr, e->fast.tails_slots,
+                               e->d_taps + e->tap_off[s], sc->n_fixes > 0 ? e->fast.tails_half(tail_half) : nullptr, e->fast.tails_slots,
                                sc->d_fixes, sc->d_fix_range, e->fast.d_chan_group};
+            if (side_tail) {
+                // from here on "the" last-stage input buffer is the partner: its delay line is what this block's tail
+                // kernel writes, its new part what the next block's bank writes
+                std::swap(e->d_stage_in[s], e->d_stage_alt);
+                e->tail_par ^= 1;
+            }
         } else if (!rc) {
             rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 3, e->S);
         }
@@ -806,13 +876,14 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         e->bank_timed = e->timing;
     } else {
         e->bank_timed = false;
+        if (e->last_tail_par >= 0) CU(cudaStreamWaitEvent(e->s_main, e->ev_tail_done[e->last_tail_par], 0));
         rc = materialize_generic(e, fmt, buf, e->raw_hist, e->total);
         if (!rc) rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 0, e->S);
     }
     if (rc) return rc;
     if (e->timing) CU(cudaEventRecord(e->ev_t1, e->s_main));
 
-    if (demod) { rc = launch_demod(e, oc, n > 0, n, fuse_tail ? &tail : nullptr); if (rc) return rc; }
+    if (demod) { rc = launch_demod(e, oc, n > 0, n, fuse_tail ? &tail : nullptr, side_par); if (rc) return rc; }
     else if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_main));
     if (e->timing) e->timing_valid = true;
 
@@ -866,6 +937,7 @@ extern "C" int sdrx_engine_sync(sdrx_engine *e) {
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
+    CU(cudaStreamSynchronize(e->s_tail));
     CU(cudaStreamSynchronize(e->s_out));
     return SDRX_OK;
 }
@@ -884,6 +956,7 @@ extern "C" int sdrx_engine_get_channel_iq(sdrx_engine *e, float *ch_iq) {
     if (e->blocks == 0) return fail(SDRX_ERR_STATE, "no block pushed yet");
     DevGuard g(e->dev);
     const OutSet &o = e->out[(e->blocks - 1) % kNOut];
+    { int rc = wait_side(e, (int)((e->blocks - 1) % kNOut)); if (rc) return rc; }   // the last stage may run on a side stream
     if (e->last_out_len > 0)
         CU(cudaMemcpy2DAsync(ch_iq, (size_t)e->last_out_len * sizeof(float2), o.ch_iq, (size_t)e->chiq_stride * sizeof(float2),
                              (size_t)e->last_out_len * sizeof(float2), (size_t)e->C, cudaMemcpyDeviceToHost, e->s_main));
@@ -1060,6 +1133,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
+    CU(cudaStreamSynchronize(e->s_tail));
     if (e->generic_stale) {      // the blob always carries the stage delay lines (a generic engine can load it)
         const int last_ = (int)((e->blocks & 1) ^ 1);
         int rc = materialize_generic(e, e->fmt, e->d_raw[last_], (long)e->raw_hist + (long)e->prev_n, e->total);
@@ -1116,8 +1190,11 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
+    CU(cudaStreamSynchronize(e->s_tail));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
+    e->tail_pending[0] = e->tail_pending[1] = false;
+    e->last_tail_par = -1; e->prev_block_side_tail = false;
     const uint8_t *p = (const uint8_t *)buf + sizeof(h);
     e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = h.blocks; e->total = h.total; e->generic_stale = false;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = h.phase[s];

@@ -13,7 +13,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import (FMT_F32, FMT_S16, FMT_U8, FLAG_FTFIR, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, CHUNK,
+from ._lib import (FMT_F32, FMT_S16, FMT_U8, FLAG_FTFIR, FLAG_TAIL_SIDE, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, CHUNK,
                    SdrxError,
                    check)
 from .config import ChannelPlan, make_translator, tables
@@ -78,7 +78,7 @@ class Engine:
     def __init__(self, plan: ChannelPlan, device: int = 0, use_lf_agc: bool = False, lf_gain_db: float = 0.0,
                  block_len: Optional[int] = None, force_generic: bool = False, demod: bool = True,
                  translators: Optional[np.ndarray] = None, partial_mix: bool = False, no_pairing: bool = False,
-                 use_ftfir: bool = False):
+                 use_ftfir: bool = False, tail_side: bool = False):
         self.lib = _lib.load()
         self.plan = plan
         self.device = device
@@ -124,7 +124,8 @@ class Engine:
         cfg.passband_shape, cfg.ramp_up, cfg.ramp_down = fp(shape), fp(rup), fp(rdn)
         cfg.flags = ((FLAG_FORCE_GENERIC if force_generic else 0) | (0 if demod else FLAG_NO_DEMOD)
                      | (FLAG_PARTIAL_MIX if partial_mix else 0) | (FLAG_NO_PAIRING if no_pairing else 0)
-                     | (FLAG_FTFIR if use_ftfir else 0))     # --ftfir, sdrx.cpp:1199 / msd.hpp:104-131
+                     | (FLAG_FTFIR if use_ftfir else 0)      # --ftfir, sdrx.cpp:1199 / msd.hpp:104-131
+                     | (FLAG_TAIL_SIDE if tail_side else 0))
         self.demod = demod
         h = C.c_void_p()
         check(self.lib.sdrx_engine_create(C.byref(cfg), C.byref(h)))

@@ -137,6 +137,34 @@ def test_conjugate_paired_bank_meets_the_parity_bar(fmt):
             assert rel_rms(a.ch_iq[c], b.ch_iq[c]) < 3e-5, c
 
 
+def test_side_stream_last_stage_variant_meets_the_parity_bar():
+    """SDRX_FLAG_TAIL_SIDE (k_chan_tail_side: last stage + detector under the next bank, ping-pong stage rows and
+    tails) against the oracle and against the default main-stream last stage, incl. a ragged block in between
+    (hand-over to the generic kernels and back) and a state save / load."""
+    from sdrx_b200 import Engine
+    scn = sc.paired_channels()
+    blocks = _blocks(scn)
+    want = run_cpu(scn, "oracle", blocks)
+    got, fast = run_engine(scn, blocks=blocks, tail_side=True)
+    assert fast
+    _assert_close(got, want, np.full(len(scn.offsets), 9.0))
+    ref, _ = run_engine(scn, blocks=blocks)
+    for a, b in zip(got, ref):
+        assert np.array_equal(a.sql, b.sql)
+        assert rel_rms(a.ch_iq, b.ch_iq) < 1e-5
+    eng = Engine(scn.plan(), tail_side=True)
+    outs = [eng.process(b) for b in blocks[:3]]
+    blob = eng.save_state()
+    rest = [eng.process(b) for b in blocks[3:]]
+    eng2 = Engine(scn.plan(), tail_side=True)
+    eng2.load_state(blob)
+    rest2 = [eng2.process(b) for b in blocks[3:]]
+    for x, y in zip(rest, rest2):
+        assert np.array_equal(x.ch_iq, y.ch_iq) and np.array_equal(x.pcm, y.pcm) and np.array_equal(x.sql, y.sql)
+    eng.close()
+    eng2.close()
+
+
 def test_full_band_960_channels_against_oracle():
     """SURVEY.md §8d config 3 at full width (960 channels), three blocks."""
     scn = sc.config3(n_blocks=3)
