@@ -13,7 +13,7 @@
 // avg' = a * avg + 0.01f * x with a = 1 - 0.01f.  The block is cut into 128-sample segments, one thread each, and
 // the recurrence is run in three short passes instead of one long one:
 //   k_fe_partial  every segment from avg = 0: B[k], so that the segment maps avg_in -> a^128 * avg_in + B[k];
-//   k_fe_scan     one warp composes those maps (double precision) into the avg at every segment start, starting
+//   k_fe_scan     one small CTA composes those maps into the avg at every segment start, starting
 //                 from the carried block-start avg -- right to a few ulp, not yet the reference's rounded sequence;
 //   k_fe_dc       every thread starts kFeBack = 3 segments early from that estimate and runs the reference's own
 //                 float recurrence: it is a contraction (0.99^384 = 0.02), so the few-ulp error dies out and the
@@ -103,25 +103,25 @@ k_fe_partial(const void *__restrict__ raw, int n, float *__restrict__ seg_b) {
 }
 
 // Pass 2: avg at every segment start, start[0] = the carried avg, start[k+1] = A * start[k] + B[k] (A = a^128),
-// composed by one warp in double precision: each lane folds a contiguous chunk, lane 0 chains the 32 chunks, every
-// lane re-walks its chunk from its chunk start.
-static __global__ void __launch_bounds__(32)
-k_fe_scan(const float *__restrict__ seg_b, int nseg, const float *__restrict__ avg_io, double A, float *__restrict__ seg_start) {
-    __shared__ double sa[32], sb[32], st[32];
+// composed by one CTA of 128 threads: each thread folds a contiguous chunk, thread 0 chains the 128 chunks, every
+// thread re-walks its chunk from its chunk start.  Single precision: the estimate only has to be right to a few ulp.
+static __global__ void __launch_bounds__(128)
+k_fe_scan(const float *__restrict__ seg_b, int nseg, const float *__restrict__ avg_io, float A, float *__restrict__ seg_start) {
+    __shared__ float sa[128], sb[128], st[128];
     const int lane = threadIdx.x;
-    const int m = (nseg + 31) / 32;
+    const int m = (nseg + 127) / 128;
     const int k0 = lane * m, k1 = min(nseg, k0 + m);
-    double a = 1.0, b = 0.0;
-    for (int k = k0; k < k1; ++k) { b = A * b + (double)seg_b[k]; a *= A; }
+    float a = 1.0f, b = 0.0f;
+    for (int k = k0; k < k1; ++k) { b = fmaf(A, b, seg_b[k]); a *= A; }
     sa[lane] = a; sb[lane] = b;
-    __syncwarp();
+    __syncthreads();
     if (lane == 0) {
-        double v = (double)avg_io[0];
-        for (int l = 0; l < 32; ++l) { st[l] = v; v = sa[l] * v + sb[l]; }
+        float v = avg_io[0];
+        for (int l = 0; l < 128; ++l) { st[l] = v; v = fmaf(sa[l], v, sb[l]); }
     }
-    __syncwarp();
-    double v = st[lane];
-    for (int k = k0; k < k1; ++k) { seg_start[k] = (float)v; v = A * v + (double)seg_b[k]; }
+    __syncthreads();
+    float v = st[lane];
+    for (int k = k0; k < k1; ++k) { seg_start[k] = v; v = fmaf(A, v, seg_b[k]); }
 }
 
 // Pass 3: remove_dc + translate_fs_4's sign / hbc pattern, segment-parallel.
@@ -194,17 +194,46 @@ k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n
 }
 
 // Half-band FIR on the even samples (fir_interleaved_24's order: k[0]*(q0+q23) + k[1]*(q1+q22) + ... left to right),
-// the odd samples through their 12-deep delay line.  One thread per IQ pair.
-static __global__ void __launch_bounds__(256)
+// the odd samples through their 12-deep delay line.  One thread per EIGHT consecutive IQ pairs: their windows overlap
+// in all but one sample each, so 32 even samples are read once (eight 16 B loads) instead of 192 separate ones.
+// Specialised for libairspy's kernel (len == 24 == kFeEvenHist: the window of pair p is ev[p .. p + 23] + the newest).
+static __global__ void __launch_bounds__(128)
 k_fe_iq(const float *__restrict__ ev, const float *__restrict__ od, int npair, const float *__restrict__ k, int len,
         float2 *__restrict__ out) {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= npair) return;
+    const int p0 = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    if (p0 >= npair) return;
+    if (len == 24 && p0 + 8 <= npair) {
+        float w[32];                                     // w[i] = ev[p0 + i]: the newest sample of pair p0 + j is w[24 + j]
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float4 v = *reinterpret_cast<const float4 *>(ev + p0 + 4 * i);
+            w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+        }
+        float kk[12];
+#pragma unroll
+        for (int i = 0; i < 12; ++i) kk[i] = __ldg(k + i);
+        const float4 o0 = *reinterpret_cast<const float4 *>(od + p0), o1 = *reinterpret_cast<const float4 *>(od + p0 + 4);
+        const float oq[8] = {o0.x, o0.y, o0.z, o0.w, o1.x, o1.y, o1.z, o1.w};
+        float2 y[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float acc = __fmul_rn(kk[0], __fadd_rn(w[24 + j], w[1 + j]));
+#pragma unroll
+            for (int i = 1; i < 12; ++i) acc = __fadd_rn(acc, __fmul_rn(kk[i], __fadd_rn(w[24 + j - i], w[1 + j + i])));
+            y[j] = make_float2(acc, oq[j]);              // od[kFeOddHist + p - 12] == od[p]
+        }
+        float4 *o4 = reinterpret_cast<float4 *>(out + p0);
+#pragma unroll
+        for (int j = 0; j < 8; j += 2) o4[j >> 1] = make_float4(y[j].x, y[j].y, y[j + 1].x, y[j + 1].y);
+        return;
+    }
     const int half = len >> 1;
-    const float *q = ev + kFeEvenHist + p;
-    float acc = __fmul_rn(__ldg(k), __fadd_rn(q[0], q[-(len - 1)]));
-    for (int i = 1; i < half; ++i) acc = __fadd_rn(acc, __fmul_rn(__ldg(k + i), __fadd_rn(q[-i], q[-(len - 1 - i)])));
-    out[p] = make_float2(acc, od[kFeOddHist + p - half]);
+    for (int p = p0; p < npair && p < p0 + 8; ++p) {
+        const float *q = ev + kFeEvenHist + p;
+        float acc = __fmul_rn(__ldg(k), __fadd_rn(q[0], q[-(len - 1)]));
+        for (int i = 1; i < half; ++i) acc = __fadd_rn(acc, __fmul_rn(__ldg(k + i), __fadd_rn(q[-i], q[-(len - 1 - i)])));
+        out[p] = make_float2(acc, od[kFeOddHist + p - half]);
+    }
 }
 
 // Block-to-block carries: the even / odd history prefixes and avg.
@@ -344,12 +373,12 @@ int fe_run(sdrx_airspy_fe *f, const void *d_raw, unsigned n) {
         const int whole = (int)(n / kFeSeg);
         if (packed) k_fe_partial<true><<<div_up(whole, 128), 128, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
         else        k_fe_partial<false><<<div_up(whole, 128), 128, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
-        k_fe_scan<<<1, 32, 0, f->st>>>(f->d_seg_b, whole, f->d_avg, f->A, f->d_seg_start);
+        k_fe_scan<<<1, 128, 0, f->st>>>(f->d_seg_b, whole, f->d_avg, (float)f->A, f->d_seg_start);
         f->launches += 2;
     }
     if (packed) k_fe_dc<true><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
     else        k_fe_dc<false><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
-    k_fe_iq<<<div_up(npair, 256), 256, 0, f->st>>>(f->d_ev, f->d_od, npair, f->d_k, f->len, f->d_iq[cur]);
+    k_fe_iq<<<div_up(div_up(npair, 8), 128), 128, 0, f->st>>>(f->d_ev, f->d_od, npair, f->d_k, f->len, f->d_iq[cur]);
     k_fe_carry<<<1, 64, 0, f->st>>>((int)n, f->d_ev, f->d_od, f->d_avg);
     CU(cudaGetLastError());
     CU(cudaEventRecord(f->ev_done, f->st));
