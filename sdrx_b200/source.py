@@ -128,25 +128,126 @@ class SyntheticSource(_SourceBase):
             yield self.block(b)
 
 
-class FileSource(_SourceBase):
-    """Replay of a raw capture: rtl_sdr u8 IQ (librtlsdr/src/rtl_sdr.c:113,:329), airspy_rx INT16_IQ /
-    FLOAT32_IQ (libairspy/airspy-tools/src/airspy_rx.c:481-482).  A trailing partial block is dropped,
-    as the device layer only ever emits whole 32 ms blocks."""
+WAV_HEADER_LEN = 44      # t_wav_file_hdr: RIFF(12) + 'fmt '(24) + 'data'(8)  (airspy_rx.c:126-159)
 
-    def __init__(self, path: str, rate: int, fmt: int, block_len: Optional[int] = None):
+# Sample kinds of a capture.  The IQ kinds go straight to Engine.push (wire formats FMT_*); the REAL kinds are the
+# ADC's 20 MS/s real stream and go through AirspyFrontEnd first (airspy.c:391-420, `airspy_rx -t 3|4|5`).
+KIND_IQ, KIND_REAL_U16, KIND_REAL_S16, KIND_REAL_PACKED12 = "iq", "real_u16", "real_s16", "real_packed12"
+
+
+@dataclass
+class WavInfo:
+    """The fields of airspy_rx's WAV header (airspy_rx.c:134-146, filled in at :1084-1096)."""
+    format_tag: int         # 1 = PCM16, 3 = float32
+    channels: int           # 2 = IQ, 1 = real
+    rate: int
+    bits: int
+    data_bytes: int
+    data_offset: int
+
+
+def read_wav_header(path: str) -> Optional[WavInfo]:
+    """Parses a RIFF/WAVE header (any chunk order, as SDR# writes extra chunks); None when the file is not RIFF."""
+    import struct
+    with open(path, "rb") as f:
+        head = f.read(12)
+        if len(head) < 12 or head[:4] != b"RIFF" or head[8:12] != b"WAVE":
+            return None
+        fmt = None
+        size = os.path.getsize(path)
+        while True:
+            ck = f.read(8)
+            if len(ck) < 8:
+                raise ValueError(f"{path}: WAV file without a data chunk")
+            cid, clen = ck[:4], struct.unpack("<I", ck[4:])[0]
+            if cid == b"fmt ":
+                body = f.read(clen + (clen & 1))
+                fmt = struct.unpack("<HHIIHH", body[:16])
+            elif cid == b"data":
+                if fmt is None:
+                    raise ValueError(f"{path}: WAV data chunk before the fmt chunk")
+                off = f.tell()
+                # a capture that was interrupted keeps chunkSize 0 (the header is patched on exit): trust the file
+                n = clen if 0 < clen <= size - off else size - off
+                return WavInfo(fmt[0], fmt[1], fmt[2], fmt[5], n, off)
+            else:
+                f.seek(clen + (clen & 1), os.SEEK_CUR)
+
+
+def wav_header(format_tag: int, channels: int, rate: int, bits: int, data_bytes: int) -> bytes:
+    """The 44-byte header airspy_rx writes (airspy_rx.c:161-190, :1080-1100)."""
+    import struct
+    align = channels * bits // 8
+    return (b"RIFF" + struct.pack("<I", (WAV_HEADER_LEN + data_bytes - 8) & 0xffffffff) + b"WAVE" + b"fmt "
+            + struct.pack("<IHHIIHH", 16, format_tag, channels, rate, (rate * align) & 0xffffffff, align, bits)
+            + b"data" + struct.pack("<I", data_bytes & 0xffffffff))
+
+
+class FileSource(_SourceBase):
+    """Replay of a capture: rtl_sdr raw u8 IQ (librtlsdr/src/rtl_sdr.c:113,:329); airspy_rx raw or WAV in INT16_IQ
+    (its default, airspy_rx.c:102) / FLOAT32_IQ (airspy_rx.c:374-387, :592-617); and airspy_rx's REAL sample types
+    (UINT16_REAL, INT16_REAL, RAW 12-bit packed: airspy.c:409-420, airspy_rx.c:389-409), whose blocks are ADC samples
+    at twice the IQ rate for :class:`AirspyFrontEnd`.  A WAV header is detected and skipped, and supplies format and
+    rate unless given.  A trailing partial block is dropped, as the device layer only ever emits whole 32 ms blocks."""
+
+    def __init__(self, path: str, rate: Optional[int] = None, fmt: Optional[int] = None, block_len: Optional[int] = None,
+                 kind: Optional[str] = None):
         super().__init__()
-        self.path, self.rate, self.fmt = path, rate, fmt
-        self.block_len = int(block_len or rate_config(rate).block_len)
-        self.dtype = {FMT_U8: np.uint8, FMT_S16: np.int16, FMT_F32: np.float32}[fmt]
-        self.n_blocks = os.path.getsize(path) // (self.block_len * 2 * np.dtype(self.dtype).itemsize)
+        self.path = path
+        self.wav = read_wav_header(path)
+        self.offset = 0
+        if self.wav is not None:
+            w = self.wav
+            self.offset = w.data_offset
+            if kind is None:
+                kind = KIND_IQ if w.channels == 2 else KIND_REAL_U16
+            if fmt is None and kind == KIND_IQ:
+                try:
+                    fmt = {(1, 16): FMT_S16, (3, 32): FMT_F32, (1, 8): FMT_U8}[(w.format_tag, w.bits)]
+                except KeyError:
+                    raise ValueError(f"{path}: unsupported WAV sample format tag {w.format_tag}, {w.bits} bits")
+            if rate is None:
+                rate = w.rate if w.channels == 2 else w.rate // 2     # a real capture carries the ADC rate
+        if rate is None:
+            raise ValueError("a raw capture carries no rate: pass rate=")
+        self.kind = kind or KIND_IQ
+        self.rate = int(rate)
+        self.block_len = int(block_len or rate_config(self.rate).block_len)
+        if self.kind == KIND_IQ:
+            if fmt is None:
+                raise ValueError("a raw IQ capture carries no sample format: pass fmt=")
+            self.fmt = fmt
+            self.dtype = {FMT_U8: np.uint8, FMT_S16: np.int16, FMT_F32: np.float32}[fmt]
+            self.items_per_block = self.block_len * 2
+        else:
+            self.fmt = FMT_F32                                   # what the front end hands the engine
+            self.dtype = {KIND_REAL_U16: np.uint16, KIND_REAL_S16: np.int16, KIND_REAL_PACKED12: np.uint32}[self.kind]
+            n_adc = self.block_len * 2                           # real samples per block
+            self.items_per_block = n_adc * 3 // 8 if self.kind == KIND_REAL_PACKED12 else n_adc
+        size = (self.wav.data_bytes if self.wav is not None else os.path.getsize(path) - self.offset)
+        self.n_blocks = size // (self.items_per_block * np.dtype(self.dtype).itemsize)
+
+    @property
+    def packed(self) -> bool:
+        return self.kind == KIND_REAL_PACKED12
 
     def blocks(self) -> Iterator[np.ndarray]:
         with open(self.path, "rb") as f:
+            f.seek(self.offset)
             for _ in range(self.n_blocks):
-                yield np.fromfile(f, dtype=self.dtype, count=self.block_len * 2)
+                blk = np.fromfile(f, dtype=self.dtype, count=self.items_per_block)
+                if self.kind == KIND_REAL_S16:
+                    # INT16_REAL is (adc - 2048) << 4 (airspy.c:58-61, :299-309, SAMPLE_SHIFT 4): undo it, exactly
+                    blk = ((blk >> 4) + 2048).astype(np.uint16)
+                yield blk
 
 
-def write_capture(path: str, src: SyntheticSource) -> None:
+def write_capture(path: str, src: _SourceBase, wav: bool = False) -> None:
+    """Writes ``src``'s blocks the way rtl_sdr / airspy_rx would: raw, or (``wav``) behind airspy_rx's WAV header."""
+    blocks = [np.ascontiguousarray(b) for b in src.blocks()]
     with open(path, "wb") as f:
-        for blk in src.blocks():
-            np.ascontiguousarray(blk).tofile(f)
+        if wav:
+            tag, bits = {FMT_S16: (1, 16), FMT_F32: (3, 32), FMT_U8: (1, 8)}[src.fmt]
+            f.write(wav_header(tag, 2, src.rate, bits, sum(b.nbytes for b in blocks)))
+        for blk in blocks:
+            blk.tofile(f)
