@@ -63,6 +63,9 @@ typedef enum { SDRX_FMT_U8 = 0, SDRX_FMT_S16 = 1, SDRX_FMT_F32 = 2 } sdrx_iq_for
 #define SDRX_FLAG_PARTIAL_MIX   0x4u  /* channel-sharded run: stop at mix_pre (this GPU's share of the pan
                                          mix); FIR2 + s16 run once, in sdrx_engine_finish_mix              */
 
+#define SDRX_MOD_AM 0       /* Modulation::AM (sdrx.cpp:151) */
+#define SDRX_MOD_FM 1       /* Modulation::FM */
+
 typedef struct sdrx_engine sdrx_engine;
 
 /* Everything sdrx.cpp:1584-1714 sets up per run.  Arrays are copied at creation. */
@@ -92,6 +95,9 @@ typedef struct {
     const float   *ramp_up;         /* [512] coeffs.hpp:2541                                       */
     const float   *ramp_down;       /* [512] coeffs.hpp:3064                                       */
     unsigned       flags;
+    const uint8_t *modulation;      /* [C] SDRX_MOD_AM / SDRX_MOD_FM: Channel::mod (sdrx.cpp:230, the
+                                       NNN.NNN/SQL/AM|FM channel syntax :1351-1358, --modulation :1197);
+                                       NULL -> AM.  FM is Demod::demod's discriminator (sdrx.cpp:181-194). */
 } sdrx_engine_config;
 
 /* Per-block outputs of boundary B.  Any pointer may be NULL. */

@@ -164,6 +164,8 @@ def _declare_oracle(lib: C.CDLL) -> None:
     lib.sdrxo_rx_demod.restype = None
     lib.sdrxo_rx_gains.argtypes = [C.c_void_p, c_float_p, c_float_p]
     lib.sdrxo_rx_gains.restype = None
+    lib.sdrxo_rx_set_modulation.argtypes = [C.c_void_p, c_int_p]
+    lib.sdrxo_rx_set_modulation.restype = None
     lib.sdrx_oracle_fft512.argtypes = [c_float_p, c_float_p]
     lib.sdrx_oracle_fft512.restype = None
 
@@ -223,6 +225,8 @@ def _declare_ref(lib: C.CDLL) -> None:
     lib.sdrxref_rx_destroy.restype = None
     lib.sdrxref_rx_pos.argtypes = [C.c_void_p, C.c_int]
     lib.sdrxref_rx_pos.restype = C.c_int
+    lib.sdrxref_rx_set_modulation.argtypes = [C.c_void_p, c_int_p]
+    lib.sdrxref_rx_set_modulation.restype = None
     lib.sdrxref_ingest.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_uint]
     lib.sdrxref_ingest.restype = C.c_float
     lib.sdrxref_rx_channelize.argtypes = [C.c_void_p, c_float_p]
@@ -544,7 +548,7 @@ class RefRx(_RxBase):
 
     def __init__(self, rate: int, offsets: Sequence[int], sql_levels: Optional[Sequence[float]] = None,
                  use_lf_agc: bool = False, lf_gain_db: float = 0.0, use_ftfir: bool = False,
-                 threaded: bool = False, backend: str = "ref"):
+                 threaded: bool = False, backend: str = "ref", modulation: Optional[Sequence[int]] = None):
         self.be = load_backend(backend)
         assert self.be.is_ref
         self.C = len(offsets)
@@ -556,6 +560,8 @@ class RefRx(_RxBase):
                                                1 if threaded else 0)
         if not self.h:
             raise ValueError(f"rate {rate} unsupported")
+        if modulation is not None:          # 0 AM / 1 FM per channel (Channel::mod, sdrx.cpp:230)
+            self.be.lib.sdrxref_rx_set_modulation(self.h, _i32(modulation).ctypes.data_as(c_int_p))
 
     def pos(self, ch: int) -> int:
         return int(self.be.lib.sdrxref_rx_pos(self.h, ch))
@@ -605,7 +611,7 @@ class OracleRx(_RxBase):
 
     def __init__(self, tables: dict, offsets: Sequence[int], sql_levels: Optional[Sequence[float]] = None,
                  pos: Optional[Sequence[int]] = None, use_lf_agc: bool = False, lf_gain_db: float = 0.0,
-                 use_ftfir: bool = False):
+                 use_ftfir: bool = False, modulation: Optional[Sequence[int]] = None):
         self.be = load_backend("oracle")
         lib = self.be.lib
         self.C = len(offsets)
@@ -633,6 +639,8 @@ class OracleRx(_RxBase):
         cfg.passband_shape, cfg.ramp_up, cfg.ramp_down = _fp(self._keep[8]), _fp(self._keep[9]), _fp(self._keep[10])
         self.h = lib.sdrxo_rx_create(C.byref(cfg))
         self.posv = posv
+        if modulation is not None:          # 0 AM / 1 FM per channel (Channel::mod, sdrx.cpp:230)
+            lib.sdrxo_rx_set_modulation(self.h, _i32(modulation).ctypes.data_as(c_int_p))
 
     def pos(self, ch: int) -> int:
         return int(self.posv[ch])

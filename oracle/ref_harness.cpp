@@ -136,7 +136,21 @@ struct RefChannel {
     int    sql_state = SQL_CLOSED;
     int    sql_state_prev = SQL_CLOSED;
     int    pos = 0;
+    int    mod = 0;                       // 0 AM, 1 FM (Channel::mod, sdrx.cpp:230)
+    iqsample_t prev{0.0f, 0.0f};          // Demod::prev_sample (sdrx.cpp:202)
 };
+
+// Demod::demod (sdrx.cpp:178-200) lives inside sdrx.cpp next to main() and cannot be included; this is the same
+// arithmetic on the reference's own iqsample_t (std::complex<float>) so that the C restatement's reading of
+// "complex / float" and of the atan2 arguments is checked against what the C++ library does.
+static float ref_demod(RefChannel &ch, iqsample_t v) {
+    if (ch.mod != 1) return std::abs(v);
+    const iqsample_t u = v / std::abs(v);
+    const float cross = u.imag() * ch.prev.real() - u.real() * ch.prev.imag();
+    const float dot = u.real() * ch.prev.real() + u.imag() * ch.prev.imag();
+    ch.prev = u;
+    return std::atan2(cross, dot);
+}
 
 struct RefRx {
     uint32_t rate = 0;
@@ -403,6 +417,12 @@ float sdrxref_ingest(void *p, const void *raw, int fmt, unsigned n_samples) {
     return 10 * std::log10(pwr_rms) - 3.0f;
 }
 
+void sdrxref_rx_set_modulation(void *p, const int *mod) {
+    auto *rx = reinterpret_cast<RefRx*>(p);
+    unsigned c = 0;
+    for (auto &ch : rx->channels) { ch.mod = mod ? mod[c] : 0; ++c; }
+}
+
 // Input side, sdrx.cpp:327-346: channelize the block already converted by
 // sdrxref_ingest() into the chunk [C][512].
 void sdrxref_rx_channelize(void *p, float *ch_iq_out /* [C][512][2] or NULL */) {
@@ -446,7 +466,7 @@ void sdrxref_rx_demod(void *p, float *audio, uint8_t *sql_state, float *snr_out,
         for (unsigned i = 0; i < CH_IQ_BUF_SIZE; ++i) {
             iqsample_t agc_adj_sample = ch.agc.adjust(iq_buffer[j]);
             if (ch.sql_state == SQL_OPEN) {
-                float s = std::abs(agc_adj_sample);          // Demod::demod AM, sdrx.cpp:178-180
+                float s = ref_demod(ch, agc_adj_sample);     // Demod::demod, sdrx.cpp:178-200
                 s = ch.agc_lf.adjust(s);
                 if (ch.sql_state_prev == SQL_CLOSED) {
                     s = ramp_up[i] * s;

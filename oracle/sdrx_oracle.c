@@ -481,6 +481,8 @@ typedef struct {
     sdrxo_lfagc agc_lf;
     float sql_level;
     int   sql_state, sql_state_prev, pos;
+    int   mod;                      /* 0 AM, 1 FM: Channel::mod (sdrx.cpp:230) */
+    cf    prev;                     /* Demod::prev_sample (sdrx.cpp:202), starts at (0, 0) */
 } chan_t;
 
 struct sdrxo_rx {
@@ -585,6 +587,23 @@ static inline void pan_mix(float *mix, unsigned i, int pos, float s) {
 
 static inline float norm2(cf z) { return z.re * z.re + z.im * z.im; }
 
+/* Demod::demod (sdrx.cpp:178-200).  AM: the envelope.  FM (flagged EXPERIMENTAL, sdrx.cpp:1197): the sample is
+ * normalised (std::complex<float> / float divides both parts), then the angle from the previous normalised sample
+ * to this one, atan2(q*pr - i*pi, i*pr + q*pi); prev_sample only moves when demod() is called, i.e. while the
+ * squelch is open (sdrx.cpp:459-461) -- the ramp-down block uses the envelope whatever the modulation (:500). */
+static inline float demod1(chan_t *ch, cf a) {
+    const float mag = hypotf(a.re, a.im);
+    if (ch->mod != 1) return mag;
+    const float i = a.re / mag, q = a.im / mag;
+    const float s = atan2f(q * ch->prev.re - i * ch->prev.im, i * ch->prev.re + q * ch->prev.im);
+    ch->prev.re = i; ch->prev.im = q;
+    return s;
+}
+
+void sdrxo_rx_set_modulation(sdrxo_rx *rx, const int *mod) {
+    for (int c = 0; c < rx->C; ++c) rx->ch[c].mod = mod ? mod[c] : 0;
+}
+
 /* sdrx.cpp:452-573 then :646-656 */
 void sdrxo_rx_demod(sdrxo_rx *rx, float *audio, uint8_t *sql_state, float *snr_out,
                     float *mix_pre, float *mix, int16_t *pcm) {
@@ -599,7 +618,7 @@ void sdrxo_rx_demod(sdrxo_rx *rx, float *audio, uint8_t *sql_state, float *snr_o
         for (unsigned i = 0; i < CH_IQ_BUF_SIZE; ++i) {
             cf a = agc_adjust1(&ch->agc, rx->chunk[j]);                 /* :457 */
             if (ch->sql_state == SQL_OPEN) {
-                float s = hypotf(a.re, a.im);                           /* :461, Demod :178-180 */
+                float s = demod1(ch, a);                                /* :461, Demod :178-200 */
                 s = lfagc_adjust1(&ch->agc_lf, s);                      /* :463 */
                 if (ch->sql_state_prev == SQL_CLOSED) s = rx->ramp_up[i] * s;   /* :466-468 */
                 pan_mix(audio_buffer_float, i, ch->pos, s);

@@ -107,6 +107,8 @@ void  sdrxo_rx_channelize(sdrxo_rx *, float *ch_iq_out);
 void  sdrxo_rx_demod(sdrxo_rx *, float *audio, uint8_t *sql_state, float *snr,
                      float *mix_pre, float *mix, int16_t *pcm);
 void  sdrxo_rx_gains(sdrxo_rx *, float *agc_gain, float *lf_gain);
+/* per-channel modulation, 0 AM (default) / 1 FM: Channel::mod, sdrx.cpp:230, :1351-1358 */
+void  sdrxo_rx_set_modulation(sdrxo_rx *, const int *mod);
 
 #ifdef __cplusplus
 }

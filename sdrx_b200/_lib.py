@@ -31,6 +31,7 @@ class EngineConfig(C.Structure):
         ("fir2_taps", c_float_p), ("fir2_ntaps", C.c_int),
         ("passband_shape", c_float_p), ("ramp_up", c_float_p), ("ramp_down", c_float_p),
         ("flags", C.c_uint),
+        ("modulation", c_u8_p),
     ]
 
 

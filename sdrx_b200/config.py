@@ -191,26 +191,38 @@ class ChannelPlan:
     offsets: List[int]
     sql_levels: List[float]
     pos: List[int] = field(default_factory=list)
+    modulation: List[str] = field(default_factory=list)     # "AM" / "FM" per channel (Channel::mod, sdrx.cpp:230); [] -> AM
 
     @classmethod
-    def from_names(cls, rate: int, args: Sequence[str], default_sql: float = 9.0) -> "ChannelPlan":
+    def from_names(cls, rate: int, args: Sequence[str], default_sql: float = 9.0, default_mod: str = "AM") -> "ChannelPlan":
+        """``default_mod`` is --modulation (sdrx.cpp:1197, :1358); a channel's own /AM|/FM suffix wins."""
         parsed = []
         for a in args:
             p = parse_channel_arg(a, default_sql)
             if p is None:
                 raise ValueError(f"Invalid channel given: {a}")
+            if not _CH_RE.match(a).group(3):
+                p = (p[0], p[1], default_mod)
             if p[0] not in [q[0] for q in parsed]:       # sdrx.cpp:1377-1380 de-duplicates
                 parsed.append(p)
         names = [p[0] for p in parsed]
         tuner = tuner_fq_for(names)
         offs = [channel_to_offset(n, tuner) for n in names]
         return cls(rate_config(rate), tuner, names, offs, [p[1] for p in parsed],
-                   [get_audio_pos(i, len(names)) for i in range(len(names))])
+                   [get_audio_pos(i, len(names)) for i in range(len(names))], [p[2] for p in parsed])
 
     @classmethod
     def from_offsets(cls, rate: int, offsets: Sequence[int], sql_levels: Optional[Sequence[float]] = None,
-                     tuner_fq: int = 122000000) -> "ChannelPlan":
+                     tuner_fq: int = 122000000, modulation: Optional[Sequence[str]] = None) -> "ChannelPlan":
         offs = [int(o) for o in offsets]
         return cls(rate_config(rate), tuner_fq, [offset_to_channel(o, tuner_fq) for o in offs], offs,
                    list(sql_levels) if sql_levels is not None else [9.0] * len(offs),
-                   [get_audio_pos(i, len(offs)) for i in range(len(offs))])
+                   [get_audio_pos(i, len(offs)) for i in range(len(offs))],
+                   list(modulation) if modulation is not None else [])
+
+    def modulation_codes(self) -> List[int]:
+        """0 AM / 1 FM per channel (SDRX_MOD_*)."""
+        mods = self.modulation or ["AM"] * len(self.offsets)
+        if len(mods) != len(self.offsets) or any(m not in ("AM", "FM") for m in mods):
+            raise ValueError("modulation must be 'AM' or 'FM' for every channel")
+        return [1 if m == "FM" else 0 for m in mods]

@@ -85,6 +85,7 @@ struct sdrx_engine {
     uint16_t *d_bitrev = nullptr;
     float *d_sql_level = nullptr;
     int *d_pos = nullptr;
+    uint8_t *d_mod = nullptr;             // [C] Channel::mod (sdrx.cpp:230)
     float *d_c_adj = nullptr, *d_fir_hist = nullptr;
     float *d_parts = nullptr;             // staging of the per-GPU partial mixes (sdrx_engine_finish_mix)
     size_t parts_cap = 0;
@@ -222,6 +223,7 @@ int reset_state(sdrx_engine *e) {
         CU(cudaMemsetAsync(e->st.sql_state, 0, C, e->s_main));
         CU(cudaMemsetAsync(e->st.sql_prev, 0, C, e->s_main));
         CU(cudaMemsetAsync(e->st.mixed, 0, C, e->s_main));
+        CU(cudaMemsetAsync(e->st.fm_prev, 0, C * sizeof(float2), e->s_main));
         CU(cudaMemsetAsync(e->d_fir_hist, 0, sizeof(float) * 2 * (size_t)std::max(e->fir2_ntaps - 1, 1), e->s_main));
         CU(cudaStreamSynchronize(e->s_main));   // the host vectors above die here
     }
@@ -268,6 +270,7 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) cudaFree(e->d_stage_in[s]);
     cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps); cudaFree(e->d_hk);
     cudaFree(e->st.agc_gain); cudaFree(e->st.agc_power); cudaFree(e->st.lf_gain); cudaFree(e->st.lf_power);
+    cudaFree(e->st.fm_prev); cudaFree(e->d_mod);
     cudaFree(e->st.sql_state); cudaFree(e->st.sql_prev); cudaFree(e->st.mixed);
     cudaFree(e->d_window); cudaFree(e->d_shape); cudaFree(e->d_ramp_up); cudaFree(e->d_ramp_down);
     cudaFree(e->d_twiddle); cudaFree(e->d_bitrev); cudaFree(e->d_sql_level); cudaFree(e->d_pos);
@@ -449,8 +452,17 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if ((rc = dalloc(&e->st.agc_gain, C)) || (rc = dalloc(&e->st.agc_power, C)) ||
             (rc = dalloc(&e->st.lf_gain, C)) || (rc = dalloc(&e->st.lf_power, C)) ||
             (rc = dalloc(&e->st.sql_state, C)) || (rc = dalloc(&e->st.sql_prev, C)) ||
-            (rc = dalloc(&e->st.mixed, C)))
+            (rc = dalloc(&e->st.mixed, C)) || (rc = dalloc(&e->st.fm_prev, C)) || (rc = dalloc(&e->d_mod, C)))
             return rc;
+        {
+            std::vector<uint8_t> mod(C, SDRX_MOD_AM);
+            for (int c = 0; c < C && cfg->modulation; ++c) {
+                if (cfg->modulation[c] > SDRX_MOD_FM) return fail(SDRX_ERR_ARG, "modulation must be SDRX_MOD_AM or SDRX_MOD_FM");
+                mod[c] = cfg->modulation[c];
+            }
+            if ((rc = upload(e->d_mod, mod.data(), C))) return rc;
+            e->st.mod = e->d_mod;
+        }
         std::vector<float> win(kChunk);
         sdrx_make_window(win.data());
         std::vector<float2> tw(kChunk / 2);
@@ -1100,7 +1112,8 @@ extern "C" int sdrx_engine_last_timing(sdrx_engine *e, float *bank_ms, float *bl
 // ------------------------------------------------------------------------------------------------
 // Carried state.  Layout: StateHeader, raw history (raw_hist * 8 bytes, wire format `fmt`), then for
 // each stage s >= 1 its [C][H-1] delay line, then AGC gain/power, LfAGC gain/power (float[C] each),
-// sql_state, sql_state_prev (u8[C] each) and the FIR2 ring as (ntaps-1) stereo frames, oldest first.
+// sql_state, sql_state_prev (u8[C] each), the FM demodulators' previous samples (float2[C]) and the FIR2 ring as
+// (ntaps-1) stereo frames, oldest first.
 namespace {
 
 struct StateHeader {
@@ -1118,7 +1131,7 @@ size_t state_bytes(const sdrx_engine *e) {
     size_t n = sizeof(StateHeader) + (size_t)e->raw_hist * 8;
     for (int s = 1; s < e->S; ++s) n += sizeof(float2) * (size_t)(e->H[s] - 1) * e->C;
     if (!(e->flags & SDRX_FLAG_NO_DEMOD))
-        n += (size_t)e->C * (4 * sizeof(float) + 2) + sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1);
+        n += (size_t)e->C * (4 * sizeof(float) + 2 + sizeof(float2)) + sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1);
     return n;
 }
 
@@ -1142,7 +1155,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     }
     uint8_t *p = (uint8_t *)buf;
     StateHeader h{};
-    h.magic = kStateMagic; h.version = 2;
+    h.magic = kStateMagic; h.version = 3;
     h.C = e->C; h.S = e->S; h.fmt = e->fmt; h.raw_hist = e->raw_hist; h.total = e->total; h.fir2_ntaps = e->fir2_ntaps;
     h.demod = (e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1;
     h.trans_pos = e->trans_pos; h.blocks = e->blocks;
@@ -1167,6 +1180,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
         CU(cudaMemcpy(p, e->st.lf_power, C * 4, cudaMemcpyDeviceToHost)); p += C * 4;
         CU(cudaMemcpy(p, e->st.sql_state, C, cudaMemcpyDeviceToHost)); p += C;
         CU(cudaMemcpy(p, e->st.sql_prev, C, cudaMemcpyDeviceToHost)); p += C;
+        CU(cudaMemcpy(p, e->st.fm_prev, C * sizeof(float2), cudaMemcpyDeviceToHost)); p += C * sizeof(float2);
         const size_t fb = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1);
         if (fb) CU(cudaMemcpy(p, e->d_fir_hist, fb, cudaMemcpyDeviceToHost));
         p += fb;
@@ -1179,7 +1193,7 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     if (size < sizeof(StateHeader)) return fail(SDRX_ERR_ARG, "state buffer too small");
     StateHeader h;
     memcpy(&h, buf, sizeof(h));
-    if (h.magic != kStateMagic || h.version != 2) return fail(SDRX_ERR_ARG, "not an sdrx_b200 state blob");
+    if (h.magic != kStateMagic || h.version != 3) return fail(SDRX_ERR_ARG, "not an sdrx_b200 state blob");
     if (h.C != e->C || h.S != e->S || h.raw_hist != e->raw_hist || h.fir2_ntaps != e->fir2_ntaps ||
         h.demod != ((e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1) || h.ftfir != (e->ftfir ? 1 : 0))
         return fail(SDRX_ERR_ARG, "state blob was saved by a differently configured engine");
@@ -1217,6 +1231,7 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
         CU(cudaMemcpy(e->st.lf_power, p, C * 4, cudaMemcpyHostToDevice)); p += C * 4;
         CU(cudaMemcpy(e->st.sql_state, p, C, cudaMemcpyHostToDevice)); p += C;
         CU(cudaMemcpy(e->st.sql_prev, p, C, cudaMemcpyHostToDevice)); p += C;
+        CU(cudaMemcpy(e->st.fm_prev, p, C * sizeof(float2), cudaMemcpyHostToDevice)); p += C * sizeof(float2);
         const size_t fb = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1);
         if (fb) CU(cudaMemcpy(e->d_fir_hist, p, fb, cudaMemcpyHostToDevice));
         p += fb;

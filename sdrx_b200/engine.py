@@ -100,6 +100,7 @@ class Engine:
         taps = np.concatenate([s[1] for s in rc_.stages]).astype(np.float32)
         sql = np.asarray(plan.sql_levels, dtype=np.float32)
         pos = np.asarray(plan.pos, dtype=np.int32)
+        mod = np.asarray(plan.modulation_codes(), dtype=np.uint8)
         fir2 = np.ascontiguousarray(t["coeff_bp4am_channel"], dtype=np.float32)
         shape = np.ascontiguousarray(t["passband_shape"], dtype=np.float32)
         rup = np.ascontiguousarray(t["ramp_up"], dtype=np.float32)
@@ -118,6 +119,7 @@ class Engine:
         cfg.block_len = self.block_len
         cfg.sql_level = fp(sql)
         cfg.pos = pos.ctypes.data_as(_lib.c_int_p)
+        cfg.modulation = mod.ctypes.data_as(_lib.c_u8_p)
         cfg.use_lf_agc = 1 if use_lf_agc else 0
         cfg.lf_gain_db = lf_gain_db
         cfg.fir2_taps, cfg.fir2_ntaps = fp(fir2), fir2.size

@@ -41,7 +41,7 @@ def shard_plan(plan: ChannelPlan, world: int, rank: int) -> ChannelPlan:
     (get_audio_pos(idx, n) depends on both, sdrx.cpp:1712), so they are sliced, not recomputed."""
     lo, hi = channel_range(len(plan.offsets), world, rank)
     return ChannelPlan(plan.rate, plan.tuner_fq, plan.names[lo:hi], plan.offsets[lo:hi], plan.sql_levels[lo:hi],
-                       plan.pos[lo:hi])
+                       plan.pos[lo:hi], plan.modulation[lo:hi])
 
 
 @dataclass

@@ -39,6 +39,7 @@ class Carrier:
     depth: float = 0.5                  # AM depth
     on: Optional[Callable[[int], bool]] = None   # block index -> keyed?  None = always on
     df_hz: float = 0.0                  # carrier offset inside the channel
+    fm_dev_hz: float = 0.0              # FM: peak deviation of the tone (0 = none); use depth=0 for pure FM
 
 
 def quantize(x: np.ndarray, fmt: int) -> np.ndarray:
@@ -112,6 +113,8 @@ class SyntheticSource(_SourceBase):
             ph = 2.0 * np.pi * (((c.offset * self.cfg.z) * n) % N).astype(np.float64) / N
             if c.df_hz:
                 ph = ph + 2.0 * np.pi * c.df_hz * t
+            if c.fm_dev_hz:             # phase = integral of 2 pi dev cos(2 pi f t)
+                ph = ph + (c.fm_dev_hz / c.tone_hz) * np.sin(2.0 * np.pi * c.tone_hz * t)
             env = c.amp * (1.0 + c.depth * np.sin(2.0 * np.pi * c.tone_hz * t))
             x += env * np.exp(1j * ph)
         _ = step_hz

@@ -48,3 +48,4 @@ if __name__ == "__main__":
     emit(sc.config2(), [0, 3, 4, 7, 11])
     emit(sc.config2(sc.FMT_S16, 4), [0, 3])
     emit(sc.centre_channel(), [0, 2])
+    emit(sc.fm_scenarios()[0], [1, 3, 4, 6])      # FM + AM channels: open, noise while open, ramp-down, re-open

@@ -25,8 +25,9 @@ def product_tables(rate: int) -> dict:
 def make_cpu_rx(scn: Scenario, backend: str = "oracle", threaded: bool = False):
     if backend == "oracle":
         return ob.OracleRx(product_tables(scn.rate), scn.offsets, scn.sql_levels, None, scn.use_lf_agc, scn.lf_gain_db,
-                           scn.use_ftfir)
-    return ob.RefRx(scn.rate, scn.offsets, scn.sql_levels, scn.use_lf_agc, scn.lf_gain_db, scn.use_ftfir, threaded, backend)
+                           scn.use_ftfir, scn.mod_codes())
+    return ob.RefRx(scn.rate, scn.offsets, scn.sql_levels, scn.use_lf_agc, scn.lf_gain_db, scn.use_ftfir, threaded, backend,
+                    scn.mod_codes())
 
 
 def run_cpu(scn: Scenario, backend: str = "oracle", blocks: Optional[List[np.ndarray]] = None) -> List[ob.BlockOut]:

@@ -24,9 +24,13 @@ class Scenario:
     use_lf_agc: bool = False
     lf_gain_db: float = 0.0
     use_ftfir: bool = False         # --ftfir (sdrx.cpp:1199): msd.hpp:104-131
+    modulation: Optional[List[str]] = None   # "AM"/"FM" per channel (sdrx.cpp:230); None -> AM
+
+    def mod_codes(self) -> Optional[List[int]]:
+        return None if self.modulation is None else [1 if m == "FM" else 0 for m in self.modulation]
 
     def plan(self) -> ChannelPlan:
-        return ChannelPlan.from_offsets(self.rate, self.offsets, self.sql_levels)
+        return ChannelPlan.from_offsets(self.rate, self.offsets, self.sql_levels, modulation=self.modulation)
 
     def source(self) -> SyntheticSource:
         return SyntheticSource(self.rate, self.carriers, self.noise_sigma, self.seed, self.fmt, self.n_blocks)
@@ -78,6 +82,27 @@ def ftfir_scenarios() -> List[Scenario]:
     c.name += "_ftfir"
     for s in (a, b, c):
         s.use_ftfir = True
+    return [a, b, c]
+
+
+def fm_scenarios() -> List[Scenario]:
+    """--modulation FM / NNN.NNN/SQL/FM (sdrx.cpp:1197, :1351-1358; Demod::demod :181-194): FM and AM channels mixed in
+    one run, FM carriers keyed so that open -> ramp-down (envelope, :500) -> closed -> open again (prev_sample kept
+    from the last open block) are all walked; one with the LfAGC active."""
+    offs = [-300, -37, 2, 121, 400, 0]
+    mods = ["FM", "AM", "FM", "FM", "AM", "FM"]
+    car = [Carrier(-300, 0.08, 800.0, 0.0, _window(0, 3), fm_dev_hz=2500.0),
+           Carrier(-37, 0.05, 1000.0, 0.5, _window(1, 99)),
+           Carrier(2, 0.1, 1500.0, 0.0, _window(1, 99), fm_dev_hz=1200.0),
+           Carrier(121, 0.03, 400.0, 0.2, lambda b: b in (0, 1, 4, 5), fm_dev_hz=3000.0),
+           Carrier(400, 0.06, 2000.0, 0.5, _window(0, 4)),
+           Carrier(0, 0.04, 600.0, 0.0, _window(2, 5), fm_dev_hz=800.0)]
+    a = Scenario("fm_mixed_10000", 10000000, offs, car, n_blocks=7, noise_sigma=0.002, modulation=mods)
+    b = Scenario("fm_mixed_10000_lfagc", 10000000, offs, car, n_blocks=7, noise_sigma=0.002, modulation=mods,
+                 use_lf_agc=True, lf_gain_db=3.0)
+    c = Scenario("fm_rtl_2400_u8", 2400000, [-3, 9], [Carrier(-3, 0.4, 1000.0, 0.0, _window(1, 6), fm_dev_hz=2000.0),
+                                                       Carrier(9, 0.2, 700.0, 0.0, fm_dev_hz=1500.0)],
+                 fmt=FMT_U8, n_blocks=8, modulation=["FM", "FM"])
     return [a, b, c]
 
 

@@ -27,9 +27,30 @@ def _assert_blocks_equal(a, b):
         assert np.array_equal(x.pcm, y.pcm), f"block {i} pcm"
 
 
+def test_fm_discriminator_recovers_the_tone():
+    """Demod::demod FM (sdrx.cpp:181-194): a carrier with peak deviation d and tone f demodulates to a sine of
+    amplitude 2 pi d / 16000 at f; the block after the carrier drops (squelch still open) is full-scale phase noise;
+    the ramp-down block after that is the envelope, not the angle (sdrx.cpp:500)."""
+    scn = sc.fm_scenarios()[0]
+    outs = run_cpu(scn, "oracle")
+    au = np.stack([o.audio for o in outs])
+    sql = np.stack([o.sql for o in outs])
+    for c, (dev, tone, blk) in {0: (2500.0, 800.0, 2), 2: (1200.0, 1500.0, 4)}.items():
+        x = au[blk, c].astype(np.float64)
+        assert sql[blk - 1, c] == 1 and sql[blk, c] == 1
+        spec = np.abs(np.fft.rfft(x * np.hanning(512)))
+        assert abs(np.argmax(spec) * (16000.0 / 512) - tone) <= 16000.0 / 512
+        assert abs(np.max(np.abs(x)) - 2 * np.pi * dev / 16000.0) < 0.03
+    assert sql[2, 0] == 1 and sql[3, 0] == 0               # carrier 0 is keyed off from block 3
+    assert np.max(np.abs(au[3, 0])) > 3.0                  # demodulated while still open: noise over the full +-pi
+    assert 0.0 < np.max(np.abs(au[4, 0])) < 0.05           # ramp-down: the (small) envelope
+    assert np.all(au[5, 0] == 0.0)
+
+
 @needs_ref
 @pytest.mark.parametrize("scn", [sc.config1(), sc.config2(n_blocks=6), sc.config2(sc.FMT_S16, 3), sc.centre_channel()]
-                         + sc.config2_variants() + sc.other_rates() + sc.ftfir_scenarios(), ids=lambda s: s.name)
+                         + sc.config2_variants() + sc.other_rates() + sc.ftfir_scenarios() + sc.fm_scenarios(),
+                         ids=lambda s: s.name)
 def test_restatement_is_bit_exact_with_reference_build(scn):
     src = scn.source()
     blocks = [src.block(b) for b in range(scn.n_blocks)]
@@ -37,7 +58,8 @@ def test_restatement_is_bit_exact_with_reference_build(scn):
 
 
 @pytest.mark.parametrize("scn,name", [(sc.config1(), None), (sc.config2(), None), (sc.config2(sc.FMT_S16, 4), None),
-                                      (sc.centre_channel(), None)], ids=lambda v: getattr(v, "name", ""))
+                                      (sc.centre_channel(), None), (sc.fm_scenarios()[0], None)],
+                         ids=lambda v: getattr(v, "name", ""))
 def test_oracle_reproduces_golden_vectors(scn, name):
     z = np.load(os.path.join(GOLDEN, scn.name + ".npz"))
     src = scn.source()
@@ -179,5 +201,12 @@ def test_channel_name_helpers_agree_between_oracle_and_host_mirror():
     plan = cf.ChannelPlan.from_names(10000000, ["118.105/12", "121.500", "121.500", "125.230/0/AM"])
     assert plan.names == ["118.105", "121.500", "125.230"] and plan.sql_levels == [12.0, 9.0, 0.0]
     assert plan.tuner_fq == 121700000
+    assert plan.modulation == ["AM", "AM", "AM"] and plan.modulation_codes() == [0, 0, 0]
+    # NNN.NNN/SQL/AM|FM and --modulation as the default for channels without a suffix (sdrx.cpp:1197, :1351-1366)
+    fm = cf.ChannelPlan.from_names(10000000, ["118.105/12/FM", "121.500", "125.230/0/AM"], default_mod="FM")
+    assert fm.modulation == ["FM", "FM", "AM"] and fm.modulation_codes() == [1, 1, 0]
+    assert cf.ChannelPlan.from_offsets(10000000, [1, 2]).modulation_codes() == [0, 0]
+    with pytest.raises(ValueError):
+        cf.ChannelPlan.from_offsets(10000000, [1, 2], modulation=["FM"]).modulation_codes()
     for off in range(-480, 480, 11):
         assert cf.channel_to_offset(cf.offset_to_channel(off, 122000000), 122000000) == off
