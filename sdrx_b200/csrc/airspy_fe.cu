@@ -36,6 +36,8 @@ namespace {
 
 constexpr int kFeSeg = 128;          // real samples per thread of k_fe_dc
 constexpr int kFeBack = 3;           // warm-up segments in front of a thread's own
+constexpr int kFeThreads = 128;      // CTA size of the block-wide passes
+constexpr int kFeMaxCtas = 1 << 20;  // ... and their largest grid (the passes walk the block with a grid stride): see fe_run
 constexpr int kFeEvenHist = 24;      // >= len - 1 = 23 rotated even samples carried between blocks
 constexpr int kFeOddHist = 12;       // len / 2 delayed odd samples
 constexpr int kFeMaxLen = 64;
@@ -72,77 +74,14 @@ __device__ __forceinline__ float dc_step(float x, float &avg) {
     return s;
 }
 
-// Pass 1: the recurrence over one segment from avg = 0 (the additive term of the segment's affine map).
-template <bool PACKED>
-static __global__ void __launch_bounds__(128)
-k_fe_partial(const void *__restrict__ raw, int n, float *__restrict__ seg_b) {
-    const int seg = blockIdx.x * blockDim.x + threadIdx.x;
-    const long s0 = (long)seg * kFeSeg;
-    if (s0 + kFeSeg > n) return;                      // only whole segments feed the scan (the last start needs no successor)
-    float avg = 0.0f;
-    uint4 q[kFeSeg / 8];
-#pragma unroll
-    for (int j = 0; j < kFeSeg / 8; ++j) {
-        if constexpr (PACKED) {
-            int v[8];
-            load_adc8<true>(raw, s0 + 8 * j, v);
-            q[j] = make_uint4(v[0] | (v[1] << 16), v[2] | (v[3] << 16), v[4] | (v[5] << 16), v[6] | (v[7] << 16));
-        } else {
-            q[j] = __ldg(reinterpret_cast<const uint4 *>(reinterpret_cast<const uint16_t *>(raw) + s0 + 8 * j));
-        }
-    }
-#pragma unroll
-    for (int j = 0; j < kFeSeg / 8; ++j) {
-        const int v[8] = {(int)(q[j].x & 0xffff), (int)(q[j].x >> 16), (int)(q[j].y & 0xffff), (int)(q[j].y >> 16),
-                          (int)(q[j].z & 0xffff), (int)(q[j].z >> 16), (int)(q[j].w & 0xffff), (int)(q[j].w >> 16)};
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-            dc_step(__fmul_rn(__fsub_rn(__int_as_float(0x4B000000 | v[k]), 8390656.0f), 1.0f / 2048.0f), avg);
-    }
-    seg_b[seg] = avg;
-}
-
-// Pass 2: avg at every segment start, start[0] = the carried avg, start[k+1] = A * start[k] + B[k] (A = a^128),
-// composed by one CTA of 128 threads: each thread folds a contiguous chunk, thread 0 chains the 128 chunks, every
-// thread re-walks its chunk from its chunk start.  Single precision: the estimate only has to be right to a few ulp.
-static __global__ void __launch_bounds__(128)
-k_fe_scan(const float *__restrict__ seg_b, int nseg, const float *__restrict__ avg_io, float A, float *__restrict__ seg_start) {
-    __shared__ float sa[128], sb[128], st[128];
-    const int lane = threadIdx.x;
-    const int m = (nseg + 127) / 128;
-    const int k0 = lane * m, k1 = min(nseg, k0 + m);
-    float a = 1.0f, b = 0.0f;
-    for (int k = k0; k < k1; ++k) { b = fmaf(A, b, seg_b[k]); a *= A; }
-    sa[lane] = a; sb[lane] = b;
-    __syncthreads();
-    if (lane == 0) {
-        float v = avg_io[0];
-        for (int l = 0; l < 128; ++l) { st[l] = v; v = fmaf(sa[l], v, sb[l]); }
-    }
-    __syncthreads();
-    float v = st[lane];
-    for (int k = k0; k < k1; ++k) { seg_start[k] = v; v = fmaf(A, v, seg_b[k]); }
-}
-
-// Pass 3: remove_dc + translate_fs_4's sign / hbc pattern, segment-parallel.
-//   raw        this block, wire format, n samples (n % 8 == 0)
-//   seg_start  estimate of avg at every segment start (k_fe_scan)
-//   avg_io     [0] avg at the block start (in), [1] avg at the block end (out)
-//   ev / od    rotated even / odd samples of the block, behind their carried history prefixes
-template <bool PACKED>
-static __global__ void __launch_bounds__(128)
-k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n, float *__restrict__ avg_io,
-        float hbc, float *__restrict__ ev, float *__restrict__ od, int exact) {
-    const int seg = blockIdx.x * blockDim.x + threadIdx.x;
-    const long s0 = exact ? 0 : (long)seg * kFeSeg;
-    if (s0 >= n || (exact && seg != 0)) return;
-    const long s1 = exact ? n : (s0 + kFeSeg < n ? s0 + kFeSeg : n);
-    const int kb = (exact || seg <= kFeBack) ? 0 : seg - kFeBack;      // segment the warm-up starts at
-    const long w0 = (long)kb * kFeSeg;
-    float avg = kb == 0 ? avg_io[0] : seg_start[kb];                   // from the block start the trajectory is the exact one
-    // Groups of eight samples travel through a ring of registers, fetched kFeAhead groups (64 samples, ~770 cycles of
-    // the recurrence) ahead of their use: the loads do not depend on the recurrence, so its dependent chain never
-    // waits for memory.  A ring slot holds the eight samples as four words of two uint16 each, whatever the wire format.
+// remove_dc over samples [w0, s1) of the block starting from `avg`; with EMIT, the samples from s0 on also go through
+// translate_fs_4's sign / hbc pattern into ev / od.  Groups of eight samples travel through a ring of registers,
+// fetched kFeAhead groups (64 samples, ~770 cycles of the recurrence) ahead of their use: the loads do not depend on
+// the recurrence, so its dependent chain never waits for memory.  A ring slot holds the eight samples as four words
+// of two uint16 each, whatever the wire format.
+template <bool PACKED, bool EMIT>
+__device__ __forceinline__ float fe_walk(const void *__restrict__ raw, long w0, long s0, long s1, float avg, float hbc,
+                                         float *__restrict__ ev, float *__restrict__ od) {
     constexpr int kFeAhead = 8;
     auto fetch = [&](long i) -> uint4 {
         if (i >= s1) return make_uint4(0, 0, 0, 0);
@@ -176,7 +115,7 @@ k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n
                     x[k] = __fmul_rn(__fsub_rn(__int_as_float(0x4B000000 | v[k]), 8390656.0f), 1.0f / 2048.0f);
 #pragma unroll
                 for (int k = 0; k < 8; ++k) s[k] = dc_step(x[k], avg);
-                if (i >= s0) {
+                if (EMIT && i >= s0) {
                     // translate_fs_4 (iqconverter_float.c:489-498): [-s0, -s1*hbc, s2, s3*hbc] per group of four
                     const long p = i >> 1;
                     float4 e, o;
@@ -190,18 +129,74 @@ k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n
             }
         }
     }
-    if (s1 == n) avg_io[1] = avg;
+    return avg;
+}
+
+// Pass 1: the recurrence over one segment from avg = 0 (the additive term of the segment's affine map).
+template <bool PACKED>
+static __global__ void __launch_bounds__(kFeThreads)
+k_fe_partial(const void *__restrict__ raw, int n, float *__restrict__ seg_b) {
+    const int whole = n / kFeSeg;                   // only whole segments feed the scan (the last start needs no successor)
+    for (int seg = blockIdx.x * blockDim.x + threadIdx.x; seg < whole; seg += gridDim.x * blockDim.x) {
+        const long s0 = (long)seg * kFeSeg;
+        seg_b[seg] = fe_walk<PACKED, false>(raw, s0, s0, s0 + kFeSeg, 0.0f, 0.0f, nullptr, nullptr);
+    }
+}
+
+// Pass 2: avg at every segment start, start[0] = the carried avg, start[k+1] = A * start[k] + B[k] (A = a^kFeSeg),
+// composed by one CTA of 128 threads: each thread folds a contiguous chunk, thread 0 chains the 128 chunks, every
+// thread re-walks its chunk from its chunk start.  Single precision: the estimate only has to be right to a few ulp.
+static __global__ void __launch_bounds__(128)
+k_fe_scan(const float *__restrict__ seg_b, int nseg, const float *__restrict__ avg_io, float A, float *__restrict__ seg_start) {
+    __shared__ float sa[128], sb[128], st[128];
+    const int lane = threadIdx.x;
+    const int m = (nseg + 127) / 128;
+    const int k0 = lane * m, k1 = min(nseg, k0 + m);
+    float a = 1.0f, b = 0.0f;
+    for (int k = k0; k < k1; ++k) { b = fmaf(A, b, seg_b[k]); a *= A; }
+    sa[lane] = a; sb[lane] = b;
+    __syncthreads();
+    if (lane == 0) {
+        float v = avg_io[0];
+        for (int l = 0; l < 128; ++l) { st[l] = v; v = fmaf(sa[l], v, sb[l]); }
+    }
+    __syncthreads();
+    float v = st[lane];
+    for (int k = k0; k < k1; ++k) { seg_start[k] = v; v = fmaf(A, v, seg_b[k]); }
+}
+
+// Pass 3: remove_dc + translate_fs_4's sign / hbc pattern, segment-parallel.
+//   raw        this block, wire format, n samples (n % 8 == 0)
+//   seg_start  estimate of avg at every segment start (k_fe_scan)
+//   avg_io     [0] avg at the block start (in), [1] avg at the block end (out)
+//   ev / od    rotated even / odd samples of the block, behind their carried history prefixes
+template <bool PACKED>
+static __global__ void __launch_bounds__(kFeThreads)
+k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n, float *__restrict__ avg_io,
+        float hbc, float *__restrict__ ev, float *__restrict__ od, int exact) {
+    const int gt = blockIdx.x * blockDim.x + threadIdx.x;
+    if (exact) {
+        if (gt == 0) avg_io[1] = fe_walk<PACKED, true>(raw, 0, 0, n, avg_io[0], hbc, ev, od);
+        return;
+    }
+    for (int seg = gt; (long)seg * kFeSeg < n; seg += gridDim.x * blockDim.x) {
+        const long s0 = (long)seg * kFeSeg;
+        const long s1 = s0 + kFeSeg < n ? s0 + kFeSeg : n;
+        const int kb = seg <= kFeBack ? 0 : seg - kFeBack;              // segment the warm-up starts at
+        const float avg0 = kb == 0 ? avg_io[0] : seg_start[kb];         // from the block start the trajectory is the exact one
+        const float avg = fe_walk<PACKED, true>(raw, (long)kb * kFeSeg, s0, s1, avg0, hbc, ev, od);
+        if (s1 == n) avg_io[1] = avg;
+    }
 }
 
 // Half-band FIR on the even samples (fir_interleaved_24's order: k[0]*(q0+q23) + k[1]*(q1+q22) + ... left to right),
 // the odd samples through their 12-deep delay line.  One thread per EIGHT consecutive IQ pairs: their windows overlap
 // in all but one sample each, so 32 even samples are read once (eight 16 B loads) instead of 192 separate ones.
 // Specialised for libairspy's kernel (len == 24 == kFeEvenHist: the window of pair p is ev[p .. p + 23] + the newest).
-static __global__ void __launch_bounds__(128)
+static __global__ void __launch_bounds__(kFeThreads)
 k_fe_iq(const float *__restrict__ ev, const float *__restrict__ od, int npair, const float *__restrict__ k, int len,
         float2 *__restrict__ out) {
-    const int p0 = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
-    if (p0 >= npair) return;
+  for (int p0 = (blockIdx.x * blockDim.x + threadIdx.x) * 8; p0 < npair; p0 += gridDim.x * blockDim.x * 8) {
     if (len == 24 && p0 + 8 <= npair) {
         float w[32];                                     // w[i] = ev[p0 + i]: the newest sample of pair p0 + j is w[24 + j]
 #pragma unroll
@@ -225,7 +220,7 @@ k_fe_iq(const float *__restrict__ ev, const float *__restrict__ od, int npair, c
         float4 *o4 = reinterpret_cast<float4 *>(out + p0);
 #pragma unroll
         for (int j = 0; j < 8; j += 2) o4[j >> 1] = make_float4(y[j].x, y[j].y, y[j + 1].x, y[j + 1].y);
-        return;
+        continue;
     }
     const int half = len >> 1;
     for (int p = p0; p < npair && p < p0 + 8; ++p) {
@@ -234,6 +229,7 @@ k_fe_iq(const float *__restrict__ ev, const float *__restrict__ od, int npair, c
         for (int i = 1; i < half; ++i) acc = __fadd_rn(acc, __fmul_rn(__ldg(k + i), __fadd_rn(q[-i], q[-(len - 1 - i)])));
         out[p] = make_float2(acc, od[kFeOddHist + p - half]);
     }
+  }
 }
 
 // Block-to-block carries: the even / odd history prefixes and avg.
@@ -369,16 +365,21 @@ int fe_run(sdrx_airspy_fe *f, const void *d_raw, unsigned n) {
     const int cur = (int)(f->calls & 1);
     const int segs = exact ? 1 : div_up(n, kFeSeg);
     const int npair = (int)(n / 2);
+    // Measured on B200 (profiles/r01v_frontend_narrow.txt): confining the passes to 4 CTAs of 512 threads with
+    // 512-sample segments -- so that they would fit into the SMs a 143-CTA bank launch leaves free -- makes every
+    // recurrence step ~200 cycles (40 warps of 1 KB-strided 16 B loads, nothing to hide their latency behind):
+    // 365 us per block instead of 43.  The wide grid stays; the passes keep their grid-stride form.
+    auto grid = [](int tasks) { return std::max(1, std::min(kFeMaxCtas, div_up(tasks, kFeThreads))); };
     if (!exact && segs > kFeBack + 1) {
         const int whole = (int)(n / kFeSeg);
-        if (packed) k_fe_partial<true><<<div_up(whole, 128), 128, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
-        else        k_fe_partial<false><<<div_up(whole, 128), 128, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
+        if (packed) k_fe_partial<true><<<grid(whole), kFeThreads, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
+        else        k_fe_partial<false><<<grid(whole), kFeThreads, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
         k_fe_scan<<<1, 128, 0, f->st>>>(f->d_seg_b, whole, f->d_avg, (float)f->A, f->d_seg_start);
         f->launches += 2;
     }
-    if (packed) k_fe_dc<true><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
-    else        k_fe_dc<false><<<div_up(segs, 128), 128, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
-    k_fe_iq<<<div_up(div_up(npair, 8), 128), 128, 0, f->st>>>(f->d_ev, f->d_od, npair, f->d_k, f->len, f->d_iq[cur]);
+    if (packed) k_fe_dc<true><<<grid(segs), kFeThreads, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
+    else        k_fe_dc<false><<<grid(segs), kFeThreads, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
+    k_fe_iq<<<grid(div_up(npair, 8)), kFeThreads, 0, f->st>>>(f->d_ev, f->d_od, npair, f->d_k, f->len, f->d_iq[cur]);
     k_fe_carry<<<1, 64, 0, f->st>>>((int)n, f->d_ev, f->d_od, f->d_avg);
     CU(cudaGetLastError());
     CU(cudaEventRecord(f->ev_done, f->st));
