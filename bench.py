@@ -342,6 +342,17 @@ def run_ours(args):
     if os.path.exists(prof):
         with open(prof) as f:
             roofline["traffic"] = json.load(f).get("bank_dram_bytes_per_launch")
+    # the HBM view of the same kernel, for completeness (the path is FP32-bound, HBM is irrelevant):
+    # algorithmic bytes per launch = the block read once + the stage-3 rows written once
+    mp = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    hbm_peak = None
+    if os.path.exists(mp):
+        with open(mp) as f:
+            hbm_peak = json.load(f).get("hbm_gbs")
+    alg_bytes = L * 8 + C_ * (L // 125) * 8
+    roofline["hbm"] = {"algorithmic_bytes_per_launch": alg_bytes, "achieved": alg_bytes / (bank_ms * 1e-3) / 1e9,
+                       "peak": hbm_peak, "unit": "GB/s",
+                       "frac": (alg_bytes / (bank_ms * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None}
 
     # ---- e2e leg: pinned host IQ in, pinned host results out, through the C ABI, every step
     pins = [PinnedBuffer(blk_bytes) for _ in range(n_distinct)]

@@ -15,7 +15,7 @@ import pytest
 from oracle import bindings as ob
 from sdrx_b200 import config as cf
 from tests import scenarios as sc
-from tests.harness import AUDIO_TOL, digest, rel_rms, run_cpu, run_engine, squelch_margin
+from tests.harness import AUDIO_TOL, digest, product_tables, rel_rms, run_cpu, run_engine, squelch_margin
 
 pytestmark = pytest.mark.gpu
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
@@ -253,6 +253,47 @@ def test_full_band_960_channels_against_oracle():
     eng = Engine(scn.plan())
     assert eng.bank_pairs == 479          # offsets -479..479 pair up; -480 and 0 ride alone
     eng.close()
+
+
+def test_long_run_full_band_sample_of_channels_against_oracle():
+    """SURVEY.md §8d config 5 in miniature: 40 blocks (1.28 s of band, enough for the translator position, the AGCs
+    and every delay line to wrap many times) through the 960-channel engine; channels are independent given the
+    block, so a sample of them -- both band edges, the centre, a conjugate pair, keyed carriers -- is
+    checked against the oracle run on just those channels.  The mix depends on all 960 channels and is not compared."""
+    from sdrx_b200 import Engine
+    rate, n_blocks = 10000000, 40
+    offs = list(range(-480, 480))
+    sample = [-480, -479, -123, -37, -1, 0, 1, 37, 200, 333, 478, 479]
+    key = {-479: lambda b: (b // 3) % 2 == 0, -37: lambda b: b % 7 < 4, 37: lambda b: b % 5 != 0, 0: lambda b: 10 <= b < 30,
+           200: lambda b: b % 11 < 9, 479: lambda b: b >= 2}
+    car = [sc.Carrier(o, 0.01 + 0.004 * i, 400.0 + 210.0 * i, 0.5, k) for i, (o, k) in enumerate(key.items())]
+    car += [sc.Carrier(o, 0.03, 1000.0 + o, 0.4) for o in (-400, -250, 90, 410)]        # strong neighbours elsewhere in the band
+    src = sc.SyntheticSource(rate, car, 0.0008, 4242, sc.FMT_F32, n_blocks)
+    orx = ob.OracleRx(product_tables(rate), sample)
+    eng = Engine(sc.ChannelPlan.from_offsets(rate, offs))
+    idx = [offs.index(o) for o in sample]
+    worst_iq, worst_au, transitions, prev = 0.0, 0.0, 0, None
+    for b in range(n_blocks):
+        blk = src.block(b)
+        want = orx.process(blk, sc.FMT_F32)
+        got = eng.process(blk, sc.FMT_F32)
+        assert np.array_equal(got.sql[idx], want.sql), f"block {b}: squelch decisions differ"
+        if prev is not None:
+            transitions += int(np.sum(prev != want.sql))
+        prev = want.sql.copy()
+        for j, c in enumerate(idx):
+            e = rel_rms(got.ch_iq[c], want.ch_iq[j])
+            worst_iq = max(worst_iq, e)
+            assert e < AUDIO_TOL, f"block {b} channel {sample[j]}: IQ rel rms {e:.3e}"
+            assert np.array_equal(got.audio[c] == 0.0, want.audio[j] == 0.0), (b, sample[j])
+            if np.any(want.audio[j] != 0.0):
+                a = rel_rms(got.audio[c], want.audio[j])
+                worst_au = max(worst_au, a)
+                assert a < AUDIO_TOL, f"block {b} channel {sample[j]}: audio rel rms {a:.3e}"
+    eng.close()
+    print(f"40-block run: worst channel-IQ rel rms {worst_iq:.3e}, worst audio rel rms {worst_au:.3e}, "
+          f"{transitions} squelch transitions in the sample")
+    assert transitions >= 20
 
 
 def test_state_save_load_and_reset_round_trip():
