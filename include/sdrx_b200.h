@@ -176,6 +176,12 @@ int      sdrx_engine_set_timing(sdrx_engine *e, int enable);
 /* Host-only self-check of the channel-bank work schedule (no GPU needed): plans `groups` slot groups x U units of
  * 125 samples over n_sms SMs; returns the number of tiling violations (0 = every output produced exactly once).  */
 int      sdrx_debug_bank_plan_check(int groups, int U, int n_sms, int *n_ctas, int *n_pieces, int *max_steps);
+/* The schedule itself: 6 ints per piece (cta, group, u_begin, u_end, seg_len, steps); returns the piece count. */
+int      sdrx_debug_bank_plan_dump(int groups, int U, int n_sms, int *out, int max_records);
+/* Debug trace of the channel bank: per-warp start / end times (globaltimer, ns) of the launches that follow;
+ * read returns the number of values copied, laid out [cta][16 warps][start, end] (tools/diag_bank_trace.py). */
+int      sdrx_debug_bank_trace(int enable);
+int      sdrx_debug_bank_trace_read(unsigned long long *out, int max_u64);
 
 /* Pinned host memory for zero-staging push_block / get_*.  */
 void *sdrx_host_alloc(size_t bytes);

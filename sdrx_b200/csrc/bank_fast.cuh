@@ -51,6 +51,7 @@ constexpr int kWrap = 24;          // table rows replicated past N so a 25-sampl
 constexpr int kFastMinSeg = 8;     // units per segment when sizing the grid: shorter ones mostly warm up
 constexpr int kFastMinSegPiece = 2;// ... but a small piece (a CTA range that straddles a group) still spreads over all warps
 constexpr int kFastWarmStart = 4;  // warm-up units of a segment at the start of the block
+constexpr int kFastPiecePenalty = 1;// steps charged to a CTA for every piece after its first (table reload + refill)
 constexpr int kFastRawHist = 768;  // raw history samples the engine keeps for this path
 
 struct FastTaps {                  // kernel parameter: lives in the constant bank
@@ -149,6 +150,14 @@ __device__ __forceinline__ void fast_unmix(u64 ps, u64 rq, float2 &plus, float2 
     minus = make_float2(a.x + b.y, a.y - b.x);
 }
 
+// Debug trace (tools/diag_bank_trace.py): when set, every warp records the globaltimer at its start and end.
+__device__ unsigned long long *g_bank_trace = nullptr;
+__device__ __forceinline__ unsigned long long bank_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
 // grid = number of CTAs in the schedule, block = kFastThreads, dynamic smem = fast_smem_bytes(N).
 //   table      [N][tstride] float2, one column per lane slot (slot = group * 16 + lane)
 //   slot_chan  [slots][NCH] channel index carried by the slot (-1: none); channel 1 of a slot is the conjugate partner
@@ -169,6 +178,8 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
     const int seg = tid >> 4;                               // == 2*w + half: slot of the staged chunk
     const FastCta me = ctas[blockIdx.x];
     int cur_group = -1;
+    unsigned long long *const trace = g_bank_trace;
+    if (trace && (tid & 31) == 0) trace[(blockIdx.x * (kFastThreads / 32) + w) * 2] = bank_now();
 
     for (int pi = me.piece_begin; pi < me.piece_end; ++pi) {
         const FastPiece pc = pieces[pi];
@@ -318,6 +329,7 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
             }
         }
     }
+    if (trace && (tid & 31) == 0) trace[(blockIdx.x * (kFastThreads / 32) + w) * 2 + 1] = bank_now();
 }
 
 // Completes the stage-3 outputs that straddle segment boundaries (only when the next kernel does not do it itself):
@@ -481,17 +493,21 @@ inline int fast_plan_schedule(int groups, int U, int n_sms, FastPlan &plan) {
             int budget = T;
             FastCta cta{pieces ? (int)pieces->size() : 0, 0};
             bool took = false;
-            while (wk < total && budget >= (took ? 3 : 2)) {
+            while (wk < total && budget >= (took ? 3 + kFastPiecePenalty : 2)) {
                 const int g = (int)(wk / U), ub = (int)(wk % U);
-                int L = max_len(ub, U - ub, budget);
+                // a further piece of the same CTA belongs to the next group: the table is reloaded and the staging
+                // pipeline refilled, which the trace (tools/diag_bank_trace.py) puts at about one step
+                const int extra = took ? kFastPiecePenalty : 0;
+                int L = max_len(ub, U - ub, budget - extra);
                 if (L == 0) break;
+                if (took && L < kFastSegs && L < U - ub) break;                  // not worth a table reload
                 if (U - ub - L > 0 && U - ub - L < 2 * kFastMinSegPiece) {       // do not leave a sliver of the group behind
                     const int all = U - ub;
-                    if (fast_piece_steps(fast_make_piece(0, ub, all, 0)) <= budget) L = all;
+                    if (fast_piece_steps(fast_make_piece(0, ub, all, 0)) <= budget - extra) L = all;
                 }
                 if (g != slot_group) { slot_group = g; slot = 0; }
                 const FastPiece p = fast_make_piece(g, ub, L, slot);
-                budget -= fast_piece_steps(p);
+                budget -= fast_piece_steps(p) + extra;
                 slot += kFastSlotsPerPiece;
                 if (pieces) { pieces->push_back(p); *max_slots = std::max(*max_slots, slot); }
                 wk += L;

@@ -1087,6 +1087,42 @@ extern "C" int sdrx_debug_bank_plan_check(int groups, int U, int n_sms, int *n_c
     return fast_check_plan(groups, U, plan);
 }
 
+// Debug: the schedule itself, one record of 6 ints per piece: cta, group, u_begin, u_end, seg_len, steps.
+extern "C" int sdrx_debug_bank_plan_dump(int groups, int U, int n_sms, int *out, int max_records) {
+    FastPlan plan;
+    if (groups < 1 || U < 1 || n_sms < 1 || !out) return -1;
+    if (fast_plan_schedule(groups, U, n_sms, plan) != SDRX_OK) return -1;
+    int n = 0;
+    for (size_t c = 0; c < plan.ctas.size(); ++c)
+        for (int i = plan.ctas[c].piece_begin; i < plan.ctas[c].piece_end && n < max_records; ++i, ++n) {
+            const FastPiece &p = plan.pieces[i];
+            int *r = out + 6 * n;
+            r[0] = (int)c; r[1] = p.group; r[2] = p.u_begin; r[3] = p.u_end; r[4] = p.seg_len; r[5] = fast_piece_steps(p);
+        }
+    return n;
+}
+
+// Debug: per-warp start / end times (globaltimer ns) of the next channel-bank launches.  enable: allocates
+// [max_ctas][16][2] u64 and points the kernel at it; read: copies it out and returns the number of u64 written.
+static unsigned long long *g_trace_buf = nullptr;
+static const int kTraceCtas = 160;
+extern "C" int sdrx_debug_bank_trace(int enable) {
+    unsigned long long *p = nullptr;
+    if (enable) {
+        if (!g_trace_buf) CU(cudaMalloc((void **)&g_trace_buf, sizeof(unsigned long long) * kTraceCtas * 16 * 2));
+        CU(cudaMemset(g_trace_buf, 0, sizeof(unsigned long long) * kTraceCtas * 16 * 2));
+        p = g_trace_buf;
+    }
+    CU(cudaMemcpyToSymbol(g_bank_trace, &p, sizeof(p)));
+    return SDRX_OK;
+}
+extern "C" int sdrx_debug_bank_trace_read(unsigned long long *out, int max_u64) {
+    if (!g_trace_buf || !out) return 0;
+    const int n = std::min(max_u64, kTraceCtas * 16 * 2);
+    if (cudaMemcpy(out, g_trace_buf, sizeof(unsigned long long) * n, cudaMemcpyDeviceToHost) != cudaSuccess) return 0;
+    return n;
+}
+
 extern "C" int sdrx_engine_uses_fast_path(sdrx_engine *e) { return e && e->use_fast ? 1 : 0; }
 extern "C" int sdrx_engine_bank_pairs(sdrx_engine *e) { return e && e->use_fast ? e->fast.n_pairs : 0; }
 extern "C" int sdrx_engine_set_timing(sdrx_engine *e, int enable) {
