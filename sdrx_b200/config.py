@@ -194,8 +194,10 @@ class ChannelPlan:
     modulation: List[str] = field(default_factory=list)     # "AM" / "FM" per channel (Channel::mod, sdrx.cpp:230); [] -> AM
 
     @classmethod
-    def from_names(cls, rate: int, args: Sequence[str], default_sql: float = 9.0, default_mod: str = "AM") -> "ChannelPlan":
-        """``default_mod`` is --modulation (sdrx.cpp:1197, :1358); a channel's own /AM|/FM suffix wins."""
+    def from_names(cls, rate: int, args: Sequence[str], default_sql: float = 9.0, default_mod: str = "AM",
+                   tuner_fq: Optional[int] = None) -> "ChannelPlan":
+        """``default_mod`` is --modulation (sdrx.cpp:1197, :1358); a channel's own /AM|/FM suffix wins.  ``tuner_fq``
+        overrides the centre frequency sdrx would pick for these channels (a capture was made at a fixed one)."""
         parsed = []
         for a in args:
             p = parse_channel_arg(a, default_sql)
@@ -206,7 +208,7 @@ class ChannelPlan:
             if p[0] not in [q[0] for q in parsed]:       # sdrx.cpp:1377-1380 de-duplicates
                 parsed.append(p)
         names = [p[0] for p in parsed]
-        tuner = tuner_fq_for(names)
+        tuner = tuner_fq_for(names) if tuner_fq is None else int(tuner_fq)
         offs = [channel_to_offset(n, tuner) for n in names]
         return cls(rate_config(rate), tuner, names, offs, [p[1] for p in parsed],
                    [get_audio_pos(i, len(names)) for i in range(len(names))], [p[2] for p in parsed])

@@ -4,6 +4,7 @@ airspy_rx's real sample types for the front end.
 CPU: the files FileSource reads back are the blocks that were written, header fields follow airspy_rx.c:126-190, the
 int16 / u8 conventions are the reference's (rtl_dev.cpp:320-323, airspy.c:58-62).
 GPU (-m gpu): a capture replayed through the engine gives what the oracle gives on the same file."""
+import os
 import struct
 
 import numpy as np
@@ -176,3 +177,39 @@ def test_replayed_packed_real_capture_through_the_front_end(tmp_path):
     assert opened
     fe.close()
     eng.close()
+
+
+def test_replay_tool_arguments():
+    """tools/replay.py takes the channel syntax of the sdrx command line and the capture kinds of FileSource."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("replay", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "replay.py"))
+    rp = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(rp)
+    a = rp.build_parser().parse_args(["cap.bin", "118.105/12/FM", "121.500", "--rate", "10000000", "--real", "packed12", "-o", "x.wav"])
+    assert a.channels == ["118.105/12/FM", "121.500"] and a.real == "packed12" and a.rate == 10000000
+    h = rp.pcm_wav_header(512)
+    assert len(h) == 44 and struct.unpack("<IHHIIHH", h[16:36]) == (16, 1, 2, 16000, 64000, 4, 16)
+    assert struct.unpack("<I", h[40:44])[0] == 2048
+
+
+@pytest.mark.gpu
+def test_replay_tool_end_to_end(tmp_path, capsys):
+    """A synthetic rtl_sdr-style capture replayed by tools/replay.py: the WAV it writes is the engine's pcm stream."""
+    import importlib.util
+    from sdrx_b200 import ChannelPlan, Engine
+    spec = importlib.util.spec_from_file_location("replay", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools", "replay.py"))
+    rp = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(rp)
+    src = SyntheticSource(RATE, [Carrier(-3, 0.4, 1000.0, 0.5, lambda b: 1 <= b < 6)], 0.01, 7, FMT_U8, 8)
+    cap, wav = str(tmp_path / "rtl.bin"), str(tmp_path / "audio.wav")
+    so.write_capture(cap, src)
+    assert rp.main([cap, "118.275", "--rate", str(RATE), "--format", "u8", "-o", wav]) == 0
+    text = capsys.readouterr().out
+    assert "open" in text and "close" in text and "118.275" in text
+    eng = Engine(ChannelPlan.from_names(RATE, ["118.275"]))
+    want = np.concatenate([eng.process(src.block(b), FMT_U8).pcm for b in range(8)])
+    eng.close()
+    w = so.read_wav_header(wav)
+    assert (w.format_tag, w.channels, w.rate, w.bits, w.data_bytes) == (1, 2, 16000, 16, want.size * 2)
+    got = np.fromfile(wav, dtype="<i2", offset=w.data_offset)
+    assert np.array_equal(got, want) and np.any(got != 0)
