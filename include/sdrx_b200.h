@@ -182,6 +182,9 @@ int      sdrx_debug_bank_plan_dump(int groups, int U, int n_sms, int *out, int m
  * read returns the number of values copied, laid out [cta][16 warps][start, end] (tools/diag_bank_trace.py). */
 int      sdrx_debug_bank_trace(int enable);
 int      sdrx_debug_bank_trace_read(unsigned long long *out, int max_u64);
+/* Same for the front end's five passes: [pass][CTA-0 start, latest CTA end] of the last call (10 values). */
+int      sdrx_debug_fe_trace(int enable);
+int      sdrx_debug_fe_trace_read(unsigned long long *out);
 
 /* Pinned host memory for zero-staging push_block / get_*.  */
 void *sdrx_host_alloc(size_t bytes);

@@ -81,6 +81,8 @@ PROTOTYPES = [
     ("sdrx_debug_bank_plan_dump", C.c_int, [C.c_int, C.c_int, C.c_int, c_int_p, C.c_int]),
     ("sdrx_debug_bank_trace", C.c_int, [C.c_int]),
     ("sdrx_debug_bank_trace_read", C.c_int, [C.POINTER(C.c_uint64), C.c_int]),
+    ("sdrx_debug_fe_trace", C.c_int, [C.c_int]),
+    ("sdrx_debug_fe_trace_read", C.c_int, [C.POINTER(C.c_uint64)]),
     ("sdrx_host_alloc", C.c_void_p, [C.c_size_t]),
     ("sdrx_host_free", None, [C.c_void_p]),
     ("sdrx_device_alloc", C.c_void_p, [C.c_int, C.c_size_t]),

@@ -24,6 +24,7 @@
 // Everything after remove_dc is a pure function of a short window and is evaluated in the reference's order,
 // un-contracted: bit-exact given bit-exact inputs.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -41,6 +42,21 @@ constexpr int kFeMaxCtas = 1 << 20;  // ... and their largest grid (the passes w
 constexpr int kFeEvenHist = 24;      // >= len - 1 = 23 rotated even samples carried between blocks
 constexpr int kFeOddHist = 12;       // len / 2 delayed odd samples
 constexpr int kFeMaxLen = 64;
+
+// Debug trace (tools/diag_fe_chain.py): when set, kernel k records the globaltimer at which its CTA 0 started in
+// slot 2k and the latest CTA end in slot 2k + 1 (k: 0 partial, 1 scan, 2 dc, 3 iq, 4 carry).
+__device__ unsigned long long *g_fe_trace = nullptr;
+__device__ __forceinline__ unsigned long long fe_now() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void fe_mark_start(int k) {
+    if (g_fe_trace && threadIdx.x == 0 && blockIdx.x == 0) g_fe_trace[2 * k] = fe_now();
+}
+__device__ __forceinline__ void fe_mark_end(int k) {
+    if (g_fe_trace && threadIdx.x == 0) atomicMax(&g_fe_trace[2 * k + 1], fe_now());
+}
 
 // eight consecutive ADC samples starting at index `idx` (a multiple of 8) of a buffer in wire format
 template <bool PACKED>
@@ -136,11 +152,13 @@ __device__ __forceinline__ float fe_walk(const void *__restrict__ raw, long w0, 
 template <bool PACKED>
 static __global__ void __launch_bounds__(kFeThreads)
 k_fe_partial(const void *__restrict__ raw, int n, float *__restrict__ seg_b) {
+    fe_mark_start(0);
     const int whole = n / kFeSeg;                   // only whole segments feed the scan (the last start needs no successor)
     for (int seg = blockIdx.x * blockDim.x + threadIdx.x; seg < whole; seg += gridDim.x * blockDim.x) {
         const long s0 = (long)seg * kFeSeg;
         seg_b[seg] = fe_walk<PACKED, false>(raw, s0, s0, s0 + kFeSeg, 0.0f, 0.0f, nullptr, nullptr);
     }
+    fe_mark_end(0);
 }
 
 // Pass 2: avg at every segment start, start[0] = the carried avg, start[k+1] = A * start[k] + B[k] (A = a^kFeSeg),
@@ -149,6 +167,7 @@ k_fe_partial(const void *__restrict__ raw, int n, float *__restrict__ seg_b) {
 static __global__ void __launch_bounds__(128)
 k_fe_scan(const float *__restrict__ seg_b, int nseg, const float *__restrict__ avg_io, float A, float *__restrict__ seg_start) {
     __shared__ float sa[128], sb[128], st[128];
+    fe_mark_start(1);
     const int lane = threadIdx.x;
     const int m = (nseg + 127) / 128;
     const int k0 = lane * m, k1 = min(nseg, k0 + m);
@@ -163,6 +182,7 @@ k_fe_scan(const float *__restrict__ seg_b, int nseg, const float *__restrict__ a
     __syncthreads();
     float v = st[lane];
     for (int k = k0; k < k1; ++k) { seg_start[k] = v; v = fmaf(A, v, seg_b[k]); }
+    fe_mark_end(1);
 }
 
 // Pass 3: remove_dc + translate_fs_4's sign / hbc pattern, segment-parallel.
@@ -175,6 +195,7 @@ static __global__ void __launch_bounds__(kFeThreads)
 k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n, float *__restrict__ avg_io,
         float hbc, float *__restrict__ ev, float *__restrict__ od, int exact) {
     const int gt = blockIdx.x * blockDim.x + threadIdx.x;
+    fe_mark_start(2);
     if (exact) {
         if (gt == 0) avg_io[1] = fe_walk<PACKED, true>(raw, 0, 0, n, avg_io[0], hbc, ev, od);
         return;
@@ -187,6 +208,7 @@ k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n
         const float avg = fe_walk<PACKED, true>(raw, (long)kb * kFeSeg, s0, s1, avg0, hbc, ev, od);
         if (s1 == n) avg_io[1] = avg;
     }
+    fe_mark_end(2);
 }
 
 // Half-band FIR on the even samples (fir_interleaved_24's order: k[0]*(q0+q23) + k[1]*(q1+q22) + ... left to right),
@@ -196,6 +218,7 @@ k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n
 static __global__ void __launch_bounds__(kFeThreads)
 k_fe_iq(const float *__restrict__ ev, const float *__restrict__ od, int npair, const float *__restrict__ k, int len,
         float2 *__restrict__ out) {
+  fe_mark_start(3);
   for (int p0 = (blockIdx.x * blockDim.x + threadIdx.x) * 8; p0 < npair; p0 += gridDim.x * blockDim.x * 8) {
     if (len == 24 && p0 + 8 <= npair) {
         float w[32];                                     // w[i] = ev[p0 + i]: the newest sample of pair p0 + j is w[24 + j]
@@ -230,6 +253,7 @@ k_fe_iq(const float *__restrict__ ev, const float *__restrict__ od, int npair, c
         out[p] = make_float2(acc, od[kFeOddHist + p - half]);
     }
   }
+  fe_mark_end(3);
 }
 
 // Block-to-block carries: the even / odd history prefixes and avg.
@@ -237,6 +261,7 @@ static __global__ void __launch_bounds__(64)
 k_fe_carry(int n, float *__restrict__ ev, float *__restrict__ od, float *__restrict__ avg_io) {
     // the even / odd prefixes slide in place: every read below happens before the barrier, every write after
     // (one CTA does it: kFeEvenHist + kFeOddHist <= 256)
+    fe_mark_start(4);
     if (blockIdx.x == 0) {
         const int npair = n >> 1;
         float keep = 0.0f;
@@ -248,6 +273,7 @@ k_fe_carry(int n, float *__restrict__ ev, float *__restrict__ od, float *__restr
         else if (t < kFeEvenHist + kFeOddHist) od[t - kFeEvenHist] = keep;
         if (t == 0) avg_io[0] = avg_io[1];
     }
+    fe_mark_end(4);
 }
 
 }  // namespace
@@ -317,6 +343,7 @@ extern "C" int sdrx_airspy_fe_create(int device, const float *hb_kernel, int hb_
     if (!g.ok) return fail(SDRX_ERR_CUDA, "cudaSetDevice failed");
     sdrx_airspy_fe *f = new sdrx_airspy_fe();
     f->dev = device; f->flags = flags; f->cap = max_samples; f->len = len;
+
     f->hbc = hb_kernel[hb_len / 2];                              // iqconverter_float.c:81
     {
         const double a = 1.0 - (double)0.01f;                    // avg' = a * avg + 0.01f * x (iqconverter_float.c:461-464)
@@ -460,4 +487,21 @@ extern "C" int sdrx_airspy_fe_avg(sdrx_airspy_fe *f, float *avg) {
     CU(cudaStreamSynchronize(f->st));
     CU(cudaMemcpy(avg, f->d_avg, sizeof(float), cudaMemcpyDeviceToHost));
     return SDRX_OK;
+}
+
+// Debug: see g_fe_trace.  enable allocates / clears 10 u64 and points the kernels at them; read copies them out.
+static unsigned long long *g_fe_trace_buf = nullptr;
+extern "C" int sdrx_debug_fe_trace(int enable) {
+    unsigned long long *p = nullptr;
+    if (enable) {
+        if (!g_fe_trace_buf) CU(cudaMalloc((void **)&g_fe_trace_buf, sizeof(unsigned long long) * 10));
+        CU(cudaMemset(g_fe_trace_buf, 0, sizeof(unsigned long long) * 10));
+        p = g_fe_trace_buf;
+    }
+    CU(cudaMemcpyToSymbol(g_fe_trace, &p, sizeof(p)));
+    return SDRX_OK;
+}
+extern "C" int sdrx_debug_fe_trace_read(unsigned long long *out) {
+    if (!g_fe_trace_buf || !out) return 0;
+    return cudaMemcpy(out, g_fe_trace_buf, sizeof(unsigned long long) * 10, cudaMemcpyDeviceToHost) == cudaSuccess ? 10 : 0;
 }

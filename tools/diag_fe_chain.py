@@ -55,4 +55,31 @@ for mode in ("fe_only", "engine_only", "independent", "chain"):
         gaps = [ev[i][0].elapsed_time(ev[i + 1][0]) * 1e3 for i in range(5, STEPS - 1)]
         r["fe_span_us_median"] = float(np.median(spans)); r["fe_period_us_median"] = float(np.median(gaps))
     res[mode] = r
+
+# ---- one timeline on the GPU's own clock: the front end's five passes of call k+1 against the bank launch of block k
+import ctypes as C
+lib = _lib.load()
+for _ in range(6):
+    fe.feed(eng, v)
+eng.sync(); fe.sync()
+lib.sdrx_debug_bank_trace(1); lib.sdrx_debug_fe_trace(1)
+for _ in range(6):
+    fe.feed(eng, v)
+# one more front-end call with no engine push behind it: it runs next to the LAST bank launch, whose trace is the one kept
+ev_in = lib.sdrx_engine_ingest_event(eng.h)
+lib.sdrx_airspy_fe_wait_event(fe.h, C.c_void_p(ev_in))
+fe.process(v, fetch=False)
+eng.sync(); fe.sync(); torch.cuda.synchronize()
+bb = (C.c_uint64 * (160 * 16 * 2))(); nb = lib.sdrx_debug_bank_trace_read(bb, len(bb))
+fb = (C.c_uint64 * 10)(); lib.sdrx_debug_fe_trace_read(fb)
+lib.sdrx_debug_bank_trace(0); lib.sdrx_debug_fe_trace(0)
+bt = np.frombuffer(bb, dtype=np.uint64)[:nb].reshape(-1, 16, 2).astype(np.int64)
+bt = bt[bt[:, 0, 0] != 0]
+b0, b1 = bt[:, :, 0].min(), bt[:, :, 1].max()
+ft = np.frombuffer(fb, dtype=np.uint64).astype(np.int64).reshape(5, 2)
+tl = {"bank": [0.0, (b1 - b0) / 1e3], "bank_ctas": int(len(bt)),
+      "bank_cta_start_spread_us": float((bt[:, :, 0].min(axis=1).max() - b0) / 1e3)}
+for name, (a, b) in zip(("fe_partial", "fe_scan", "fe_dc", "fe_iq", "fe_carry"), ft):
+    tl[name] = [(a - b0) / 1e3, (b - b0) / 1e3]
+res["timeline_us_relative_to_bank_start"] = tl
 print(json.dumps(res, indent=1))
