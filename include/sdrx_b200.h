@@ -231,6 +231,9 @@ typedef struct sdrx_airspy_fe sdrx_airspy_fe;
                                    sample per uint16 (0..4095)                                                     */
 #define SDRX_FE_EXACT_DC 0x2u   /* run remove_dc (one recurrence over the whole stream) on a single thread: bit-exact by
                                    construction, ~4 ms per 640 000 samples; the default is segment-parallel          */
+#define SDRX_FE_BESIDE_ENGINE 0x4u /* the front end feeds an sdrx_engine on the same GPU: remove_dc runs in its narrow form
+                                   (512-sample segments, 5 CTAs, input staged through shared memory) so that it fits
+                                   the SMs the channel bank's launch leaves free; same results, same 1e-6 bar       */
 /* hb_kernel: HB_KERNEL_FLOAT (libairspy filters.h:28-30, 47 taps); max_samples: most REAL samples per call (multiple of 8) */
 int   sdrx_airspy_fe_create(int device, const float *hb_kernel, int hb_len, unsigned max_samples, unsigned flags,
                             sdrx_airspy_fe **out);                                        /* iqconverter_float_create */

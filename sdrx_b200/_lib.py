@@ -117,7 +117,7 @@ PROTOTYPES = [
     ("sdrx_engine_ingest_event", C.c_void_p, [C.c_void_p]),
     ("sdrx_airspy_fe_wait_event", C.c_int, [C.c_void_p, C.c_void_p]),
 ]
-FE_PACKED12, FE_EXACT_DC = 0x1, 0x2
+FE_PACKED12, FE_EXACT_DC, FE_BESIDE_ENGINE = 0x1, 0x2, 0x4
 
 _LIB = None
 

@@ -9,7 +9,7 @@ from typing import Optional
 import numpy as np
 
 from . import _lib
-from ._lib import FE_EXACT_DC, FE_PACKED12, check
+from ._lib import FE_BESIDE_ENGINE, FE_EXACT_DC, FE_PACKED12, check
 from .config import tables
 
 
@@ -22,13 +22,14 @@ class AirspyFrontEnd:
     """``process(raw)``: n real ADC samples (uint16 0..4095, or uint32 words when ``packed``) -> n/2 complex64 IQ."""
 
     def __init__(self, max_samples: int = 640000, packed: bool = False, exact_dc: bool = False, device: int = 0,
-                 kernel: Optional[np.ndarray] = None):
+                 kernel: Optional[np.ndarray] = None, beside_engine: bool = False):
         self.lib = _lib.load()
         self.packed = packed
         self.device = device
         k = hb_kernel() if kernel is None else np.ascontiguousarray(kernel, np.float32)
         h = C.c_void_p()
-        flags = (FE_PACKED12 if packed else 0) | (FE_EXACT_DC if exact_dc else 0)
+        flags = ((FE_PACKED12 if packed else 0) | (FE_EXACT_DC if exact_dc else 0)
+                 | (FE_BESIDE_ENGINE if beside_engine else 0))
         check(self.lib.sdrx_airspy_fe_create(device, k.ctypes.data_as(_lib.c_float_p), int(k.size), int(max_samples), flags,
                                              C.byref(h)))
         self.h = h

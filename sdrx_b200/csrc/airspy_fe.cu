@@ -211,6 +211,166 @@ k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n
     fe_mark_end(2);
 }
 
+// ---- the same two passes in their NARROW form (SDRX_FE_BESIDE_ENGINE): few threads, long chains, input staged ----
+// A front end that feeds a channel bank on the same GPU has to live in the 3 SMs the bank's 145-CTA launch leaves free
+// (profiles/r01y_frontend_timeline.txt).  The wide passes above are ~600 SM-us of work per block; this form cuts the
+// recurrences to 3x the stream (512-sample segments, one warm-up segment: 0.99^512 = 0.006) on 1250 threads, and
+// gets the segments -- which lie 1 KB apart, so a thread reading its own would touch a cache line per lane -- through
+// shared memory: the CTA copies the next 32 samples of all its 512 segments with coalesced 16 B cp.async (8 segments
+// per warp instruction, whole sectors), three tiles deep, rows padded to 80 B (conflict-free 128-bit reads).  The
+// outputs go back the same way: a warp parks its 32 rows of ev / od in shared memory and writes them out 64 B per
+// segment (8 segments per store instruction instead of 32 half sectors -- the stores were the pass's bottleneck).
+// 1250 segments are 3 CTAs: one round on the 3 spare SMs.
+constexpr int kNSeg = 512, kNBack = 1, kNThreads = 512, kNTile = 32, kNStages = 3;
+constexpr int kNRow = 80;                                      // bytes per staged row: 64 (u16) or 48 (packed) + pad
+constexpr int kNORow = 80;                                     // ... and per output row (64 B of ev or od + pad)
+inline size_t fe_narrow_smem() { return (size_t)kNStages * kNThreads * kNRow + (size_t)kNThreads * 2 * kNORow; }
+
+// EMIT = false: pass 1 (seg_b); EMIT = true: pass 3 (ev / od, avg_io[1]).  Tiles are counted from base = s0 - 512 * EMIT.
+// Sample and byte indices are 32-bit here (sdrx_airspy_fe_create bounds max_samples for this form); everything that
+// does not change from tile to tile is worked out once, in front of the loop.
+template <bool PACKED, bool EMIT>
+static __global__ void __launch_bounds__(kNThreads)
+k_fe_walk_narrow(const void *__restrict__ raw, int n, const float *__restrict__ seg_start, float *__restrict__ avg_io,
+                 float hbc, float *__restrict__ ev, float *__restrict__ od, float *__restrict__ seg_b) {
+    extern __shared__ __align__(16) unsigned char stage[];
+    unsigned char *const obuf = stage + (size_t)kNStages * kNThreads * kNRow;     // [thread][ev, od][kNORow]
+    fe_mark_start(EMIT ? 2 : 0);
+    constexpr int kBytes = PACKED ? kNTile * 3 / 2 : kNTile * 2;       // bytes of one row of a tile
+    constexpr int kChunks = kBytes / 16;
+    constexpr int kTiles = (EMIT ? kNSeg * (1 + kNBack) : kNSeg) / kNTile;
+    constexpr int kGroups = kNTile / 8;
+    const int t = threadIdx.x;
+    const int seg0 = blockIdx.x * kNThreads;
+    const int nseg = EMIT ? (n + kNSeg - 1) / kNSeg : n / kNSeg;
+    const int back = EMIT ? kNSeg * kNBack : 0;
+    const uint8_t *rb = reinterpret_cast<const uint8_t *>(raw);
+    const int end_byte = PACKED ? n / 2 * 3 : n * 2;
+
+    // loader: chunk `it` of this thread is (row, ch) = ((t + it * kNThreads) / kChunks, ... % kChunks) in every tile
+    int g_ofs[kChunks];                        // byte offset of the chunk in tile 0 (negative in front of the block)
+    unsigned s_ofs[kChunks];                   // its place inside a stage
+    bool l_ok[kChunks];
+#pragma unroll
+    for (int it = 0; it < kChunks; ++it) {
+        const int q = t + it * kNThreads, row = q / kChunks, ch = q % kChunks;
+        const int smp = (seg0 + row) * kNSeg - back;
+        g_ofs[it] = (PACKED ? smp / 2 * 3 : smp * 2) + ch * 16;
+        s_ofs[it] = (unsigned)(row * kNRow + ch * 16);
+        l_ok[it] = seg0 + row < nseg;
+    }
+    const unsigned stage_s = (unsigned)__cvta_generic_to_shared(stage);
+    auto issue = [&](int j) {
+        if (j < kTiles) {
+            const unsigned slot = (unsigned)(j % kNStages) * kNThreads * kNRow;
+#pragma unroll
+            for (int it = 0; it < kChunks; ++it) {
+                const int byte = g_ofs[it] + j * kBytes;
+                if (!l_ok[it] || byte < 0 || byte >= end_byte) continue;
+                if (byte + 16 <= end_byte) {
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(stage_s + slot + s_ofs[it]), "l"(rb + byte) : "memory");
+                } else {                                            // packed words: the buffer may end inside a chunk
+                    for (int b = 0; byte + b < end_byte; b += 4)
+                        *reinterpret_cast<uint32_t *>(stage + slot + s_ofs[it] + b) = *reinterpret_cast<const uint32_t *>(rb + byte + b);
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    // walker: this thread's segment
+    const int seg = seg0 + t;
+    const bool mine = seg < nseg;
+    const int s0 = seg * kNSeg;
+    const int s1 = EMIT ? min(s0 + kNSeg, n) : s0 + kNSeg;
+    const int base = s0 - back;
+    int lo = s0;                                                // first sample this thread walks
+    float avg = 0.0f;
+    if (EMIT && mine) {
+        const int kb = seg <= kNBack ? 0 : seg - kNBack;
+        lo = kb * kNSeg;
+        avg = kb == 0 ? avg_io[0] : seg_start[kb];
+    }
+    // write-out: lane (r, g) of pass k copies group g of row wbase + 8k + lane / 4 (kGroups == 4)
+    static_assert(kGroups == 4, "the write-out below maps four lanes to a row");
+    const int lane = t & 31, wbase = t & ~31, og = lane & 3;
+    int o_i0[kGroups], o_end[kGroups];         // first sample index of the group in tile 0 / end of the row's segment
+#pragma unroll
+    for (int k = 0; k < kGroups; ++k) {
+        const int r = wbase + 8 * k + (lane >> 2);
+        const int rs0 = (seg0 + r) * kNSeg;
+        o_i0[k] = rs0 - back + 8 * og;
+        o_end[k] = seg0 + r < nseg ? min(rs0 + kNSeg, n) : 0;
+    }
+
+    static_assert(kNStages == 3, "the wait below counts two tiles in flight");
+    issue(0); issue(1);
+    for (int j = 0; j < kTiles; ++j) {
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        __syncthreads();
+        const unsigned char *row = stage + (size_t)(j % kNStages) * kNThreads * kNRow + t * kNRow;
+        if (mine && base + (j + 1) * kNTile > lo && base + j * kNTile < s1) {
+            uint32_t w[kBytes / 4];                               // the row of this tile, read with conflict-free 128-bit loads
+#pragma unroll
+            for (int c = 0; c < kChunks; ++c) {
+                const uint4 q = *reinterpret_cast<const uint4 *>(row + 16 * c);
+                w[4 * c] = q.x; w[4 * c + 1] = q.y; w[4 * c + 2] = q.z; w[4 * c + 3] = q.w;
+            }
+#pragma unroll
+            for (int g = 0; g < kGroups; ++g) {
+                const int i = base + j * kNTile + 8 * g;
+                if (i < lo || i >= s1) continue;
+                int v[8];
+                if constexpr (PACKED) {
+                    const uint32_t a = w[3 * g], b = w[3 * g + 1], c = w[3 * g + 2];
+                    v[0] = (a >> 20) & 0xfff; v[1] = (a >> 8) & 0xfff; v[2] = ((a & 0xff) << 4) | ((b >> 28) & 0xf);
+                    v[3] = (b >> 16) & 0xfff; v[4] = (b >> 4) & 0xfff; v[5] = ((b & 0xf) << 8) | ((c >> 24) & 0xff);
+                    v[6] = (c >> 12) & 0xfff; v[7] = c & 0xfff;
+                } else {
+                    const uint32_t a = w[4 * g], b = w[4 * g + 1], c = w[4 * g + 2], d = w[4 * g + 3];
+                    v[0] = a & 0xffff; v[1] = a >> 16; v[2] = b & 0xffff; v[3] = b >> 16;
+                    v[4] = c & 0xffff; v[5] = c >> 16; v[6] = d & 0xffff; v[7] = d >> 16;
+                }
+                // (raw - 2048) / 2048 in one exact step: (2^23 + v) * 2^-11 - 4097 == v / 2048 - 1, representable, so the
+                // fused multiply-add rounds nothing and the value is convert_samples_float's bit for bit
+                float x[8], sv[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) x[k] = __fmaf_rn(__int_as_float(0x4B000000 | v[k]), 1.0f / 2048.0f, -4097.0f);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) sv[k] = dc_step(x[k], avg);
+                if (EMIT && i >= s0) {
+                    float4 e, o;
+                    e.x = -sv[0];              o.x = __fmul_rn(-sv[1], hbc);
+                    e.y = sv[2];               o.y = __fmul_rn(sv[3], hbc);
+                    e.z = -sv[4];              o.z = __fmul_rn(-sv[5], hbc);
+                    e.w = sv[6];               o.w = __fmul_rn(sv[7], hbc);
+                    *reinterpret_cast<float4 *>(obuf + (2 * t) * kNORow + 16 * g) = e;
+                    *reinterpret_cast<float4 *>(obuf + (2 * t + 1) * kNORow + 16 * g) = o;
+                }
+            }
+        }
+        if (EMIT && j * kNTile >= back) {                        // this tile lies in the segments' own range: write it out
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < kGroups; ++k) {
+                const int i = o_i0[k] + j * kNTile;
+                if (i < o_end[k]) {
+                    const int r = wbase + 8 * k + (lane >> 2);
+                    *reinterpret_cast<float4 *>(ev + kFeEvenHist + (i >> 1)) = *reinterpret_cast<const float4 *>(obuf + (2 * r) * kNORow + 16 * og);
+                    *reinterpret_cast<float4 *>(od + kFeOddHist + (i >> 1)) = *reinterpret_cast<const float4 *>(obuf + (2 * r + 1) * kNORow + 16 * og);
+                }
+            }
+            __syncwarp();
+        }
+        issue(j + kNStages - 1);
+    }
+    if (mine) {
+        if (!EMIT) seg_b[seg] = avg;
+        else if (s1 == n) avg_io[1] = avg;
+    }
+    fe_mark_end(EMIT ? 2 : 0);
+}
+
 // Half-band FIR on the even samples (fir_interleaved_24's order: k[0]*(q0+q23) + k[1]*(q1+q22) + ... left to right),
 // the odd samples through their 12-deep delay line.  One thread per EIGHT consecutive IQ pairs: their windows overlap
 // in all but one sample each, so 32 even samples are read once (eight 16 B loads) instead of 192 separate ones.
@@ -289,7 +449,9 @@ struct sdrx_airspy_fe {
     uint8_t *d_raw = nullptr;            // wire-format staging of one call
     uint8_t *h_stage = nullptr;          // pinned staging for pageable callers
     float *d_seg_b = nullptr, *d_seg_start = nullptr;   // per-segment affine terms / avg estimates (k_fe_partial, k_fe_scan)
-    double A = 0.0;                      // (1 - 0.01f)^kFeSeg
+    double A = 0.0;                      // (1 - 0.01f)^kFeSeg (or ^kNSeg: narrow)
+    bool narrow = false;                 // SDRX_FE_BESIDE_ENGINE
+    cudaEvent_t out_free = nullptr;      // sdrx_airspy_fe_wait_event: the next call's output write waits for this
     float *d_ev = nullptr, *d_od = nullptr, *d_k = nullptr, *d_avg = nullptr;
     float2 *d_iq[2] = {nullptr, nullptr};    // ring: the consumer of call k may still read while call k+1 runs
     uint64_t total = 0;                  // real samples seen so far
@@ -333,6 +495,8 @@ extern "C" int sdrx_airspy_fe_create(int device, const float *hb_kernel, int hb_
     if ((len & 1) || len - 1 > kFeEvenHist || len / 2 > kFeOddHist || len > kFeMaxLen)
         return fail(SDRX_ERR_UNSUPPORTED, "half-band kernels other than libairspy's 47-tap family (len/2+1 even, <= 24) are not implemented");
     if (max_samples < 8 || max_samples % 8) return fail(SDRX_ERR_ARG, "max_samples must be a positive multiple of 8");
+    if ((flags & SDRX_FE_BESIDE_ENGINE) && max_samples > (1u << 28))
+        return fail(SDRX_ERR_ARG, "SDRX_FE_BESIDE_ENGINE: max_samples above 2^28 (32-bit indices in the narrow passes)");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
         cudaGetLastError();
@@ -348,7 +512,8 @@ extern "C" int sdrx_airspy_fe_create(int device, const float *hb_kernel, int hb_
     {
         const double a = 1.0 - (double)0.01f;                    // avg' = a * avg + 0.01f * x (iqconverter_float.c:461-464)
         f->A = 1.0;
-        for (int i = 0; i < kFeSeg; ++i) f->A *= a;
+        f->narrow = (flags & SDRX_FE_BESIDE_ENGINE) != 0;
+        for (int i = 0; i < (f->narrow ? kNSeg : kFeSeg); ++i) f->A *= a;
     }
     std::vector<float> k((size_t)len);
     for (int i = 0, j = 0; i < len; ++i, j += 2) k[i] = hb_kernel[j];   // iqconverter_float.c:91-94
@@ -376,6 +541,15 @@ extern "C" int sdrx_airspy_fe_create(int device, const float *hb_kernel, int hb_
         cudaFuncSetAttribute(k_fe_partial<true>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
         cudaFuncSetAttribute(k_fe_partial<false>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
         cudaFuncSetAttribute(k_fe_scan, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        const int nsm = (int)fe_narrow_smem();
+        cudaFuncSetAttribute(k_fe_walk_narrow<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, nsm);
+        cudaFuncSetAttribute(k_fe_walk_narrow<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, nsm);
+        cudaFuncSetAttribute(k_fe_walk_narrow<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, nsm);
+        cudaFuncSetAttribute(k_fe_walk_narrow<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, nsm);
+        cudaFuncSetAttribute(k_fe_walk_narrow<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaFuncSetAttribute(k_fe_walk_narrow<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaFuncSetAttribute(k_fe_walk_narrow<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
+        cudaFuncSetAttribute(k_fe_walk_narrow<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, mx);
         cudaGetLastError();
     }
     int rc = sdrx_airspy_fe_reset(f);
@@ -397,15 +571,32 @@ int fe_run(sdrx_airspy_fe *f, const void *d_raw, unsigned n) {
     // recurrence step ~200 cycles (40 warps of 1 KB-strided 16 B loads, nothing to hide their latency behind):
     // 365 us per block instead of 43.  The wide grid stays; the passes keep their grid-stride form.
     auto grid = [](int tasks) { return std::max(1, std::min(kFeMaxCtas, div_up(tasks, kFeThreads))); };
+    if (f->narrow && !exact) {
+        const int nsegs = div_up(n, kNSeg), whole = (int)(n / kNSeg);
+        const size_t sm = fe_narrow_smem();
+        if (nsegs > kNBack + 1) {
+            if (packed) k_fe_walk_narrow<true, false><<<div_up(whole, kNThreads), kNThreads, sm, f->st>>>(d_raw, (int)n, nullptr, nullptr, 0.0f, nullptr, nullptr, f->d_seg_b);
+            else        k_fe_walk_narrow<false, false><<<div_up(whole, kNThreads), kNThreads, sm, f->st>>>(d_raw, (int)n, nullptr, nullptr, 0.0f, nullptr, nullptr, f->d_seg_b);
+            k_fe_scan<<<1, 128, 0, f->st>>>(f->d_seg_b, whole, f->d_avg, (float)f->A, f->d_seg_start);
+            f->launches += 2;
+        }
+        if (packed) k_fe_walk_narrow<true, true><<<div_up(nsegs, kNThreads), kNThreads, sm, f->st>>>(d_raw, (int)n, f->d_seg_start, f->d_avg, f->hbc, f->d_ev, f->d_od, nullptr);
+        else        k_fe_walk_narrow<false, true><<<div_up(nsegs, kNThreads), kNThreads, sm, f->st>>>(d_raw, (int)n, f->d_seg_start, f->d_avg, f->hbc, f->d_ev, f->d_od, nullptr);
+    } else {
     if (!exact && segs > kFeBack + 1) {
-        const int whole = (int)(n / kFeSeg);
-        if (packed) k_fe_partial<true><<<grid(whole), kFeThreads, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
-        else        k_fe_partial<false><<<grid(whole), kFeThreads, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
-        k_fe_scan<<<1, 128, 0, f->st>>>(f->d_seg_b, whole, f->d_avg, (float)f->A, f->d_seg_start);
-        f->launches += 2;
+            const int whole = (int)(n / kFeSeg);
+            if (packed) k_fe_partial<true><<<grid(whole), kFeThreads, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
+            else        k_fe_partial<false><<<grid(whole), kFeThreads, 0, f->st>>>(d_raw, (int)n, f->d_seg_b);
+            k_fe_scan<<<1, 128, 0, f->st>>>(f->d_seg_b, whole, f->d_avg, (float)f->A, f->d_seg_start);
+            f->launches += 2;
+        }
+        if (packed) k_fe_dc<true><<<grid(segs), kFeThreads, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
+        else        k_fe_dc<false><<<grid(segs), kFeThreads, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
     }
-    if (packed) k_fe_dc<true><<<grid(segs), kFeThreads, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
-    else        k_fe_dc<false><<<grid(segs), kFeThreads, 0, f->st>>>(d_raw, f->d_seg_start, (int)n, f->d_avg, f->hbc, f->d_ev, f->d_od, exact);
+    if (f->out_free) {       // everything up to here only touched the front end's own scratch; the output ring slot is the consumer's
+        CU(cudaStreamWaitEvent(f->st, f->out_free, 0));
+        f->out_free = nullptr;
+    }
     k_fe_iq<<<grid(div_up(npair, 8)), kFeThreads, 0, f->st>>>(f->d_ev, f->d_od, npair, f->d_k, f->len, f->d_iq[cur]);
     k_fe_carry<<<1, 64, 0, f->st>>>((int)n, f->d_ev, f->d_od, f->d_avg);
     CU(cudaGetLastError());
@@ -464,12 +655,12 @@ extern "C" const float *sdrx_airspy_fe_output(sdrx_airspy_fe *f, unsigned *n_pai
     if (n_pairs) *n_pairs = f->last_pairs;
     return reinterpret_cast<const float *>(f->d_iq[(f->calls + 1) & 1]);    // the buffer the last call wrote
 }
-// Orders the front end's stream behind an event of the consumer (e.g. sdrx_engine_ingest_event after the push that
-// read the previous output): the output ring is two deep, so waiting for the consumer of call k-1 frees call k+1's buffer.
+// Orders the NEXT call's output write behind an event of the consumer (e.g. sdrx_engine_ingest_event after the push
+// that read the previous output): the output ring is two deep, so waiting for the consumer of call k-1 frees call
+// k+1's slot.  Only the last pass writes the ring, so the copy in and the remove_dc passes of call k+1 still run ahead.
 extern "C" int sdrx_airspy_fe_wait_event(sdrx_airspy_fe *f, void *cuda_event) {
     if (!f || !cuda_event) return fail(SDRX_ERR_ARG, "null argument");
-    DevGuard g(f->dev);
-    CU(cudaStreamWaitEvent(f->st, (cudaEvent_t)cuda_event, 0));
+    f->out_free = (cudaEvent_t)cuda_event;
     return SDRX_OK;
 }
 extern "C" void *sdrx_airspy_fe_done_event(sdrx_airspy_fe *f) { return f ? (void *)f->ev_done : nullptr; }

@@ -104,13 +104,15 @@ def test_library_exports_every_symbol_the_header_declares():
 # ------------------------------------------------------------------------------------------------ GPU
 @pytest.mark.gpu
 @pytest.mark.parametrize("packed", [False, True], ids=["u16", "packed12"])
-@pytest.mark.parametrize("exact", [True, False], ids=["exact_dc", "parallel_dc"])
+@pytest.mark.parametrize("exact", [True, False, "narrow"], ids=["exact_dc", "parallel_dc", "narrow_dc"])
 def test_cuda_front_end_against_oracle(packed, exact):
     from sdrx_b200 import AirspyFrontEnd
-    chunks = [8, 640, 65536, 4096, 200000, 24, 640000] if not exact else [8, 640, 65536, 4096, 24]
+    narrow = exact == "narrow"                  # SDRX_FE_BESIDE_ENGINE: 512-sample segments staged through shared memory
+    exact = exact is True
+    chunks = [8, 640, 65536, 4096, 200000, 24, 640000, 1032, 520, 512, 1536] if not exact else [8, 640, 65536, 4096, 24]
     x = adc_stream(sum(chunks), seed=11)
     o = ob.OracleAirspyFE(hb())
-    fe = AirspyFrontEnd(max_samples=640000, packed=packed, exact_dc=exact)
+    fe = AirspyFrontEnd(max_samples=640000, packed=packed, exact_dc=exact, beside_engine=narrow)
     pos, worst, differing, total = 0, 0.0, 0, 0
     for n in chunks:
         raw = x[pos:pos + n]
@@ -122,7 +124,7 @@ def test_cuda_front_end_against_oracle(packed, exact):
         worst = max(worst, float(np.max(np.abs(got - want))))
         differing += int(np.count_nonzero(got != want))
         total += want.size
-    print(f"front end ({'packed' if packed else 'u16'}, {'exact' if exact else 'parallel'} dc): "
+    print(f"front end ({'packed' if packed else 'u16'}, {'exact' if exact else 'narrow' if narrow else 'parallel'} dc): "
           f"{differing} of {total} IQ samples differ from the oracle, max abs {worst:.3e}")
     assert worst < 1e-6                                    # full scale is 1.0
     fe.reset()
@@ -132,7 +134,8 @@ def test_cuda_front_end_against_oracle(packed, exact):
 
 
 @pytest.mark.gpu
-def test_front_end_feeds_the_channel_bank():
+@pytest.mark.parametrize("beside", [False, True], ids=["wide", "beside_engine"])
+def test_front_end_feeds_the_channel_bank(beside):
     """20 MS/s real ADC samples -> front end -> engine (device to device) == oracle front end -> oracle chain."""
     from sdrx_b200 import AirspyFrontEnd, ChannelPlan, Engine
     from tests.harness import AUDIO_TOL, product_tables, rel_rms
@@ -148,7 +151,7 @@ def test_front_end_feeds_the_channel_bank():
     x = np.clip(np.rint(x), 0, 4095).astype(np.uint16)
     ofe = ob.OracleAirspyFE(hb())
     orx = ob.OracleRx(product_tables(rate), offs)
-    fe = AirspyFrontEnd(max_samples=2 * L)
+    fe = AirspyFrontEnd(max_samples=2 * L, beside_engine=beside)
     eng = Engine(ChannelPlan.from_offsets(rate, offs))
     opened = False
     for b in range(n_blocks):

@@ -56,7 +56,7 @@ for packed in (False, True):
 offs = list(range(-480, 480))
 plan = ChannelPlan.from_offsets(10000000, offs)
 eng = Engine(plan)
-fe = AirspyFrontEnd(max_samples=N, packed=True)
+fe = AirspyFrontEnd(max_samples=N, packed=True, beside_engine=True)
 blocks = [ob.airspy_pack12(adc_stream(N, seed=20 + i)) for i in range(4)]
 pins = [PinnedBuffer(b.nbytes) for b in blocks]
 for p, b in zip(pins, blocks):

@@ -12,7 +12,7 @@ from oracle import bindings as ob
 N, STEPS = 640000, 40
 offs = list(range(-480, 480))
 eng = Engine(ChannelPlan.from_offsets(10000000, offs))
-fe = AirspyFrontEnd(max_samples=N, packed=True)
+fe = AirspyFrontEnd(max_samples=N, packed=True, beside_engine=os.environ.get("FE_NARROW", "0") == "1")
 blk = ob.airspy_pack12(adc_stream(N, seed=20))
 pin = PinnedBuffer(blk.nbytes); v = pin.view(np.uint32, blk.size); v[:] = blk
 st_fe = torch.cuda.ExternalStream(fe.stream)

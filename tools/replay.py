@@ -69,7 +69,7 @@ def main(argv=None) -> int:
               f"tuner {plan.tuner_fq / 1e6:.3f} MHz; channels "
               + ", ".join(f"{n}[{o:+d}]/{int(s)}/{m}" for n, o, s, m in zip(plan.names, plan.offsets, plan.sql_levels, plan.modulation)))
     eng = Engine(plan, device=args.device, use_lf_agc=args.lf_agc, lf_gain_db=args.volume, use_ftfir=args.ftfir)
-    fe = AirspyFrontEnd(max_samples=2 * src.block_len, packed=src.packed, device=args.device) if src.kind != "iq" else None
+    fe = AirspyFrontEnd(max_samples=2 * src.block_len, packed=src.packed, device=args.device, beside_engine=True) if src.kind != "iq" else None
     out = open(args.output, "wb") if args.output else None
     if out:
         out.write(pcm_wav_header(0))
