@@ -254,7 +254,9 @@ uint64_t sdrx_airspy_fe_launch_count(sdrx_airspy_fe *f);
 /* Orders the engine's ingest stream behind a CUDA event recorded by another producer (e.g. the front end above). */
 int   sdrx_engine_wait_event(sdrx_engine *e, void *cuda_event);
 /* ... and the other way round: the event after which the buffer given to the last push_block_device is free again;
- * the front end's output ring is two deep, so waiting for it before every call keeps a streaming producer safe.  */
+ * the front end's output ring is two deep, so handing it to sdrx_airspy_fe_wait_event before every call keeps a
+ * streaming producer safe: the NEXT call's output write (its last pass only) is ordered behind the event, which must
+ * stay alive until that call has been made.                                                                        */
 void *sdrx_engine_ingest_event(sdrx_engine *e);        /* cudaEvent_t, NULL before the first push */
 int   sdrx_airspy_fe_wait_event(sdrx_airspy_fe *f, void *cuda_event);
 

@@ -483,6 +483,7 @@ extern "C" int sdrx_airspy_fe_reset(sdrx_airspy_fe *f) {
     f->total = 0;
     f->calls = 0;
     f->last_pairs = 0;
+    f->out_free = nullptr;
     return SDRX_OK;
 }
 
