@@ -468,3 +468,35 @@ def test_errors_are_reported_not_swallowed():
     eng.close()
     with pytest.raises(SdrxError):
         Engine(scn.plan(), device=99)
+
+
+def test_bank_trace_reports_every_cta_of_the_schedule():
+    """sdrx_debug_bank_trace / sdrx_debug_bank_plan_dump (tools/diag_bank_trace.py): the kernel's own per-warp clock
+    readings cover exactly the CTAs of the schedule, start before they end, and agree with the event-timed launch."""
+    import ctypes as C
+    from sdrx_b200 import Engine, _lib
+    lib = _lib.load()
+    scn = sc.config3(n_blocks=2)
+    eng = Engine(scn.plan())
+    src = scn.source()
+    blk = src.block(0)
+    eng.process(blk, scn.fmt)
+    assert lib.sdrx_debug_bank_trace(1) == 0
+    eng.set_timing(True)
+    eng.process(blk, scn.fmt)
+    bank_ms, _ = eng.last_timing()
+    eng.set_timing(False)
+    buf = (C.c_uint64 * (160 * 16 * 2))()
+    n = lib.sdrx_debug_bank_trace_read(buf, len(buf))
+    lib.sdrx_debug_bank_trace(0)
+    eng.close()
+    t = np.frombuffer(buf, dtype=np.uint64)[:n].reshape(-1, 16, 2).astype(np.int64)
+    used = t[:, 0, 0] != 0
+    plan = np.zeros((400, 6), np.int32)
+    groups = (479 + 2 + 15) // 16          # 479 conjugate pairs + 2 single channels, 16 lane slots per group
+    pieces = lib.sdrx_debug_bank_plan_dump(groups, 2560, 148, plan.ctypes.data_as(_lib.c_int_p), 400)
+    assert pieces > 0 and int(used.sum()) == int(plan[:pieces, 0].max()) + 1
+    t = t[used]
+    assert np.all(t[:, :, 1] > t[:, :, 0])
+    span_us = (t[:, :, 1].max() - t[:, :, 0].min()) / 1e3
+    assert 0.5 * bank_ms * 1e3 < span_us <= bank_ms * 1e3 + 1.0, (span_us, bank_ms)
