@@ -216,12 +216,15 @@ k_fe_dc(const void *__restrict__ raw, const float *__restrict__ seg_start, int n
 // (profiles/r01y_frontend_timeline.txt).  The wide passes above are ~600 SM-us of work per block; this form cuts the
 // recurrences to 3x the stream (512-sample segments, one warm-up segment: 0.99^512 = 0.006) on 1250 threads, and
 // gets the segments -- which lie 1 KB apart, so a thread reading its own would touch a cache line per lane -- through
-// shared memory: the CTA copies the next 32 samples of all its 512 segments with coalesced 16 B cp.async (8 segments
+// shared memory: the CTA copies the next 32 samples of all its segments with coalesced 16 B cp.async (8 segments
 // per warp instruction, whole sectors), three tiles deep, rows padded to 80 B (conflict-free 128-bit reads).  The
 // outputs go back the same way: a warp parks its 32 rows of ev / od in shared memory and writes them out 64 B per
-// segment (8 segments per store instruction instead of 32 half sectors -- the stores were the pass's bottleneck).
-// 1250 segments are 3 CTAs: one round on the 3 spare SMs.
-constexpr int kNSeg = 512, kNBack = 1, kNThreads = 512, kNTile = 32, kNStages = 3;
+// segment (8 segments per store instruction instead of 32 half sectors).
+// CTA size, measured on the 960-channel chain (tools/bench_frontend.py): 512 threads (3 CTAs, 205 KB each: every one
+// needs an SM to itself) 197 us per block, 256 threads 180, 128 threads 172, 64 threads 171 -- small CTAs slip in
+// next to the engine's side-stream kernels and, because the consumer wait only guards the last pass, mostly run
+// ahead of the bank launch they feed.  128 threads: 10 CTAs of 51 KB.
+constexpr int kNSeg = 512, kNBack = 1, kNThreads = 128, kNTile = 32, kNStages = 3;
 constexpr int kNRow = 80;                                      // bytes per staged row: 64 (u16) or 48 (packed) + pad
 constexpr int kNORow = 80;                                     // ... and per output row (64 B of ev or od + pad)
 inline size_t fe_narrow_smem() { return (size_t)kNStages * kNThreads * kNRow + (size_t)kNThreads * 2 * kNORow; }
