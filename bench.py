@@ -46,27 +46,21 @@ FLOP_CHAIN = FLOP_BANK + 202.0 / 625
 NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12
 
 
-def workload(name: str):
-    from sdrx_b200 import Carrier, ChannelPlan
+def workload(name: str, sql_level=None):
+    from sdrx_b200 import workloads as wl
     if name == "config3":
-        offs = list(range(-480, 480))
-        desc = "config3: Airspy 10 MS/s f32 IQ, full 8 MHz band, 960 channels at 8.33 kHz spacing, squelch+panorama"
-    elif name == "config2":
-        offs = [-360, -121, -37, -1, 2, 40, 250, 479]
-        desc = "config2: Airspy 10 MS/s f32 IQ, 8 channels at 8.33 kHz designators, squelch+panorama"
-    else:
-        raise SystemExit(f"unknown workload {name}")
-    rng = np.random.Generator(np.random.PCG64(777))
-    act = sorted(rng.choice(len(offs), size=min(len(offs), 24), replace=False).tolist())
-    carriers = [Carrier(offs[k], float(10 ** rng.uniform(-2.4, -1.3)), float(rng.uniform(300, 3000)), 0.5,
-                        (lambda b, k=k: (b + k) % 4 != 0)) for k in act]
-    return ChannelPlan.from_offsets(RATE, offs), carriers, desc
+        return wl.config3(960, sql_level)
+    if name == "config2":
+        return wl.config2()
+    raise SystemExit(f"unknown workload {name}")
+
+
+N_DISTINCT = 8            # distinct synthetic blocks (two keying epochs of the carriers); the device ring cycles them
 
 
 def synth_blocks(carriers, n: int, seed: int):
-    from sdrx_b200 import SyntheticSource
-    src = SyntheticSource(RATE, carriers, noise_sigma=0.0008, seed=seed, n_blocks=n)
-    return [src.block(b) for b in range(n)]
+    from sdrx_b200 import workloads as wl
+    return wl.synth_blocks(carriers, n, seed)
 
 
 class ClockSampler:
@@ -226,7 +220,7 @@ def run_reference(args):
     if rank != 0:
         return 0
     plan, carriers, desc = workload(args.workload)
-    blocks = synth_blocks(carriers, 2, 1)
+    blocks = synth_blocks(carriers, 2, 1)       # blocks 0, 1 of the GPU arm's rank-0 stream
     C_ = len(plan.offsets)
     L = plan.rate.block_len
     per_step, kind, backend, used = time_reference(plan, blocks, args.steps, max(args.warmup, 1), C_)
@@ -267,63 +261,118 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def max_over_ranks(x: float) -> float:
+        t = torch.tensor([x], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
     plan, carriers, desc = workload(args.workload)
     C_ = len(plan.offsets)
     L = plan.rate.block_len
     lib = _lib.load()
     eng = Engine(plan, device=local)
-    stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
-
-    # ---- synthetic IQ: a few distinct blocks, laid out as a device ring larger than L2 (126 MB)
-    n_distinct = 4
-    blocks = synth_blocks(carriers, n_distinct, 1 + rank)
-    blk_bytes = blocks[0].nbytes
-    ring = max(8, int(np.ceil(140e6 / blk_bytes)))          # 55 x 2.56 MB = 141 MB of f32 IQ
-    d_ring = lib.sdrx_device_alloc(local, ring * blk_bytes)
-    if not d_ring:
-        raise SystemExit("device ring allocation failed")
-    for i in range(ring):
-        b = blocks[i % n_distinct]
-        _lib.check(lib.sdrx_device_upload(local, C.c_void_p(d_ring + i * blk_bytes), b.ctypes.data_as(C.c_void_p), blk_bytes))
-
-    def step_device(i):
-        eng.push_device(d_ring + (i % ring) * blk_bytes, 2, L)
-
-    # ---- value leg
-    for i in range(max(args.warmup, 3)):
-        step_device(i)
-    eng.sync()
     try:
         uuid = torch.cuda.get_device_properties(local).uuid
     except Exception:
         uuid = None
-    sampler = ClockSampler(local, uuid)
-    barrier()
-    sampler.start()
-    l0 = eng.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record(stream)
-    for i in range(args.steps):
-        step_device(args.warmup + i)
-    eng.join()                      # the last blocks' side-stream kernels (recurrences, mix) are inside the timed region
-    ev1.record(stream)
-    eng.sync()
-    barrier()
-    launches = eng.launch_count - l0
-    clocks = sampler.stop()
-    ms = ev0.elapsed_time(ev1)
-    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total = float(t.item())
-    per_step_ms = ms_total / args.steps
+
+    # ---- synthetic IQ: N_DISTINCT distinct blocks, laid out as a device ring larger than L2 (126 MB)
+    blocks = synth_blocks(carriers, N_DISTINCT, 1 + rank)
+    blk_bytes = blocks[0].nbytes
+    ring = int(np.ceil(140e6 / blk_bytes / N_DISTINCT)) * N_DISTINCT      # 56 x 2.56 MB = 143 MB of f32 IQ
+    d_ring = lib.sdrx_device_alloc(local, ring * blk_bytes)
+    if not d_ring:
+        raise SystemExit("device ring allocation failed")
+    for i in range(ring):
+        b = blocks[i % N_DISTINCT]
+        _lib.check(lib.sdrx_device_upload(local, C.c_void_p(d_ring + i * blk_bytes), b.ctypes.data_as(C.c_void_p), blk_bytes))
+    pins = [PinnedBuffer(blk_bytes) for _ in range(N_DISTINCT)]
+    for p, b in zip(pins, blocks):
+        p.view(np.complex64, L)[:] = b
+    hviews = [p.view(np.complex64, L) for p in pins]
+
+    def value_leg(e, steps, warmup, sample_clocks=False):
+        """`steps` blocks from the device ring, whole chain, CUDA events on the engine's stream; max over ranks."""
+        stream = torch.cuda.ExternalStream(e.stream, device=torch.device("cuda", local))
+        for i in range(warmup):
+            e.push_device(d_ring + (i % ring) * blk_bytes, 2, L)
+        e.sync()
+        sampler = ClockSampler(local, uuid) if sample_clocks else None
+        barrier()
+        if sampler:
+            sampler.start()
+        l0 = e.launch_count
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record(stream)
+        for i in range(steps):
+            e.push_device(d_ring + ((warmup + i) % ring) * blk_bytes, 2, L)
+        e.join()                    # the last blocks' side-stream kernels (recurrences, mix) are inside the timed region
+        ev1.record(stream)
+        e.sync()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms = max_over_ranks(ev0.elapsed_time(ev1))
+        return ms / steps, e.launch_count - l0, clocks
+
+    def e2e_leg(e, steps):
+        """The same chain through the C-ABI call a host makes: push_block from pinned host memory, fetch_outputs into
+        pinned host memory (squelch, SNR, mix, pcm, power and the SPARSE per-channel audio: 2 KB per open channel),
+        wait_outputs LAG blocks later -- so the copies of one block overlap the kernels of its neighbours and the
+        device->host->device round trip is off the critical path.  Every step moves its own input and its own results
+        across the host link inside the timed region; d2h bytes are counted from what actually crossed."""
+        stream = torch.cuda.ExternalStream(e.stream, device=torch.device("cuda", local))
+        LAG = 3
+        want = ("audio_rows", "audio_chan", "n_audio", "sql_state", "snr", "mix", "pcm", "pwr_dbfs")
+        osets = [e.make_output_buffers(pinned=True, want=want) for _ in range(LAG + 1)]
+        fixed = C_ * 1 + C_ * 4 + 1024 * 4 + 1024 * 2 + 4 + 4            # sql, snr, mix, pcm, pwr, n_audio
+        for i in range(4):
+            e.push(hviews[i % N_DISTINCT])
+            e.outputs_into(osets[i % (LAG + 1)][0])
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        ev0.record(stream)
+        host = [0.0, 0.0, 0.0]                  # host seconds spent inside push / fetch / wait (diagnostic)
+        rows = 0
+        for i in range(steps):
+            h0 = time.perf_counter()
+            e.push(hviews[i % N_DISTINCT])
+            h1 = time.perf_counter()
+            e.fetch_outputs(osets[i % (LAG + 1)][0])
+            h2 = time.perf_counter()
+            if i >= LAG:
+                e.wait_outputs(LAG)             # block i-LAG's audio / squelch / pcm are in host memory now
+                rows += int(osets[(i - LAG) % (LAG + 1)][1]["n_audio"][0])
+            h3 = time.perf_counter()
+            host[0] += h1 - h0
+            host[1] += h2 - h1
+            host[2] += h3 - h2
+        for back in range(min(LAG, steps) - 1, -1, -1):
+            e.wait_outputs(back)                # drain: every block's results are in host memory inside the timed region
+            rows += int(osets[(steps - 1 - back) % (LAG + 1)][1]["n_audio"][0])
+        e.join()
+        ev1.record(stream)
+        e.sync()
+        wall = (time.perf_counter() - t0) * 1e3
+        barrier()
+        ms = max_over_ranks(max(ev0.elapsed_time(ev1), wall))    # host-inclusive: the later of device span and wall clock
+        open_rows = rows / steps
+        return {"value": world * C_ * L / (ms / steps * 1e-3) / 1e6, "unit": "channel-MS/s",
+                "h2d_bytes_per_step": blk_bytes, "d2h_bytes_per_step": int(round(fixed + open_rows * (2048 + 4))),
+                "open_channels_per_step": open_rows, "ms_per_step": ms / steps,
+                "host_us_per_step": {"push": host[0] / steps * 1e6, "fetch": host[1] / steps * 1e6,
+                                     "wait": host[2] / steps * 1e6}}
+
+    # ---- value leg
+    per_step_ms, launches, clocks = value_leg(eng, args.steps, args.warmup, sample_clocks=True)
     value = world * C_ * L / (per_step_ms * 1e-3) / 1e6
 
     # ---- per-kernel time of the dominant kernel (channel bank), CUDA events around it on its stream
     eng.set_timing(True)
     bank, whole = [], []
     for i in range(min(args.steps, 20)):
-        step_device(i)
+        eng.push_device(d_ring + (i % ring) * blk_bytes, 2, L)
         eng.sync()
         a, b = eng.last_timing()
         bank.append(a)
@@ -334,9 +383,12 @@ def run_ours(args):
     flop_bank = FLOP_BANK if eng.uses_fast_path else FLOP_CHAIN
     achieved = flop_bank * C_ * L / (bank_ms * 1e-3) / 1e12
     roofline = {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "peak_nominal": NOMINAL_FP32_TFLOPS, "frac_nominal": achieved / NOMINAL_FP32_TFLOPS,
                 "traffic": None, "kernel": "channel bank (mix + decimating FIR stages)" if eng.uses_fast_path
                 else "generic channelizer kernels (all stages)",
-                "kernel_ms": bank_ms, "block_ms_serialised": statistics.mean(whole), "share_of_step": bank_ms / statistics.mean(whole),
+                "kernel_ms": bank_ms, "block_ms_serialised": statistics.mean(whole),
+                "share_of_step": bank_ms / per_step_ms, "share_of_serialised_block": bank_ms / statistics.mean(whole),
+                "chain_frac": FLOP_CHAIN * C_ * L / (per_step_ms * 1e-3) / 1e12 / peak,
                 "algorithmic_flop_per_channel_sample": flop_bank, "peak_source": peak_how}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
@@ -354,48 +406,8 @@ def run_ours(args):
                        "peak": hbm_peak, "unit": "GB/s",
                        "frac": (alg_bytes / (bank_ms * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None}
 
-    # ---- e2e leg: pinned host IQ in, pinned host results out, through the C ABI, every step
-    pins = [PinnedBuffer(blk_bytes) for _ in range(n_distinct)]
-    for p, b in zip(pins, blocks):
-        p.view(np.complex64, L)[:] = b
-    hviews = [p.view(np.complex64, L) for p in pins]
-    # Streaming use of the API: push block i (H2D from pinned memory), queue its read-back into pinned result
-    # buffers, and only then wait for block i-3's results -- so the copies of one block overlap the kernels of
-    # its neighbours and the device->host->device round trip is off the critical path.  Every step still moves its own input and its own results across PCIe inside the timed region.
-    LAG = 3                                  # the host reads block i-LAG's results while blocks i-LAG+1 .. i are in flight
-    osets = [eng.make_output_buffers(pinned=True) for _ in range(LAG + 1)]
-    d2h = osets[0][2]
-    for i in range(4):
-        eng.push(hviews[i % n_distinct])
-        eng.outputs_into(osets[i % (LAG + 1)][0])
-    barrier()
-    t0 = time.perf_counter()
-    ev0.record(stream)
-    host = [0.0, 0.0, 0.0]                  # host seconds spent inside push / fetch / wait (diagnostic)
-    for i in range(args.steps):
-        h0 = time.perf_counter()
-        eng.push(hviews[i % n_distinct])
-        h1 = time.perf_counter()
-        eng.fetch_outputs(osets[i % (LAG + 1)][0])
-        h2 = time.perf_counter()
-        if i >= LAG:
-            eng.wait_outputs(LAG)           # block i-LAG's audio / squelch / pcm are in host memory now
-        h3 = time.perf_counter()
-        host[0] += h1 - h0
-        host[1] += h2 - h1
-        host[2] += h3 - h2
-    for back in range(min(LAG, args.steps) - 1, -1, -1):
-        eng.wait_outputs(back)              # drain: every block's results are in host memory inside the timed region
-    eng.join()
-    ev1.record(stream)
-    eng.sync()
-    wall = (time.perf_counter() - t0) * 1e3
-    barrier()
-    e2e_ms = max(ev0.elapsed_time(ev1), wall)       # host-inclusive: the later of device span and wall clock
-    t = torch.tensor([e2e_ms], device="cuda", dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_val = world * C_ * L / (float(t.item()) / args.steps * 1e-3) / 1e6
+    # ---- e2e leg
+    e2e = e2e_leg(eng, args.steps)
     # what the wire allows: one block's H2D and one block's D2H alone, pinned memory, CUDA events (diagnostic)
     def _copy_gbs(dst, src, nbytes, reps=20):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -409,11 +421,34 @@ def run_ours(args):
         return nbytes * reps / (a.elapsed_time(b) * 1e-3) / 1e9
     hbuf = torch.empty(blk_bytes, dtype=torch.uint8, pin_memory=True)
     dbuf = torch.empty(blk_bytes, dtype=torch.uint8, device="cuda")
-    pcie = {"h2d_gbs_block": _copy_gbs(dbuf, hbuf, blk_bytes), "d2h_gbs_block": _copy_gbs(hbuf, dbuf, blk_bytes)}
-    e2e = {"value": e2e_val, "unit": "channel-MS/s", "h2d_bytes_per_step": blk_bytes, "d2h_bytes_per_step": d2h, "pcie": pcie,
-           "ms_per_step": float(t.item()) / args.steps,
-           "host_us_per_step": {"push": host[0] / args.steps * 1e6, "fetch": host[1] / args.steps * 1e6,
-                                "wait": host[2] / args.steps * 1e6}}
+    e2e["pcie"] = {"h2d_gbs_block": _copy_gbs(dbuf, hbuf, blk_bytes), "d2h_gbs_block": _copy_gbs(hbuf, dbuf, blk_bytes)}
+
+    # ---- sustained leg: config 5's regime -- seconds of back-to-back blocks, clocks sampled all the way through
+    sustained = None
+    if args.sustain > 0:
+        n_sus = max(args.steps, int(args.sustain / (per_step_ms * 1e-3)))
+        sus_ms, _, sus_clk = value_leg(eng, n_sus, 3, sample_clocks=True)
+        sustained = {"seconds": sus_ms * n_sus * 1e-3, "steps": n_sus, "ms_per_step": sus_ms,
+                     "value": world * C_ * L / (sus_ms * 1e-3) / 1e6, "ratio_to_value": per_step_ms / sus_ms,
+                     "clocks": sus_clk}
+
+    # ---- worst case of boundary B: sql_level 0 opens every squelch (sdrx.cpp:569): all channels run both recurrences,
+    #      the ordered mix walks every channel, every audio row crosses the host link
+    worst = None
+    if not args.no_worst:
+        wplan, _, _ = workload(args.workload, sql_level=0.0)
+        weng = Engine(wplan, device=local)
+        w_ms, _, _ = value_leg(weng, args.steps, args.warmup)
+        w_e2e = e2e_leg(weng, args.steps)
+        worst = {"what": "same blocks, sql_level 0 on every channel: all squelches open (sdrx.cpp:569)",
+                 "ms_per_step": w_ms, "value": world * C_ * L / (w_ms * 1e-3) / 1e6, "ratio_to_value": per_step_ms / w_ms,
+                 "e2e": w_e2e}
+        weng.close()
+
+    # ---- parity of the bench's own workload against the oracle (--check): every channel, every distinct block
+    check = None
+    if args.check and rank == 0:
+        check = check_against_oracle(plan, blocks, local)
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only): bounded sample of the same workload
     cpu = None
@@ -437,13 +472,43 @@ def run_ours(args):
                        "specialised_bank": bool(eng.uses_fast_path)},
             "realtime_channels": value / (RATE / 1e6),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "worst_case": worst, "sustained": sustained,
         }
+        if check is not None:
+            line["parity_check"] = check
         print(json.dumps(line))
     eng.close()
     lib.sdrx_device_free(local, C.c_void_p(d_ring))
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def check_against_oracle(plan, blocks, device):
+    """bench.py --check: the bench's own blocks through the CUDA engine and through the CPU oracle (the checker, never
+    the thing measured): squelch decisions must agree exactly, channel IQ / audio within 1e-4 relative RMS per channel."""
+    from oracle import bindings as ob
+    from sdrx_b200 import Engine
+    from tests.harness import product_tables, rel_rms, squelch_margin
+    orx = ob.OracleRx(product_tables(RATE), plan.offsets, plan.sql_levels)
+    eng = Engine(plan, device=device)
+    worst_iq = worst_au = 0.0
+    margin = float("inf")
+    sql_ok, opened = True, 0
+    for blk in blocks:
+        w = orx.process(blk, 2)
+        g = eng.process(blk, 2)
+        sql_ok = sql_ok and bool(np.array_equal(g.sql, w.sql))
+        opened += int(w.sql.sum())
+        margin = min(margin, squelch_margin(w.snr, np.asarray(plan.sql_levels)))
+        for c in range(len(plan.offsets)):
+            worst_iq = max(worst_iq, rel_rms(g.ch_iq[c], w.ch_iq[c]))
+            if np.any(w.audio[c] != 0.0):
+                worst_au = max(worst_au, rel_rms(g.audio[c], w.audio[c]))
+    eng.close()
+    return {"blocks": len(blocks), "channels": len(plan.offsets), "squelch_decisions_equal": sql_ok,
+            "open_channel_blocks": opened, "oracle_squelch_margin_db": margin, "worst_channel_iq_rel_rms": worst_iq,
+            "worst_audio_rel_rms": worst_au, "bar": 1e-4}
 
 
 def main():
@@ -454,6 +519,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="config3", choices=["config3", "config2"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-worst", action="store_true", help="skip the worst_case leg (every squelch open)")
+    ap.add_argument("--sustain", type=float, default=3.2, help="seconds of back-to-back blocks in the sustained leg (0: skip)")
+    ap.add_argument("--check", action="store_true", help="also run the bench's own blocks through the CPU oracle and report parity")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     return run_reference(args) if args.impl == "reference" else run_ours(args)

@@ -56,10 +56,6 @@ typedef enum { SDRX_FMT_U8 = 0, SDRX_FMT_S16 = 1, SDRX_FMT_F32 = 2 } sdrx_iq_for
                                          could share a translator table as conjugates                       */
 #define SDRX_FLAG_FTFIR         0x10u /* --ftfir (sdrx.cpp:1199,:1692): the first stage is the frequency-translating FIR,
                                          msd.hpp:104-131 + calculateOutputTranslated :341-423, instead of mix + FIR      */
-#define SDRX_FLAG_TAIL_SIDE     0x20u /* specialised path, experimental: run the last MSD stage together with the detector under
-                                         the next block's bank (k_chan_tail_side, own stream, ping-pong stage rows) instead
-                                         of on the main stream (k_chan_fir_fast).  Measured slower on B200 (one 7 KB CTA per
-                                         SM next to a bank CTA, ~30 us of latency each): off by default.                  */
 #define SDRX_FLAG_PARTIAL_MIX   0x4u  /* channel-sharded run: stop at mix_pre (this GPU's share of the pan
                                          mix); FIR2 + s16 run once, in sdrx_engine_finish_mix              */
 
@@ -111,6 +107,14 @@ typedef struct {
     float   *pwr_dbfs;   /* [1]       Metadata.pwr_dbfs (rtl_dev.cpp:329-341)                       */
     float   *agc_gain;   /* [C]       AGC::gain()   (agc.hpp:46)                                    */
     float   *lf_gain;    /* [C]       LfAGC::gain() (agc.hpp:101)                                   */
+    /* Sparse form of `audio`: only channels whose squelch is open or ramping down contribute to the mix
+     * (sdrx.cpp:459-463, :498-501); every other row of `audio` is exact zeros.  n_audio[0] = number of such channels,
+     * audio_chan[k] = their indices (ascending), audio_rows[k][512] = their audio, k < n_audio[0]; later rows are left
+     * untouched.  With sdrx_engine_fetch_outputs these three must be pinned (sdrx_host_alloc): the device writes them
+     * straight across the host link, so a block costs 2 KB per OPEN channel instead of 2 KB per channel.         */
+    float   *audio_rows; /* [C][512]  capacity; rows [0, n_audio) valid                              */
+    int32_t *audio_chan; /* [C]                                                                     */
+    int32_t *n_audio;    /* [1]                                                                     */
 } sdrx_block_outputs;
 
 const char *sdrx_last_error(void);

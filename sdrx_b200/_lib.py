@@ -13,7 +13,7 @@ c_u8_p = C.POINTER(C.c_uint8)
 c_i16_p = C.POINTER(C.c_int16)
 
 FMT_U8, FMT_S16, FMT_F32 = 0, 1, 2
-FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, FLAG_FTFIR, FLAG_TAIL_SIDE = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20
+FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, FLAG_FTFIR = 0x1, 0x2, 0x4, 0x8, 0x10
 CHUNK = 512
 
 
@@ -39,7 +39,7 @@ class BlockOutputs(C.Structure):
     _fields_ = [
         ("audio", c_float_p), ("sql_state", c_u8_p), ("snr", c_float_p), ("mix_pre", c_float_p),
         ("mix", c_float_p), ("pcm", c_i16_p), ("pwr_dbfs", c_float_p), ("agc_gain", c_float_p),
-        ("lf_gain", c_float_p),
+        ("lf_gain", c_float_p), ("audio_rows", c_float_p), ("audio_chan", c_int_p), ("n_audio", c_int_p),
     ]
 
 

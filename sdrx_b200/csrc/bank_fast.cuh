@@ -36,6 +36,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "host_common.h"
 
 namespace sdrx {
 
@@ -378,10 +379,8 @@ struct FastBank {
     int period_units = 1;              // units after which the translator phase repeats: N / gcd(N, 125)
     FastTaps taps{};
     FastSchedule sched[2];             // small cache keyed by U (block length / 125)
-    float2 *d_tails = nullptr;         // two halves (ping-pong): the side-stream tail kernel of block b reads one
-                                       // while the bank of block b+1 writes the other
-    int tails_slots = 0;               // capacity of one half in slots per channel
-    float2 *tails_half(int h) const { return d_tails + (size_t)h * 4 * (size_t)tails_slots * C; }
+    float2 *d_tails = nullptr;         // [C][tails_slots][4] partial stage-3 sums across segment boundaries
+    int tails_slots = 0;               // capacity in slots per channel
     int C = 0;
     float2 *d_table_slot = nullptr;    // [N][groups*16] one column per slot (own copy only when paired)
     int tstride = 0;
@@ -405,7 +404,10 @@ inline bool fast_eligible(int S, const int *m, const int *H, int N) {
     if (S < 3) return false;
     if (m[0] != 5 || m[1] != 5 || m[2] != 5) return false;
     if (H[0] != 17 || H[1] != 19 || H[2] != 21) return false;
-    if (N < 1 || fast_smem_bytes(N) > 227 * 1024) return false;
+    // the table is staged with kWrap rows replicated past N and the row index wraps by one subtraction per 25-sample
+    // body: both need N > kWrap (N == 1 is the reference's single centre-channel run, which has no translator at all
+    // -- sdrx.cpp:1408, :1684 -- and goes through the generic kernels)
+    if (N <= kWrap || fast_smem_bytes(N) > 227 * 1024) return false;
     return true;
 }
 
@@ -615,7 +617,7 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
 template <int FMT>
 int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int valid_lo, int N, int pos0, unsigned n,
                 float2 *s3, long s3_stride, int s3_off, uint64_t *launches, cudaEvent_t ev0 = nullptr,
-                cudaEvent_t ev1 = nullptr, const FastSchedule **deferred_fix = nullptr, int tail_half = 0) {
+                cudaEvent_t ev1 = nullptr, const FastSchedule **deferred_fix = nullptr) {
     const int U = (int)(n / kUnit);
     FastSchedule *sc = nullptr;
     for (auto &s : fb.sched) if (s.U == U) sc = &s;
@@ -631,25 +633,25 @@ int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int va
         CU(cudaDeviceSynchronize());
         cudaFree(fb.d_tails);
         fb.d_tails = nullptr;
-        CU(cudaMalloc((void **)&fb.d_tails, 2 * sizeof(float2) * 4 * (size_t)sc->n_slots * fb.C));
+        CU(cudaMalloc((void **)&fb.d_tails, sizeof(float2) * 4 * (size_t)sc->n_slots * fb.C));
         fb.tails_slots = sc->n_slots;
     }
     if (ev0) CU(cudaEventRecord(ev0, st));
     if (fb.nch == 2)
         k_bank_fast<FMT, 2><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
             raw, hist, valid_lo, fb.d_table_slot, fb.tstride, fb.d_slot_chan, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U,
-            s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots);
+            s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots);
     else
         k_bank_fast<FMT, 1><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
             raw, hist, valid_lo, fb.d_table_slot, fb.tstride, fb.d_slot_chan, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U,
-            s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots);
+            s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots);
     if (ev1) CU(cudaEventRecord(ev1, st));
     ++*launches;
     if (deferred_fix) *deferred_fix = sc;           // the caller's next kernel applies the fix list itself
     else if (sc->n_fixes > 0) {
         const int per_group = kFastCh * fb.nch;
         const int threads = sc->n_fixes * per_group;
-        k_fix_tails<<<div_up(threads, 256), 256, 0, st>>>(s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots, sc->d_fixes,
+        k_fix_tails<<<div_up(threads, 256), 256, 0, st>>>(s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots, sc->d_fixes,
                                                           sc->n_fixes, fb.d_slot_chan, per_group);
         ++*launches;
     }
@@ -716,13 +718,13 @@ inline int fast_init(FastBank &fb, int C, int N, const float *h1, const float *h
     CU(cudaMalloc((void **)&fb.d_chan_group, sizeof(int) * chan_group.size()));
     CU(cudaMemcpy(fb.d_chan_group, chan_group.data(), sizeof(int) * chan_group.size(), cudaMemcpyHostToDevice));
 
-    const int smem = (int)fast_smem_bytes(N);
-    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_U8, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_S16, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_F32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_U8, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_S16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    CU(cudaFuncSetAttribute(k_bank_fast<SDRX_FMT_F32, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    {
+        const size_t smem = fast_smem_bytes(N);
+        const void *fn[6] = {(const void *)k_bank_fast<SDRX_FMT_U8, 1>, (const void *)k_bank_fast<SDRX_FMT_S16, 1>,
+                             (const void *)k_bank_fast<SDRX_FMT_F32, 1>, (const void *)k_bank_fast<SDRX_FMT_U8, 2>,
+                             (const void *)k_bank_fast<SDRX_FMT_S16, 2>, (const void *)k_bank_fast<SDRX_FMT_F32, 2>};
+        for (const void *f : fn) { int rc = raise_dyn_smem(f, smem); if (rc) return rc; }
+    }
     fb.enabled = true;
     return SDRX_OK;
 }

@@ -34,6 +34,8 @@ struct OutSet {                   // device-side results of one block
     float   *pwr = nullptr;       // [1]
     uint8_t *sql = nullptr;       // [C] snapshot of the state after the decision
     float   *agc_gain = nullptr, *lf_gain = nullptr;   // [C] snapshots
+    int     *audio_idx = nullptr; // [C] channels whose audio is mixed this block, ascending (k_mix_fir2_pcm)
+    int     *n_audio = nullptr;   // [1] how many
 };
 
 }  // namespace
@@ -89,19 +91,13 @@ struct sdrx_engine {
     float *d_c_adj = nullptr, *d_fir_hist = nullptr;
     float *d_parts = nullptr;             // staging of the per-GPU partial mixes (sdrx_engine_finish_mix)
     size_t parts_cap = 0;
+    unsigned *d_ticket = nullptr;         // arrival counter of k_mix_fir2_pcm's CTAs (the last one runs FIR2); self-resetting
+    float *d_rows_scratch = nullptr;      // [C][512] compacted audio rows for callers whose result buffers are pageable
     FastBank fast;                        // specialised channel bank (bank_fast.cuh)
     bool use_fast = false;
     bool tail_fusable = false;            // last stage as one per-channel kernel fed by the bank's rows + tail fix-ups
     bool tail_fast = false;               // ... in its specialised form (67 taps, decimate by 5: k_chan_fir_fast)
     FirTaps<67> tail_taps{};
-    bool tail_side = false;               // ... and under the next bank on its own side stream (k_chan_tail_side)
-    cudaStream_t s_tail = nullptr;        // last stage + detector of block b (needs only the 9 KB a bank CTA leaves)
-    float2 *d_stage_alt = nullptr;        // ping-pong partner of d_stage_in[S-1]: block b+1's bank writes it while block b's tail kernel reads the other
-    cudaEvent_t ev_tail_done[2] = {nullptr, nullptr};   // tail kernel that read row / tails buffer `par` is complete
-    bool tail_pending[2] = {false, false};
-    int tail_par = 0;                     // row / tails buffer the next fused block uses
-    int last_tail_par = -1;               // buffer of the most recent side-stream tail kernel (-1: none outstanding)
-    bool prev_block_side_tail = false;
     bool ftfir = false;                   // --ftfir: stage 0 is the frequency-translating FIR (msd.hpp:104-131)
     int ft_sets = 0;                      // coefficient sets, N / m[0] (msd.hpp:196)
     float2 *d_hk = nullptr;               // [ft_sets * H0][Cpad]
@@ -115,7 +111,8 @@ struct sdrx_engine {
     int phase[SDRX_MAX_STAGES] = {0};    // inputs seen since the stage's last output (m - isn_)
     int ft_k = 0;                        // S::k_ of stage 0 (msd.hpp:434), same for every channel
     int fmt = -1;                        // wire format of the stream so far
-    uint64_t blocks = 0;
+    uint64_t blocks = 0;                 // output sets handed out so far (push_block and demod_block): selects out[blocks % kNOut]
+    uint64_t pushes = 0;                 // blocks through the channelizer: its parity selects the raw ping-pong buffer
     unsigned prev_n = 0;                 // samples of the previous block (for the raw carry)
     uint64_t total = 0;                  // samples pushed so far (what of the raw history belongs to the stream)
     bool generic_stale = false;          // stage 1-2 delay lines not maintained (the specialised bank ran last)
@@ -204,13 +201,9 @@ void agc_defaults(AgcParams &p, float attack, float decay, float reference, floa
 
 int reset_state(sdrx_engine *e) {
     const size_t C = (size_t)e->C;
-    CU(cudaStreamSynchronize(e->s_tail));
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
-    e->tail_pending[0] = e->tail_pending[1] = false;
-    e->tail_par = 0; e->last_tail_par = -1; e->prev_block_side_tail = false;
-    if (e->d_stage_alt) CU(cudaMemsetAsync(e->d_stage_alt, 0, sizeof(float2) * (size_t)e->stage_stride[e->S - 1] * C, e->s_main));
     for (int b = 0; b < kNBuf; ++b) CU(cudaMemsetAsync(e->d_raw[b], 0, e->raw_buf_bytes, e->s_main));
     for (int s = 1; s < e->S; ++s)
         CU(cudaMemsetAsync(e->d_stage_in[s], 0, sizeof(float2) * (size_t)e->stage_stride[s] * C, e->s_main));
@@ -225,6 +218,7 @@ int reset_state(sdrx_engine *e) {
         CU(cudaMemsetAsync(e->st.mixed, 0, C, e->s_main));
         CU(cudaMemsetAsync(e->st.fm_prev, 0, C * sizeof(float2), e->s_main));
         CU(cudaMemsetAsync(e->d_fir_hist, 0, sizeof(float) * 2 * (size_t)std::max(e->fir2_ntaps - 1, 1), e->s_main));
+        CU(cudaMemsetAsync(e->d_ticket, 0, sizeof(unsigned), e->s_main));
         CU(cudaStreamSynchronize(e->s_main));   // the host vectors above die here
     }
     CU(cudaStreamSynchronize(e->s_main));
@@ -233,6 +227,7 @@ int reset_state(sdrx_engine *e) {
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = 0;
     e->fmt = -1;
     e->blocks = 0;
+    e->pushes = 0;
     e->prev_n = 0;
     e->total = 0;
     e->generic_stale = false;
@@ -259,14 +254,12 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
         OutSet &o = e->out[b];
         cudaFree(o.ch_iq); cudaFree(o.audio); cudaFree(o.snr); cudaFree(o.mix_pre); cudaFree(o.mix);
         cudaFree(o.pcm); cudaFree(o.pwr); cudaFree(o.sql); cudaFree(o.agc_gain); cudaFree(o.lf_gain);
+        cudaFree(o.audio_idx); cudaFree(o.n_audio);
         if (e->ev_side_done[b]) cudaEventDestroy(e->ev_side_done[b]);
         if (e->ev_fetch_done[b]) cudaEventDestroy(e->ev_fetch_done[b]);
         cudaFree(e->d_gate[b]); cudaFree(e->d_pwr_partial[b]);
     }
     if (e->ev_head_done) cudaEventDestroy(e->ev_head_done);
-    for (int b = 0; b < 2; ++b) if (e->ev_tail_done[b]) cudaEventDestroy(e->ev_tail_done[b]);
-    cudaFree(e->d_stage_alt);
-    if (e->s_tail) cudaStreamDestroy(e->s_tail);
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) cudaFree(e->d_stage_in[s]);
     cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps); cudaFree(e->d_hk);
     cudaFree(e->st.agc_gain); cudaFree(e->st.agc_power); cudaFree(e->st.lf_gain); cudaFree(e->st.lf_power);
@@ -274,7 +267,7 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     cudaFree(e->st.sql_state); cudaFree(e->st.sql_prev); cudaFree(e->st.mixed);
     cudaFree(e->d_window); cudaFree(e->d_shape); cudaFree(e->d_ramp_up); cudaFree(e->d_ramp_down);
     cudaFree(e->d_twiddle); cudaFree(e->d_bitrev); cudaFree(e->d_sql_level); cudaFree(e->d_pos);
-    cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist); cudaFree(e->d_parts);
+    cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist); cudaFree(e->d_parts); cudaFree(e->d_ticket); cudaFree(e->d_rows_scratch);
     e->fast.destroy();
     if (e->ev_t0) cudaEventDestroy(e->ev_t0);
     if (e->ev_t1) cudaEventDestroy(e->ev_t1);
@@ -318,8 +311,6 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     CU(cudaStreamCreateWithFlags(&e->s_side, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->ev_head_done, cudaEventDisableTiming));
-    CU(cudaStreamCreateWithFlags(&e->s_tail, cudaStreamNonBlocking));
-    for (int b = 0; b < 2; ++b) CU(cudaEventCreateWithFlags(&e->ev_tail_done[b], cudaEventDisableTiming));
     for (int b = 0; b < kNOut; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_side_done[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_fetch_done[b], cudaEventDisableTiming));
@@ -434,6 +425,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if ((rc = dalloc(&o.sql, C))) return rc;
         if ((rc = dalloc(&o.agc_gain, C))) return rc;
         if ((rc = dalloc(&o.lf_gain, C))) return rc;
+        if ((rc = dalloc(&o.audio_idx, C))) return rc;
+        if ((rc = dalloc(&o.n_audio, 1))) return rc;
     }
 
     if (!(e->flags & SDRX_FLAG_NO_DEMOD)) {
@@ -494,31 +487,22 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             (rc = dalloc(&e->d_c_adj, c_adj.size())) || (rc = upload(e->d_c_adj, c_adj.data(), c_adj.size())) ||
             (rc = dalloc(&e->d_fir_hist, 2 * (size_t)std::max(cfg->fir2_ntaps - 1, 1))))
             return rc;
+        if ((rc = dalloc(&e->d_ticket, 1))) return rc;
         e->tb = DemodTables{e->d_window, e->d_twiddle, e->d_bitrev, e->d_shape, e->d_ramp_up, e->d_ramp_down};
         if ((size_t)C * 4 > 160 * 1024) return fail(SDRX_ERR_UNSUPPORTED, "more than 40960 channels per engine");
-        CU(cudaFuncSetAttribute(k_mix_fir2_pcm, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)(sizeof(float) * 2 * (size_t)(cfg->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad)));
+        { int rc2 = raise_dyn_smem((const void *)k_mix_fir2_pcm, mix_smem_bytes(e->Cpad, cfg->fir2_ntaps)); if (rc2) return rc2; }
         if (S >= 1) {       // the per-channel tail kernel stages the last stage's input row in shared memory when fused
             size_t row = (size_t)(e->H[S - 1] - 1) + (size_t)kChunk * e->m[S - 1];
             e->tail_fusable = row * sizeof(float2) <= 100 * 1024 && (e->H[S - 1] - 1) / 2 + 1 <= kTailMaxHalf;
             if (e->tail_fusable)
-                CU(cudaFuncSetAttribute(k_chan_head<kHeadFir>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)(sizeof(float2) * row)));
+                { int rc2 = raise_dyn_smem((const void *)k_chan_head<kHeadFir>, sizeof(float2) * row); if (rc2) return rc2; }
             e->tail_fast = e->tail_fusable && e->H[S - 1] == 67 && e->m[S - 1] == 5 && e->chiq_stride % 2 == 0;
             if (e->tail_fast) {
                 const float *h = e->taps.data() + e->tap_off[S - 1];
                 for (int i = 0; i < 67; ++i) e->tail_taps.h[i] = make_float2(h[i], h[i]);
-                CU(cudaFuncSetAttribute(k_chan_fir_fast<67, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        (int)fir_fast_smem(67, 5, kChunk * 5)));
+                { int rc2 = raise_dyn_smem((const void *)k_chan_fir_fast<67, 5>, fir_fast_smem(67, 5, kChunk * 5)); if (rc2) return rc2; }
                 CU(cudaFuncSetAttribute(k_chan_fir_fast<67, 5>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                         (int)cudaSharedmemCarveoutMaxShared));
-                CU(cudaFuncSetAttribute(k_chan_tail_side<67, 5>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                        (int)cudaSharedmemCarveoutMaxShared));
-                e->tail_side = e->use_fast && (cfg->flags & SDRX_FLAG_TAIL_SIDE);
-                if (e->tail_side) {
-                    int rc2 = dalloc(&e->d_stage_alt, (size_t)e->stage_stride[S - 1] * C);
-                    if (rc2) return rc2;
-                }
             }
         }
     }
@@ -667,21 +651,20 @@ int materialize_generic(sdrx_engine *e, int fmt, const uint8_t *buf, long end_id
 }
 
 template <int FMT>
-int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o, const FastSchedule **deferred,
-                     int tail_half) {
+int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o, const FastSchedule **deferred) {
     float2 *dst; long stride; int off;
     if (e->S > 3) { dst = e->d_stage_in[3]; stride = e->stage_stride[3]; off = e->H[3] - 1; }
     else          { dst = o.ch_iq;          stride = e->chiq_stride;     off = 0; }
     return fast_launch<FMT>(e->fast, e->s_main, raw, e->raw_hist, valid_lo, e->N, (int)e->trans_pos, n,
                             dst, stride, off, &e->launches,
-                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred, tail_half);
+                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred);
 }
 int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o,
-                         const FastSchedule **deferred = nullptr, int tail_half = 0) {
+                         const FastSchedule **deferred = nullptr) {
     switch (fmt) {
-        case SDRX_FMT_U8:  return launch_bank_fast<SDRX_FMT_U8>(e, raw, valid_lo, n, o, deferred, tail_half);
-        case SDRX_FMT_S16: return launch_bank_fast<SDRX_FMT_S16>(e, raw, valid_lo, n, o, deferred, tail_half);
-        default:           return launch_bank_fast<SDRX_FMT_F32>(e, raw, valid_lo, n, o, deferred, tail_half);
+        case SDRX_FMT_U8:  return launch_bank_fast<SDRX_FMT_U8>(e, raw, valid_lo, n, o, deferred);
+        case SDRX_FMT_S16: return launch_bank_fast<SDRX_FMT_S16>(e, raw, valid_lo, n, o, deferred);
+        default:           return launch_bank_fast<SDRX_FMT_F32>(e, raw, valid_lo, n, o, deferred);
     }
 }
 
@@ -703,58 +686,40 @@ int launch_prep(sdrx_engine *e, cudaStream_t st, int fmt, uint8_t *buf, const ui
 // Boundary B on the chunk in o.ch_iq (output set `idx`).  Only the last MSD stage (when `fused`) runs on the main
 // stream; the squelch detector, the recurrences and the mix follow on the side stream, where their CTAs sit next
 // to the next block's channel-bank CTAs (none of them needs more than the 9 KB of shared memory the bank leaves).
-int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr,
-                 int side_par = -1) {
+int launch_mix(sdrx_engine *e, cudaStream_t st, OutSet &o, const float *pwr_partial, int n_partial, unsigned n_samples,
+               float *pwr, const float *ext_parts, int n_ext, int do_fir) {
+    k_mix_fir2_pcm<<<kMixCtas, kMixThreads, mix_smem_bytes(e->Cpad, e->fir2_ntaps), st>>>(
+        o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps, e->d_fir_hist, o.mix_pre, o.mix, o.pcm, pwr_partial,
+        n_partial, n_samples, pwr, ext_parts, n_ext, do_fir, o.audio_idx, o.n_audio, e->d_ticket);
+    ++e->launches;
+    CU(cudaGetLastError());
+    return SDRX_OK;
+}
+
+int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr) {
     OutSet &o = e->out[idx];
     const TailSnap snap{o.sql, o.agc_gain, o.lf_gain};
-    if (fused && side_par >= 0) {
-        // last stage + detector under the next block's bank: main (bank done) -> s_tail -> s_side (recurrences, mix)
-        CU(cudaEventRecord(e->ev_head_done, e->s_main));
-        CU(cudaStreamWaitEvent(e->s_tail, e->ev_head_done, 0));
-        if (!e->prev_block_side_tail && e->blocks > 0) {       // the previous block's detector ran on s_side: order behind it
-            const int pidx = (int)((e->blocks - 1) % kNOut);
-            if (e->side_pending[pidx]) CU(cudaStreamWaitEvent(e->s_tail, e->ev_side_done[pidx], 0));
-        }
-        float2 *rows_next = (fused->stage_in == e->d_stage_alt) ? e->d_stage_in[e->S - 1] : e->d_stage_alt;
-        k_chan_tail_side<67, 5><<<e->C, kHeadThreads, 0, e->s_tail>>>(*fused, rows_next, e->tail_taps, o.ch_iq, e->chiq_stride, e->st,
-                                                                      e->tb, e->d_sql_level, o.snr, e->d_gate[idx], snap);
-        CU(cudaGetLastError());
-        CU(cudaEventRecord(e->ev_tail_done[side_par], e->s_tail));
-        e->tail_pending[side_par] = true;
-        e->last_tail_par = side_par;
-        CU(cudaStreamWaitEvent(e->s_side, e->ev_tail_done[side_par], 0));
+    if (fused) {
+        const size_t dyn = sizeof(float2) * (size_t)(fused->H - 1 + fused->n_in);
+        if (e->tail_fast && fused->n_in == kChunk * 5 && fused->first >= 0 && fused->first < 5)
+            k_chan_fir_fast<67, 5><<<e->C, kHeadThreads, fir_fast_smem(67, 5, fused->n_in), e->s_main>>>(*fused, e->tail_taps, o.ch_iq,
+                                                                                                        e->chiq_stride);
+        else
+            k_chan_head<kHeadFir><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
+                                                                          o.snr, e->d_gate[idx], snap);
         ++e->launches;
-        e->prev_block_side_tail = true;
-    } else {
-        if (fused) {
-            const size_t dyn = sizeof(float2) * (size_t)(fused->H - 1 + fused->n_in);
-            if (e->tail_fast && fused->n_in == kChunk * 5 && fused->first >= 0 && fused->first < 5)
-                k_chan_fir_fast<67, 5><<<e->C, kHeadThreads, fir_fast_smem(67, 5, fused->n_in), e->s_main>>>(*fused, e->tail_taps, o.ch_iq,
-                                                                                                            e->chiq_stride);
-            else
-                k_chan_head<kHeadFir><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
-                                                                              o.snr, e->d_gate[idx], snap);
-            ++e->launches;
-        }
-        CU(cudaGetLastError());
-        CU(cudaEventRecord(e->ev_head_done, e->s_main));
-        CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
-        if (e->prev_block_side_tail && e->last_tail_par >= 0)  // the previous block's detector ran on s_tail: order behind it
-            CU(cudaStreamWaitEvent(e->s_side, e->ev_tail_done[e->last_tail_par], 0));
-        k_chan_head<kHeadDetect><<<e->C, kHeadThreads, 0, e->s_side>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
-                                                                       e->d_sql_level, o.snr, e->d_gate[idx], snap);
-        ++e->launches;
-        e->prev_block_side_tail = false;
     }
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(e->ev_head_done, e->s_main));
+    CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
+    k_chan_head<kHeadDetect><<<e->C, kHeadThreads, 0, e->s_side>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
+                                                                   e->d_sql_level, o.snr, e->d_gate[idx], snap);
     k_chan_recur<<<div_up(e->C, kRecurCh), 32, 0, e->s_side>>>(o.ch_iq, e->chiq_stride, e->st, e->d_gate[idx], e->tb, e->agc, e->lf, e->lf_active,
                                              o.audio, snap, e->C);
-    const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad;
-    k_mix_fir2_pcm<<<1, 1024, smem, e->s_side>>>(o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps,
-                                                 e->d_fir_hist, o.mix_pre, o.mix, o.pcm, e->d_pwr_partial[idx],
-                                                 have_power ? kPwrPartials : 0, n_samples, have_power ? o.pwr : nullptr,
-                                                 nullptr, 0, (e->flags & SDRX_FLAG_PARTIAL_MIX) ? 0 : 1);
     e->launches += 2;
-    CU(cudaGetLastError());
+    int rc = launch_mix(e, e->s_side, o, e->d_pwr_partial[idx], have_power ? kPwrPartials : 0, n_samples,
+                        have_power ? o.pwr : nullptr, nullptr, 0, (e->flags & SDRX_FLAG_PARTIAL_MIX) ? 0 : 1);
+    if (rc) return rc;
     if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_side));
     CU(cudaEventRecord(e->ev_side_done[idx], e->s_side));
     e->side_pending[idx] = true;
@@ -768,7 +733,18 @@ int wait_side(sdrx_engine *e, int idx) {
     return SDRX_OK;
 }
 
-int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out, cudaStream_t st) {
+// device-visible alias of a pinned host pointer (nullptr: pageable / unknown)
+void *device_view(const void *host) {
+    if (!host) return nullptr;
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    if (attr.type != cudaMemoryTypeHost && attr.type != cudaMemoryTypeManaged) return nullptr;
+    return attr.devicePointer;
+}
+
+// `blocking`: the caller synchronises `st` itself afterwards and pageable sparse buffers are allowed (staged through a
+// device scratch array and copied after the count is known); otherwise the sparse fields must be pinned.
+int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out, cudaStream_t st, bool blocking) {
     const size_t C = (size_t)e->C;
     auto d2h = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
         return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
@@ -782,17 +758,43 @@ int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out,
     CU(d2h(out->pwr_dbfs, o.pwr, sizeof(float)));
     CU(d2h(out->agc_gain, o.agc_gain, C * sizeof(float)));
     CU(d2h(out->lf_gain, o.lf_gain, C * sizeof(float)));
+    if (out->audio_rows || out->audio_chan || out->n_audio) {
+        float *rows = (float *)device_view(out->audio_rows);
+        int *chan = (int *)device_view(out->audio_chan);
+        int *cnt = (int *)device_view(out->n_audio);
+        const bool direct = (!out->audio_rows || rows) && (!out->audio_chan || chan) && (!out->n_audio || cnt);
+        const int grid = (int)std::min<size_t>(C, 128);
+        if (direct) {
+            k_export_audio<<<grid, 128, 0, st>>>(o.audio, o.audio_idx, o.n_audio, rows, chan, cnt);
+            ++e->launches;
+            CU(cudaGetLastError());
+        } else {
+            if (!blocking) return fail(SDRX_ERR_ARG, "fetch_outputs: audio_rows / audio_chan / n_audio must be pinned (sdrx_host_alloc)");
+            int n = 0;
+            CU(cudaMemcpyAsync(&n, o.n_audio, sizeof(int), cudaMemcpyDeviceToHost, st));
+            CU(cudaStreamSynchronize(st));
+            if (out->n_audio) *out->n_audio = n;
+            if (out->audio_chan && n > 0) CU(d2h(out->audio_chan, o.audio_idx, sizeof(int) * (size_t)n));
+            if (out->audio_rows && n > 0) {
+                if (!e->d_rows_scratch) CU(cudaMalloc((void **)&e->d_rows_scratch, sizeof(float) * C * kChunk));
+                k_export_audio<<<grid, 128, 0, st>>>(o.audio, o.audio_idx, o.n_audio, e->d_rows_scratch, nullptr, nullptr);
+                ++e->launches;
+                CU(cudaGetLastError());
+                CU(d2h(out->audio_rows, e->d_rows_scratch, sizeof(float) * (size_t)n * kChunk));
+            }
+        }
+    }
     return SDRX_OK;
 }
 
 int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsigned n) {
     if (fmt != SDRX_FMT_U8 && fmt != SDRX_FMT_S16 && fmt != SDRX_FMT_F32) return fail(SDRX_ERR_ARG, "unknown IQ format");
     if (n > e->block_len) return fail(SDRX_ERR_ARG, "block longer than block_len");
-    if (e->fmt >= 0 && e->fmt != fmt && e->blocks > 0)
+    if (e->fmt >= 0 && e->fmt != fmt && e->pushes > 0)
         return fail(SDRX_ERR_STATE, "wire format changed mid-stream (the carried raw history is format specific); reset first");
     e->fmt = fmt;
     const int bps = raw_bytes_per_sample(fmt);
-    const int cur = (int)(e->blocks & 1), prv = cur ^ 1;      // raw ping-pong
+    const int cur = (int)(e->pushes & 1), prv = cur ^ 1;      // raw ping-pong
     const int oc = (int)(e->blocks % kNOut);                 // output set of this block
     uint8_t *buf = e->d_raw[cur];
     const size_t hist_bytes = (size_t)e->raw_hist * bps;
@@ -852,35 +854,15 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     const bool fast = e->use_fast && n > 0 && n % kUnit == 0 && phase_in[0] == 0 && phase_in[1] == 0 && phase_in[2] == 0;
     int rc;
     const bool fuse_tail = fast && demod && e->tail_fusable && e->S == e->fast.stages_fused + 1;
-    const int s_last = e->S - 1;
-    const bool side_tail = fuse_tail && e->tail_side && e->tail_fast && n_out[s_last - 1] == kChunk * 5 &&
-                           first[s_last] == 4;
-    int side_par = -1;
     TailFirArgs tail{};
     if (fast) {
         const FastSchedule *sc = nullptr;
-        int tail_half = 0;
-        if (side_tail) {
-            // row / tails buffer `par` was last read by the tail kernel two fused blocks ago
-            side_par = e->tail_par;
-            tail_half = side_par;
-            if (e->tail_pending[side_par]) CU(cudaStreamWaitEvent(e->s_main, e->ev_tail_done[side_par], 0));
-        } else if (e->last_tail_par >= 0) {
-            // this block works in place on the row buffer whose delay line the last side-stream tail kernel writes
-            CU(cudaStreamWaitEvent(e->s_main, e->ev_tail_done[e->last_tail_par], 0));
-        }
-        rc = launch_bank_fast_fmt(e, fmt, buf, valid_lo, n, o, fuse_tail ? &sc : nullptr, tail_half);
+        rc = launch_bank_fast_fmt(e, fmt, buf, valid_lo, n, o, fuse_tail ? &sc : nullptr);
         if (!rc && fuse_tail) {
-            const int s = s_last;
+            const int s = e->S - 1;
             tail = TailFirArgs{e->d_stage_in[s], e->stage_stride[s], n_out[s - 1], e->H[s], e->m[s], first[s],
-                               e->d_taps + e->tap_off[s], sc->n_fixes > 0 ? e->fast.tails_half(tail_half) : nullptr, e->fast.tails_slots,
+                               e->d_taps + e->tap_off[s], sc->n_fixes > 0 ? e->fast.d_tails : nullptr, e->fast.tails_slots,
                                sc->d_fixes, sc->d_fix_range, e->fast.d_chan_group};
-            if (side_tail) {
-                // from here on "the" last-stage input buffer is the partner: its delay line is what this block's tail
-                // kernel writes, its new part what the next block's bank writes
-                std::swap(e->d_stage_in[s], e->d_stage_alt);
-                e->tail_par ^= 1;
-            }
         } else if (!rc) {
             rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 3, e->S);
         }
@@ -888,14 +870,13 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         e->bank_timed = e->timing;
     } else {
         e->bank_timed = false;
-        if (e->last_tail_par >= 0) CU(cudaStreamWaitEvent(e->s_main, e->ev_tail_done[e->last_tail_par], 0));
         rc = materialize_generic(e, fmt, buf, e->raw_hist, e->total);
         if (!rc) rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 0, e->S);
     }
     if (rc) return rc;
     if (e->timing) CU(cudaEventRecord(e->ev_t1, e->s_main));
 
-    if (demod) { rc = launch_demod(e, oc, n > 0, n, fuse_tail ? &tail : nullptr, side_par); if (rc) return rc; }
+    if (demod) { rc = launch_demod(e, oc, n > 0, n, fuse_tail ? &tail : nullptr); if (rc) return rc; }
     else if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_main));
     if (e->timing) e->timing_valid = true;
 
@@ -906,6 +887,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     e->last_out_len = out_len;
     e->last_demod = demod;
     ++e->blocks;
+    ++e->pushes;
     return SDRX_OK;
 }
 
@@ -933,8 +915,8 @@ extern "C" int sdrx_engine_wait_event(sdrx_engine *e, void *cuda_event) {
 // The event that completes when the last pushed block's ingest copy (and raw carry) has run: a device-side producer
 // may overwrite the buffer it handed to push_block_device after this.
 extern "C" void *sdrx_engine_ingest_event(sdrx_engine *e) {
-    if (!e || e->blocks == 0) return nullptr;
-    return (void *)e->ev_copied[(e->blocks - 1) & 1];
+    if (!e || e->pushes == 0) return nullptr;
+    return (void *)e->ev_copied[(e->pushes - 1) & 1];
 }
 
 extern "C" int sdrx_engine_last_out_len(sdrx_engine *e, unsigned *out_len) {
@@ -949,7 +931,6 @@ extern "C" int sdrx_engine_sync(sdrx_engine *e) {
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
-    CU(cudaStreamSynchronize(e->s_tail));
     CU(cudaStreamSynchronize(e->s_out));
     return SDRX_OK;
 }
@@ -983,7 +964,7 @@ extern "C" int sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs 
     if (!e->last_demod) return fail(SDRX_ERR_STATE, "the last block did not yield 512 samples per channel; boundary B did not run");
     DevGuard g(e->dev);
     int rc = wait_side(e, (int)((e->blocks - 1) % kNOut));
-    if (!rc) rc = copy_outputs(e, e->out[(e->blocks - 1) % kNOut], out, e->s_main);
+    if (!rc) rc = copy_outputs(e, e->out[(e->blocks - 1) % kNOut], out, e->s_main, true);
     if (rc) return rc;
     CU(cudaStreamSynchronize(e->s_main));
     return SDRX_OK;
@@ -1001,7 +982,7 @@ extern "C" int sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_output
     DevGuard g(e->dev);
     const int idx = (int)((e->blocks - 1) % kNOut);
     if (e->side_pending[idx]) CU(cudaStreamWaitEvent(e->s_out, e->ev_side_done[idx], 0));
-    int rc = copy_outputs(e, e->out[idx], out, e->s_out);
+    int rc = copy_outputs(e, e->out[idx], out, e->s_out, false);
     if (rc) return rc;
     CU(cudaEventRecord(e->ev_fetch_done[idx], e->s_out));
     e->fetch_pending[idx] = true;
@@ -1033,7 +1014,7 @@ extern "C" int sdrx_engine_demod_block(sdrx_engine *e, const float *ch_iq, float
     if (rc) return rc;
     e->last_out_len = kChunk;
     e->last_demod = true;
-    ++e->blocks;      // the output set alternates like a pushed block's; the channelizer state is untouched
+    ++e->blocks;      // takes the next output set like a pushed block; the channelizer (raw ping-pong, e->pushes) is untouched
     return SDRX_OK;
 }
 
@@ -1053,11 +1034,7 @@ extern "C" int sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_
     OutSet &o = e->out[idx];
     { int rc = wait_side(e, idx); if (rc) return rc; }
     CU(cudaMemcpyAsync(e->d_parts, parts, bytes, cudaMemcpyHostToDevice, e->s_main));
-    const size_t smem = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1 + kChunk) + sizeof(int) * (size_t)e->Cpad;
-    k_mix_fir2_pcm<<<1, 1024, smem, e->s_main>>>(o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps, e->d_fir_hist,
-                                                 o.mix_pre, o.mix, o.pcm, nullptr, 0, 0, nullptr, e->d_parts, n_parts, 1);
-    ++e->launches;
-    CU(cudaGetLastError());
+    { int rc = launch_mix(e, e->s_main, o, nullptr, 0, 0, nullptr, e->d_parts, n_parts, 1); if (rc) return rc; }
     if (mix_pre) CU(cudaMemcpyAsync(mix_pre, o.mix_pre, sizeof(float) * 2 * kChunk, cudaMemcpyDeviceToHost, e->s_main));
     if (mix) CU(cudaMemcpyAsync(mix, o.mix, sizeof(float) * 2 * kChunk, cudaMemcpyDeviceToHost, e->s_main));
     if (pcm) CU(cudaMemcpyAsync(pcm, o.pcm, sizeof(int16_t) * 2 * kChunk, cudaMemcpyDeviceToHost, e->s_main));
@@ -1182,9 +1159,8 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
-    CU(cudaStreamSynchronize(e->s_tail));
     if (e->generic_stale) {      // the blob always carries the stage delay lines (a generic engine can load it)
-        const int last_ = (int)((e->blocks & 1) ^ 1);
+        const int last_ = (int)((e->pushes & 1) ^ 1);
         int rc = materialize_generic(e, e->fmt, e->d_raw[last_], (long)e->raw_hist + (long)e->prev_n, e->total);
         if (rc) return rc;
         CU(cudaStreamSynchronize(e->s_main));
@@ -1194,12 +1170,12 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     h.magic = kStateMagic; h.version = 3;
     h.C = e->C; h.S = e->S; h.fmt = e->fmt; h.raw_hist = e->raw_hist; h.total = e->total; h.fir2_ntaps = e->fir2_ntaps;
     h.demod = (e->flags & SDRX_FLAG_NO_DEMOD) ? 0 : 1;
-    h.trans_pos = e->trans_pos; h.blocks = e->blocks;
+    h.trans_pos = e->trans_pos; h.blocks = e->pushes;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) { h.phase[s] = e->phase[s]; h.H[s] = e->H[s]; }
     h.ft_k = e->ft_k; h.ftfir = e->ftfir ? 1 : 0;
     memcpy(p, &h, sizeof(h)); p += sizeof(h);
     const int bps = e->fmt >= 0 ? raw_bytes_per_sample(e->fmt) : 8;
-    const int last = (int)((e->blocks & 1) ^ 1);
+    const int last = (int)((e->pushes & 1) ^ 1);
     memset(p, 0, (size_t)e->raw_hist * 8);
     CU(cudaMemcpy(p, e->d_raw[last] + (size_t)e->prev_n * bps, (size_t)e->raw_hist * bps, cudaMemcpyDeviceToHost));
     p += (size_t)e->raw_hist * 8;
@@ -1240,18 +1216,15 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
-    CU(cudaStreamSynchronize(e->s_tail));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
-    e->tail_pending[0] = e->tail_pending[1] = false;
-    e->last_tail_par = -1; e->prev_block_side_tail = false;
     const uint8_t *p = (const uint8_t *)buf + sizeof(h);
-    e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = h.blocks; e->total = h.total; e->generic_stale = false;
+    e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = e->pushes = h.blocks; e->total = h.total; e->generic_stale = false;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = h.phase[s];
     e->ft_k = h.ft_k;
     e->prev_n = 0;          // the history is parked at the very front of the "previous" buffer
     e->last_out_len = 0; e->last_demod = false; e->timing_valid = false;
-    const int last = (int)((e->blocks & 1) ^ 1);
+    const int last = (int)((e->pushes & 1) ^ 1);
     CU(cudaMemcpy(e->d_raw[last], p, (size_t)e->raw_hist * 8, cudaMemcpyHostToDevice));
     p += (size_t)e->raw_hist * 8;
     for (int s = 1; s < e->S; ++s) {

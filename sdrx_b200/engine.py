@@ -13,7 +13,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import (FMT_F32, FMT_S16, FMT_U8, FLAG_FTFIR, FLAG_TAIL_SIDE, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, CHUNK,
+from ._lib import (FMT_F32, FMT_S16, FMT_U8, FLAG_FTFIR, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, CHUNK,
                    SdrxError,
                    check)
 from .config import ChannelPlan, make_translator, tables
@@ -78,7 +78,7 @@ class Engine:
     def __init__(self, plan: ChannelPlan, device: int = 0, use_lf_agc: bool = False, lf_gain_db: float = 0.0,
                  block_len: Optional[int] = None, force_generic: bool = False, demod: bool = True,
                  translators: Optional[np.ndarray] = None, partial_mix: bool = False, no_pairing: bool = False,
-                 use_ftfir: bool = False, tail_side: bool = False):
+                 use_ftfir: bool = False):
         self.lib = _lib.load()
         self.plan = plan
         self.device = device
@@ -109,9 +109,16 @@ class Engine:
         cfg = _lib.EngineConfig()
         cfg.device = device
         cfg.n_channels = self.C
-        cfg.translator_len = self.N
-        cfg.translators = tr.view(np.float32).ctypes.data_as(_lib.c_float_p)
-        cfg.has_translator = has.ctypes.data_as(_lib.c_u8_p)
+        if translators is None and not has.any():
+            # every channel sits on the tuner frequency: the reference builds no translator at all (empty vector,
+            # sdrx.cpp:1684-1690) -- sdrx's canonical single-channel run
+            cfg.translator_len = 0
+            cfg.translators = None
+            cfg.has_translator = None
+        else:
+            cfg.translator_len = self.N
+            cfg.translators = tr.view(np.float32).ctypes.data_as(_lib.c_float_p)
+            cfg.has_translator = has.ctypes.data_as(_lib.c_u8_p)
         cfg.n_stages = len(rc_.stages)
         cfg.m = m.ctypes.data_as(_lib.c_int_p)
         cfg.ntaps = nt.ctypes.data_as(_lib.c_int_p)
@@ -126,8 +133,7 @@ class Engine:
         cfg.passband_shape, cfg.ramp_up, cfg.ramp_down = fp(shape), fp(rup), fp(rdn)
         cfg.flags = ((FLAG_FORCE_GENERIC if force_generic else 0) | (0 if demod else FLAG_NO_DEMOD)
                      | (FLAG_PARTIAL_MIX if partial_mix else 0) | (FLAG_NO_PAIRING if no_pairing else 0)
-                     | (FLAG_FTFIR if use_ftfir else 0)      # --ftfir, sdrx.cpp:1199 / msd.hpp:104-131
-                     | (FLAG_TAIL_SIDE if tail_side else 0))
+                     | (FLAG_FTFIR if use_ftfir else 0))     # --ftfir, sdrx.cpp:1199 / msd.hpp:104-131
         self.demod = demod
         h = C.c_void_p()
         check(self.lib.sdrx_engine_create(C.byref(cfg), C.byref(h)))
@@ -180,7 +186,8 @@ class Engine:
         C_ = self.C
         spec = {"audio": (np.float32, C_ * CHUNK), "sql_state": (np.uint8, C_), "snr": (np.float32, C_),
                 "mix_pre": (np.float32, 2 * CHUNK), "mix": (np.float32, 2 * CHUNK), "pcm": (np.int16, 2 * CHUNK),
-                "pwr_dbfs": (np.float32, 1), "agc_gain": (np.float32, C_), "lf_gain": (np.float32, C_)}
+                "pwr_dbfs": (np.float32, 1), "agc_gain": (np.float32, C_), "lf_gain": (np.float32, C_),
+                "audio_rows": (np.float32, C_ * CHUNK), "audio_chan": (np.int32, C_), "n_audio": (np.int32, 1)}
         o = _lib.BlockOutputs()
         arrays, keep, total = {}, [], 0
         for name in want:
@@ -194,10 +201,19 @@ class Engine:
                 a = np.empty(n, dt)
             arrays[name] = a
             total += nbytes
-            ptr_t = {np.float32: _lib.c_float_p, np.uint8: _lib.c_u8_p, np.int16: _lib.c_i16_p}[dt]
+            ptr_t = {np.float32: _lib.c_float_p, np.uint8: _lib.c_u8_p, np.int16: _lib.c_i16_p, np.int32: _lib.c_int_p}[dt]
             setattr(o, name, a.ctypes.data_as(ptr_t))
         arrays["_keep"] = keep
         return o, arrays, total
+
+    @staticmethod
+    def dense_audio(arrays, n_channels: int) -> np.ndarray:
+        """Expand the sparse audio of :meth:`make_output_buffers` (``audio_rows`` / ``audio_chan`` / ``n_audio``) into
+        the dense ``[C][512]`` array ``audio`` would have returned (closed channels are exact zeros)."""
+        n = int(arrays["n_audio"][0])
+        out = np.zeros((n_channels, CHUNK), np.float32)
+        out[arrays["audio_chan"][:n]] = arrays["audio_rows"][:n * CHUNK].reshape(n, CHUNK)
+        return out
 
     def outputs_into(self, struct) -> None:
         check(self.lib.sdrx_engine_get_outputs(self.h, C.byref(struct)))

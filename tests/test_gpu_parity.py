@@ -201,34 +201,6 @@ def test_conjugate_paired_bank_meets_the_parity_bar(fmt):
             assert rel_rms(a.ch_iq[c], b.ch_iq[c]) < 3e-5, c
 
 
-def test_side_stream_last_stage_variant_meets_the_parity_bar():
-    """SDRX_FLAG_TAIL_SIDE (k_chan_tail_side: last stage + detector under the next bank, ping-pong stage rows and
-    tails) against the oracle and against the default main-stream last stage, incl. a ragged block in between
-    (hand-over to the generic kernels and back) and a state save / load."""
-    from sdrx_b200 import Engine
-    scn = sc.paired_channels()
-    blocks = _blocks(scn)
-    want = run_cpu(scn, "oracle", blocks)
-    got, fast = run_engine(scn, blocks=blocks, tail_side=True)
-    assert fast
-    _assert_close(got, want, np.full(len(scn.offsets), 9.0))
-    ref, _ = run_engine(scn, blocks=blocks)
-    for a, b in zip(got, ref):
-        assert np.array_equal(a.sql, b.sql)
-        assert rel_rms(a.ch_iq, b.ch_iq) < 1e-5
-    eng = Engine(scn.plan(), tail_side=True)
-    outs = [eng.process(b) for b in blocks[:3]]
-    blob = eng.save_state()
-    rest = [eng.process(b) for b in blocks[3:]]
-    eng2 = Engine(scn.plan(), tail_side=True)
-    eng2.load_state(blob)
-    rest2 = [eng2.process(b) for b in blocks[3:]]
-    for x, y in zip(rest, rest2):
-        assert np.array_equal(x.ch_iq, y.ch_iq) and np.array_equal(x.pcm, y.pcm) and np.array_equal(x.sql, y.sql)
-    eng.close()
-    eng2.close()
-
-
 def test_full_band_960_channels_against_oracle():
     """SURVEY.md §8d config 3 at full width (960 channels), three blocks."""
     scn = sc.config3(n_blocks=3)
@@ -253,6 +225,116 @@ def test_full_band_960_channels_against_oracle():
     eng = Engine(scn.plan())
     assert eng.bank_pairs == 479          # offsets -479..479 pair up; -480 and 0 ride alone
     eng.close()
+
+
+def test_full_band_every_squelch_open_against_oracle():
+    """The worst case of boundary B: sql_level 0 opens every squelch (sdrx.cpp:569), so all 960 channels
+    run both recurrences and the ordered pan mix walks 960 rows.  Eight blocks: per-channel audio, squelch, the
+    ordered mix_pre / mix / pcm against the oracle; then the oracle's own channel IQ through boundary B alone
+    (sdrx_engine_demod_block), where the 960-term ordered sums must come out bit for bit."""
+    from sdrx_b200 import Engine
+    scn = sc.config3(n_blocks=8)
+    scn.sql_levels = [0.0] * len(scn.offsets)
+    blocks = _blocks(scn)
+    want = run_cpu(scn, "oracle", blocks)
+    assert all(o.sql.all() for o in want)
+    got, fast = run_engine(scn, blocks=blocks)
+    assert fast
+    _assert_close(got, want, np.zeros(len(scn.offsets)))
+    for g, w in zip(got[1:], want[1:]):
+        assert np.count_nonzero(np.any(g.audio != 0.0, axis=1)) == len(scn.offsets)
+        assert rel_rms(g.mix_pre, w.mix_pre) < AUDIO_TOL
+    eng = Engine(scn.plan())
+    for b, w in enumerate(want):
+        o = eng.demod_block(w.ch_iq)
+        assert np.array_equal(o.audio, w.audio), f"block {b} audio"
+        assert np.array_equal(o.mix_pre, w.mix_pre), f"block {b}: ordered 960-channel mix"
+        assert np.array_equal(o.mix, w.mix) and np.array_equal(o.pcm, w.pcm), f"block {b} FIR2 / s16"
+    eng.close()
+
+
+def test_single_centre_channel_without_translator_table():
+    """sdrx's canonical single-channel run tunes the dongle to the channel, so ch_offset == 0 and
+    the translator is an EMPTY vector (sdrx.cpp:1408, :1684): translator_len 0 at the C ABI.  The specialised bank
+    needs a table period of at least 25 rows and must not be picked; the generic kernels are bit-exact."""
+    from sdrx_b200 import Engine
+    scn = sc.Scenario("single_centre_10000", 10000000, [0], [sc.Carrier(0, 0.1, 800.0, 0.5, lambda b: b >= 1)],
+                      n_blocks=4, noise_sigma=0.002)
+    blocks = _blocks(scn)
+    want = run_cpu(scn, "oracle", blocks)
+    eng = Engine(scn.plan())
+    assert not eng.uses_fast_path
+    got = [eng.process(b) for b in blocks]
+    eng.close()
+    _assert_exact(got, want)
+    # ... and an engine with a short table (N < 25) next to one with the full table on the same GPU: each keeps its
+    # own shared-memory limits (ADVICE r1: the per-function attribute is process-wide and must never be lowered)
+    big = Engine(sc.config2().plan())
+    small = Engine(scn.plan())
+    sb = _blocks(sc.config2(n_blocks=2))
+    o1 = big.process(sb[0])
+    small.process(blocks[0])
+    o2 = big.process(sb[1])
+    ref, _ = run_engine(sc.config2(n_blocks=2), blocks=sb)
+    assert np.array_equal(o1.ch_iq, ref[0].ch_iq) and np.array_equal(o2.ch_iq, ref[1].ch_iq)
+    big.close()
+    small.close()
+
+
+def test_sparse_audio_equals_dense_audio():
+    """audio_rows / audio_chan / n_audio (only the channels that are mixed this block cross the host link) expand to
+    exactly the dense audio array, through fetch_outputs with pinned buffers and get_outputs with pageable ones."""
+    from sdrx_b200 import Engine
+    scn = sc.paired_channels()
+    blocks = _blocks(scn)
+    ref, _ = run_engine(scn, blocks=blocks)
+    eng = Engine(scn.plan())
+    lag = 2
+    sets = [eng.make_output_buffers(pinned=True, want=("audio_rows", "audio_chan", "n_audio", "sql_state", "pcm"))
+            for _ in range(lag + 1)]
+    got = []
+    for i, blk in enumerate(blocks):
+        eng.push(blk)
+        eng.fetch_outputs(sets[i % (lag + 1)][0])
+        if i >= lag:
+            eng.wait_outputs(lag)
+            got.append(Engine.dense_audio(sets[(i - lag) % (lag + 1)][1], eng.C))
+    for back in range(lag - 1, -1, -1):
+        eng.wait_outputs(back)
+        got.append(Engine.dense_audio(sets[(len(blocks) - 1 - back) % (lag + 1)][1], eng.C))
+    n_open = 0
+    for g, r in zip(got, ref):
+        assert np.array_equal(g, r.audio)
+        n_open += int(np.count_nonzero(np.any(r.audio != 0.0, axis=1)))
+    assert 0 < n_open < len(blocks) * eng.C          # the scenario has both open and closed channels
+    eng.reset()
+    o, arrays, _ = eng.make_output_buffers(pinned=False, want=("audio_rows", "audio_chan", "n_audio"))
+    for blk, r in zip(blocks, ref):
+        eng.push(blk)
+        eng.outputs_into(o)
+        assert np.array_equal(Engine.dense_audio(arrays, eng.C), r.audio)
+    with pytest.raises(Exception):
+        eng.fetch_outputs(o)                         # the streaming form needs pinned sparse buffers
+    eng.close()
+
+
+def test_demod_block_between_pushes_leaves_the_channelizer_alone():
+    """sdrx_engine_demod_block takes an output set but must not advance the raw ping-pong that
+    push_block's carried history lives in."""
+    from sdrx_b200 import Engine
+    scn = sc.config2(n_blocks=6)
+    blocks = _blocks(scn)
+    ref, _ = run_engine(scn, blocks=blocks)
+    eng = Engine(scn.plan())
+    other = Engine(scn.plan())
+    for b, blk in enumerate(blocks):
+        eng.push(blk)
+        iq = eng.channel_iq()
+        assert np.array_equal(iq, ref[b].ch_iq), f"block {b}: channel IQ after an interleaved demod_block"
+        if b % 2 == 0:
+            eng.demod_block(ref[b].ch_iq)            # boundary B again, on the same engine, between two pushes
+    eng.close()
+    other.close()
 
 
 def test_long_run_full_band_sample_of_channels_against_oracle():
