@@ -222,6 +222,8 @@ int sdrx_lfagc_adjust(int device, sdrx_agc_state *s, const float *in, unsigned n
 typedef struct sdrx_fir sdrx_fir;
 /* kind 1 FIR (fir.hpp:78), 2 FIR2 (fir.hpp:130), 3 FIR3<iqsample_t> (fir.hpp:28) */
 int  sdrx_fir_create(int kind, const float *c, int n, int device, sdrx_fir **out);
+int  sdrx_fir_clone(const sdrx_fir *src, sdrx_fir **out);   /* implicit copy of FIR/FIR2/FIR3: taps, gain AND delay line
+                                                              (buf_, pos_ are plain members, fir.hpp:69-74, :176-182) */
 void sdrx_fir_destroy(sdrx_fir *f);
 int  sdrx_fir_set_gain(sdrx_fir *f, float gain_db);                                     /* fir.hpp:51  */
 int  sdrx_fir_filter(sdrx_fir *f, const float *in, unsigned in_len, float *out);        /* fir.hpp:34  */

@@ -11,7 +11,7 @@
 
 #include <cstdio>
 
-#include "../sdrx_b200.h"
+#include <sdrx_b200.h>       // -I<repo>/include (the headers themselves may be copied next to sdrx.cpp)
 #include "iqsample.hpp"
 
 namespace sdrx_b200_detail {

@@ -41,7 +41,9 @@ public:
         if (!s.live) return;
         s.live = false;
         --n_live_;
-        if (s.job.latch) { s.job = Job{}; --n_pending_; }
+        // the reference's ~DS joins its worker, which finishes a job already handed over (ds.hpp:36-41): run it, so a
+        // thread blocked on that block's latch (sdrx.cpp:340) is released
+        if (s.job.latch) { run_one_(s); --n_pending_; }
         dirty_ = true;
         if (n_live_ == 0) { sdrx_engine_destroy(eng_); eng_ = nullptr; slots_.clear(); }
         else if (n_pending_ == n_live_) run_all_();
@@ -78,8 +80,24 @@ private:
         s.job.latch->count_down();
         s.job = Job{};
     }
-    bool rebuild_(unsigned len) {
-        sdrx_engine_destroy(eng_);
+    // A block longer than the engine's capacity: a larger engine takes over WITH the delay lines and trans_pos of the
+    // old one (MSD::decimate takes any in_len and keeps its state, msd.hpp:75) -- same as sdrx_msd_decimate's growth.
+    bool grow_(unsigned len) {
+        sdrx_engine *old = eng_;
+        eng_ = nullptr;
+        std::vector<unsigned char> st(old ? sdrx_engine_state_size(old) : 0);
+        int rc = old ? sdrx_engine_save_state(old, st.data(), st.size()) : 0;
+        const bool ok = rebuild_(len, false) && eng_ && !rc && old &&
+                        sdrx_engine_load_state(eng_, st.data(), st.size()) == 0;
+        sdrx_engine_destroy(old);
+        if (!ok && eng_) {
+            std::fprintf(stderr, "sdrx_b200: DS bank: could not carry the delay lines into the larger engine: %s\n", sdrx_last_error());
+            batchable_ = false;
+        }
+        return ok;
+    }
+    bool rebuild_(unsigned len, bool destroy_old = true) {
+        if (destroy_old) sdrx_engine_destroy(eng_);
         eng_ = nullptr;
         order_.clear();
         for (size_t i = 0; i < slots_.size(); ++i) if (slots_[i].live) order_.push_back((int)i);
@@ -132,7 +150,8 @@ private:
             if (!data) { data = s.job.data; len = s.job.len; }
             else if (s.job.data != data || s.job.len != len) uniform = false;
         }
-        if (dirty_ || (batchable_ && len > cap_)) rebuild_(len);
+        if (dirty_) rebuild_(len);
+        else if (batchable_ && len > cap_) grow_(len);
         bool done = false;
         if (uniform && batchable_ && eng_ && len > 0) {
             unsigned n = 0;
@@ -155,6 +174,9 @@ private:
                 batchable_ = false;
             }
         }
+        // not batchable (or the batched pass failed): one sdrx_msd_decimate per channel.  After a FAILED batched pass the
+        // per-slot MSD objects have not seen the stream so far, so their delay lines restart -- a CUDA failure is not
+        // recoverable mid-stream, the message above says so; the latches are still counted down so nobody hangs.
         if (!done)
             for (Slot &s : slots_) if (s.live && s.job.latch) run_one_(s);
     }

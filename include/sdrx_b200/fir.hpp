@@ -11,16 +11,17 @@
 #include <type_traits>
 #include <vector>
 
-#include "../sdrx_b200.h"
+#include <sdrx_b200.h>       // -I<repo>/include (the headers themselves may be copied next to sdrx.cpp)
 
 namespace sdrx_b200_detail {
-class FirHandle {          // shared by the three classes; copying re-creates the filter with zeroed history
+class FirHandle {          // shared by the three classes; a copy carries taps, gain and the delay line, like the reference's implicit copy (fir.hpp:69-74)
 public:
     FirHandle() = default;
     FirHandle(int kind, const std::vector<float> &c, int device = 0) : kind_(kind), c_(c), device_(device) { create_(); }
     FirHandle(const FirHandle &o) : kind_(o.kind_), c_(o.c_), device_(o.device_), gain_(o.gain_) {
-        create_();
-        if (h_ && gain_ != 0.0f) sdrx_fir_set_gain(h_, gain_);
+        if (!o.h_) return;
+        int rc = sdrx_fir_clone(o.h_, &h_);
+        if (rc) std::fprintf(stderr, "sdrx_b200: sdrx_fir_clone failed (%d): %s\n", rc, sdrx_last_error());
     }
     FirHandle &operator=(FirHandle o) { swap_(o); return *this; }
     ~FirHandle() { sdrx_fir_destroy(h_); }

@@ -13,7 +13,7 @@
 #include <cstdio>
 #include <vector>
 
-#include "../sdrx_b200.h"
+#include <sdrx_b200.h>       // -I<repo>/include (the headers themselves may be copied next to sdrx.cpp)
 #include "iqsample.hpp"
 
 class MSD {

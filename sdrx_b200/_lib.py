@@ -99,6 +99,7 @@ PROTOTYPES = [
     ("sdrx_agc_adjust", C.c_int, [C.c_int, C.POINTER(AgcState), c_float_p, C.c_uint, c_float_p]),
     ("sdrx_lfagc_adjust", C.c_int, [C.c_int, C.POINTER(AgcState), c_float_p, C.c_uint, c_float_p]),
     ("sdrx_fir_create", C.c_int, [C.c_int, c_float_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    ("sdrx_fir_clone", C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     ("sdrx_fir_destroy", None, [C.c_void_p]),
     ("sdrx_fir_set_gain", C.c_int, [C.c_void_p, C.c_float]),
     ("sdrx_fir_filter", C.c_int, [C.c_void_p, c_float_p, C.c_uint, c_float_p]),

@@ -34,6 +34,7 @@ struct OutSet {                   // device-side results of one block
     float   *pwr = nullptr;       // [1]
     uint8_t *sql = nullptr;       // [C] snapshot of the state after the decision
     float   *agc_gain = nullptr, *lf_gain = nullptr;   // [C] snapshots
+    uint8_t *mixed = nullptr;     // [Cpad] 1 where this block's audio goes into the mix (k_chan_recur -> k_mix_fir2_pcm)
     int     *audio_idx = nullptr; // [C] channels whose audio is mixed this block, ascending (k_mix_fir2_pcm)
     int     *n_audio = nullptr;   // [1] how many
 };
@@ -56,9 +57,16 @@ struct sdrx_engine {
     int fir2_ntaps = 0;
 
     cudaStream_t s_main = nullptr, s_copy = nullptr;
-    cudaStream_t s_side = nullptr;        // latency-bound tail of boundary B (k_chan_recur, k_mix_fir2_pcm): overlaps the next bank
-    cudaEvent_t ev_head_done = nullptr;   // k_chan_head of the current block has been queued behind this point (main -> side)
-    cudaEvent_t ev_side_done[kNOut] = {};   // side-stream work that reads / writes output set b is complete
+    // Boundary B runs under the following blocks' channel banks as a three-deep pipeline, one stream per kernel: the
+    // detector of block b+2, the recurrences of block b+1 and the mix of block b overlap (each kernel only depends on
+    // its own predecessor -- squelch state, AGC state, FIR2 ring -- and on the previous kernel of its own block), so a
+    // step costs the longest of them, not their sum
+    cudaStream_t s_side = nullptr;        // k_chan_head<kHeadDetect>
+    cudaStream_t s_recur = nullptr;       // k_chan_recur
+    cudaStream_t s_mix = nullptr;         // k_mix_fir2_pcm
+    cudaEvent_t ev_head_done = nullptr;   // the last MSD stage of the current block has been queued behind this point (main -> side)
+    cudaEvent_t ev_det_done[kNOut] = {}, ev_recur_done[kNOut] = {};
+    cudaEvent_t ev_side_done[kNOut] = {};   // all of boundary B that reads / writes output set b is complete (recorded behind the mix)
     bool side_pending[kNOut] = {};
     cudaStream_t s_out = nullptr;         // asynchronous result fetch (sdrx_engine_fetch_outputs): D2H overlaps the next block
     cudaEvent_t ev_fetch_done[kNOut] = {};
@@ -202,6 +210,8 @@ void agc_defaults(AgcParams &p, float attack, float decay, float reference, floa
 int reset_state(sdrx_engine *e) {
     const size_t C = (size_t)e->C;
     CU(cudaStreamSynchronize(e->s_side));
+    CU(cudaStreamSynchronize(e->s_recur));
+    CU(cudaStreamSynchronize(e->s_mix));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
     for (int b = 0; b < kNBuf; ++b) CU(cudaMemsetAsync(e->d_raw[b], 0, e->raw_buf_bytes, e->s_main));
@@ -215,10 +225,10 @@ int reset_state(sdrx_engine *e) {
         CU(cudaMemcpyAsync(e->st.lf_power, p1.data(), C * 4, cudaMemcpyHostToDevice, e->s_main));
         CU(cudaMemsetAsync(e->st.sql_state, 0, C, e->s_main));
         CU(cudaMemsetAsync(e->st.sql_prev, 0, C, e->s_main));
-        CU(cudaMemsetAsync(e->st.mixed, 0, C, e->s_main));
+        for (int b = 0; b < kNOut; ++b) CU(cudaMemsetAsync(e->out[b].mixed, 0, (size_t)e->Cpad, e->s_main));
         CU(cudaMemsetAsync(e->st.fm_prev, 0, C * sizeof(float2), e->s_main));
         CU(cudaMemsetAsync(e->d_fir_hist, 0, sizeof(float) * 2 * (size_t)std::max(e->fir2_ntaps - 1, 1), e->s_main));
-        CU(cudaMemsetAsync(e->d_ticket, 0, sizeof(unsigned), e->s_main));
+        CU(cudaMemsetAsync(e->d_ticket, 0, 2 * sizeof(unsigned), e->s_main));
         CU(cudaStreamSynchronize(e->s_main));   // the host vectors above die here
     }
     CU(cudaStreamSynchronize(e->s_main));
@@ -254,7 +264,9 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
         OutSet &o = e->out[b];
         cudaFree(o.ch_iq); cudaFree(o.audio); cudaFree(o.snr); cudaFree(o.mix_pre); cudaFree(o.mix);
         cudaFree(o.pcm); cudaFree(o.pwr); cudaFree(o.sql); cudaFree(o.agc_gain); cudaFree(o.lf_gain);
-        cudaFree(o.audio_idx); cudaFree(o.n_audio);
+        cudaFree(o.audio_idx); cudaFree(o.n_audio); cudaFree(o.mixed);
+        if (e->ev_det_done[b]) cudaEventDestroy(e->ev_det_done[b]);
+        if (e->ev_recur_done[b]) cudaEventDestroy(e->ev_recur_done[b]);
         if (e->ev_side_done[b]) cudaEventDestroy(e->ev_side_done[b]);
         if (e->ev_fetch_done[b]) cudaEventDestroy(e->ev_fetch_done[b]);
         cudaFree(e->d_gate[b]); cudaFree(e->d_pwr_partial[b]);
@@ -264,7 +276,7 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps); cudaFree(e->d_hk);
     cudaFree(e->st.agc_gain); cudaFree(e->st.agc_power); cudaFree(e->st.lf_gain); cudaFree(e->st.lf_power);
     cudaFree(e->st.fm_prev); cudaFree(e->d_mod);
-    cudaFree(e->st.sql_state); cudaFree(e->st.sql_prev); cudaFree(e->st.mixed);
+    cudaFree(e->st.sql_state); cudaFree(e->st.sql_prev);
     cudaFree(e->d_window); cudaFree(e->d_shape); cudaFree(e->d_ramp_up); cudaFree(e->d_ramp_down);
     cudaFree(e->d_twiddle); cudaFree(e->d_bitrev); cudaFree(e->d_sql_level); cudaFree(e->d_pos);
     cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist); cudaFree(e->d_parts); cudaFree(e->d_ticket); cudaFree(e->d_rows_scratch);
@@ -277,6 +289,8 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     if (e->s_main) cudaStreamDestroy(e->s_main);
     if (e->s_copy) cudaStreamDestroy(e->s_copy);
     if (e->s_side) cudaStreamDestroy(e->s_side);
+    if (e->s_recur) cudaStreamDestroy(e->s_recur);
+    if (e->s_mix) cudaStreamDestroy(e->s_mix);
     if (e->s_out) cudaStreamDestroy(e->s_out);
     delete e;
 }
@@ -309,10 +323,14 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     CU(cudaStreamCreateWithFlags(&e->s_main, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_side, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&e->s_recur, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&e->s_mix, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->ev_head_done, cudaEventDisableTiming));
     for (int b = 0; b < kNOut; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_side_done[b], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&e->ev_det_done[b], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&e->ev_recur_done[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_fetch_done[b], cudaEventDisableTiming));
     }
     for (int b = 0; b < kNBuf; ++b) {
@@ -425,6 +443,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if ((rc = dalloc(&o.sql, C))) return rc;
         if ((rc = dalloc(&o.agc_gain, C))) return rc;
         if ((rc = dalloc(&o.lf_gain, C))) return rc;
+        if ((rc = dalloc(&o.mixed, (size_t)e->Cpad))) return rc;
         if ((rc = dalloc(&o.audio_idx, C))) return rc;
         if ((rc = dalloc(&o.n_audio, 1))) return rc;
     }
@@ -445,7 +464,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if ((rc = dalloc(&e->st.agc_gain, C)) || (rc = dalloc(&e->st.agc_power, C)) ||
             (rc = dalloc(&e->st.lf_gain, C)) || (rc = dalloc(&e->st.lf_power, C)) ||
             (rc = dalloc(&e->st.sql_state, C)) || (rc = dalloc(&e->st.sql_prev, C)) ||
-            (rc = dalloc(&e->st.mixed, C)) || (rc = dalloc(&e->st.fm_prev, C)) || (rc = dalloc(&e->d_mod, C)))
+            (rc = dalloc(&e->st.fm_prev, C)) || (rc = dalloc(&e->d_mod, C)))
             return rc;
         {
             std::vector<uint8_t> mod(C, SDRX_MOD_AM);
@@ -487,7 +506,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             (rc = dalloc(&e->d_c_adj, c_adj.size())) || (rc = upload(e->d_c_adj, c_adj.data(), c_adj.size())) ||
             (rc = dalloc(&e->d_fir_hist, 2 * (size_t)std::max(cfg->fir2_ntaps - 1, 1))))
             return rc;
-        if ((rc = dalloc(&e->d_ticket, 1))) return rc;
+        if ((rc = dalloc(&e->d_ticket, 2))) return rc;
         e->tb = DemodTables{e->d_window, e->d_twiddle, e->d_bitrev, e->d_shape, e->d_ramp_up, e->d_ramp_down};
         if ((size_t)C * 4 > 160 * 1024) return fail(SDRX_ERR_UNSUPPORTED, "more than 40960 channels per engine");
         { int rc2 = raise_dyn_smem((const void *)k_mix_fir2_pcm, mix_smem_bytes(e->Cpad, cfg->fir2_ntaps)); if (rc2) return rc2; }
@@ -688,9 +707,10 @@ int launch_prep(sdrx_engine *e, cudaStream_t st, int fmt, uint8_t *buf, const ui
 // to the next block's channel-bank CTAs (none of them needs more than the 9 KB of shared memory the bank leaves).
 int launch_mix(sdrx_engine *e, cudaStream_t st, OutSet &o, const float *pwr_partial, int n_partial, unsigned n_samples,
                float *pwr, const float *ext_parts, int n_ext, int do_fir) {
+    // sdrx_engine_finish_mix (ext_parts) may run next to a block's own mix kernel: it takes its own arrival counter
     k_mix_fir2_pcm<<<kMixCtas, kMixThreads, mix_smem_bytes(e->Cpad, e->fir2_ntaps), st>>>(
-        o.audio, e->st.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps, e->d_fir_hist, o.mix_pre, o.mix, o.pcm, pwr_partial,
-        n_partial, n_samples, pwr, ext_parts, n_ext, do_fir, o.audio_idx, o.n_audio, e->d_ticket);
+        o.audio, o.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps, e->d_fir_hist, o.mix_pre, o.mix, o.pcm, pwr_partial,
+        n_partial, n_samples, pwr, ext_parts, n_ext, do_fir, o.audio_idx, o.n_audio, e->d_ticket + (ext_parts ? 1 : 0));
     ++e->launches;
     CU(cudaGetLastError());
     return SDRX_OK;
@@ -714,14 +734,18 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
     CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
     k_chan_head<kHeadDetect><<<e->C, kHeadThreads, 0, e->s_side>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
                                                                    e->d_sql_level, o.snr, e->d_gate[idx], snap);
-    k_chan_recur<<<div_up(e->C, kRecurCh), 32, 0, e->s_side>>>(o.ch_iq, e->chiq_stride, e->st, e->d_gate[idx], e->tb, e->agc, e->lf, e->lf_active,
-                                             o.audio, snap, e->C);
+    CU(cudaEventRecord(e->ev_det_done[idx], e->s_side));
+    CU(cudaStreamWaitEvent(e->s_recur, e->ev_det_done[idx], 0));
+    k_chan_recur<<<div_up(e->C, 32), 32, 0, e->s_recur>>>(o.ch_iq, e->chiq_stride, e->st, e->d_gate[idx], e->tb, e->agc, e->lf,
+                                                          e->lf_active, o.audio, snap, e->C, o.mixed);
+    CU(cudaEventRecord(e->ev_recur_done[idx], e->s_recur));
+    CU(cudaStreamWaitEvent(e->s_mix, e->ev_recur_done[idx], 0));
     e->launches += 2;
-    int rc = launch_mix(e, e->s_side, o, e->d_pwr_partial[idx], have_power ? kPwrPartials : 0, n_samples,
+    int rc = launch_mix(e, e->s_mix, o, e->d_pwr_partial[idx], have_power ? kPwrPartials : 0, n_samples,
                         have_power ? o.pwr : nullptr, nullptr, 0, (e->flags & SDRX_FLAG_PARTIAL_MIX) ? 0 : 1);
     if (rc) return rc;
-    if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_side));
-    CU(cudaEventRecord(e->ev_side_done[idx], e->s_side));
+    if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_mix));
+    CU(cudaEventRecord(e->ev_side_done[idx], e->s_mix));
     e->side_pending[idx] = true;
     return SDRX_OK;
 }
@@ -931,6 +955,8 @@ extern "C" int sdrx_engine_sync(sdrx_engine *e) {
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
+    CU(cudaStreamSynchronize(e->s_recur));
+    CU(cudaStreamSynchronize(e->s_mix));
     CU(cudaStreamSynchronize(e->s_out));
     return SDRX_OK;
 }
@@ -1159,6 +1185,8 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
+    CU(cudaStreamSynchronize(e->s_recur));
+    CU(cudaStreamSynchronize(e->s_mix));
     if (e->generic_stale) {      // the blob always carries the stage delay lines (a generic engine can load it)
         const int last_ = (int)((e->pushes & 1) ^ 1);
         int rc = materialize_generic(e, e->fmt, e->d_raw[last_], (long)e->raw_hist + (long)e->prev_n, e->total);
@@ -1216,6 +1244,8 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     CU(cudaStreamSynchronize(e->s_copy));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
+    CU(cudaStreamSynchronize(e->s_recur));
+    CU(cudaStreamSynchronize(e->s_mix));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
     const uint8_t *p = (const uint8_t *)buf + sizeof(h);

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -166,28 +167,41 @@ __global__ void k_lfagc_adjust(const float *__restrict__ in, unsigned n, float *
     gp[0] = g; gp[1] = p;
 }
 
+// Scratch of the AGC entry points: the state struct is the caller's plain data, so the device buffers live here, one
+// grow-only set per device, behind a mutex (AGC::adjust is called per sample by sdrx.cpp:457 -- no allocation per call).
+struct AgcScratch { float *d_in = nullptr, *d_out = nullptr, *d_gp = nullptr; size_t cap = 0; };
+std::mutex g_agc_mu;
+AgcScratch g_agc_scratch[64];
+
 template <bool LF>
 int agc_run(int device, sdrx_agc_state *s, const float *in, unsigned n, float *out) {
     if (!s || (!in && n) || (!out && n)) return fail(SDRX_ERR_ARG, "null argument");
     if (n == 0) return SDRX_OK;
+    if (device < 0 || device >= 64) return fail(SDRX_ERR_ARG, "device ordinal out of range");
     DevGuard g(device);
     if (!g.ok) return fail(SDRX_ERR_CUDA, "no CUDA device: sdrx_b200 has no CPU path");
     const size_t elems = LF ? n : 2 * (size_t)n;
-    float *d_in = nullptr, *d_out = nullptr, *d_gp = nullptr;
-    CU(cudaMalloc(&d_in, elems * 4));
-    CU(cudaMalloc(&d_out, elems * 4));
-    CU(cudaMalloc(&d_gp, 8));
+    std::lock_guard<std::mutex> lk(g_agc_mu);
+    AgcScratch &sc = g_agc_scratch[device];
+    if (!sc.d_gp) CU(cudaMalloc(&sc.d_gp, 8));
+    if (elems > sc.cap) {
+        cudaFree(sc.d_in); cudaFree(sc.d_out);
+        sc.d_in = sc.d_out = nullptr; sc.cap = 0;
+        const size_t cap = std::max<size_t>(elems, 4096);
+        CU(cudaMalloc(&sc.d_in, cap * 4));
+        CU(cudaMalloc(&sc.d_out, cap * 4));
+        sc.cap = cap;
+    }
     float gp[2] = {s->gain, s->power};
-    CU(cudaMemcpy(d_in, in, elems * 4, cudaMemcpyHostToDevice));
-    CU(cudaMemcpy(d_gp, gp, 8, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(sc.d_in, in, elems * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(sc.d_gp, gp, 8, cudaMemcpyHostToDevice));
     AgcParams a{s->attack, s->decay, s->reference, s->min_gain, s->max_gain, s->alpha};
-    if (LF) k_lfagc_adjust<<<1, 1>>>(d_in, n, d_out, a, s->active, d_gp);
-    else    k_agc_adjust<<<1, 1>>>((const float2 *)d_in, n, (float2 *)d_out, a, d_gp);
+    if (LF) k_lfagc_adjust<<<1, 1>>>(sc.d_in, n, sc.d_out, a, s->active, sc.d_gp);
+    else    k_agc_adjust<<<1, 1>>>((const float2 *)sc.d_in, n, (float2 *)sc.d_out, a, sc.d_gp);
     CU(cudaGetLastError());
-    CU(cudaMemcpy(out, d_out, elems * 4, cudaMemcpyDeviceToHost));
-    CU(cudaMemcpy(gp, d_gp, 8, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(out, sc.d_out, elems * 4, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(gp, sc.d_gp, 8, cudaMemcpyDeviceToHost));
     s->gain = gp[0]; s->power = gp[1];
-    cudaFree(d_in); cudaFree(d_out); cudaFree(d_gp);
     return SDRX_OK;
 }
 
@@ -207,6 +221,8 @@ struct sdrx_fir {
     std::vector<float> c, c_adj;
     float gain_db = 0.0f;
     float *d_c = nullptr, *d_hist = nullptr;     // hist: (n-1) frames of `lanes` floats, oldest first
+    float *d_buf = nullptr, *d_out = nullptr;    // grow-only scratch of filter(): [hist | new] frames, outputs
+    size_t buf_cap = 0, out_cap = 0;
 };
 
 namespace {
@@ -247,8 +263,27 @@ extern "C" int sdrx_fir_create(int kind, const float *c, int n, int device, sdrx
 extern "C" void sdrx_fir_destroy(sdrx_fir *f) {
     if (!f) return;
     DevGuard g(f->device);
-    cudaFree(f->d_c); cudaFree(f->d_hist);
+    cudaFree(f->d_c); cudaFree(f->d_hist); cudaFree(f->d_buf); cudaFree(f->d_out);
     delete f;
+}
+
+// The reference's FIR classes are implicitly copyable and a copy carries the delay line (buf_ and pos_ are plain
+// members, fir.hpp:69-74, :121-127, :176-182): coefficients, gain and the device-side history.
+extern "C" int sdrx_fir_clone(const sdrx_fir *src, sdrx_fir **out) {
+    if (!src || !out) return fail(SDRX_ERR_ARG, "null argument");
+    *out = nullptr;
+    sdrx_fir *f = nullptr;
+    int rc = sdrx_fir_create(src->kind, src->c.data(), src->n, src->device, &f);
+    if (rc) return rc;
+    DevGuard g(src->device);
+    f->gain_db = src->gain_db;
+    f->c_adj = src->c_adj;
+    const size_t hist = (size_t)std::max(1, (src->n - 1) * src->lanes);
+    cudaError_t e1 = cudaMemcpy(f->d_c, f->c_adj.data(), sizeof(float) * f->n, cudaMemcpyHostToDevice);
+    cudaError_t e2 = cudaMemcpy(f->d_hist, src->d_hist, sizeof(float) * hist, cudaMemcpyDeviceToDevice);
+    if (e1 != cudaSuccess || e2 != cudaSuccess) { sdrx_fir_destroy(f); cudaGetLastError(); return fail(SDRX_ERR_CUDA, "sdrx_fir_clone: copy failed"); }
+    *out = f;
+    return SDRX_OK;
 }
 
 extern "C" int sdrx_fir_set_gain(sdrx_fir *f, float gain_db) {   // fir.hpp:51-60
@@ -268,15 +303,22 @@ extern "C" int sdrx_fir_filter(sdrx_fir *f, const float *in, unsigned in_len, fl
     const int lanes = f->lanes;
     const int frames = f->kind == 3 ? (int)in_len : (int)in_len / lanes;
     const size_t hist = (size_t)(f->n - 1) * lanes, fresh = (size_t)frames * lanes;
-    float *d_buf = nullptr, *d_out = nullptr;
-    CU(cudaMalloc(&d_buf, sizeof(float) * (hist + fresh)));
-    CU(cudaMalloc(&d_out, sizeof(float) * fresh));
+    if (hist + fresh > f->buf_cap) {
+        cudaFree(f->d_buf); f->d_buf = nullptr; f->buf_cap = 0;
+        CU(cudaMalloc(&f->d_buf, sizeof(float) * (hist + fresh)));
+        f->buf_cap = hist + fresh;
+    }
+    if (fresh > f->out_cap) {
+        cudaFree(f->d_out); f->d_out = nullptr; f->out_cap = 0;
+        CU(cudaMalloc(&f->d_out, sizeof(float) * fresh));
+        f->out_cap = fresh;
+    }
+    float *d_buf = f->d_buf, *d_out = f->d_out;
     if (hist) CU(cudaMemcpy(d_buf, f->d_hist, sizeof(float) * hist, cudaMemcpyDeviceToDevice));
     CU(cudaMemcpy(d_buf + hist, in, sizeof(float) * fresh, cudaMemcpyHostToDevice));
     k_fir_frames<<<div_up((long)fresh, 256), 256>>>(d_buf, lanes, frames, f->d_c, f->n, d_out);
     CU(cudaGetLastError());
     CU(cudaMemcpy(out, d_out, sizeof(float) * fresh, cudaMemcpyDeviceToHost));
     if (hist) CU(cudaMemcpy(f->d_hist, d_buf + fresh, sizeof(float) * hist, cudaMemcpyDeviceToDevice));
-    cudaFree(d_buf); cudaFree(d_out);
     return SDRX_OK;
 }

@@ -146,6 +146,15 @@ class _FirBase:
             check(self.lib.sdrx_fir_filter(self.h, _fp(x), x.size, _fp(out)))
         return out
 
+    def copy(self):
+        """The reference's implicit copy (fir.hpp:69-74, :176-182): taps, gain and the delay line as it stands."""
+        o = object.__new__(type(self))
+        o.lib = self.lib
+        h = C.c_void_p()
+        check(self.lib.sdrx_fir_clone(self.h, C.byref(h)))
+        o.h, o._gain = h, self._gain
+        return o
+
     def close(self):
         if getattr(self, "h", None):
             self.lib.sdrx_fir_destroy(self.h)

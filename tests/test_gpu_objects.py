@@ -67,4 +67,12 @@ def test_fir_classes_match_oracle_bit_for_bit():
         a.setGain(3.5)
         o.set_gain(3.5)
         assert np.array_equal(a.filter(data[:512]), o.filter(data[:512]))
+        # a copy carries the delay line and the gain (the reference's implicit copy, fir.hpp:69-74, :176-182): both
+        # continue the stream exactly like the oracle, which kept running
+        b = a.copy()
+        want = o.filter(data[512:1024])
+        assert np.array_equal(b.filter(data[512:1024]), want), (kind, "copy")
+        assert np.array_equal(a.filter(data[512:1024]), want), (kind, "original after the copy")
+        assert b.gain() == 3.5
+        b.close()
         a.close()
