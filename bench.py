@@ -445,6 +445,12 @@ def run_ours(args):
                  "e2e": w_e2e}
         weng.close()
 
+    # ---- channel-sharded leg (configs 3/5 over N GPUs): ONE stream, 960/N channels per GPU, NCCL broadcast of every
+    #      block, NCCL gather of the partial mixes -- strong scaling, next to the replica numbers above
+    sharded = None
+    if world > 1 and not args.no_sharded:
+        sharded = sharded_leg(args, plan, blocks, hviews, d_ring, blk_bytes, ring, world, rank, local, barrier, max_over_ranks)
+
     # ---- parity of the bench's own workload against the oracle (--check): every channel, every distinct block
     check = None
     if args.check and rank == 0:
@@ -472,7 +478,7 @@ def run_ours(args):
                        "specialised_bank": bool(eng.uses_fast_path)},
             "realtime_channels": value / (RATE / 1e6),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "worst_case": worst, "sustained": sustained,
+            "worst_case": worst, "sustained": sustained, "channel_sharded": sharded,
         }
         if check is not None:
             line["parity_check"] = check
@@ -482,6 +488,92 @@ def run_ours(args):
     if world > 1:
         dist.destroy_process_group()
     return 0
+
+
+def sharded_leg(args, plan, blocks, hviews, d_ring, blk_bytes, ring, world, rank, local, barrier, max_over_ranks):
+    """One 10 MS/s stream, its channels split over the ranks (sdrx_b200/sharded.py): per block one NCCL collective in
+    (broadcast from rank 0, or all-gather of per-rank slices), one small NCCL all-gather of the partial mixes out, the
+    mix finished on rank 0.  K blocks through the pipeline (depth 4), wall clock around the whole run incl. the final
+    drain, max over ranks.  `value`: the block already lies on rank 0's GPU; `e2e`: every block is copied from pinned
+    host memory inside the timed region and every rank's results land in pinned host memory."""
+    import torch
+    import torch.distributed as dist
+    from sdrx_b200.sharded import ShardedReceiver
+    C_ = len(plan.offsets)
+    L = plan.rate.block_len
+    K = args.sharded_blocks
+    dev = torch.device("cuda", local)
+    # every rank needs rank 0's blocks for the all-gather ingest (each copies its own slice): hand them round once, untimed
+    shared = [torch.empty(2 * L, dtype=torch.float32, device=dev) for _ in range(N_DISTINCT)]
+    for i, t in enumerate(shared):
+        if rank == 0:
+            t.copy_(torch.from_numpy(blocks[i].view(np.float32)))
+        dist.broadcast(t, src=0)
+    torch.cuda.synchronize()
+    if rank != 0:
+        for i, t in enumerate(shared):
+            hviews[i].view(np.float32)[:] = t.cpu().numpy()
+    out = {"workload": f"one 10 MS/s f32 stream, {C_} channels split {C_ // world}-per-GPU over {world} GPUs (configs 3/5, channel-sharded)",
+           "blocks": K, "scaling": "strong", "pipeline_depth": 4}
+
+    def run(ingest, from_host):
+        rx = ShardedReceiver(plan, device=local, ingest=ingest, depth=4)
+        def feed(i):
+            if from_host:
+                rx.submit(hviews[i % N_DISTINCT])
+            else:
+                rx.submit(device_block=shared[i % N_DISTINCT])
+        for i in range(8):
+            feed(i)
+            if i >= 3:
+                rx.collect()
+        for _ in range(3):
+            rx.collect()
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(K):
+            feed(i)
+            if i >= 3:
+                rx.collect()
+        for _ in range(3):
+            rx.collect()
+        torch.cuda.synchronize()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        rx.close()
+        barrier()
+        return {"ms_per_block": dt / K * 1e3, "value": C_ * L * K / dt / 1e6}
+
+    for ingest in ("broadcast", "allgather"):
+        v = run(ingest, False)
+        e = run(ingest, True)
+        out[ingest] = {"value": v["value"], "ms_per_block": v["ms_per_block"],
+                       "e2e": {"value": e["value"], "ms_per_block": e["ms_per_block"],
+                               "h2d_bytes_per_block_src" if ingest == "broadcast" else "h2d_bytes_per_block_per_rank":
+                                   blk_bytes if ingest == "broadcast" else blk_bytes // world}}
+    # the collective alone: K broadcasts / all-gathers of one block back to back, CUDA events on the comm stream
+    buf = torch.empty(2 * L, dtype=torch.float32, device=dev)
+    part = torch.empty(2 * L // world, dtype=torch.float32, device=dev)
+    mix = torch.empty(world * 1024, dtype=torch.float32, device=dev)
+    mp = torch.empty(1024, dtype=torch.float32, device=dev)
+    for name, fn in (("broadcast_us", lambda: dist.broadcast(buf, src=0)),
+                     ("allgather_block_us", lambda: dist.all_gather_into_tensor(buf, part)),
+                     ("allgather_mix_us", lambda: dist.all_gather_into_tensor(mix, mp))):
+        for _ in range(10):
+            fn()
+        torch.cuda.synchronize()
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(200):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        out[name] = max_over_ranks(a.elapsed_time(b)) / 200 * 1e3
+    best = min(("broadcast", "allgather"), key=lambda k: out[k]["ms_per_block"])
+    out["value"] = out[best]["value"]
+    out["e2e"] = out[best]["e2e"]
+    out["best_ingest"] = best
+    return out if rank == 0 else None
 
 
 def check_against_oracle(plan, blocks, device):
@@ -521,6 +613,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-worst", action="store_true", help="skip the worst_case leg (every squelch open)")
     ap.add_argument("--sustain", type=float, default=3.2, help="seconds of back-to-back blocks in the sustained leg (0: skip)")
+    ap.add_argument("--no-sharded", action="store_true", help="N > 1: skip the channel-sharded (one stream over N GPUs) leg")
+    ap.add_argument("--sharded-blocks", type=int, default=2000, help="blocks of the channel-sharded leg")
     ap.add_argument("--check", action="store_true", help="also run the bench's own blocks through the CPU oracle and report parity")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

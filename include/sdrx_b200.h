@@ -160,6 +160,23 @@ int  sdrx_engine_join(sdrx_engine *e);
  * (sdrx.cpp:649-656).  mix_pre / mix / pcm (host, 1024 each) may be NULL.                                  */
 int  sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_parts, float *mix_pre, float *mix, int16_t *pcm);
 
+/* ---- plumbing for callers that drive the engine from their own CUDA streams (the channel-sharded receiver,
+ * sdrx_b200/sharded.py: NCCL broadcast of the block in, NCCL gather of the partial mixes out) -- no host synchronisation:
+ *   wait_stream          the next push_block_device's ingest is ordered behind everything queued on `cuda_stream` so far
+ *   stream_wait_ingest   `cuda_stream` waits until the last pushed block has been copied out of the caller's buffer
+ *   stream_wait_outputs  `cuda_stream` waits until boundary B of the last pushed block is complete
+ *   device_outputs       DEVICE pointers of the results of the block pushed `back` pushes ago (0 = last; valid until four
+ *                        more blocks have been pushed; audio_rows is NULL, audio_chan / n_audio are the device-side list)
+ *   finish_mix_async     sdrx_engine_finish_mix with the partials already on the device (`d_parts`, [n_parts][1024]), queued
+ *                        on `cuda_stream`; mix_pre / mix / pcm (pinned host, may be NULL) are valid once the caller has
+ *                        synchronised with that stream.                                                              */
+int  sdrx_engine_wait_stream(sdrx_engine *e, void *cuda_stream);
+int  sdrx_engine_stream_wait_ingest(sdrx_engine *e, void *cuda_stream);
+int  sdrx_engine_stream_wait_outputs(sdrx_engine *e, void *cuda_stream);
+int  sdrx_engine_device_outputs(sdrx_engine *e, int back, sdrx_block_outputs *dev);
+int  sdrx_engine_finish_mix_async(sdrx_engine *e, const float *d_parts, int n_parts, void *cuda_stream, float *mix_pre,
+                                  float *mix, int16_t *pcm);
+
 /* Carried state (MSD delay lines + trans_pos, AGC/LfAGC gain+power, squelch states, FIR2 ring):
  * what the reference keeps in its objects between blocks (SURVEY.md §5 checkpoint/resume). */
 size_t sdrx_engine_state_size(sdrx_engine *e);
@@ -186,6 +203,11 @@ int      sdrx_debug_bank_plan_dump(int groups, int U, int n_sms, int *out, int m
  * read returns the number of values copied, laid out [cta][16 warps][start, end] (tools/diag_bank_trace.py). */
 int      sdrx_debug_bank_trace(int enable);
 int      sdrx_debug_bank_trace_read(unsigned long long *out, int max_u64);
+/* Per-kernel completion times of the engine's last blocks, as its streams reached them: enable, push >= max_blocks blocks, read.
+ * out[block][9] = ms after the enable: start of the block on the main stream, prep, channel bank, last MSD stage, detector, AGC,
+ * envelope, LfAGC, mix (-1: not run).  Returns the number of blocks written (<= 16).  tools/diag_timeline.py.            */
+int      sdrx_debug_timeline(sdrx_engine *e, int enable);
+int      sdrx_debug_timeline_read(sdrx_engine *e, float *out, int max_blocks);
 /* Same for the front end's five passes: [pass][CTA-0 start, latest CTA end] of the last call (10 values). */
 int      sdrx_debug_fe_trace(int enable);
 int      sdrx_debug_fe_trace_read(unsigned long long *out);

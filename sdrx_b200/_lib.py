@@ -67,6 +67,13 @@ PROTOTYPES = [
     ("sdrx_engine_sync", C.c_int, [C.c_void_p]),
     ("sdrx_engine_join", C.c_int, [C.c_void_p]),
     ("sdrx_engine_finish_mix", C.c_int, [C.c_void_p, c_float_p, C.c_int, c_float_p, c_float_p, c_i16_p]),
+    ("sdrx_engine_wait_stream", C.c_int, [C.c_void_p, C.c_void_p]),
+    ("sdrx_engine_stream_wait_ingest", C.c_int, [C.c_void_p, C.c_void_p]),
+    ("sdrx_engine_stream_wait_outputs", C.c_int, [C.c_void_p, C.c_void_p]),
+    ("sdrx_engine_device_outputs", C.c_int, [C.c_void_p, C.c_int, C.POINTER(BlockOutputs)]),
+    ("sdrx_engine_finish_mix_async", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, c_float_p, c_float_p, c_i16_p]),
+    ("sdrx_debug_timeline", C.c_int, [C.c_void_p, C.c_int]),
+    ("sdrx_debug_timeline_read", C.c_int, [C.c_void_p, c_float_p, C.c_int]),
     ("sdrx_engine_state_size", C.c_size_t, [C.c_void_p]),
     ("sdrx_engine_save_state", C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     ("sdrx_engine_load_state", C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),

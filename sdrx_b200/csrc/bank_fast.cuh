@@ -53,6 +53,7 @@ constexpr int kFastMinSeg = 8;     // units per segment when sizing the grid: sh
 constexpr int kFastMinSegPiece = 2;// ... but a small piece (a CTA range that straddles a group) still spreads over all warps
 constexpr int kFastWarmStart = 4;  // warm-up units of a segment at the start of the block
 constexpr int kFastPiecePenalty = 1;// steps charged to a CTA for every piece after its first (table reload + refill)
+constexpr int kFastSideSms = 3;    // SMs the schedule leaves without a bank CTA (== kSideSms, demod.cuh)
 constexpr int kFastRawHist = 768;  // raw history samples the engine keeps for this path
 
 struct FastTaps {                  // kernel parameter: lives in the constant bank
@@ -676,6 +677,7 @@ inline int fast_init(FastBank &fb, int C, int N, const float *h1, const float *h
     int dev = 0;
     CU(cudaGetDevice(&dev));
     CU(cudaDeviceGetAttribute(&fb.n_sms, cudaDevAttrMultiProcessorCount, dev));
+    fb.n_sms = std::max(fb.n_sms - kFastSideSms, 1);        // SMs left to the latency-bound side kernels (demod.cuh kSideSms)
 
     // ---- slots: conjugate pairs share a slot when enough channels pair up to shrink the work
     std::vector<uint8_t> has_v((size_t)C, 0);

@@ -17,6 +17,7 @@
 #include "demod.cuh"
 
 using namespace sdrx;
+static_assert(kFastSideSms == kSideSms, "the bank leaves the SMs the side kernels expect");
 
 namespace {
 
@@ -27,7 +28,7 @@ constexpr uint32_t kStateMagic = 0x58524453u;  // "SDRX"
 
 struct OutSet {                   // device-side results of one block
     float2  *ch_iq = nullptr;     // [C][512]
-    float   *audio = nullptr;     // [C][512]
+    float   *audio = nullptr;     // [512][Cpad] SAMPLE-major (k_chan_lfagc's lanes are channels); rows leave through k_export_audio
     float   *snr = nullptr;       // [C]
     float   *mix_pre = nullptr, *mix = nullptr;   // [1024]
     int16_t *pcm = nullptr;       // [1024]
@@ -35,6 +36,7 @@ struct OutSet {                   // device-side results of one block
     uint8_t *sql = nullptr;       // [C] snapshot of the state after the decision
     float   *agc_gain = nullptr, *lf_gain = nullptr;   // [C] snapshots
     uint8_t *mixed = nullptr;     // [Cpad] 1 where this block's audio goes into the mix (k_chan_recur -> k_mix_fir2_pcm)
+    CUtensorMap iq_map;           // ch_iq as the AGC's TMA source: FLOAT32 [C][2 * 512], 32 x 160 boxes, 128 B swizzle
     int     *audio_idx = nullptr; // [C] channels whose audio is mixed this block, ascending (k_mix_fir2_pcm)
     int     *n_audio = nullptr;   // [1] how many
 };
@@ -99,8 +101,23 @@ struct sdrx_engine {
     float *d_c_adj = nullptr, *d_fir_hist = nullptr;
     float *d_parts = nullptr;             // staging of the per-GPU partial mixes (sdrx_engine_finish_mix)
     size_t parts_cap = 0;
+    float2 *d_agc_iq = nullptr;           // [512][Cpad] gain-adjusted channel IQ, sample-major (k_chan_agc -> k_chan_env)
+    float *d_env = nullptr;               // [512][Cpad] envelope / discriminator output (k_chan_env -> k_chan_lfagc)
+    float2 *d_fm_new = nullptr;           // [C] prev_sample of the FM demodulators after this block (k_chan_env -> k_chan_lfagc)
+    // debug timeline (sdrx_debug_timeline): completion time of every kernel of the last kTlBlocks blocks
+    static constexpr int kTlBlocks = 16, kTlKinds = 10;
+    bool tl_on = false;
+    cudaEvent_t tl_ev[kTlBlocks][kTlKinds] = {};
+    cudaEvent_t tl_base = nullptr;
+    uint64_t tl_first = 0;                // e->blocks when the timeline was switched on
+    cudaEvent_t ev_ext = nullptr;         // sdrx_engine_wait_stream: marks the caller's stream
+    static constexpr int kNFin = 4;       // sdrx_engine_finish_mix_async results in flight
+    float *d_fin_mix_pre[kNFin] = {}, *d_fin_mix[kNFin] = {};
+    int16_t *d_fin_pcm[kNFin] = {};
+    uint64_t n_fin = 0;
     unsigned *d_ticket = nullptr;         // arrival counter of k_mix_fir2_pcm's CTAs (the last one runs FIR2); self-resetting
-    float *d_rows_scratch = nullptr;      // [C][512] compacted audio rows for callers whose result buffers are pageable
+    float *d_rows_scratch[2] = {nullptr, nullptr};   // [C][512] audio rows on their way to a dense / pageable host array: one per
+                                                     // stream that copies results out (blocking gets: main, fetches: s_out)
     FastBank fast;                        // specialised channel bank (bank_fast.cuh)
     bool use_fast = false;
     bool tail_fusable = false;            // last stage as one per-channel kernel fed by the bank's rows + tail fix-ups
@@ -183,6 +200,30 @@ extern "C" int sdrx_device_upload(int device, void *d_dst, const void *h_src, si
 
 // ------------------------------------------------------------------------------------------------
 namespace {
+
+// The tensor map k_chan_agc reads a block's channel IQ through (demod.cuh).  The encoder lives in the driver library: it
+// is fetched through the runtime (cudaGetDriverEntryPoint), so nothing links against libcuda.
+int make_iq_map(CUtensorMap *map, float2 *ch_iq, long iq_stride, int C) {
+    typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    if (!encode) {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        CU(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+        if (!fn || q != cudaDriverEntryPointSuccess) return fail(SDRX_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
+        encode = (encode_fn)fn;
+    }
+    const cuuint64_t dims[2] = {(cuuint64_t)(2 * kChunk), (cuuint64_t)C};
+    const cuuint64_t strides[1] = {(cuuint64_t)iq_stride * sizeof(float2)};
+    const cuuint32_t box[2] = {(cuuint32_t)(2 * kRecurTile), (cuuint32_t)kAgcBoxRows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ch_iq, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(SDRX_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+    return SDRX_OK;
+}
 
 template <typename T>
 int dalloc(T **p, size_t count) {
@@ -279,7 +320,12 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     cudaFree(e->st.sql_state); cudaFree(e->st.sql_prev);
     cudaFree(e->d_window); cudaFree(e->d_shape); cudaFree(e->d_ramp_up); cudaFree(e->d_ramp_down);
     cudaFree(e->d_twiddle); cudaFree(e->d_bitrev); cudaFree(e->d_sql_level); cudaFree(e->d_pos);
-    cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist); cudaFree(e->d_parts); cudaFree(e->d_ticket); cudaFree(e->d_rows_scratch);
+    cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist); cudaFree(e->d_parts); cudaFree(e->d_ticket); cudaFree(e->d_rows_scratch[0]); cudaFree(e->d_rows_scratch[1]);
+    cudaFree(e->d_agc_iq); cudaFree(e->d_env); cudaFree(e->d_fm_new);
+    for (int b = 0; b < sdrx_engine::kNFin; ++b) { cudaFree(e->d_fin_mix_pre[b]); cudaFree(e->d_fin_mix[b]); cudaFree(e->d_fin_pcm[b]); }
+    if (e->ev_ext) cudaEventDestroy(e->ev_ext);
+    if (e->tl_base) cudaEventDestroy(e->tl_base);
+    for (auto &row : e->tl_ev) for (cudaEvent_t ev : row) if (ev) cudaEventDestroy(ev);
     e->fast.destroy();
     if (e->ev_t0) cudaEventDestroy(e->ev_t0);
     if (e->ev_t1) cudaEventDestroy(e->ev_t1);
@@ -323,10 +369,17 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     CU(cudaStreamCreateWithFlags(&e->s_main, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_side, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&e->s_recur, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&e->s_mix, cudaStreamNonBlocking));
+    {
+        // the recurrences and the mix are few, long CTAs that need most of a free SM's shared memory; the detector is 960
+        // short ones that would otherwise keep nibbling at it: higher priority puts the long ones first in line
+        int lo = 0, hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU(cudaStreamCreateWithPriority(&e->s_recur, cudaStreamNonBlocking, hi));
+        CU(cudaStreamCreateWithPriority(&e->s_mix, cudaStreamNonBlocking, hi));
+    }
     CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->ev_head_done, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&e->ev_ext, cudaEventDisableTiming));
     for (int b = 0; b < kNOut; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_side_done[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_det_done[b], cudaEventDisableTiming));
@@ -434,7 +487,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         int rc;
         if ((rc = dalloc(&o.ch_iq, (size_t)C * e->chiq_stride))) return rc;
         if (e->flags & SDRX_FLAG_NO_DEMOD) continue;
-        if ((rc = dalloc(&o.audio, (size_t)C * kChunk))) return rc;
+        if ((rc = dalloc(&o.audio, (size_t)e->Cpad * kChunk))) return rc;
+        if ((rc = make_iq_map(&o.iq_map, o.ch_iq, e->chiq_stride, C))) return rc;
         if ((rc = dalloc(&o.snr, C))) return rc;
         if ((rc = dalloc(&o.mix_pre, 2 * kChunk))) return rc;
         if ((rc = dalloc(&o.mix, 2 * kChunk))) return rc;
@@ -507,6 +561,11 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             (rc = dalloc(&e->d_fir_hist, 2 * (size_t)std::max(cfg->fir2_ntaps - 1, 1))))
             return rc;
         if ((rc = dalloc(&e->d_ticket, 2))) return rc;
+        if ((rc = raise_dyn_smem((const void *)k_chan_agc, kAgcSmem)) || (rc = raise_dyn_smem((const void *)k_chan_lfagc, kLfSmem)))
+            return rc;
+        if ((rc = dalloc(&e->d_agc_iq, (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_env, (size_t)e->Cpad * kChunk)) ||
+            (rc = dalloc(&e->d_fm_new, C)))
+            return rc;
         e->tb = DemodTables{e->d_window, e->d_twiddle, e->d_bitrev, e->d_shape, e->d_ramp_up, e->d_ramp_down};
         if ((size_t)C * 4 > 160 * 1024) return fail(SDRX_ERR_UNSUPPORTED, "more than 40960 channels per engine");
         { int rc2 = raise_dyn_smem((const void *)k_mix_fir2_pcm, mix_smem_bytes(e->Cpad, cfg->fir2_ntaps)); if (rc2) return rc2; }
@@ -530,7 +589,9 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     // the channel bank, which needs all of it.
     {
         const int mx = (int)cudaSharedmemCarveoutMaxShared;
-        CU(cudaFuncSetAttribute(k_chan_recur, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_chan_agc, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_chan_env, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
+        CU(cudaFuncSetAttribute(k_chan_lfagc, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
         CU(cudaFuncSetAttribute(k_mix_fir2_pcm, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
         CU(cudaFuncSetAttribute(k_chan_head<kHeadFir>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
         CU(cudaFuncSetAttribute(k_chan_head<kHeadDetect>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
@@ -588,6 +649,13 @@ extern "C" int sdrx_engine_reset(sdrx_engine *e) {
 namespace {
 
 enum SrcKind { SRC_HOST, SRC_DEVICE, SRC_NONE };
+
+// debug timeline: kinds in the order a block walks them
+enum TlKind { TL_START = 0, TL_PREP, TL_BANK, TL_TAIL, TL_DET, TL_AGC, TL_ENV, TL_LFAGC, TL_MIX, TL_N };
+inline void tl_mark(sdrx_engine *e, int kind, cudaStream_t st) {
+    if (!e->tl_on) return;
+    cudaEventRecord(e->tl_ev[e->blocks % sdrx_engine::kTlBlocks][kind], st);
+}
 
 // Stages [s_begin, s_end) of the chain.  `hist` = buffer index of call-relative input 0, `pos0` its
 // trans_pos_, `valid_lo` the first buffer index that holds stream samples.
@@ -709,7 +777,7 @@ int launch_mix(sdrx_engine *e, cudaStream_t st, OutSet &o, const float *pwr_part
                float *pwr, const float *ext_parts, int n_ext, int do_fir) {
     // sdrx_engine_finish_mix (ext_parts) may run next to a block's own mix kernel: it takes its own arrival counter
     k_mix_fir2_pcm<<<kMixCtas, kMixThreads, mix_smem_bytes(e->Cpad, e->fir2_ntaps), st>>>(
-        o.audio, o.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps, e->d_fir_hist, o.mix_pre, o.mix, o.pcm, pwr_partial,
+        o.audio, e->Cpad, o.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps, e->d_fir_hist, o.mix_pre, o.mix, o.pcm, pwr_partial,
         n_partial, n_samples, pwr, ext_parts, n_ext, do_fir, o.audio_idx, o.n_audio, e->d_ticket + (ext_parts ? 1 : 0));
     ++e->launches;
     CU(cudaGetLastError());
@@ -730,21 +798,32 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
         ++e->launches;
     }
     CU(cudaGetLastError());
+    tl_mark(e, TL_TAIL, e->s_main);
     CU(cudaEventRecord(e->ev_head_done, e->s_main));
     CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
+    CU(cudaStreamWaitEvent(e->s_recur, e->ev_head_done, 0));
     k_chan_head<kHeadDetect><<<e->C, kHeadThreads, 0, e->s_side>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
                                                                    e->d_sql_level, o.snr, e->d_gate[idx], snap);
+    tl_mark(e, TL_DET, e->s_side);
     CU(cudaEventRecord(e->ev_det_done[idx], e->s_side));
+    // the AGC runs whatever the squelch state (sdrx.cpp:457): next to the detector, not behind it
+    k_chan_agc<<<recur_ctas(e->C), kRecurThreads, kAgcSmem, e->s_recur>>>(o.iq_map, e->st, e->agc, e->d_agc_iq, e->Cpad, snap, e->C);
+    tl_mark(e, TL_AGC, e->s_recur);
     CU(cudaStreamWaitEvent(e->s_recur, e->ev_det_done[idx], 0));
-    k_chan_recur<<<div_up(e->C, 32), 32, 0, e->s_recur>>>(o.ch_iq, e->chiq_stride, e->st, e->d_gate[idx], e->tb, e->agc, e->lf,
-                                                          e->lf_active, o.audio, snap, e->C, o.mixed);
+    k_chan_env<<<dim3(e->Cpad / 32, kChunk / 4), dim3(32, 4), 0, e->s_recur>>>(e->d_agc_iq, e->Cpad, e->st, e->d_gate[idx], e->d_env,
+                                                                                e->d_fm_new, e->C);
+    tl_mark(e, TL_ENV, e->s_recur);
+    k_chan_lfagc<<<recur_ctas(e->C), kRecurThreads, kLfSmem, e->s_recur>>>(e->d_env, e->Cpad, e->st, e->d_gate[idx], e->tb, e->lf, e->lf_active, o.audio, snap,
+                                                           e->C, o.mixed, e->d_fm_new);
+    tl_mark(e, TL_LFAGC, e->s_recur);
     CU(cudaEventRecord(e->ev_recur_done[idx], e->s_recur));
     CU(cudaStreamWaitEvent(e->s_mix, e->ev_recur_done[idx], 0));
-    e->launches += 2;
+    e->launches += 4;
     int rc = launch_mix(e, e->s_mix, o, e->d_pwr_partial[idx], have_power ? kPwrPartials : 0, n_samples,
                         have_power ? o.pwr : nullptr, nullptr, 0, (e->flags & SDRX_FLAG_PARTIAL_MIX) ? 0 : 1);
     if (rc) return rc;
     if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_mix));
+    tl_mark(e, TL_MIX, e->s_mix);
     CU(cudaEventRecord(e->ev_side_done[idx], e->s_mix));
     e->side_pending[idx] = true;
     return SDRX_OK;
@@ -773,7 +852,19 @@ int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out,
     auto d2h = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
         return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
     };
-    CU(d2h(out->audio, o.audio, C * kChunk * sizeof(float)));
+    const int xgrid = (int)std::min<size_t>(C, 128);
+    float *&rows_scratch = e->d_rows_scratch[blocking ? 0 : 1];
+    auto scratch = [&]() -> int {
+        if (!rows_scratch) CU(cudaMalloc((void **)&rows_scratch, sizeof(float) * C * kChunk));
+        return SDRX_OK;
+    };
+    if (out->audio) {             // the dense [C][512] array: rows out of the sample-major device array, then one copy
+        { int rc = scratch(); if (rc) return rc; }
+        k_export_audio<<<xgrid, 128, 0, st>>>(o.audio, e->Cpad, nullptr, nullptr, (int)C, rows_scratch, nullptr, nullptr);
+        ++e->launches;
+        CU(cudaGetLastError());
+        CU(d2h(out->audio, rows_scratch, C * kChunk * sizeof(float)));
+    }
     CU(d2h(out->sql_state, o.sql, C));
     CU(d2h(out->snr, o.snr, C * sizeof(float)));
     CU(d2h(out->mix_pre, o.mix_pre, 2 * kChunk * sizeof(float)));
@@ -787,9 +878,8 @@ int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out,
         int *chan = (int *)device_view(out->audio_chan);
         int *cnt = (int *)device_view(out->n_audio);
         const bool direct = (!out->audio_rows || rows) && (!out->audio_chan || chan) && (!out->n_audio || cnt);
-        const int grid = (int)std::min<size_t>(C, 128);
         if (direct) {
-            k_export_audio<<<grid, 128, 0, st>>>(o.audio, o.audio_idx, o.n_audio, rows, chan, cnt);
+            k_export_audio<<<xgrid, 128, 0, st>>>(o.audio, e->Cpad, o.audio_idx, o.n_audio, 0, rows, chan, cnt);
             ++e->launches;
             CU(cudaGetLastError());
         } else {
@@ -800,11 +890,11 @@ int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out,
             if (out->n_audio) *out->n_audio = n;
             if (out->audio_chan && n > 0) CU(d2h(out->audio_chan, o.audio_idx, sizeof(int) * (size_t)n));
             if (out->audio_rows && n > 0) {
-                if (!e->d_rows_scratch) CU(cudaMalloc((void **)&e->d_rows_scratch, sizeof(float) * C * kChunk));
-                k_export_audio<<<grid, 128, 0, st>>>(o.audio, o.audio_idx, o.n_audio, e->d_rows_scratch, nullptr, nullptr);
+                { int rc = scratch(); if (rc) return rc; }
+                k_export_audio<<<xgrid, 128, 0, st>>>(o.audio, e->Cpad, o.audio_idx, o.n_audio, 0, rows_scratch, nullptr, nullptr);
                 ++e->launches;
                 CU(cudaGetLastError());
-                CU(d2h(out->audio_rows, e->d_rows_scratch, sizeof(float) * (size_t)n * kChunk));
+                CU(d2h(out->audio_rows, rows_scratch, sizeof(float) * (size_t)n * kChunk));
             }
         }
     }
@@ -867,12 +957,14 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         int rc = launch_prep(e, e->s_copy, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps,
                              e->d_pwr_partial[oc]);
         if (rc) return rc;
+        tl_mark(e, TL_PREP, e->s_copy);
         CU(cudaEventRecord(e->ev_copied[cur], e->s_copy));
         CU(cudaStreamWaitEvent(e->s_main, e->ev_copied[cur], 0));
         CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));   // every kernel that read buffer `prv` is queued before this point
     }
     { int rc = wait_side(e, oc); if (rc) return rc; }       // block b-kNOut's recurrences / mix / read-back used this output set
     if (e->timing) CU(cudaEventRecord(e->ev_t0, e->s_main));
+    tl_mark(e, TL_START, e->s_main);
 
     const int valid_lo = (int)std::max<long>(0, (long)e->raw_hist - (long)std::min<uint64_t>(e->total, (uint64_t)e->raw_hist));
     const bool fast = e->use_fast && n > 0 && n % kUnit == 0 && phase_in[0] == 0 && phase_in[1] == 0 && phase_in[2] == 0;
@@ -898,6 +990,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         if (!rc) rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 0, e->S);
     }
     if (rc) return rc;
+    tl_mark(e, TL_BANK, e->s_main);
     if (e->timing) CU(cudaEventRecord(e->ev_t1, e->s_main));
 
     if (demod) { rc = launch_demod(e, oc, n > 0, n, fuse_tail ? &tail : nullptr); if (rc) return rc; }
@@ -1065,6 +1158,93 @@ extern "C" int sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_
     if (mix) CU(cudaMemcpyAsync(mix, o.mix, sizeof(float) * 2 * kChunk, cudaMemcpyDeviceToHost, e->s_main));
     if (pcm) CU(cudaMemcpyAsync(pcm, o.pcm, sizeof(int16_t) * 2 * kChunk, cudaMemcpyDeviceToHost, e->s_main));
     CU(cudaStreamSynchronize(e->s_main));
+    return SDRX_OK;
+}
+
+// Debug: completion times (ms after the moment the timeline was switched on) of every kernel of the last blocks, as the
+// streams reached them: [block][start-of-main, prep, bank, last stage, detector, agc, envelope, lfagc, mix].
+extern "C" int sdrx_debug_timeline(sdrx_engine *e, int enable) {
+    if (!e) return fail(SDRX_ERR_ARG, "null engine");
+    DevGuard g(e->dev);
+    if (enable) {
+        if (!e->tl_base) {
+            CU(cudaEventCreate(&e->tl_base));
+            for (auto &row : e->tl_ev) for (int k = 0; k < TL_N; ++k) CU(cudaEventCreate(&row[k]));
+        }
+        CU(cudaEventRecord(e->tl_base, e->s_main));
+        e->tl_first = e->blocks;
+    }
+    e->tl_on = enable != 0;
+    return SDRX_OK;
+}
+extern "C" int sdrx_debug_timeline_read(sdrx_engine *e, float *out, int max_blocks) {
+    if (!e || !out || !e->tl_base) return 0;
+    DevGuard g(e->dev);
+    if (sdrx_engine_sync(e) != SDRX_OK) return 0;
+    const uint64_t n = std::min<uint64_t>({(uint64_t)max_blocks, e->blocks - e->tl_first, (uint64_t)sdrx_engine::kTlBlocks});
+    for (uint64_t i = 0; i < n; ++i) {
+        const uint64_t b = e->blocks - n + i;
+        for (int k = 0; k < TL_N; ++k) {
+            float ms = -1.0f;
+            if (cudaEventElapsedTime(&ms, e->tl_base, e->tl_ev[b % sdrx_engine::kTlBlocks][k]) != cudaSuccess) { cudaGetLastError(); ms = -1.0f; }
+            out[i * TL_N + k] = ms;
+        }
+    }
+    return (int)n;
+}
+
+extern "C" int sdrx_engine_wait_stream(sdrx_engine *e, void *cuda_stream) {
+    if (!e) return fail(SDRX_ERR_ARG, "null engine");
+    DevGuard g(e->dev);
+    CU(cudaEventRecord(e->ev_ext, (cudaStream_t)cuda_stream));
+    CU(cudaStreamWaitEvent(e->s_copy, e->ev_ext, 0));
+    return SDRX_OK;
+}
+extern "C" int sdrx_engine_stream_wait_ingest(sdrx_engine *e, void *cuda_stream) {
+    if (!e) return fail(SDRX_ERR_ARG, "null engine");
+    if (e->pushes == 0) return SDRX_OK;
+    DevGuard g(e->dev);
+    CU(cudaStreamWaitEvent((cudaStream_t)cuda_stream, e->ev_copied[(e->pushes - 1) & 1], 0));
+    return SDRX_OK;
+}
+extern "C" int sdrx_engine_stream_wait_outputs(sdrx_engine *e, void *cuda_stream) {
+    if (!e) return fail(SDRX_ERR_ARG, "null engine");
+    if (e->blocks == 0) return SDRX_OK;
+    DevGuard g(e->dev);
+    const int idx = (int)((e->blocks - 1) % kNOut);
+    if (e->side_pending[idx]) CU(cudaStreamWaitEvent((cudaStream_t)cuda_stream, e->ev_side_done[idx], 0));
+    else CU(cudaStreamWaitEvent((cudaStream_t)cuda_stream, e->ev_head_done, 0));
+    return SDRX_OK;
+}
+extern "C" int sdrx_engine_device_outputs(sdrx_engine *e, int back, sdrx_block_outputs *dev) {
+    if (!e || !dev || back < 0 || back > kNOut - 2) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) .. 4");
+    if (e->blocks < (uint64_t)back + 1) return fail(SDRX_ERR_STATE, "no such block");
+    const OutSet &o = e->out[(e->blocks - 1 - back) % kNOut];
+    memset(dev, 0, sizeof(*dev));
+    dev->audio = nullptr;         /* on the device the audio is sample-major: not part of this view */
+    dev->sql_state = o.sql; dev->snr = o.snr; dev->mix_pre = o.mix_pre; dev->mix = o.mix; dev->pcm = o.pcm;
+    dev->pwr_dbfs = o.pwr; dev->agc_gain = o.agc_gain; dev->lf_gain = o.lf_gain; dev->audio_chan = o.audio_idx; dev->n_audio = o.n_audio;
+    return SDRX_OK;
+}
+extern "C" int sdrx_engine_finish_mix_async(sdrx_engine *e, const float *d_parts, int n_parts, void *cuda_stream, float *mix_pre,
+                                            float *mix, int16_t *pcm) {
+    if (!e || !d_parts || n_parts < 1) return fail(SDRX_ERR_ARG, "null argument");
+    if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
+    DevGuard g(e->dev);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const int k = (int)(e->n_fin++ % sdrx_engine::kNFin);
+    if (!e->d_fin_mix_pre[k]) {
+        int rc;
+        if ((rc = dalloc(&e->d_fin_mix_pre[k], 2 * kChunk)) || (rc = dalloc(&e->d_fin_mix[k], 2 * kChunk)) ||
+            (rc = dalloc(&e->d_fin_pcm[k], 2 * kChunk)))
+            return rc;
+    }
+    OutSet o{};
+    o.mix_pre = e->d_fin_mix_pre[k]; o.mix = e->d_fin_mix[k]; o.pcm = e->d_fin_pcm[k];
+    { int rc = launch_mix(e, st, o, nullptr, 0, 0, nullptr, d_parts, n_parts, 1); if (rc) return rc; }
+    if (mix_pre) CU(cudaMemcpyAsync(mix_pre, o.mix_pre, sizeof(float) * 2 * kChunk, cudaMemcpyDeviceToHost, st));
+    if (mix) CU(cudaMemcpyAsync(mix, o.mix, sizeof(float) * 2 * kChunk, cudaMemcpyDeviceToHost, st));
+    if (pcm) CU(cudaMemcpyAsync(pcm, o.pcm, sizeof(int16_t) * 2 * kChunk, cudaMemcpyDeviceToHost, st));
     return SDRX_OK;
 }
 

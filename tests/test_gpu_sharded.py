@@ -34,3 +34,28 @@ def test_two_channel_shards_reproduce_the_unsharded_engine(force_generic):
         assert np.array_equal(m1[0], w.mix_pre) and np.array_equal(m1[1], w.mix) and np.array_equal(m1[2], w.pcm)
     for e in [whole, one] + parts:
         e.close()
+
+
+def test_channel_sharded_receiver_over_nccl():
+    """Row e2: the pipelined ShardedReceiver with the nccl backend on two GPUs -- NCCL broadcast (and the
+    all-gather ingest) of every block, NCCL gather of the partial mixes, mix finished on rank 0 -- against a single-GPU
+    engine on the same blocks.  Skips below two devices."""
+    import json
+    import os
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", "29571", os.path.join(here, "nccl_sharded_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("NCCL_SHARDED ")][-1]
+    res = json.loads(line[len("NCCL_SHARDED "):])
+    print(line)
+    for ingest in ("broadcast", "allgather"):
+        assert res[ingest]["squelch_equal"]
+        assert res[ingest]["worst_audio_rel_rms"] < 1e-4 and res[ingest]["worst_mix_rel_rms"] < 1e-4
+        assert res[ingest]["worst_pcm_lsb"] <= 2
