@@ -203,7 +203,7 @@ namespace {
 
 // The tensor map k_chan_agc reads a block's channel IQ through (demod.cuh).  The encoder lives in the driver library: it
 // is fetched through the runtime (cudaGetDriverEntryPoint), so nothing links against libcuda.
-int make_iq_map(CUtensorMap *map, float2 *ch_iq, long iq_stride, int C) {
+int make_map_2d(CUtensorMap *map, void *base, cuuint64_t inner, cuuint64_t rows, cuuint64_t pitch_bytes, cuuint32_t box_inner, cuuint32_t box_rows) {
     typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -215,11 +215,11 @@ int make_iq_map(CUtensorMap *map, float2 *ch_iq, long iq_stride, int C) {
         if (!fn || q != cudaDriverEntryPointSuccess) return fail(SDRX_ERR_CUDA, "cuTensorMapEncodeTiled is not available in this driver");
         encode = (encode_fn)fn;
     }
-    const cuuint64_t dims[2] = {(cuuint64_t)(2 * kChunk), (cuuint64_t)C};
-    const cuuint64_t strides[1] = {(cuuint64_t)iq_stride * sizeof(float2)};
-    const cuuint32_t box[2] = {(cuuint32_t)(2 * kRecurTile), (cuuint32_t)kAgcBoxRows};
+    const cuuint64_t dims[2] = {inner, rows};
+    const cuuint64_t strides[1] = {pitch_bytes};
+    const cuuint32_t box[2] = {box_inner, box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, ch_iq, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(SDRX_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
     return SDRX_OK;
@@ -488,7 +488,9 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if ((rc = dalloc(&o.ch_iq, (size_t)C * e->chiq_stride))) return rc;
         if (e->flags & SDRX_FLAG_NO_DEMOD) continue;
         if ((rc = dalloc(&o.audio, (size_t)e->Cpad * kChunk))) return rc;
-        if ((rc = make_iq_map(&o.iq_map, o.ch_iq, e->chiq_stride, C))) return rc;
+        if ((rc = make_map_2d(&o.iq_map, o.ch_iq, 2 * kChunk, (cuuint64_t)C, (cuuint64_t)e->chiq_stride * sizeof(float2), 2 * kRecurTile,
+                              kAgcBoxRows)))
+            return rc;
         if ((rc = dalloc(&o.snr, C))) return rc;
         if ((rc = dalloc(&o.mix_pre, 2 * kChunk))) return rc;
         if ((rc = dalloc(&o.mix, 2 * kChunk))) return rc;
