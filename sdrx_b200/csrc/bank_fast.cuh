@@ -46,8 +46,10 @@ constexpr int kFastThreads = kFastCh * kFastSegs;
 constexpr int kUnit = 125;         // raw samples per stage-3 output
 constexpr int kBody = 25;          // raw samples per stage-2 output
 constexpr int kXBody = 26;         // float2 per staged 25-sample body (+1: every body starts 16 B aligned)
-constexpr int kXSeg = 5 * kXBody;  // float2 per staged segment chunk; 1040 B puts the two segments of a warp
-                                   // 4 banks apart, so their 16 B broadcast reads never collide
+constexpr int kXRing = 3;          // staged bodies per segment: the one being computed and two in flight (a body takes a
+                                   // 16-warp SM ~1.5 us, an L2 round trip ~1 us)
+constexpr int kXSeg = kXRing * kXBody;   // float2 per segment's ring; 624 B puts the two segments of a warp 28 banks apart,
+                                   // so their 16 B broadcast reads never collide
 constexpr int kWrap = 24;          // table rows replicated past N so a 25-sample body never wraps
 constexpr int kFastMinSeg = 8;     // units per segment when sizing the grid: shorter ones mostly warm up
 constexpr int kFastMinSegPiece = 2;// ... but a small piece (a CTA range that straddles a group) still spreads over all warps
@@ -171,7 +173,7 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
             float2 *__restrict__ tails, int n_slots) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2 *tb = reinterpret_cast<float2 *>(smem_raw);                       // [(N + kWrap)][16]
-    float2 *xs = tb + (size_t)(N + kWrap) * kFastCh;                         // [2][kFastSegs][kXSeg]
+    float2 *xs = tb + (size_t)(N + kWrap) * kFastCh;                         // [kFastSegs][kXRing][kXBody]
 
     const int tid = threadIdx.x;
     const int ch = tid & (kFastCh - 1);
@@ -204,54 +206,82 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
         const int my_steps = have ? warm + (u1 - u0) : 0;
         const int nsteps = ((pc.u_begin == 0 && !fast_cut(pc)) ? kFastWarmStart : 1) + pc.seg_len;   // the longest segment's
 
-        // Staging: the 16 threads of a segment fetch that segment's next 125 samples (8 coalesced rows of
-        // 128 B) while the current chunk is computed.  F32 goes global->shared with cp.async; u8/s16 are
-        // loaded early into registers, converted and stored after the compute.
+        // Staging: the 16 threads of a segment fetch that segment's samples one 25-sample body at a time into a ring of
+        // kXRing bodies, two bodies ahead of the one being computed.  F32 goes global->shared with cp.async; u8/s16 are
+        // loaded early into registers, converted and stored after the compute.  (A whole double-buffered unit per segment
+        // used to sit here: 66 KB of the SM; the ring is 20 KB, and what it frees lets the last-stage kernel of the
+        // previous block run NEXT TO the bank instead of between two banks.)
+        // The hot loop is issue-bound, so the per-body bookkeeping is kept to running offsets: fo / co = byte offset of the
+        // ring slot the next fetch fills / the next body reads (0, 208, 416), gidx = raw index of this lane's first sample of
+        // the next body to fetch.
         const long my_raw0 = (long)hist + (long)kUnit * (u0 - warm) + ch;
         float2 *my_xs = xs + seg * kXSeg;
-        typename RawTraits<FMT>::vec pre[8];
-        auto fetch = [&](int t, int buf) {
-            if (t >= my_steps) return;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int i = ch + 16 * j;
-                if (i < kUnit) {
-                    const long idx = my_raw0 + (long)kUnit * t + 16 * j;
-                    if constexpr (FMT == SDRX_FMT_F32) {
-                        const unsigned dst = (unsigned)__cvta_generic_to_shared(my_xs + buf * kFastSegs * kXSeg + (i / kBody) * kXBody + i % kBody);
-                        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(reinterpret_cast<const float2 *>(raw) + idx) : "memory");
-                    } else if constexpr (FMT == SDRX_FMT_S16) {
-                        unsigned v;
-                        asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(v) : "l"(reinterpret_cast<const short2 *>(raw) + idx));
-                        pre[j] = make_short2((short)(v & 0xffff), (short)(v >> 16));
-                    } else {
-                        unsigned short v;
-                        asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(v) : "l"(reinterpret_cast<const uchar2 *>(raw) + idx));
-                        pre[j] = make_uchar2((unsigned char)(v & 0xff), (unsigned char)(v >> 8));
-                    }
+        const int my_bodies = 5 * my_steps;
+        constexpr unsigned kSlotBytes = kXBody * sizeof(float2);
+        const unsigned ring_s = (unsigned)__cvta_generic_to_shared(my_xs) + (unsigned)ch * (unsigned)sizeof(float2);
+        const bool second = ch < kBody - 16;               // lanes 0-8 also carry samples 16-24 of a body
+        unsigned fo = 0, co = 0;
+        long gidx = my_raw0;
+        int to_fetch = my_bodies;                          // bodies not yet fetched
+        typename RawTraits<FMT>::vec pre[2];
+        long pre_idx = 0;
+        unsigned pre_off = 0;
+        bool pre_valid = false;
+        auto fetch = [&]() {                               // the next body of this segment -> its ring slot
+            if (to_fetch > 0) {
+                if constexpr (FMT == SDRX_FMT_F32) {
+                    const float2 *g = reinterpret_cast<const float2 *>(raw) + gidx;
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ring_s + fo), "l"(g) : "memory");
+                    if (second) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ring_s + fo + 128u), "l"(g + 16) : "memory");
+                } else if constexpr (FMT == SDRX_FMT_S16) {
+                    unsigned v0, v1 = 0;
+                    asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(v0) : "l"(reinterpret_cast<const short2 *>(raw) + gidx));
+                    if (second) asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(v1) : "l"(reinterpret_cast<const short2 *>(raw) + gidx + 16));
+                    pre[0] = make_short2((short)(v0 & 0xffff), (short)(v0 >> 16));
+                    pre[1] = make_short2((short)(v1 & 0xffff), (short)(v1 >> 16));
+                } else {
+                    unsigned short v0, v1 = 0;
+                    asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(v0) : "l"(reinterpret_cast<const uchar2 *>(raw) + gidx));
+                    if (second) asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(v1) : "l"(reinterpret_cast<const uchar2 *>(raw) + gidx + 16));
+                    pre[0] = make_uchar2((unsigned char)(v0 & 0xff), (unsigned char)(v0 >> 8));
+                    pre[1] = make_uchar2((unsigned char)(v1 & 0xff), (unsigned char)(v1 >> 8));
                 }
             }
+            if constexpr (FMT == SDRX_FMT_F32) asm volatile("cp.async.commit_group;" ::: "memory");
+            else { pre_valid = to_fetch > 0; pre_idx = gidx; pre_off = fo; }
+            --to_fetch;
+            gidx += kBody;
+            fo = fo == 2 * kSlotBytes ? 0u : fo + kSlotBytes;
         };
-        auto land = [&](int t, int buf) {                  // make chunk t visible in xs[buf] (before the warp sync)
+        // make the body fetched last-but-one (F32: all but the youngest cp.async group; u8/s16: what the last fetch left in
+        // registers) visible in its slot, before the warp sync
+        auto land = [&]() {
             if constexpr (FMT == SDRX_FMT_F32) {
-                asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
             } else {
-                if (t >= my_steps) return;
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int i = ch + 16 * j;
-                    if (i < kUnit) {
-                        float2 v = convert_iq<FMT>(pre[j]);
-                        if (my_raw0 + (long)kUnit * t + 16 * j < valid_lo) v = make_float2(0.0f, 0.0f);   // before the stream
-                        my_xs[buf * kFastSegs * kXSeg + (i / kBody) * kXBody + i % kBody] = v;
-                    }
+                if (!pre_valid) return;
+                float2 *slot = reinterpret_cast<float2 *>(reinterpret_cast<unsigned char *>(my_xs) + pre_off) + ch;
+                float2 v = convert_iq<FMT>(pre[0]);
+                if (pre_idx < valid_lo) v = make_float2(0.0f, 0.0f);                // before the stream
+                slot[0] = v;
+                if (second) {
+                    float2 w2 = convert_iq<FMT>(pre[1]);
+                    if (pre_idx + 16 < valid_lo) w2 = make_float2(0.0f, 0.0f);
+                    slot[16] = w2;
                 }
             }
         };
-        __syncwarp();                                      // the warp is done with its previous piece's window
-        fetch(0, 0);
-        land(0, 0);
-        __syncwarp();                                      // a segment's window is private to its half warp: no CTA barrier
+        __syncwarp();                                      // the warp is done with its previous piece's ring
+        if constexpr (FMT == SDRX_FMT_F32) {
+            fetch();                                       // body 0
+            fetch();                                       // body 1
+            land();                                        // body 0 is in; body 1 may still be in flight
+        } else {
+            fetch();
+            land();                                        // body 0 is in
+            fetch();                                       // body 1 stays in registers until the end of body 0
+        }
+        __syncwarp();                                      // a segment's ring is private to its half warp: no CTA barrier
 
         // per-thread filter state
         u64 a[NCH][8], b[NCH][4], c3[NCH][5];
@@ -275,12 +305,15 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
         }
 
         for (int t = 0; t < nsteps; ++t) {
-            if (t + 1 < nsteps) fetch(t + 1, (t + 1) & 1);
-            if (t < my_steps) {
-                const float2 *xseg = my_xs + (t & 1) * kFastSegs * kXSeg;
 #pragma unroll 1
-                for (int p = 0; p < 5; ++p) {
-                    fast_body<NCH>(xseg + p * kXBody, tb + row * kFastCh + ch, taps, a, b);
+            for (int p = 0; p < 5; ++p) {
+                // F32: body jb + 2 goes into the slot body jb - 1 left (the warp sync at the end of jb - 1 has passed).
+                // u8/s16: body jb + 1 is in registers (fetched during jb - 1) and is stored at the end of jb.
+                if constexpr (FMT == SDRX_FMT_F32) fetch();
+                if (t < my_steps) {
+                    fast_body<NCH>(reinterpret_cast<const float2 *>(reinterpret_cast<const unsigned char *>(my_xs) + co),
+                                   tb + row * kFastCh + ch, taps, a, b);
+                    co = co == 2 * kSlotBytes ? 0u : co + kSlotBytes;
                     row += kBody;
                     if (row >= N) row -= N;
 #pragma unroll
@@ -298,6 +331,11 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
                         }
                     }
                 }
+                land();                                    // F32: at most the youngest group (body jb + 2) still in flight
+                if constexpr (FMT != SDRX_FMT_F32) fetch();
+                __syncwarp();
+            }
+            if (t < my_steps) {
                 if (t >= warm) {
                     float2 y[2];
                     if (NCH == 2) fast_unmix(c3[0][0], c3[NCH - 1][0], y[0], y[1]);
@@ -311,9 +349,8 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
                     c3[c][0] = c3[c][1]; c3[c][1] = c3[c][2]; c3[c][2] = c3[c][3]; c3[c][3] = c3[c][4]; c3[c][4] = 0ull;
                 }
             }
-            if (t + 1 < nsteps) land(t + 1, (t + 1) & 1);
-            __syncwarp();
         }
+        if constexpr (FMT == SDRX_FMT_F32) asm volatile("cp.async.wait_group 0;" ::: "memory");
         // what this segment contributes to the (up to four) outputs that follow it
         if (have && u1 < U) {
             float2 y[4][2];
@@ -355,7 +392,7 @@ static __global__ void k_fix_tails(float2 *__restrict__ s3, long s3_stride, int 
 }
 
 inline size_t fast_smem_bytes(int N) {
-    return sizeof(float2) * ((size_t)(N + kWrap) * kFastCh + 2 * kFastSegs * kXSeg);
+    return sizeof(float2) * ((size_t)(N + kWrap) * kFastCh + kFastSegs * kXSeg);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -380,8 +417,11 @@ struct FastBank {
     int period_units = 1;              // units after which the translator phase repeats: N / gcd(N, 125)
     FastTaps taps{};
     FastSchedule sched[2];             // small cache keyed by U (block length / 125)
-    float2 *d_tails = nullptr;         // [C][tails_slots][4] partial stage-3 sums across segment boundaries
-    int tails_slots = 0;               // capacity in slots per channel
+    float2 *d_tails = nullptr;         // two halves (ping-pong) of [C][tails_slots][4] partial stage-3 sums across segment
+                                       // boundaries: the last-stage kernel of block b reads one under the bank of block
+                                       // b+1, which writes the other
+    int tails_slots = 0;               // capacity of one half in slots per channel
+    float2 *tails_half(int h) const { return d_tails + (size_t)h * 4 * (size_t)tails_slots * C; }
     int C = 0;
     float2 *d_table_slot = nullptr;    // [N][groups*16] one column per slot (own copy only when paired)
     int tstride = 0;
@@ -618,7 +658,7 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
 template <int FMT>
 int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int valid_lo, int N, int pos0, unsigned n,
                 float2 *s3, long s3_stride, int s3_off, uint64_t *launches, cudaEvent_t ev0 = nullptr,
-                cudaEvent_t ev1 = nullptr, const FastSchedule **deferred_fix = nullptr) {
+                cudaEvent_t ev1 = nullptr, const FastSchedule **deferred_fix = nullptr, int tail_half = 0) {
     const int U = (int)(n / kUnit);
     FastSchedule *sc = nullptr;
     for (auto &s : fb.sched) if (s.U == U) sc = &s;
@@ -634,25 +674,25 @@ int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int va
         CU(cudaDeviceSynchronize());
         cudaFree(fb.d_tails);
         fb.d_tails = nullptr;
-        CU(cudaMalloc((void **)&fb.d_tails, sizeof(float2) * 4 * (size_t)sc->n_slots * fb.C));
+        CU(cudaMalloc((void **)&fb.d_tails, 2 * sizeof(float2) * 4 * (size_t)sc->n_slots * fb.C));
         fb.tails_slots = sc->n_slots;
     }
     if (ev0) CU(cudaEventRecord(ev0, st));
     if (fb.nch == 2)
         k_bank_fast<FMT, 2><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
             raw, hist, valid_lo, fb.d_table_slot, fb.tstride, fb.d_slot_chan, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U,
-            s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots);
+            s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots);
     else
         k_bank_fast<FMT, 1><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
             raw, hist, valid_lo, fb.d_table_slot, fb.tstride, fb.d_slot_chan, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U,
-            s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots);
+            s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots);
     if (ev1) CU(cudaEventRecord(ev1, st));
     ++*launches;
     if (deferred_fix) *deferred_fix = sc;           // the caller's next kernel applies the fix list itself
     else if (sc->n_fixes > 0) {
         const int per_group = kFastCh * fb.nch;
         const int threads = sc->n_fixes * per_group;
-        k_fix_tails<<<div_up(threads, 256), 256, 0, st>>>(s3, s3_stride, s3_off, fb.d_tails, fb.tails_slots, sc->d_fixes,
+        k_fix_tails<<<div_up(threads, 256), 256, 0, st>>>(s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots, sc->d_fixes,
                                                           sc->n_fixes, fb.d_slot_chan, per_group);
         ++*launches;
     }

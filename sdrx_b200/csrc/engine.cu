@@ -123,6 +123,14 @@ struct sdrx_engine {
     bool tail_fusable = false;            // last stage as one per-channel kernel fed by the bank's rows + tail fix-ups
     bool tail_fast = false;               // ... in its specialised form (67 taps, decimate by 5: k_chan_fir_fast)
     FirTaps<67> tail_taps{};
+    // The specialised last stage (k_chan_fir_fast) runs on the detector's stream, UNDER the next block's bank (the bank's
+    // staging ring leaves room for two of its CTAs per SM): the bank of block b+1 writes one stage-row / tails buffer while
+    // the last stage of block b reads the other and slides its delay line into the partner.
+    float2 *d_stage_alt = nullptr;        // ping-pong partner of d_stage_in[S-1]
+    cudaEvent_t ev_tail_done[2] = {nullptr, nullptr};   // last-stage kernel that read row / tails buffer `par` is complete
+    bool tail_pending[2] = {false, false};
+    int tail_par = 0;                     // row / tails buffer the next fused block uses
+    int last_tail_par = -1;               // buffer of the most recent side-stream last stage (-1: none outstanding)
     bool ftfir = false;                   // --ftfir: stage 0 is the frequency-translating FIR (msd.hpp:104-131)
     int ft_sets = 0;                      // coefficient sets, N / m[0] (msd.hpp:196)
     float2 *d_hk = nullptr;               // [ft_sets * H0][Cpad]
@@ -255,6 +263,9 @@ int reset_state(sdrx_engine *e) {
     CU(cudaStreamSynchronize(e->s_mix));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
+    e->tail_pending[0] = e->tail_pending[1] = false;
+    e->tail_par = 0; e->last_tail_par = -1;
+    if (e->d_stage_alt) CU(cudaMemsetAsync(e->d_stage_alt, 0, sizeof(float2) * (size_t)e->stage_stride[e->S - 1] * C, e->s_main));
     for (int b = 0; b < kNBuf; ++b) CU(cudaMemsetAsync(e->d_raw[b], 0, e->raw_buf_bytes, e->s_main));
     for (int s = 1; s < e->S; ++s)
         CU(cudaMemsetAsync(e->d_stage_in[s], 0, sizeof(float2) * (size_t)e->stage_stride[s] * C, e->s_main));
@@ -313,6 +324,8 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
         cudaFree(e->d_gate[b]); cudaFree(e->d_pwr_partial[b]);
     }
     if (e->ev_head_done) cudaEventDestroy(e->ev_head_done);
+    for (int b = 0; b < 2; ++b) if (e->ev_tail_done[b]) cudaEventDestroy(e->ev_tail_done[b]);
+    cudaFree(e->d_stage_alt);
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) cudaFree(e->d_stage_in[s]);
     cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps); cudaFree(e->d_hk);
     cudaFree(e->st.agc_gain); cudaFree(e->st.agc_power); cudaFree(e->st.lf_gain); cudaFree(e->st.lf_power);
@@ -380,6 +393,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->ev_head_done, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&e->ev_ext, cudaEventDisableTiming));
+    for (int b = 0; b < 2; ++b) CU(cudaEventCreateWithFlags(&e->ev_tail_done[b], cudaEventDisableTiming));
     for (int b = 0; b < kNOut; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_side_done[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_det_done[b], cudaEventDisableTiming));
@@ -583,6 +597,10 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
                 { int rc2 = raise_dyn_smem((const void *)k_chan_fir_fast<67, 5>, fir_fast_smem(67, 5, kChunk * 5)); if (rc2) return rc2; }
                 CU(cudaFuncSetAttribute(k_chan_fir_fast<67, 5>, cudaFuncAttributePreferredSharedMemoryCarveout,
                                         (int)cudaSharedmemCarveoutMaxShared));
+                if (e->use_fast) {
+                    int rc2 = dalloc(&e->d_stage_alt, (size_t)e->stage_stride[S - 1] * C);
+                    if (rc2) return rc2;
+                }
             }
         }
     }
@@ -740,20 +758,20 @@ int materialize_generic(sdrx_engine *e, int fmt, const uint8_t *buf, long end_id
 }
 
 template <int FMT>
-int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o, const FastSchedule **deferred) {
+int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o, const FastSchedule **deferred, int tail_half) {
     float2 *dst; long stride; int off;
     if (e->S > 3) { dst = e->d_stage_in[3]; stride = e->stage_stride[3]; off = e->H[3] - 1; }
     else          { dst = o.ch_iq;          stride = e->chiq_stride;     off = 0; }
     return fast_launch<FMT>(e->fast, e->s_main, raw, e->raw_hist, valid_lo, e->N, (int)e->trans_pos, n,
                             dst, stride, off, &e->launches,
-                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred);
+                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred, tail_half);
 }
 int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o,
-                         const FastSchedule **deferred = nullptr) {
+                         const FastSchedule **deferred = nullptr, int tail_half = 0) {
     switch (fmt) {
-        case SDRX_FMT_U8:  return launch_bank_fast<SDRX_FMT_U8>(e, raw, valid_lo, n, o, deferred);
-        case SDRX_FMT_S16: return launch_bank_fast<SDRX_FMT_S16>(e, raw, valid_lo, n, o, deferred);
-        default:           return launch_bank_fast<SDRX_FMT_F32>(e, raw, valid_lo, n, o, deferred);
+        case SDRX_FMT_U8:  return launch_bank_fast<SDRX_FMT_U8>(e, raw, valid_lo, n, o, deferred, tail_half);
+        case SDRX_FMT_S16: return launch_bank_fast<SDRX_FMT_S16>(e, raw, valid_lo, n, o, deferred, tail_half);
+        default:           return launch_bank_fast<SDRX_FMT_F32>(e, raw, valid_lo, n, o, deferred, tail_half);
     }
 }
 
@@ -786,24 +804,40 @@ int launch_mix(sdrx_engine *e, cudaStream_t st, OutSet &o, const float *pwr_part
     return SDRX_OK;
 }
 
-int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr) {
+int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, const TailFirArgs *fused = nullptr, int side_par = -1) {
     OutSet &o = e->out[idx];
     const TailSnap snap{o.sql, o.agc_gain, o.lf_gain};
-    if (fused) {
-        const size_t dyn = sizeof(float2) * (size_t)(fused->H - 1 + fused->n_in);
-        if (e->tail_fast && fused->n_in == kChunk * 5 && fused->first >= 0 && fused->first < 5)
-            k_chan_fir_fast<67, 5><<<e->C, kHeadThreads, fir_fast_smem(67, 5, fused->n_in), e->s_main>>>(*fused, e->tail_taps, o.ch_iq,
-                                                                                                        e->chiq_stride);
-        else
-            k_chan_head<kHeadFir><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
-                                                                          o.snr, e->d_gate[idx], snap);
+    if (fused && side_par >= 0) {
+        // the specialised last stage under the next block's bank: main (bank done) -> detector stream -> recurrences
+        CU(cudaEventRecord(e->ev_head_done, e->s_main));
+        CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
+        float2 *rows_next = (fused->stage_in == e->d_stage_alt) ? e->d_stage_in[e->S - 1] : e->d_stage_alt;
+        k_chan_fir_fast<67, 5><<<e->C, kHeadThreads, fir_fast_smem(67, 5, fused->n_in), e->s_side>>>(*fused, rows_next, e->tail_taps, o.ch_iq,
+                                                                                                    e->chiq_stride);
         ++e->launches;
+        CU(cudaGetLastError());
+        tl_mark(e, TL_TAIL, e->s_side);
+        CU(cudaEventRecord(e->ev_tail_done[side_par], e->s_side));
+        e->tail_pending[side_par] = true;
+        e->last_tail_par = side_par;
+        CU(cudaStreamWaitEvent(e->s_recur, e->ev_tail_done[side_par], 0));
+    } else {
+        if (fused) {
+            const size_t dyn = sizeof(float2) * (size_t)(fused->H - 1 + fused->n_in);
+            if (e->tail_fast && fused->n_in == kChunk * 5 && fused->first >= 0 && fused->first < 5)
+                k_chan_fir_fast<67, 5><<<e->C, kHeadThreads, fir_fast_smem(67, 5, fused->n_in), e->s_main>>>(*fused, fused->stage_in, e->tail_taps,
+                                                                                                            o.ch_iq, e->chiq_stride);
+            else
+                k_chan_head<kHeadFir><<<e->C, kHeadThreads, dyn, e->s_main>>>(*fused, o.ch_iq, e->chiq_stride, e->st, e->tb, e->d_sql_level,
+                                                                              o.snr, e->d_gate[idx], snap);
+            ++e->launches;
+        }
+        CU(cudaGetLastError());
+        tl_mark(e, TL_TAIL, e->s_main);
+        CU(cudaEventRecord(e->ev_head_done, e->s_main));
+        CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
+        CU(cudaStreamWaitEvent(e->s_recur, e->ev_head_done, 0));
     }
-    CU(cudaGetLastError());
-    tl_mark(e, TL_TAIL, e->s_main);
-    CU(cudaEventRecord(e->ev_head_done, e->s_main));
-    CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
-    CU(cudaStreamWaitEvent(e->s_recur, e->ev_head_done, 0));
     k_chan_head<kHeadDetect><<<e->C, kHeadThreads, 0, e->s_side>>>(TailFirArgs{}, o.ch_iq, e->chiq_stride, e->st, e->tb,
                                                                    e->d_sql_level, o.snr, e->d_gate[idx], snap);
     tl_mark(e, TL_DET, e->s_side);
@@ -972,15 +1006,35 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     const bool fast = e->use_fast && n > 0 && n % kUnit == 0 && phase_in[0] == 0 && phase_in[1] == 0 && phase_in[2] == 0;
     int rc;
     const bool fuse_tail = fast && demod && e->tail_fusable && e->S == e->fast.stages_fused + 1;
+    const int s_last = e->S - 1;
+    const bool side_tail = fuse_tail && e->tail_fast && e->d_stage_alt && n_out[s_last - 1] == kChunk * 5 && first[s_last] >= 0 &&
+                           first[s_last] < 5;
+    int side_par = -1;
     TailFirArgs tail{};
     if (fast) {
         const FastSchedule *sc = nullptr;
-        rc = launch_bank_fast_fmt(e, fmt, buf, valid_lo, n, o, fuse_tail ? &sc : nullptr);
+        int tail_half = 0;
+        if (side_tail) {
+            // row / tails buffer `par` was last read by the last-stage kernel two fused blocks ago
+            side_par = e->tail_par;
+            tail_half = side_par;
+            if (e->tail_pending[side_par]) CU(cudaStreamWaitEvent(e->s_main, e->ev_tail_done[side_par], 0));
+        } else if (e->last_tail_par >= 0) {
+            // this block works in place on the row buffer whose delay line the last side-stream last stage writes
+            CU(cudaStreamWaitEvent(e->s_main, e->ev_tail_done[e->last_tail_par], 0));
+        }
+        rc = launch_bank_fast_fmt(e, fmt, buf, valid_lo, n, o, fuse_tail ? &sc : nullptr, tail_half);
         if (!rc && fuse_tail) {
-            const int s = e->S - 1;
+            const int s = s_last;
             tail = TailFirArgs{e->d_stage_in[s], e->stage_stride[s], n_out[s - 1], e->H[s], e->m[s], first[s],
-                               e->d_taps + e->tap_off[s], sc->n_fixes > 0 ? e->fast.d_tails : nullptr, e->fast.tails_slots,
+                               e->d_taps + e->tap_off[s], sc->n_fixes > 0 ? e->fast.tails_half(tail_half) : nullptr, e->fast.tails_slots,
                                sc->d_fixes, sc->d_fix_range, e->fast.d_chan_group};
+            if (side_tail) {
+                // from here on "the" last-stage input buffer is the partner: its delay line is what this block's last-stage
+                // kernel writes, its new part what the next block's bank writes
+                std::swap(e->d_stage_in[s], e->d_stage_alt);
+                e->tail_par ^= 1;
+            }
         } else if (!rc) {
             rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 3, e->S);
         }
@@ -988,6 +1042,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         e->bank_timed = e->timing;
     } else {
         e->bank_timed = false;
+        if (e->last_tail_par >= 0) CU(cudaStreamWaitEvent(e->s_main, e->ev_tail_done[e->last_tail_par], 0));
         rc = materialize_generic(e, fmt, buf, e->raw_hist, e->total);
         if (!rc) rc = launch_bank_generic_fmt(e, fmt, buf, e->raw_hist, (int)e->trans_pos, valid_lo, first, n_out, o, 0, e->S);
     }
@@ -995,7 +1050,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     tl_mark(e, TL_BANK, e->s_main);
     if (e->timing) CU(cudaEventRecord(e->ev_t1, e->s_main));
 
-    if (demod) { rc = launch_demod(e, oc, n > 0, n, fuse_tail ? &tail : nullptr); if (rc) return rc; }
+    if (demod) { rc = launch_demod(e, oc, n > 0, n, fuse_tail ? &tail : nullptr, side_par); if (rc) return rc; }
     else if (e->timing) CU(cudaEventRecord(e->ev_t2, e->s_main));
     if (e->timing) e->timing_valid = true;
 
@@ -1430,6 +1485,8 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     CU(cudaStreamSynchronize(e->s_mix));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
+    e->tail_pending[0] = e->tail_pending[1] = false;
+    e->last_tail_par = -1;
     const uint8_t *p = (const uint8_t *)buf + sizeof(h);
     e->fmt = h.fmt; e->trans_pos = h.trans_pos; e->blocks = e->pushes = h.blocks; e->total = h.total; e->generic_stale = false;
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) e->phase[s] = h.phase[s];
