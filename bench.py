@@ -48,6 +48,8 @@ NOMINAL_FP32_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12
 
 def workload(name: str, sql_level=None):
     from sdrx_b200 import workloads as wl
+    if name == "config4":
+        return wl.config4_stream(0)
     if name == "config3":
         return wl.config3(960, sql_level)
     if name == "config2":
@@ -267,6 +269,8 @@ def run_ours(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    if args.workload == "config4":
+        return run_config4(args, world, rank, local, barrier, max_over_ranks)
     plan, carriers, desc = workload(args.workload)
     C_ = len(plan.offsets)
     L = plan.rate.block_len
@@ -490,6 +494,120 @@ def run_ours(args):
     return 0
 
 
+def run_config4(args, world, rank, local, barrier, max_over_ranks):
+    """BASELINE.json config 4: 64 independent 10 MS/s streams x 128 channels (every 7th 8.33 kHz designator), stream-sharded
+    64 / world per GPU.  All streams of a GPU go through ONE engine (sdrx_engine_config.n_streams): one launch sequence
+    per block.  `value`: blocks resident in HBM; `e2e`: every stream's block crosses the host link as s16 IQ (the Airspy
+    INT16_IQ wire format: 64 f32 streams would be 164 MB per step) and every stream's squelch / pcm / open audio rows
+    come back.  The synthetic data is 8 generated streams x 2 blocks; engine stream s replays generated stream s % 8
+    from block s // 8 on, so no two engine streams see the same sequence."""
+    import torch
+    import torch.distributed as dist
+    from sdrx_b200 import Engine, PinnedBuffer, _lib, workloads as wl
+    from sdrx_b200.source import quantize
+    lib = _lib.load()
+    total_streams = args.streams
+    NS = max(1, total_streams // world)
+    plan, _, desc = wl.config4_stream(0)
+    Cs, L = len(plan.offsets), plan.rate.block_len
+    G, NB = 8, 2
+    gen = []
+    for g in range(G):
+        _, car, _ = wl.config4_stream(rank * G + g)
+        gen.append(wl.synth_blocks(car, NB, 1 + rank * G + g))
+    def step_block(k, fmt_bytes):
+        rows = [gen[s_ % G][(k + s_ // G) % NB] for s_ in range(NS)]
+        if fmt_bytes == 8:
+            return np.stack(rows)
+        return np.stack([quantize(r, 1) for r in rows])
+    n_distinct = 2
+    eng = Engine(plan, device=local, n_streams=NS)
+    stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
+    blk = [step_block(k, 8) for k in range(n_distinct)]
+    nbytes = blk[0].nbytes
+    d = lib.sdrx_device_alloc(local, n_distinct * nbytes)
+    for k in range(n_distinct):
+        _lib.check(lib.sdrx_device_upload(local, C.c_void_p(d + k * nbytes), blk[k].ctypes.data_as(C.c_void_p), nbytes))
+    steps, warm = max(8, args.steps // 8), 3
+    for i in range(warm):
+        eng.push_device(d + (i % n_distinct) * nbytes, 2, L)
+    eng.sync()
+    barrier()
+    sampler = ClockSampler(local, None)
+    sampler.start()
+    l0 = eng.launch_count
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for i in range(steps):
+        eng.push_device(d + (i % n_distinct) * nbytes, 2, L)
+    eng.join()
+    ev1.record(stream)
+    eng.sync()
+    barrier()
+    clocks = sampler.stop()
+    launches = eng.launch_count - l0
+    ms = max_over_ranks(ev0.elapsed_time(ev1)) / steps
+    value = world * NS * Cs * L / (ms * 1e-3) / 1e6
+    eng.close()
+    lib.sdrx_device_free(local, C.c_void_p(d))
+    # ---- e2e: s16 wire format from pinned host memory, results into pinned host memory
+    eng = Engine(plan, device=local, n_streams=NS)
+    stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
+    hb = [step_block(k, 4) for k in range(n_distinct)]
+    pins = [PinnedBuffer(hb[0].nbytes) for _ in range(n_distinct)]
+    hv = []
+    for pb, a in zip(pins, hb):
+        v = pb.view(np.int16, a.size).reshape(a.shape)
+        v[:] = a
+        hv.append(v)
+    LAG = 2
+    want = ("audio_rows", "audio_chan", "n_audio", "sql_state", "snr", "pcm", "pwr_dbfs")
+    osets = [eng.make_output_buffers(pinned=True, want=want) for _ in range(LAG + 1)]
+    for i in range(3):
+        eng.push(hv[i % n_distinct])
+        eng.outputs_into(osets[i % (LAG + 1)][0])
+    barrier()
+    t0 = time.perf_counter()
+    ev0.record(stream)
+    rows = 0
+    for i in range(steps):
+        eng.push(hv[i % n_distinct])
+        eng.fetch_outputs(osets[i % (LAG + 1)][0])
+        if i >= LAG:
+            eng.wait_outputs(LAG)
+            rows += int(osets[(i - LAG) % (LAG + 1)][1]["n_audio"].sum())
+    for back in range(min(LAG, steps) - 1, -1, -1):
+        eng.wait_outputs(back)
+        rows += int(osets[(steps - 1 - back) % (LAG + 1)][1]["n_audio"].sum())
+    eng.join()
+    ev1.record(stream)
+    eng.sync()
+    wall = (time.perf_counter() - t0) * 1e3
+    barrier()
+    e_ms = max_over_ranks(max(ev0.elapsed_time(ev1), wall)) / steps
+    fixed = NS * (Cs * 5 + 1024 * 2 + 4 + 4)
+    e2e = {"value": world * NS * Cs * L / (e_ms * 1e-3) / 1e6, "unit": "channel-MS/s", "ms_per_step": e_ms,
+           "h2d_bytes_per_step": int(hb[0].nbytes), "d2h_bytes_per_step": int(round(fixed + rows / steps * 2052)),
+           "wire_format": "s16", "open_channels_per_step": rows / steps}
+    eng.close()
+    if rank == 0:
+        line = {"metric": "channel-MS/s", "value": value, "unit": "channel-MS/s", "n_gpus": world, "steps": steps, "warmup": warm,
+                "ms_per_step": ms, "higher_is_better": True, "scaling": "strong" if total_streams == args.streams else "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": f"config4: {total_streams} independent 10 MS/s streams x {Cs} channels (every 7th 8.33 kHz designator), "
+                                       f"{NS} streams per GPU in one engine", "streams": total_streams, "streams_per_gpu": NS,
+                           "channels_per_stream": Cs, "block_len": L, "sample_rate": RATE, "wire_format": "f32 (value) / s16 (e2e)",
+                           "parallelism": f"stream-sharded x{world}, no collective",
+                           "l2": f"{NS * L * 8 * n_distinct / 1e6:.0f} MB of raw blocks per GPU cycle through the engine (> 126 MB L2)"
+                                 if NS * L * 8 * n_distinct > 126e6 else "raw blocks fit L2 at this stream count"},
+                "realtime_channels": value / (RATE / 1e6), "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+                "roofline": None, "cpu_baseline": None}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
 def sharded_leg(args, plan, blocks, hviews, d_ring, blk_bytes, ring, world, rank, local, barrier, max_over_ranks):
     """One 10 MS/s stream, its channels split over the ranks (sdrx_b200/sharded.py): per block one NCCL collective in
     (broadcast from rank 0, or all-gather of per-rank slices), one small NCCL all-gather of the partial mixes out, the
@@ -609,7 +727,8 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="config3", choices=["config3", "config2"])
+    ap.add_argument("--workload", default="config3", choices=["config3", "config2", "config4"])
+    ap.add_argument("--streams", type=int, default=64, help="config4: independent streams over all GPUs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-worst", action="store_true", help="skip the worst_case leg (every squelch open)")
     ap.add_argument("--sustain", type=float, default=3.2, help="seconds of back-to-back blocks in the sustained leg (0: skip)")

@@ -94,6 +94,14 @@ typedef struct {
     const uint8_t *modulation;      /* [C] SDRX_MOD_AM / SDRX_MOD_FM: Channel::mod (sdrx.cpp:230, the
                                        NNN.NNN/SQL/AM|FM channel syntax :1351-1358, --modulation :1197);
                                        NULL -> AM.  FM is Demod::demod's discriminator (sdrx.cpp:181-194). */
+    int            n_streams;       /* 0 / 1: one IQ stream (one dongle, sdrx.cpp:1742-1745).  > 1: that many independent
+                                       streams, all listening to the SAME channel plan (the arrays above describe one
+                                       stream), processed in lockstep by ONE launch sequence per block (BASELINE.json config 4:
+                                       many small receivers on one GPU).  push_block then takes n_streams blocks back to
+                                       back ([n_streams][n_samples]); every per-channel result has n_streams * n_channels
+                                       entries, stream-major; mix_pre / mix / pcm / pwr_dbfs / n_audio have one entry (or 1024)
+                                       per stream, and audio_chan holds stream-local channel numbers, n_channels per stream.
+                                       Needs the specialised bank (10 MS/s chain), whole blocks, n_channels % 16 == 0.       */
 } sdrx_engine_config;
 
 /* Per-block outputs of boundary B.  Any pointer may be NULL. */
@@ -101,6 +109,7 @@ typedef struct {
     float   *audio;      /* [C][512]  the sample that is mixed per channel (0 where none)          */
     uint8_t *sql_state;  /* [C]       squelch state after this block's decision (sdrx.cpp:569-573)  */
     float   *snr;        /* [C]       sdrx.cpp:566                                                  */
+    /* (multi-stream engines: C = n_streams * n_channels below, [1024] and [1] are per stream, stream-major) */
     float   *mix_pre;    /* [1024]    stereo mix before FIR2 (sdrx.cpp:471-532)                     */
     float   *mix;        /* [1024]    after FIR2 (sdrx.cpp:646)                                     */
     int16_t *pcm;        /* [1024]    sdrx.cpp:649-656                                              */

@@ -32,6 +32,7 @@ class EngineConfig(C.Structure):
         ("passband_shape", c_float_p), ("ramp_up", c_float_p), ("ramp_down", c_float_p),
         ("flags", C.c_uint),
         ("modulation", c_u8_p),
+        ("n_streams", C.c_int),
     ]
 
 

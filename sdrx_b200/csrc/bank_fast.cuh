@@ -167,10 +167,10 @@ __device__ __forceinline__ unsigned long long bank_now() {
 //   slot_chan  [slots][NCH] channel index carried by the slot (-1: none); channel 1 of a slot is the conjugate partner
 template <int FMT, int NCH>
 static __global__ void __launch_bounds__(kFastThreads, 1)
-k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *__restrict__ table, int tstride,
+k_bank_fast(const void *__restrict__ raw_all, int hist, int valid_lo, const float2 *__restrict__ table, int tstride,
             const int *__restrict__ slot_chan, int N, int pos0, const FastTaps taps, const FastCta *__restrict__ ctas,
             const FastPiece *__restrict__ pieces, int U, float2 *__restrict__ s3, long s3_stride, int s3_off,
-            float2 *__restrict__ tails, int n_slots) {
+            float2 *__restrict__ tails, int n_slots, int gps, long stream_bytes) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2 *tb = reinterpret_cast<float2 *>(smem_raw);                       // [(N + kWrap)][16]
     float2 *xs = tb + (size_t)(N + kWrap) * kFastCh;                         // [kFastSegs][kXRing][kXBody]
@@ -187,10 +187,14 @@ k_bank_fast(const void *__restrict__ raw, int hist, int valid_lo, const float2 *
 
     for (int pi = me.piece_begin; pi < me.piece_end; ++pi) {
         const FastPiece pc = pieces[pi];
-        if (pc.group != cur_group) {
+        // multi-stream engine: slot group g belongs to stream g / gps and uses the translator tables of group g % gps (every
+        // stream listens to the same channel plan); the stream's raw block lies stream_bytes further
+        const int tgroup = pc.group % gps;
+        const void *raw = reinterpret_cast<const unsigned char *>(raw_all) + (long)(pc.group / gps) * stream_bytes;
+        if (tgroup != cur_group) {
             __syncthreads();                               // every warp is done with the previous group's table
-            cur_group = pc.group;
-            const float2 *src = table + pc.group * kFastCh;           // 16 B aligned: tstride and the group base are multiples of 16
+            cur_group = tgroup;
+            const float2 *src = table + tgroup * kFastCh;             // 16 B aligned: tstride and the group base are multiples of 16
             for (int idx = tid; idx < (N + kWrap) * (kFastCh / 2); idx += kFastThreads) {   // all copies in flight at once
                 const int row = idx >> 3, c8 = idx & 7;
                 const unsigned dst = (unsigned)__cvta_generic_to_shared(tb + row * kFastCh + 2 * c8);
@@ -412,7 +416,9 @@ struct FastBank {
     int stages_fused = 0;              // leading MSD stages the kernel covers (3)
     int n_sms = 148;
     int nch = 1;                       // channels per lane slot: 2 when conjugate pairing pays
-    int groups = 0;                    // ceil(slots / 16)
+    int groups = 0;                    // slot groups of 16 over ALL streams: n_streams * gps
+    int gps = 0;                       // groups per stream (ceil(slots of one stream / 16))
+    int n_streams = 1;
     int n_pairs = 0;
     int period_units = 1;              // units after which the translator phase repeats: N / gcd(N, 125)
     FastTaps taps{};
@@ -658,7 +664,7 @@ inline int fast_build_schedule(FastBank &fb, FastSchedule &out, int U) {
 template <int FMT>
 int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int valid_lo, int N, int pos0, unsigned n,
                 float2 *s3, long s3_stride, int s3_off, uint64_t *launches, cudaEvent_t ev0 = nullptr,
-                cudaEvent_t ev1 = nullptr, const FastSchedule **deferred_fix = nullptr, int tail_half = 0) {
+                cudaEvent_t ev1 = nullptr, const FastSchedule **deferred_fix = nullptr, int tail_half = 0, long stream_bytes = 0) {
     const int U = (int)(n / kUnit);
     FastSchedule *sc = nullptr;
     for (auto &s : fb.sched) if (s.U == U) sc = &s;
@@ -681,11 +687,11 @@ int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int va
     if (fb.nch == 2)
         k_bank_fast<FMT, 2><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
             raw, hist, valid_lo, fb.d_table_slot, fb.tstride, fb.d_slot_chan, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U,
-            s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots);
+            s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots, fb.gps, stream_bytes);
     else
         k_bank_fast<FMT, 1><<<sc->n_ctas, kFastThreads, fast_smem_bytes(N), st>>>(
             raw, hist, valid_lo, fb.d_table_slot, fb.tstride, fb.d_slot_chan, N, pos0, fb.taps, sc->d_ctas, sc->d_pieces, U,
-            s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots);
+            s3, s3_stride, s3_off, fb.tails_half(tail_half), fb.tails_slots, fb.gps, stream_bytes);
     if (ev1) CU(cudaEventRecord(ev1, st));
     ++*launches;
     if (deferred_fix) *deferred_fix = sc;           // the caller's next kernel applies the fix list itself
@@ -702,9 +708,11 @@ int fast_launch(FastBank &fb, cudaStream_t st, const void *raw, int hist, int va
 
 // tables: the caller's translator tables [C][N] float2 (host) or nullptr; has[c] == 0 -> no translator (the slot's
 // table column is (1, 0): multiplying by it is exact).
+// C channels PER STREAM; every stream carries the same channel plan (tables), channel c of stream s is engine channel s * C + c.
 inline int fast_init(FastBank &fb, int C, int N, const float *h1, const float *h2, const float *h3, const float *tables,
-                     const uint8_t *has, bool allow_pairs) {
-    fb.C = C;
+                     const uint8_t *has, bool allow_pairs, int n_streams = 1) {
+    fb.C = C * n_streams;
+    fb.n_streams = n_streams;
     fb.stages_fused = 3;
     {
         int a = N, b = kUnit;
@@ -738,15 +746,17 @@ inline int fast_init(FastBank &fb, int C, int N, const float *h1, const float *h
         }
     }
     const int slots = (int)slot_chan.size() / fb.nch;
-    fb.groups = (slots + kFastCh - 1) / kFastCh;
-    slot_chan.resize((size_t)fb.groups * kFastCh * fb.nch, -1);
-    fb.tstride = fb.groups * kFastCh;
+    fb.gps = (slots + kFastCh - 1) / kFastCh;
+    fb.groups = fb.gps * n_streams;
+    slot_chan.resize((size_t)fb.gps * kFastCh * fb.nch, -1);
+    fb.tstride = fb.gps * kFastCh;
     std::vector<float2> tslot((size_t)N * fb.tstride, make_float2(1.0f, 0.0f));
-    std::vector<int> chan_group((size_t)C, 0);
-    for (int s = 0; s < fb.groups * kFastCh; ++s) {
+    std::vector<int> chan_group((size_t)C * n_streams, 0);
+    for (int s = 0; s < fb.gps * kFastCh; ++s) {
         for (int q = 0; q < fb.nch; ++q) {
             const int c = slot_chan[(size_t)s * fb.nch + q];
-            if (c >= 0) chan_group[c] = s / kFastCh;
+            if (c >= 0)
+                for (int k = 0; k < n_streams; ++k) chan_group[(size_t)k * C + c] = k * fb.gps + s / kFastCh;
         }
         const int c0 = slot_chan[(size_t)s * fb.nch];
         if (c0 < 0 || !has_v[c0]) continue;
@@ -755,6 +765,12 @@ inline int fast_init(FastBank &fb, int C, int N, const float *h1, const float *h
     }
     CU(cudaMalloc((void **)&fb.d_table_slot, sizeof(float2) * tslot.size()));
     CU(cudaMemcpy(fb.d_table_slot, tslot.data(), sizeof(float2) * tslot.size(), cudaMemcpyHostToDevice));
+    {   // the slots of stream k carry the same channels, k * C further
+        const size_t one = slot_chan.size();
+        slot_chan.resize(one * n_streams);
+        for (int k = 1; k < n_streams; ++k)
+            for (size_t i = 0; i < one; ++i) slot_chan[k * one + i] = slot_chan[i] < 0 ? -1 : slot_chan[i] + k * C;
+    }
     CU(cudaMalloc((void **)&fb.d_slot_chan, sizeof(int) * slot_chan.size()));
     CU(cudaMemcpy(fb.d_slot_chan, slot_chan.data(), sizeof(int) * slot_chan.size(), cudaMemcpyHostToDevice));
     CU(cudaMalloc((void **)&fb.d_chan_group, sizeof(int) * chan_group.size()));

@@ -157,10 +157,15 @@ k_carry_hist(float2 *__restrict__ buf, long stride, int hist, int n_in) {
 //   CTAs [n_power, ..): the raw delay line between the two ping-pong input buffers:
 //                      dst[0..hist) = src[n_in .. n_in+hist), byte granular (src holds [hist | n_in]).
 // The power CTAs only read dst[hist..], the carry CTAs only write dst[0..hist): no hazard.
+// blockIdx.y = stream of a multi-stream engine (each stream's [hist | block] sits stream_bytes further; partials n_power apart).
 template <int FMT>
 static __global__ void __launch_bounds__(256)
-k_prep(const void *__restrict__ raw, int hist, int n, float *__restrict__ partial, int n_power,
-       uint8_t *__restrict__ dst, const uint8_t *__restrict__ src, long n_in_bytes, int hist_bytes) {
+k_prep(const void *__restrict__ raw_, int hist, int n, float *__restrict__ partial_, int n_power,
+       uint8_t *__restrict__ dst_, const uint8_t *__restrict__ src_, long n_in_bytes, int hist_bytes, long stream_bytes) {
+    const void *raw = reinterpret_cast<const uint8_t *>(raw_) + blockIdx.y * stream_bytes;
+    uint8_t *dst = dst_ + blockIdx.y * stream_bytes;
+    const uint8_t *src = src_ + blockIdx.y * stream_bytes;
+    float *partial = partial_ + blockIdx.y * n_power;
     if ((int)blockIdx.x >= n_power) {
         const int i = ((int)blockIdx.x - n_power) * 256 + threadIdx.x;
         if (i < hist_bytes) dst[i] = src[n_in_bytes + i];

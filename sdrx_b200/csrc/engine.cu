@@ -46,7 +46,9 @@ struct OutSet {                   // device-side results of one block
 struct sdrx_engine {
     int dev = 0;
     unsigned flags = 0;
-    int C = 0, Cpad = 0, N = 0, S = 0;
+    int C = 0, Cpad = 0, N = 0, S = 0;   // C: channels over all streams (NS * Cs)
+    int NS = 1, Cs = 0;                  // streams, channels per stream (sdrx_engine_config.n_streams / n_channels)
+    size_t raw_stream_bytes = 0;         // one stream's [raw_hist | block_len] slot of a raw buffer
     int m[SDRX_MAX_STAGES] = {0}, H[SDRX_MAX_STAGES] = {0}, tap_off[SDRX_MAX_STAGES] = {0};
     std::vector<float> taps;
     unsigned block_len = 0;
@@ -268,7 +270,7 @@ int reset_state(sdrx_engine *e) {
     if (e->d_stage_alt) CU(cudaMemsetAsync(e->d_stage_alt, 0, sizeof(float2) * (size_t)e->stage_stride[e->S - 1] * C, e->s_main));
     for (int b = 0; b < kNBuf; ++b) CU(cudaMemsetAsync(e->d_raw[b], 0, e->raw_buf_bytes, e->s_main));
     for (int s = 1; s < e->S; ++s)
-        CU(cudaMemsetAsync(e->d_stage_in[s], 0, sizeof(float2) * (size_t)e->stage_stride[s] * C, e->s_main));
+        if (e->d_stage_in[s]) CU(cudaMemsetAsync(e->d_stage_in[s], 0, sizeof(float2) * (size_t)e->stage_stride[s] * C, e->s_main));
     if (!(e->flags & SDRX_FLAG_NO_DEMOD)) {
         std::vector<float> ones(C, 1.0f), p0(C, e->agc_power0), p1(C, e->lf_power0);
         CU(cudaMemcpyAsync(e->st.agc_gain, ones.data(), C * 4, cudaMemcpyHostToDevice, e->s_main));
@@ -279,8 +281,8 @@ int reset_state(sdrx_engine *e) {
         CU(cudaMemsetAsync(e->st.sql_prev, 0, C, e->s_main));
         for (int b = 0; b < kNOut; ++b) CU(cudaMemsetAsync(e->out[b].mixed, 0, (size_t)e->Cpad, e->s_main));
         CU(cudaMemsetAsync(e->st.fm_prev, 0, C * sizeof(float2), e->s_main));
-        CU(cudaMemsetAsync(e->d_fir_hist, 0, sizeof(float) * 2 * (size_t)std::max(e->fir2_ntaps - 1, 1), e->s_main));
-        CU(cudaMemsetAsync(e->d_ticket, 0, 2 * sizeof(unsigned), e->s_main));
+        CU(cudaMemsetAsync(e->d_fir_hist, 0, sizeof(float) * e->NS * 2 * (size_t)std::max(e->fir2_ntaps - 1, 1), e->s_main));
+        CU(cudaMemsetAsync(e->d_ticket, 0, 2 * sizeof(unsigned) * e->NS, e->s_main));
         CU(cudaStreamSynchronize(e->s_main));   // the host vectors above die here
     }
     CU(cudaStreamSynchronize(e->s_main));
@@ -357,9 +359,11 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
 namespace {
 
 int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
-    const int C = cfg->n_channels, S = cfg->n_stages;
+    const int NS = std::max(cfg->n_streams, 1), Cs = cfg->n_channels;
+    const int C = NS * Cs, S = cfg->n_stages;            // per-channel arrays below: stream-major, the plan repeated per stream
     e->dev = cfg->device;
     e->flags = cfg->flags;
+    e->NS = NS; e->Cs = Cs;
     e->C = C;
     e->Cpad = (C + 31) / 32 * 32;
     e->N = std::max(cfg->translator_len, 1);
@@ -411,7 +415,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     CU(cudaEventCreate(&e->ev_b1));
 
     // raw ping-pong: [raw_hist | block_len] samples at the widest wire format
-    e->raw_buf_bytes = ((size_t)e->raw_hist + e->block_len) * 8 + 64;
+    e->raw_stream_bytes = (((size_t)e->raw_hist + e->block_len) * 8 + 255) / 256 * 256;
+    e->raw_buf_bytes = e->raw_stream_bytes * NS + 64;
     for (int b = 0; b < kNBuf; ++b) {
         int rc = dalloc(&e->d_raw[b], e->raw_buf_bytes);
         if (rc) return rc;
@@ -422,11 +427,12 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         std::vector<float2> t((size_t)e->N * e->Cpad, make_float2(1.0f, 0.0f));
         std::vector<uint8_t> has(e->Cpad, 0);
         for (int c = 0; c < C; ++c) {
+            const int cs = c % Cs;
             const bool on = cfg->translators && cfg->translator_len > 0 &&
-                            (cfg->has_translator ? cfg->has_translator[c] != 0 : true);
+                            (cfg->has_translator ? cfg->has_translator[cs] != 0 : true);
             has[c] = on ? 1 : 0;
             if (!on) continue;
-            const float *row = cfg->translators + (size_t)c * cfg->translator_len * 2;
+            const float *row = cfg->translators + (size_t)cs * cfg->translator_len * 2;
             for (int n = 0; n < e->N; ++n) t[(size_t)n * e->Cpad + c] = make_float2(row[2 * n], row[2 * n + 1]);
         }
         int rc = dalloc(&e->d_table_t, t.size());
@@ -444,8 +450,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         std::vector<float2> hk((size_t)e->ft_sets * H * e->Cpad, make_float2(0.0f, 0.0f));
         const float *h = e->taps.data() + e->tap_off[0];
         for (int c = 0; c < C; ++c) {
-            if (cfg->has_translator && !cfg->has_translator[c]) continue;
-            const float *row = cfg->translators + (size_t)c * N * 2;
+            if (cfg->has_translator && !cfg->has_translator[c % Cs]) continue;
+            const float *row = cfg->translators + (size_t)(c % Cs) * N * 2;
             size_t j = (size_t)((N - (H - 1) % N) % N);
             for (int set = 0; set < e->ft_sets; ++set) {
                 size_t k = j;
@@ -473,6 +479,9 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         for (int s = 1; s < S; ++s) {
             cap = cap / (size_t)e->m[s - 1] + 1;
             e->stage_stride[s] = (long)((e->H[s] - 1) + cap + 3) / 4 * 4;
+            // a multi-stream engine only ever runs the specialised bank: it needs the last stage's rows, not the
+            // generic kernels' stage-1 / stage-2 rows (4 GB at 64 x 128 channels)
+            if (NS > 1 && s < S - 1) continue;
             int rc = dalloc(&e->d_stage_in[s], (size_t)e->stage_stride[s] * C);
             if (rc) return rc;
         }
@@ -484,15 +493,15 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         for (int s = 0; s < S; ++s) cap = cap / (size_t)e->m[s] + 1;
         e->chiq_stride = (long)std::max<size_t>(kChunk, (cap + 3) / 4 * 4);
         for (int b = 0; b < kNOut; ++b) {
-            int rc = dalloc(&e->d_pwr_partial[b], kPwrPartials);
+            int rc = dalloc(&e->d_pwr_partial[b], (size_t)kPwrPartials * NS);
             if (rc) return rc;
             if ((rc = dalloc(&e->d_gate[b], C))) return rc;
         }
     }
     if (want_fast) {
-        int rc = fast_init(e->fast, C, e->N, e->taps.data() + e->tap_off[0], e->taps.data() + e->tap_off[1],
+        int rc = fast_init(e->fast, Cs, e->N, e->taps.data() + e->tap_off[0], e->taps.data() + e->tap_off[1],
                            e->taps.data() + e->tap_off[2], cfg->translator_len > 0 ? cfg->translators : nullptr,
-                           cfg->has_translator, !(cfg->flags & SDRX_FLAG_NO_PAIRING));
+                           cfg->has_translator, !(cfg->flags & SDRX_FLAG_NO_PAIRING), NS);
         if (rc) return rc;
         e->use_fast = true;
     }
@@ -506,16 +515,16 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
                               kAgcBoxRows)))
             return rc;
         if ((rc = dalloc(&o.snr, C))) return rc;
-        if ((rc = dalloc(&o.mix_pre, 2 * kChunk))) return rc;
-        if ((rc = dalloc(&o.mix, 2 * kChunk))) return rc;
-        if ((rc = dalloc(&o.pcm, 2 * kChunk))) return rc;
-        if ((rc = dalloc(&o.pwr, 1))) return rc;
+        if ((rc = dalloc(&o.mix_pre, (size_t)NS * 2 * kChunk))) return rc;
+        if ((rc = dalloc(&o.mix, (size_t)NS * 2 * kChunk))) return rc;
+        if ((rc = dalloc(&o.pcm, (size_t)NS * 2 * kChunk))) return rc;
+        if ((rc = dalloc(&o.pwr, NS))) return rc;
         if ((rc = dalloc(&o.sql, C))) return rc;
         if ((rc = dalloc(&o.agc_gain, C))) return rc;
         if ((rc = dalloc(&o.lf_gain, C))) return rc;
         if ((rc = dalloc(&o.mixed, (size_t)e->Cpad))) return rc;
         if ((rc = dalloc(&o.audio_idx, C))) return rc;
-        if ((rc = dalloc(&o.n_audio, 1))) return rc;
+        if ((rc = dalloc(&o.n_audio, NS))) return rc;
     }
 
     if (!(e->flags & SDRX_FLAG_NO_DEMOD)) {
@@ -539,8 +548,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         {
             std::vector<uint8_t> mod(C, SDRX_MOD_AM);
             for (int c = 0; c < C && cfg->modulation; ++c) {
-                if (cfg->modulation[c] > SDRX_MOD_FM) return fail(SDRX_ERR_ARG, "modulation must be SDRX_MOD_AM or SDRX_MOD_FM");
-                mod[c] = cfg->modulation[c];
+                if (cfg->modulation[c % Cs] > SDRX_MOD_FM) return fail(SDRX_ERR_ARG, "modulation must be SDRX_MOD_AM or SDRX_MOD_FM");
+                mod[c] = cfg->modulation[c % Cs];
             }
             if ((rc = upload(e->d_mod, mod.data(), C))) return rc;
             e->st.mod = e->d_mod;
@@ -560,8 +569,10 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         }
         std::vector<float> sql(C, 9.0f);
         std::vector<int> pos(C, 0);
-        if (cfg->sql_level) sql.assign(cfg->sql_level, cfg->sql_level + C);
-        if (cfg->pos) pos.assign(cfg->pos, cfg->pos + C);
+        for (int c = 0; c < C; ++c) {
+            if (cfg->sql_level) sql[c] = cfg->sql_level[c % Cs];
+            if (cfg->pos) pos[c] = cfg->pos[c % Cs];
+        }
         std::vector<float> c_adj(cfg->fir2_taps, cfg->fir2_taps + cfg->fir2_ntaps);
         if (cfg->lf_gain_db != 0.0f)            // FIR2::setGain, fir.hpp:160-170 (the ctor leaves c_adj_ = c_)
             for (auto &c : c_adj) c = c * std::pow(10.0f, cfg->lf_gain_db / 20.0f);
@@ -574,9 +585,9 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             (rc = dalloc(&e->d_sql_level, C)) || (rc = upload(e->d_sql_level, sql.data(), C)) ||
             (rc = dalloc(&e->d_pos, C)) || (rc = upload(e->d_pos, pos.data(), C)) ||
             (rc = dalloc(&e->d_c_adj, c_adj.size())) || (rc = upload(e->d_c_adj, c_adj.data(), c_adj.size())) ||
-            (rc = dalloc(&e->d_fir_hist, 2 * (size_t)std::max(cfg->fir2_ntaps - 1, 1))))
+            (rc = dalloc(&e->d_fir_hist, (size_t)NS * 2 * (size_t)std::max(cfg->fir2_ntaps - 1, 1))))
             return rc;
-        if ((rc = dalloc(&e->d_ticket, 2))) return rc;
+        if ((rc = dalloc(&e->d_ticket, 2 * (size_t)NS))) return rc;
         if ((rc = raise_dyn_smem((const void *)k_chan_agc, kAgcSmem)) || (rc = raise_dyn_smem((const void *)k_chan_lfagc, kLfSmem)))
             return rc;
         if ((rc = dalloc(&e->d_agc_iq, (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_env, (size_t)e->Cpad * kChunk)) ||
@@ -619,6 +630,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_S16>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
         CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_F32>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     }
+    if (NS > 1 && !e->use_fast)
+        return fail(SDRX_ERR_UNSUPPORTED, "a multi-stream engine needs the specialised channel bank (the 10 MS/s chain, translator tables, no --ftfir / FORCE_GENERIC)");
     return reset_state(e);
 }
 
@@ -631,6 +644,9 @@ extern "C" int sdrx_engine_create(const sdrx_engine_config *cfg, sdrx_engine **o
     if (cfg->n_stages < 1 || cfg->n_stages > SDRX_MAX_STAGES) return fail(SDRX_ERR_ARG, "n_stages out of range");
     if (!cfg->m || !cfg->ntaps || !cfg->taps) return fail(SDRX_ERR_ARG, "stage list missing");
     if (cfg->block_len < 1) return fail(SDRX_ERR_ARG, "block_len < 1");
+    if (cfg->n_streams < 0 || cfg->n_streams > 4096) return fail(SDRX_ERR_ARG, "n_streams out of range");
+    if (cfg->n_streams > 1 && cfg->n_channels % 16 != 0)
+        return fail(SDRX_ERR_UNSUPPORTED, "a multi-stream engine needs a multiple of 16 channels per stream");
     for (int s = 0; s < cfg->n_stages; ++s) {
         if (cfg->m[s] < 1) return fail(SDRX_ERR_ARG, "stage m < 1");
         // msd.hpp:169-170 asserts a non-empty, odd-length (folded FIR) coefficient vector
@@ -764,7 +780,7 @@ int launch_bank_fast(sdrx_engine *e, const uint8_t *raw, int valid_lo, unsigned 
     else          { dst = o.ch_iq;          stride = e->chiq_stride;     off = 0; }
     return fast_launch<FMT>(e->fast, e->s_main, raw, e->raw_hist, valid_lo, e->N, (int)e->trans_pos, n,
                             dst, stride, off, &e->launches,
-                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred, tail_half);
+                            e->timing ? e->ev_b0 : nullptr, e->timing ? e->ev_b1 : nullptr, deferred, tail_half, (long)e->raw_stream_bytes);
 }
 int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_lo, unsigned n, OutSet &o,
                          const FastSchedule **deferred = nullptr, int tail_half = 0) {
@@ -778,12 +794,13 @@ int launch_bank_fast_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int valid_
 // power partials of the new block (when boundary B will run) + the raw delay line, one launch
 int launch_prep(sdrx_engine *e, cudaStream_t st, int fmt, uint8_t *buf, const uint8_t *prev, unsigned n, bool power, int hist_bytes, long prev_bytes, float *partial) {
     const int np = power ? kPwrPartials : 0;
-    const int grid = np + div_up(hist_bytes, 256);
-    if (grid == 0) return SDRX_OK;
+    const dim3 grid(np + div_up(hist_bytes, 256), e->NS);
+    if (grid.x == 0) return SDRX_OK;
+    const long sb = (long)e->raw_stream_bytes;
     switch (fmt) {
-        case SDRX_FMT_U8:  k_prep<SDRX_FMT_U8><<<grid, 256, 0, st>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
-        case SDRX_FMT_S16: k_prep<SDRX_FMT_S16><<<grid, 256, 0, st>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
-        default:           k_prep<SDRX_FMT_F32><<<grid, 256, 0, st>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes); break;
+        case SDRX_FMT_U8:  k_prep<SDRX_FMT_U8><<<grid, 256, 0, st>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes, sb); break;
+        case SDRX_FMT_S16: k_prep<SDRX_FMT_S16><<<grid, 256, 0, st>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes, sb); break;
+        default:           k_prep<SDRX_FMT_F32><<<grid, 256, 0, st>>>(buf, e->raw_hist, (int)n, partial, np, buf, prev, prev_bytes, hist_bytes, sb); break;
     }
     ++e->launches;
     CU(cudaGetLastError());
@@ -796,9 +813,9 @@ int launch_prep(sdrx_engine *e, cudaStream_t st, int fmt, uint8_t *buf, const ui
 int launch_mix(sdrx_engine *e, cudaStream_t st, OutSet &o, const float *pwr_partial, int n_partial, unsigned n_samples,
                float *pwr, const float *ext_parts, int n_ext, int do_fir) {
     // sdrx_engine_finish_mix (ext_parts) may run next to a block's own mix kernel: it takes its own arrival counter
-    k_mix_fir2_pcm<<<kMixCtas, kMixThreads, mix_smem_bytes(e->Cpad, e->fir2_ntaps), st>>>(
-        o.audio, e->Cpad, o.mixed, e->d_pos, e->C, e->d_c_adj, e->fir2_ntaps, e->d_fir_hist, o.mix_pre, o.mix, o.pcm, pwr_partial,
-        n_partial, n_samples, pwr, ext_parts, n_ext, do_fir, o.audio_idx, o.n_audio, e->d_ticket + (ext_parts ? 1 : 0));
+    k_mix_fir2_pcm<<<dim3(kMixCtas, ext_parts ? 1 : e->NS), kMixThreads, mix_smem_bytes(e->Cpad, e->fir2_ntaps), st>>>(
+        o.audio, e->Cpad, o.mixed, e->d_pos, e->Cs, e->d_c_adj, e->fir2_ntaps, e->d_fir_hist, o.mix_pre, o.mix, o.pcm, pwr_partial,
+        n_partial, n_samples, pwr, ext_parts, n_ext, do_fir, o.audio_idx, o.n_audio, e->d_ticket + (ext_parts ? e->NS : 0));
     ++e->launches;
     CU(cudaGetLastError());
     return SDRX_OK;
@@ -888,7 +905,8 @@ int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out,
     auto d2h = [&](void *dst, const void *src, size_t bytes) -> cudaError_t {
         return dst ? cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, st) : cudaSuccess;
     };
-    const int xgrid = (int)std::min<size_t>(C, 128);
+    const dim3 xgrid((unsigned)std::min<int>(e->Cs, 128), (unsigned)e->NS);
+    const size_t NS = (size_t)e->NS;
     float *&rows_scratch = e->d_rows_scratch[blocking ? 0 : 1];
     auto scratch = [&]() -> int {
         if (!rows_scratch) CU(cudaMalloc((void **)&rows_scratch, sizeof(float) * C * kChunk));
@@ -896,17 +914,17 @@ int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out,
     };
     if (out->audio) {             // the dense [C][512] array: rows out of the sample-major device array, then one copy
         { int rc = scratch(); if (rc) return rc; }
-        k_export_audio<<<xgrid, 128, 0, st>>>(o.audio, e->Cpad, nullptr, nullptr, (int)C, rows_scratch, nullptr, nullptr);
+        k_export_audio<<<xgrid, 128, 0, st>>>(o.audio, e->Cpad, nullptr, nullptr, e->Cs, rows_scratch, nullptr, nullptr, e->Cs);
         ++e->launches;
         CU(cudaGetLastError());
         CU(d2h(out->audio, rows_scratch, C * kChunk * sizeof(float)));
     }
     CU(d2h(out->sql_state, o.sql, C));
     CU(d2h(out->snr, o.snr, C * sizeof(float)));
-    CU(d2h(out->mix_pre, o.mix_pre, 2 * kChunk * sizeof(float)));
-    CU(d2h(out->mix, o.mix, 2 * kChunk * sizeof(float)));
-    CU(d2h(out->pcm, o.pcm, 2 * kChunk * sizeof(int16_t)));
-    CU(d2h(out->pwr_dbfs, o.pwr, sizeof(float)));
+    CU(d2h(out->mix_pre, o.mix_pre, NS * 2 * kChunk * sizeof(float)));
+    CU(d2h(out->mix, o.mix, NS * 2 * kChunk * sizeof(float)));
+    CU(d2h(out->pcm, o.pcm, NS * 2 * kChunk * sizeof(int16_t)));
+    CU(d2h(out->pwr_dbfs, o.pwr, NS * sizeof(float)));
     CU(d2h(out->agc_gain, o.agc_gain, C * sizeof(float)));
     CU(d2h(out->lf_gain, o.lf_gain, C * sizeof(float)));
     if (out->audio_rows || out->audio_chan || out->n_audio) {
@@ -915,11 +933,12 @@ int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out,
         int *cnt = (int *)device_view(out->n_audio);
         const bool direct = (!out->audio_rows || rows) && (!out->audio_chan || chan) && (!out->n_audio || cnt);
         if (direct) {
-            k_export_audio<<<xgrid, 128, 0, st>>>(o.audio, e->Cpad, o.audio_idx, o.n_audio, 0, rows, chan, cnt);
+            k_export_audio<<<xgrid, 128, 0, st>>>(o.audio, e->Cpad, o.audio_idx, o.n_audio, 0, rows, chan, cnt, e->Cs);
             ++e->launches;
             CU(cudaGetLastError());
         } else {
             if (!blocking) return fail(SDRX_ERR_ARG, "fetch_outputs: audio_rows / audio_chan / n_audio must be pinned (sdrx_host_alloc)");
+            if (NS > 1) return fail(SDRX_ERR_UNSUPPORTED, "multi-stream engine: audio_rows / audio_chan / n_audio must be pinned (sdrx_host_alloc)");
             int n = 0;
             CU(cudaMemcpyAsync(&n, o.n_audio, sizeof(int), cudaMemcpyDeviceToHost, st));
             CU(cudaStreamSynchronize(st));
@@ -927,7 +946,7 @@ int copy_outputs(sdrx_engine *e, const OutSet &o, const sdrx_block_outputs *out,
             if (out->audio_chan && n > 0) CU(d2h(out->audio_chan, o.audio_idx, sizeof(int) * (size_t)n));
             if (out->audio_rows && n > 0) {
                 { int rc = scratch(); if (rc) return rc; }
-                k_export_audio<<<xgrid, 128, 0, st>>>(o.audio, e->Cpad, o.audio_idx, o.n_audio, 0, rows_scratch, nullptr, nullptr);
+                k_export_audio<<<xgrid, 128, 0, st>>>(o.audio, e->Cpad, o.audio_idx, o.n_audio, 0, rows_scratch, nullptr, nullptr, e->Cs);
                 ++e->launches;
                 CU(cudaGetLastError());
                 CU(d2h(out->audio_rows, rows_scratch, sizeof(float) * (size_t)n * kChunk));
@@ -967,8 +986,23 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     // buffer `cur` was last read by block b-1's raw carry (and before that by block b-2's kernels)
     CU(cudaStreamWaitEvent(e->s_copy, e->ev_raw_free[cur], 0));
     if (n > 0) {
+        // one stream: a plain copy; several: the caller's [n_streams][n] blocks land behind each stream's history prefix
+        const size_t row = (size_t)n * bps;
+        auto copy_in = [&](const void *from, cudaMemcpyKind k) -> cudaError_t {
+            if (e->NS == 1) return cudaMemcpyAsync(buf + hist_bytes, from, row, k, e->s_copy);
+            if (k != cudaMemcpyDeviceToDevice)
+                return cudaMemcpy2DAsync(buf + hist_bytes, e->raw_stream_bytes, from, row, row, (size_t)e->NS, k, e->s_copy);
+            // device to device: one plain copy per stream (a 2-D device copy of 64 rows of 2.56 MB fails on this driver with
+            // "unspecified launch failure"; 24 rows work)
+            for (int q = 0; q < e->NS; ++q) {
+                const cudaError_t r = cudaMemcpyAsync(buf + hist_bytes + (size_t)q * e->raw_stream_bytes, (const uint8_t *)from + (size_t)q * row,
+                                                      row, k, e->s_copy);
+                if (r != cudaSuccess) return r;
+            }
+            return cudaSuccess;
+        };
         if (kind == SRC_DEVICE) {
-            CU(cudaMemcpyAsync(buf + hist_bytes, src, (size_t)n * bps, cudaMemcpyDeviceToDevice, e->s_copy));
+            CU(copy_in(src, cudaMemcpyDeviceToDevice));
         } else {
             cudaPointerAttributes attr{};
             bool pinned = cudaPointerGetAttributes(&attr, src) == cudaSuccess &&
@@ -976,13 +1010,13 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
             cudaGetLastError();
             const void *from = src;
             if (!pinned) {
-                if (!e->h_stage[cur]) CU(cudaMallocHost((void **)&e->h_stage[cur], (size_t)e->block_len * 8));
+                if (!e->h_stage[cur]) CU(cudaMallocHost((void **)&e->h_stage[cur], (size_t)e->block_len * 8 * e->NS));
                 if (e->stage_busy[cur]) CU(cudaEventSynchronize(e->ev_copied[cur]));
-                memcpy(e->h_stage[cur], src, (size_t)n * bps);
+                memcpy(e->h_stage[cur], src, row * e->NS);
                 e->stage_busy[cur] = true;
                 from = e->h_stage[cur];
             }
-            CU(cudaMemcpyAsync(buf + hist_bytes, from, (size_t)n * bps, cudaMemcpyHostToDevice, e->s_copy));
+            CU(copy_in(from, cudaMemcpyHostToDevice));
         }
     }
     // ---- still on the copy stream, off the compute stream's critical path: the raw delay line (last raw_hist
@@ -1004,6 +1038,8 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
 
     const int valid_lo = (int)std::max<long>(0, (long)e->raw_hist - (long)std::min<uint64_t>(e->total, (uint64_t)e->raw_hist));
     const bool fast = e->use_fast && n > 0 && n % kUnit == 0 && phase_in[0] == 0 && phase_in[1] == 0 && phase_in[2] == 0;
+    if (e->NS > 1 && !(fast && demod))
+        return fail(SDRX_ERR_UNSUPPORTED, "multi-stream engine: blocks must be whole (block_len samples per stream)");
     int rc;
     const bool fuse_tail = fast && demod && e->tail_fusable && e->S == e->fast.stages_fused + 1;
     const int s_last = e->S - 1;
@@ -1196,6 +1232,7 @@ extern "C" int sdrx_engine_demod_block(sdrx_engine *e, const float *ch_iq, float
 
 extern "C" int sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_parts, float *mix_pre, float *mix, int16_t *pcm) {
     if (!e || !parts || n_parts < 1) return fail(SDRX_ERR_ARG, "null argument");
+    if (e->NS > 1) return fail(SDRX_ERR_UNSUPPORTED, "finish_mix: single-stream engines only");
     if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
     DevGuard g(e->dev);
     const size_t bytes = sizeof(float) * 2 * kChunk * (size_t)n_parts;
@@ -1417,6 +1454,7 @@ extern "C" size_t sdrx_engine_state_size(sdrx_engine *e) { return e ? state_byte
 
 extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     if (!e || !buf) return fail(SDRX_ERR_ARG, "null argument");
+    if (e->NS > 1) return fail(SDRX_ERR_UNSUPPORTED, "state save / load of a multi-stream engine is not implemented");
     if (size < state_bytes(e)) return fail(SDRX_ERR_ARG, "state buffer too small");
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));
@@ -1467,6 +1505,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
 
 extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t size) {
     if (!e || !buf) return fail(SDRX_ERR_ARG, "null argument");
+    if (e->NS > 1) return fail(SDRX_ERR_UNSUPPORTED, "state save / load of a multi-stream engine is not implemented");
     if (size < sizeof(StateHeader)) return fail(SDRX_ERR_ARG, "state buffer too small");
     StateHeader h;
     memcpy(&h, buf, sizeof(h));

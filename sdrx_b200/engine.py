@@ -78,17 +78,22 @@ class Engine:
     def __init__(self, plan: ChannelPlan, device: int = 0, use_lf_agc: bool = False, lf_gain_db: float = 0.0,
                  block_len: Optional[int] = None, force_generic: bool = False, demod: bool = True,
                  translators: Optional[np.ndarray] = None, partial_mix: bool = False, no_pairing: bool = False,
-                 use_ftfir: bool = False):
+                 use_ftfir: bool = False, n_streams: int = 1):
+        """``n_streams`` > 1: that many independent IQ streams, all listening to ``plan``, in one engine (one launch
+        sequence per block for all of them, BASELINE.json config 4): :meth:`push` then takes ``[n_streams][block]``
+        and every per-channel result has ``n_streams * len(plan.offsets)`` entries, stream-major."""
         self.lib = _lib.load()
         self.plan = plan
         self.device = device
-        self.C = len(plan.offsets)
+        self.NS = max(1, int(n_streams))
+        self.Cs = len(plan.offsets)
+        self.C = self.NS * self.Cs
         rc_ = plan.rate
         self.N = rc_.N
         self.block_len = int(block_len or rc_.block_len)
         t = tables()
         if translators is None:
-            tr = np.zeros((self.C, self.N), dtype=np.complex64)
+            tr = np.zeros((self.Cs, self.N), dtype=np.complex64)
             for c, off in enumerate(plan.offsets):
                 if off != 0:
                     tr[c] = make_translator(rc_.N, rc_.z, off)
@@ -108,7 +113,8 @@ class Engine:
         fp = lambda a: a.ctypes.data_as(_lib.c_float_p)   # noqa: E731
         cfg = _lib.EngineConfig()
         cfg.device = device
-        cfg.n_channels = self.C
+        cfg.n_channels = self.Cs
+        cfg.n_streams = self.NS
         if translators is None and not has.any():
             # every channel sits on the tuner frequency: the reference builds no translator at all (empty vector,
             # sdrx.cpp:1684-1690) -- sdrx's canonical single-channel run
@@ -144,7 +150,7 @@ class Engine:
         """Queue one block (host array; pinned arrays from :class:`PinnedBuffer` avoid the staging copy)."""
         raw = np.ascontiguousarray(raw)
         check(self.lib.sdrx_engine_push_block(self.h, raw.ctypes.data_as(C.c_void_p),
-                                              fmt_of(raw) if fmt is None else fmt, n_samples_of(raw)))
+                                              fmt_of(raw) if fmt is None else fmt, n_samples_of(raw) // self.NS))
         self._keep = raw      # a pinned source must stay alive until the copy has run
 
     def push_device(self, d_ptr: int, fmt: int, n_samples: int) -> None:
@@ -166,10 +172,10 @@ class Engine:
         audio = np.empty((C_, CHUNK), np.float32)
         sql = np.empty(C_, np.uint8)
         snr = np.empty(C_, np.float32)
-        mix_pre = np.empty(2 * CHUNK, np.float32)
-        mix = np.empty(2 * CHUNK, np.float32)
-        pcm = np.empty(2 * CHUNK, np.int16)
-        pwr = np.empty(1, np.float32)
+        mix_pre = np.empty(self.NS * 2 * CHUNK, np.float32)
+        mix = np.empty(self.NS * 2 * CHUNK, np.float32)
+        pcm = np.empty(self.NS * 2 * CHUNK, np.int16)
+        pwr = np.empty(self.NS, np.float32)
         ag = np.empty(C_, np.float32)
         lg = np.empty(C_, np.float32)
         o = _lib.BlockOutputs()
@@ -178,16 +184,17 @@ class Engine:
         o.mix_pre, o.mix, o.pcm, o.pwr_dbfs = fp(mix_pre), fp(mix), pcm.ctypes.data_as(_lib.c_i16_p), fp(pwr)
         o.agc_gain, o.lf_gain = fp(ag), fp(lg)
         check(self.lib.sdrx_engine_get_outputs(self.h, C.byref(o)))
-        return BlockOut(float(pwr[0]), self.channel_iq() if with_iq else None, audio, sql, snr, mix_pre, mix, pcm, ag, lg)
+        return BlockOut(float(pwr[0]) if self.NS == 1 else pwr, self.channel_iq() if with_iq else None, audio, sql, snr, mix_pre, mix,
+                        pcm, ag, lg)
 
     def make_output_buffers(self, pinned: bool = True, want: Sequence[str] = ("audio", "sql_state", "snr", "mix", "pcm", "pwr_dbfs")):
         """Reusable result buffers for :meth:`outputs_into` (pinned: D2H straight into them).  Returns
         ``(struct, arrays, nbytes)``; only the fields named in ``want`` are fetched."""
-        C_ = self.C
+        C_, NS = self.C, self.NS
         spec = {"audio": (np.float32, C_ * CHUNK), "sql_state": (np.uint8, C_), "snr": (np.float32, C_),
-                "mix_pre": (np.float32, 2 * CHUNK), "mix": (np.float32, 2 * CHUNK), "pcm": (np.int16, 2 * CHUNK),
-                "pwr_dbfs": (np.float32, 1), "agc_gain": (np.float32, C_), "lf_gain": (np.float32, C_),
-                "audio_rows": (np.float32, C_ * CHUNK), "audio_chan": (np.int32, C_), "n_audio": (np.int32, 1)}
+                "mix_pre": (np.float32, NS * 2 * CHUNK), "mix": (np.float32, NS * 2 * CHUNK), "pcm": (np.int16, NS * 2 * CHUNK),
+                "pwr_dbfs": (np.float32, NS), "agc_gain": (np.float32, C_), "lf_gain": (np.float32, C_),
+                "audio_rows": (np.float32, C_ * CHUNK), "audio_chan": (np.int32, C_), "n_audio": (np.int32, NS)}
         o = _lib.BlockOutputs()
         arrays, keep, total = {}, [], 0
         for name in want:
@@ -207,12 +214,16 @@ class Engine:
         return o, arrays, total
 
     @staticmethod
-    def dense_audio(arrays, n_channels: int) -> np.ndarray:
+    def dense_audio(arrays, n_channels: int, n_streams: int = 1) -> np.ndarray:
         """Expand the sparse audio of :meth:`make_output_buffers` (``audio_rows`` / ``audio_chan`` / ``n_audio``) into
-        the dense ``[C][512]`` array ``audio`` would have returned (closed channels are exact zeros)."""
-        n = int(arrays["n_audio"][0])
+        the dense ``[C][512]`` array ``audio`` would have returned (closed channels are exact zeros).  ``n_channels``
+        counts all streams; each stream's list and rows start ``n_channels / n_streams`` entries further."""
         out = np.zeros((n_channels, CHUNK), np.float32)
-        out[arrays["audio_chan"][:n]] = arrays["audio_rows"][:n * CHUNK].reshape(n, CHUNK)
+        per = n_channels // n_streams
+        rows = arrays["audio_rows"].reshape(n_channels, CHUNK)
+        for s in range(n_streams):
+            n = int(arrays["n_audio"][s])
+            out[s * per + arrays["audio_chan"][s * per:s * per + n]] = rows[s * per:s * per + n]
         return out
 
     def outputs_into(self, struct) -> None:

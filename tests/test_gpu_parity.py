@@ -320,6 +320,58 @@ def test_sparse_audio_equals_dense_audio():
     eng.close()
 
 
+def test_multi_stream_engine_matches_one_engine_per_stream():
+    """BASELINE.json config 4 in miniature: several independent 10 MS/s streams that listen to the same channel plan go
+    through ONE engine (sdrx_engine_config.n_streams: one launch sequence per block for all of them); every stream's
+    results must be what an engine of its own gives, and what the oracle gives."""
+    from sdrx_b200 import Engine, workloads as wl
+    NS, NB = 3, 5
+    plan, _, _ = wl.config4_stream(0, n_channels=32)
+    blocks = []
+    for s_ in range(NS):
+        _, car, _ = wl.config4_stream(s_, n_channels=32)
+        blocks.append(wl.synth_blocks(car, NB, 100 + s_, noise_sigma=0.002))
+    multi = Engine(plan, n_streams=NS)
+    assert multi.uses_fast_path
+    singles = [Engine(plan) for _ in range(NS)]
+    orx = ob.OracleRx(product_tables(10000000), plan.offsets)
+    Cs = len(plan.offsets)
+    sets = multi.make_output_buffers(pinned=True, want=("audio_rows", "audio_chan", "n_audio", "pcm"))
+    opened = 0
+    for b in range(NB):
+        raw = np.stack([blocks[s_][b] for s_ in range(NS)])
+        got = multi.process(raw)
+        multi.outputs_into(sets[0])
+        dense = Engine.dense_audio(sets[1], multi.C, NS)
+        assert np.array_equal(dense, got.audio), "sparse per-stream audio lists"
+        assert np.array_equal(sets[1]["pcm"], got.pcm)
+        for s_ in range(NS):
+            one = singles[s_].process(blocks[s_][b])
+            sl = slice(s_ * Cs, (s_ + 1) * Cs)
+            assert np.array_equal(got.sql[sl], one.sql), (b, s_)
+            assert np.array_equal(got.audio[sl] == 0.0, one.audio == 0.0)
+            for c in range(Cs):
+                assert rel_rms(got.ch_iq[sl][c], one.ch_iq[c]) < 3e-5, (b, s_, c)
+            assert rel_rms(got.mix[s_ * 1024:(s_ + 1) * 1024], one.mix) < AUDIO_TOL or not np.any(one.mix)
+            assert np.max(np.abs(got.pcm[s_ * 1024:(s_ + 1) * 1024].astype(np.int32) - one.pcm.astype(np.int32))) <= 2
+            assert abs(float(got.pwr_dbfs[s_]) - one.pwr_dbfs) < 1e-3
+            if s_ == 1:
+                w = orx.process(blocks[s_][b], sc.FMT_F32)
+                assert np.array_equal(got.sql[sl], w.sql)
+                for c in range(Cs):
+                    assert rel_rms(got.ch_iq[sl][c], w.ch_iq[c]) < AUDIO_TOL
+                    if np.any(w.audio[c] != 0.0):
+                        assert rel_rms(got.audio[sl][c], w.audio[c]) < AUDIO_TOL
+            opened += int(one.sql.sum())
+    assert opened > 0
+    with pytest.raises(Exception):
+        multi.push(np.zeros((NS, 1000), np.complex64))      # ragged blocks are a single-stream feature
+    for e_ in [multi] + singles:
+        e_.close()
+    with pytest.raises(Exception):
+        Engine(wl.config3(24)[0], n_streams=2)               # 24 channels per stream: not a multiple of 16
+
+
 def test_demod_block_between_pushes_leaves_the_channelizer_alone():
     """sdrx_engine_demod_block takes an output set but must not advance the raw ping-pong that
     push_block's carried history lives in."""
