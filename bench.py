@@ -512,9 +512,10 @@ def run_config4(args, world, rank, local, barrier, max_over_ranks):
     Cs, L = len(plan.offsets), plan.rate.block_len
     G, NB = 8, 2
     gen = []
+    srank = rank if args.seed_rank < 0 else args.seed_rank      # (debug) the data another rank would generate
     for g in range(G):
-        _, car, _ = wl.config4_stream(rank * G + g)
-        gen.append(wl.synth_blocks(car, NB, 1 + rank * G + g))
+        _, car, _ = wl.config4_stream(srank * G + g)
+        gen.append(wl.synth_blocks(car, NB, 1 + srank * G + g))
     def step_block(k, fmt_bytes):
         rows = [gen[s_ % G][(k + s_ // G) % NB] for s_ in range(NS)]
         if fmt_bytes == 8:
@@ -550,6 +551,8 @@ def run_config4(args, world, rank, local, barrier, max_over_ranks):
     value = world * NS * Cs * L / (ms * 1e-3) / 1e6
     eng.close()
     lib.sdrx_device_free(local, C.c_void_p(d))
+    if args.verbose:
+        sys.stderr.write(f"[rank {rank}] config4 value leg done: {ms * 1e3:.1f} us per step\n")
     # ---- e2e: s16 wire format from pinned host memory, results into pinned host memory
     eng = Engine(plan, device=local, n_streams=NS)
     stream = torch.cuda.ExternalStream(eng.stream, device=torch.device("cuda", local))
@@ -728,6 +731,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="config3", choices=["config3", "config2", "config4"])
+    ap.add_argument("--seed-rank", type=int, default=-1, help=argparse.SUPPRESS)
+    ap.add_argument("--verbose", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--streams", type=int, default=64, help="config4: independent streams over all GPUs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-worst", action="store_true", help="skip the worst_case leg (every squelch open)")

@@ -990,10 +990,8 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         const size_t row = (size_t)n * bps;
         auto copy_in = [&](const void *from, cudaMemcpyKind k) -> cudaError_t {
             if (e->NS == 1) return cudaMemcpyAsync(buf + hist_bytes, from, row, k, e->s_copy);
-            if (k != cudaMemcpyDeviceToDevice)
-                return cudaMemcpy2DAsync(buf + hist_bytes, e->raw_stream_bytes, from, row, row, (size_t)e->NS, k, e->s_copy);
-            // device to device: one plain copy per stream (a 2-D device copy of 64 rows of 2.56 MB fails on this driver with
-            // "unspecified launch failure"; 24 rows work)
+            // one plain copy per stream: a 2-D copy of 64 rows of 2.56 MB failed on this driver ("unspecified launch
+            // failure" device to device; 24 rows worked), so the 2-D form is not used for any direction
             for (int q = 0; q < e->NS; ++q) {
                 const cudaError_t r = cudaMemcpyAsync(buf + hist_bytes + (size_t)q * e->raw_stream_bytes, (const uint8_t *)from + (size_t)q * row,
                                                       row, k, e->s_copy);
