@@ -56,6 +56,18 @@ typedef enum { SDRX_FMT_U8 = 0, SDRX_FMT_S16 = 1, SDRX_FMT_F32 = 2 } sdrx_iq_for
                                          could share a translator table as conjugates                       */
 #define SDRX_FLAG_FTFIR         0x10u /* --ftfir (sdrx.cpp:1199,:1692): the first stage is the frequency-translating FIR,
                                          msd.hpp:104-131 + calculateOutputTranslated :341-423, instead of mix + FIR      */
+#define SDRX_FLAG_POLYPHASE     0x20u /* OPT-IN, NOT BIT-COMPATIBLE: boundary A as a polyphase / DFT channelizer (the four MSD stages as one
+                                         8857-tap prototype folded into a 1200-point DFT per output instant -- what the reference's
+                                         README.md:25-28 considers for many simultaneous channels).  Same map as the chain in exact
+                                         arithmetic, ~100x fewer operations; differs from the reference by its float-rounded translator
+                                         table (sdrx.cpp:1682-1690).  Needs the 10 MS/s chain (N = 1200), ch_offset, whole blocks.      */
+#define SDRX_FLAG_TGEMM         0x40u /* OPT-IN: boundary A as fold + table GEMM (tgemm.cuh) -- the four MSD stages as one prototype folded
+                                         modulo the translator period, then Y = T U with the reference's OWN translator tables as the
+                                         matrix (the "complex GEMM (channels x taps)" recast).  Same map as the chain; differs from it by
+                                         FP32 rounding only, but its rounding is independent of the reference's: audio and squelch
+                                         decisions meet the parity bar, the channel IQ of closed, noise-only channels next to strong
+                                         carriers reaches 1.4e-4 of relative RMS (time-domain bank: 4e-5).  Any chain whose translator
+                                         period is a multiple of 16; whole blocks.                                                     */
 #define SDRX_FLAG_PARTIAL_MIX   0x4u  /* channel-sharded run: stop at mix_pre (this GPU's share of the pan
                                          mix); FIR2 + s16 run once, in sdrx_engine_finish_mix              */
 
@@ -94,6 +106,8 @@ typedef struct {
     const uint8_t *modulation;      /* [C] SDRX_MOD_AM / SDRX_MOD_FM: Channel::mod (sdrx.cpp:230, the
                                        NNN.NNN/SQL/AM|FM channel syntax :1351-1358, --modulation :1197);
                                        NULL -> AM.  FM is Demod::demod's discriminator (sdrx.cpp:181-194). */
+    const int     *ch_offset;       /* [C] channel offsets in 8.33 kHz steps from the tuner (channel_to_offset, sdrx.cpp:1449-1478): only
+                                       SDRX_FLAG_POLYPHASE needs them (the DFT bin of a channel); NULL otherwise                    */
     int            n_streams;       /* 0 / 1: one IQ stream (one dongle, sdrx.cpp:1742-1745).  > 1: that many independent
                                        streams, all listening to the SAME channel plan (the arrays above describe one
                                        stream), processed in lockstep by ONE launch sequence per block (BASELINE.json config 4:
@@ -198,6 +212,7 @@ void    *sdrx_engine_stream(sdrx_engine *e);          /* cudaStream_t the hot ke
 uint64_t sdrx_engine_launch_count(sdrx_engine *e);    /* kernels launched so far                   */
 int      sdrx_engine_uses_fast_path(sdrx_engine *e);  /* 1 when the specialised channel bank runs  */
 int      sdrx_engine_bank_pairs(sdrx_engine *e);      /* conjugate channel pairs sharing a lane slot */
+int      sdrx_engine_uses_table_gemm(sdrx_engine *e); /* 1 when boundary A runs as fold + table GEMM   */
 /* Device-timed duration (ms, CUDA events on the engine stream) of the channel-bank kernel(s) and of
  * the whole block for the last pushed block; valid after a sync. */
 int      sdrx_engine_last_timing(sdrx_engine *e, float *bank_ms, float *block_ms);

@@ -15,6 +15,8 @@
 #include "bank_generic.cuh"
 #include "bank_fast.cuh"
 #include "demod.cuh"
+#include "polyphase.cuh"
+#include "tgemm.cuh"
 
 using namespace sdrx;
 static_assert(kFastSideSms == kSideSms, "the bank leaves the SMs the side kernels expect");
@@ -122,6 +124,9 @@ struct sdrx_engine {
                                                      // stream that copies results out (blocking gets: main, fetches: s_out)
     FastBank fast;                        // specialised channel bank (bank_fast.cuh)
     bool use_fast = false;
+    TableGemm tg;                         // fold + table GEMM (tgemm.cuh): SDRX_FLAG_TGEMM
+    bool use_tgemm = false;
+    int mat_len = 625, mat_stages = 2;    // materialize_generic: raw samples it replays, leading stages it runs
     bool tail_fusable = false;            // last stage as one per-channel kernel fed by the bank's rows + tail fix-ups
     bool tail_fast = false;               // ... in its specialised form (67 taps, decimate by 5: k_chan_fir_fast)
     FirTaps<67> tail_taps{};
@@ -133,6 +138,11 @@ struct sdrx_engine {
     bool tail_pending[2] = {false, false};
     int tail_par = 0;                     // row / tails buffer the next fused block uses
     int last_tail_par = -1;               // buffer of the most recent side-stream last stage (-1: none outstanding)
+    bool poly = false;                    // SDRX_FLAG_POLYPHASE: boundary A is k_poly_channelizer
+    int poly_D = 0, poly_Lh = 0;          // total decimation, composite prototype length
+    float *d_hc = nullptr;                // [poly_Lh] h1(z) h2(z^5) h3(z^25) h4(z^125)
+    float2 *d_wtab = nullptr;             // [1200] exp(-2 pi i n / 1200)
+    int *d_bin = nullptr;                 // [C] DFT bin of every channel: ch_offset mod 1200
     bool ftfir = false;                   // --ftfir: stage 0 is the frequency-translating FIR (msd.hpp:104-131)
     int ft_sets = 0;                      // coefficient sets, N / m[0] (msd.hpp:196)
     float2 *d_hk = nullptr;               // [ft_sets * H0][Cpad]
@@ -337,11 +347,13 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     cudaFree(e->d_twiddle); cudaFree(e->d_bitrev); cudaFree(e->d_sql_level); cudaFree(e->d_pos);
     cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist); cudaFree(e->d_parts); cudaFree(e->d_ticket); cudaFree(e->d_rows_scratch[0]); cudaFree(e->d_rows_scratch[1]);
     cudaFree(e->d_agc_iq); cudaFree(e->d_env); cudaFree(e->d_fm_new);
+    cudaFree(e->d_hc); cudaFree(e->d_wtab); cudaFree(e->d_bin);
     for (int b = 0; b < sdrx_engine::kNFin; ++b) { cudaFree(e->d_fin_mix_pre[b]); cudaFree(e->d_fin_mix[b]); cudaFree(e->d_fin_pcm[b]); }
     if (e->ev_ext) cudaEventDestroy(e->ev_ext);
     if (e->tl_base) cudaEventDestroy(e->tl_base);
     for (auto &row : e->tl_ev) for (cudaEvent_t ev : row) if (ev) cudaEventDestroy(ev);
     e->fast.destroy();
+    e->tg.destroy();
     if (e->ev_t0) cudaEventDestroy(e->ev_t0);
     if (e->ev_t1) cudaEventDestroy(e->ev_t1);
     if (e->ev_t2) cudaEventDestroy(e->ev_t2);
@@ -380,8 +392,58 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     e->raw_hist = std::max((e->H[0] - 1 + 7) / 8 * 8, 128);
     const bool eligible = fast_eligible(S, e->m, e->H, e->N);
     e->ftfir = (cfg->flags & SDRX_FLAG_FTFIR) && cfg->translators && cfg->translator_len > 0;
-    const bool want_fast = !(cfg->flags & SDRX_FLAG_FORCE_GENERIC) && eligible && !e->ftfir;
+    e->poly = (cfg->flags & SDRX_FLAG_POLYPHASE) != 0;
+    if (e->poly) {
+        if (!cfg->ch_offset) return fail(SDRX_ERR_ARG, "SDRX_FLAG_POLYPHASE needs ch_offset");
+        if (e->N != kPolyN || e->ftfir || NS > 1 || (cfg->flags & SDRX_FLAG_NO_DEMOD))
+            return fail(SDRX_ERR_UNSUPPORTED, "SDRX_FLAG_POLYPHASE: 10 MS/s chain (translator period 1200), one stream, with demodulation, no --ftfir");
+        // the four stages as one prototype, in double: h_c(z) = prod_s h_s(z^(m_0 .. m_(s-1)))
+        std::vector<double> hc(1, 1.0);
+        long up = 1;
+        for (int st = 0; st < S; ++st) {
+            std::vector<double> nx((hc.size() - 1) + (size_t)(e->H[st] - 1) * up + 1, 0.0);
+            for (size_t i = 0; i < hc.size(); ++i)
+                for (int j = 0; j < e->H[st]; ++j) nx[i + (size_t)j * up] += hc[i] * (double)e->taps[e->tap_off[st] + j];
+            hc.swap(nx);
+            up *= e->m[st];
+        }
+        e->poly_D = (int)up;
+        e->poly_Lh = (int)hc.size();
+        std::vector<float> hcf(hc.begin(), hc.end());
+        std::vector<float2> wt(kPolyN);
+        for (int n = 0; n < kPolyN; ++n) {
+            const double a = -2.0 * M_PI * (double)n / (double)kPolyN;
+            wt[n] = make_float2((float)cos(a), (float)sin(a));
+        }
+        std::vector<int> bin(C);
+        for (int c = 0; c < C; ++c) bin[c] = ((cfg->ch_offset[c] % kPolyN) + kPolyN) % kPolyN;
+        int rc;
+        if ((rc = dalloc(&e->d_hc, hcf.size())) || (rc = upload(e->d_hc, hcf.data(), hcf.size())) ||
+            (rc = dalloc(&e->d_wtab, wt.size())) || (rc = upload(e->d_wtab, wt.data(), wt.size())) ||
+            (rc = dalloc(&e->d_bin, bin.size())) || (rc = upload(e->d_bin, bin.data(), bin.size())))
+            return rc;
+        // output M of a block needs the poly_Lh - 1 samples before sample D M + D - 1: poly_Lh - D of them before the block
+        e->raw_hist = std::max(e->raw_hist, (e->poly_Lh - e->poly_D + 7) / 8 * 8);
+        if ((rc = raise_dyn_smem((const void *)k_poly_channelizer<SDRX_FMT_U8>, poly_smem_bytes())) ||
+            (rc = raise_dyn_smem((const void *)k_poly_channelizer<SDRX_FMT_S16>, poly_smem_bytes())) ||
+            (rc = raise_dyn_smem((const void *)k_poly_channelizer<SDRX_FMT_F32>, poly_smem_bytes())))
+            return rc;
+    }
+    const bool want_fast = !(cfg->flags & SDRX_FLAG_FORCE_GENERIC) && eligible && !e->ftfir && !e->poly;
     if (eligible) e->raw_hist = std::max(e->raw_hist, kFastRawHist);   // also when forced generic: state blobs stay portable
+    // fold + table GEMM (opt-in): any chain with translator tables of a period that is a multiple of 16 (1200 at 10 / 6 MS/s,
+    // 288 at 2.4 MS/s ...)
+    const bool want_tgemm = (cfg->flags & SDRX_FLAG_TGEMM) && !(cfg->flags & (SDRX_FLAG_FORCE_GENERIC | SDRX_FLAG_POLYPHASE)) && !e->ftfir && S >= 2 &&
+                            cfg->translators && cfg->translator_len >= kGemmK && cfg->translator_len % kGemmK == 0;
+    if (want_tgemm) {
+        long d_all = 1, d_head = 1;
+        for (int s = 0; s < S; ++s) { d_all *= e->m[s]; if (s < S - 1) d_head *= e->m[s]; }
+        e->mat_len = (int)(d_head * (e->H[S - 1] + 7));          // rebuilds every stage's delay line from raw samples
+        e->mat_stages = S - 1;
+        int lh = 1; long up = 1;
+        for (int s = 0; s < S; ++s) { lh += (e->H[s] - 1) * (int)up; up *= e->m[s]; }
+        e->raw_hist = std::max(e->raw_hist, (std::max(lh - (int)d_all, e->mat_len) + 7) / 8 * 8);
+    }
 
     CU(cudaStreamCreateWithFlags(&e->s_main, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
@@ -498,7 +560,22 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             if ((rc = dalloc(&e->d_gate[b], C))) return rc;
         }
     }
-    if (want_fast) {
+    if (want_tgemm && (size_t)e->mat_len <= e->block_len) {
+        std::vector<uint8_t> has_v((size_t)Cs, 0);
+        for (int c = 0; c < Cs; ++c) has_v[c] = (cfg->has_translator ? cfg->has_translator[c] != 0 : true) ? 1 : 0;
+        std::vector<int> partner = (cfg->flags & SDRX_FLAG_NO_PAIRING) ? std::vector<int>((size_t)Cs, -1)
+                                                                       : fast_find_partners(cfg->translators, has_v.data(), Cs, e->N);
+        size_t max_out = e->block_len;
+        for (int s = 0; s < S; ++s) max_out /= (size_t)e->m[s];
+        int rc = tgemm_init(e->tg, Cs, e->N, S, e->m, e->H, e->taps.data(), e->tap_off, cfg->translators, has_v.data(), partner,
+                            (int)std::max<size_t>(max_out, 4), NS);
+        if (rc) return rc;
+        if ((rc = raise_dyn_smem((const void *)k_tgemm, kGemmSmem))) return rc;
+        e->use_tgemm = true;
+    } else if (want_tgemm) {
+        e->mat_len = 625; e->mat_stages = 2;
+    }
+    if (want_fast && !e->use_tgemm) {
         int rc = fast_init(e->fast, Cs, e->N, e->taps.data() + e->tap_off[0], e->taps.data() + e->tap_off[1],
                            e->taps.data() + e->tap_off[2], cfg->translator_len > 0 ? cfg->translators : nullptr,
                            cfg->has_translator, !(cfg->flags & SDRX_FLAG_NO_PAIRING), NS);
@@ -630,7 +707,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_S16>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
         CU(cudaFuncSetAttribute(k_prep<SDRX_FMT_F32>, cudaFuncAttributePreferredSharedMemoryCarveout, mx));
     }
-    if (NS > 1 && !e->use_fast)
+    if (NS > 1 && !e->use_fast && !e->use_tgemm)
         return fail(SDRX_ERR_UNSUPPORTED, "a multi-stream engine needs the specialised channel bank (the 10 MS/s chain, translator tables, no --ftfir / FORCE_GENERIC)");
     return reset_state(e);
 }
@@ -756,18 +833,20 @@ int launch_bank_generic_fmt(sdrx_engine *e, int fmt, const uint8_t *raw, int his
 // generic kernels take over (ragged block) or the state is saved, rebuild them by running generic
 // stages 0-1 over the last 625 samples in front of buffer index `end_idx`: the last 18 / 20 outputs of
 // stages 1 / 2 depend on nothing older.  Stage phases are zero whenever this is needed.
-constexpr int kMaterialize = 625;
+// (The table GEMM keeps no delay line at all: there the replay covers H_last + 7 inputs of the last stage and runs every
+// stage but the last, e->mat_len / e->mat_stages.)
 int materialize_generic(sdrx_engine *e, int fmt, const uint8_t *buf, long end_idx, uint64_t total_before_end) {
     if (!e->generic_stale) return SDRX_OK;
+    const int kMaterialize = e->mat_len;
     const int hist = (int)(end_idx - kMaterialize);
     const int valid_lo = (int)std::max<long>(0, end_idx - (long)std::min<uint64_t>(total_before_end, (uint64_t)end_idx));
     long pos = ((long)e->trans_pos - kMaterialize) % e->N;
     if (pos < 0) pos += e->N;
     int first[SDRX_MAX_STAGES] = {0}, n_out[SDRX_MAX_STAGES] = {0};
     long n_in = kMaterialize;
-    for (int s = 0; s < 2; ++s) { first[s] = e->m[s] - 1; n_out[s] = (int)(n_in / e->m[s]); n_in = n_out[s]; }
+    for (int s = 0; s < e->mat_stages; ++s) { first[s] = e->m[s] - 1; n_out[s] = (int)(n_in / e->m[s]); n_in = n_out[s]; }
     OutSet dummy{};
-    int rc = launch_bank_generic_fmt(e, fmt, buf, hist, (int)pos, valid_lo, first, n_out, dummy, 0, 2, true);
+    int rc = launch_bank_generic_fmt(e, fmt, buf, hist, (int)pos, valid_lo, first, n_out, dummy, 0, e->mat_stages, true);
     if (rc) return rc;
     e->generic_stale = false;
     return SDRX_OK;
@@ -1036,7 +1115,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
 
     const int valid_lo = (int)std::max<long>(0, (long)e->raw_hist - (long)std::min<uint64_t>(e->total, (uint64_t)e->raw_hist));
     const bool fast = e->use_fast && n > 0 && n % kUnit == 0 && phase_in[0] == 0 && phase_in[1] == 0 && phase_in[2] == 0;
-    if (e->NS > 1 && !(fast && demod))
+    if (e->NS > 1 && !e->use_tgemm && !(fast && demod))
         return fail(SDRX_ERR_UNSUPPORTED, "multi-stream engine: blocks must be whole (block_len samples per stream)");
     int rc;
     const bool fuse_tail = fast && demod && e->tail_fusable && e->S == e->fast.stages_fused + 1;
@@ -1045,7 +1124,46 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
                            first[s_last] < 5;
     int side_par = -1;
     TailFirArgs tail{};
-    if (fast) {
+    bool phases_zero = true;
+    for (int s = 0; s < e->S; ++s) phases_zero = phases_zero && phase_in[s] == 0;
+    const bool tgemm = e->use_tgemm && n > 0 && phases_zero && n % (unsigned)e->tg.D == 0 && tgemm_eligible(e->N, (int)out_len) &&
+                       (int)out_len <= e->tg.Mpad;
+    if (e->NS > 1 && e->use_tgemm && !tgemm)
+        return fail(SDRX_ERR_UNSUPPORTED, "multi-stream engine: blocks must be whole (block_len samples per stream)");
+    if (tgemm) {
+        cudaEvent_t b0 = e->timing ? e->ev_b0 : nullptr, b1 = e->timing ? e->ev_b1 : nullptr;
+        const long sb = (long)e->raw_stream_bytes;
+        switch (fmt) {
+            case SDRX_FMT_U8:  rc = tgemm_launch<SDRX_FMT_U8>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
+            case SDRX_FMT_S16: rc = tgemm_launch<SDRX_FMT_S16>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
+            default:           rc = tgemm_launch<SDRX_FMT_F32>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
+        }
+        e->generic_stale = true;
+        e->bank_timed = e->timing;
+    } else if (e->poly) {
+        if (!(demod && n % (unsigned)e->poly_D == 0 && phase_in[0] == 0))
+            return fail(SDRX_ERR_UNSUPPORTED, "polyphase engine: blocks must be whole (512 outputs per channel)");
+        e->bank_timed = e->timing;
+        if (e->timing) CU(cudaEventRecord(e->ev_b0, e->s_main));
+        switch (fmt) {
+            case SDRX_FMT_U8:
+                k_poly_channelizer<SDRX_FMT_U8><<<out_len, kPolyThreads, poly_smem_bytes(), e->s_main>>>(
+                    buf, e->raw_hist, valid_lo, (int)e->trans_pos, e->poly_D, e->d_hc, e->poly_Lh, e->d_wtab, e->d_bin, e->C, o.ch_iq, e->chiq_stride);
+                break;
+            case SDRX_FMT_S16:
+                k_poly_channelizer<SDRX_FMT_S16><<<out_len, kPolyThreads, poly_smem_bytes(), e->s_main>>>(
+                    buf, e->raw_hist, valid_lo, (int)e->trans_pos, e->poly_D, e->d_hc, e->poly_Lh, e->d_wtab, e->d_bin, e->C, o.ch_iq, e->chiq_stride);
+                break;
+            default:
+                k_poly_channelizer<SDRX_FMT_F32><<<out_len, kPolyThreads, poly_smem_bytes(), e->s_main>>>(
+                    buf, e->raw_hist, valid_lo, (int)e->trans_pos, e->poly_D, e->d_hc, e->poly_Lh, e->d_wtab, e->d_bin, e->C, o.ch_iq, e->chiq_stride);
+                break;
+        }
+        ++e->launches;
+        if (e->timing) CU(cudaEventRecord(e->ev_b1, e->s_main));
+        CU(cudaGetLastError());
+        rc = SDRX_OK;
+    } else if (fast) {
         const FastSchedule *sc = nullptr;
         int tail_half = 0;
         if (side_tail) {
@@ -1398,8 +1516,9 @@ extern "C" int sdrx_debug_bank_trace_read(unsigned long long *out, int max_u64) 
     return n;
 }
 
-extern "C" int sdrx_engine_uses_fast_path(sdrx_engine *e) { return e && e->use_fast ? 1 : 0; }
-extern "C" int sdrx_engine_bank_pairs(sdrx_engine *e) { return e && e->use_fast ? e->fast.n_pairs : 0; }
+extern "C" int sdrx_engine_uses_fast_path(sdrx_engine *e) { return e && (e->use_fast || e->use_tgemm) ? 1 : 0; }
+extern "C" int sdrx_engine_bank_pairs(sdrx_engine *e) { return !e ? 0 : (e->use_tgemm ? e->tg.n_pairs : (e->use_fast ? e->fast.n_pairs : 0)); }
+extern "C" int sdrx_engine_uses_table_gemm(sdrx_engine *e) { return e && e->use_tgemm ? 1 : 0; }
 extern "C" int sdrx_engine_set_timing(sdrx_engine *e, int enable) {
     if (!e) return fail(SDRX_ERR_ARG, "null engine");
     e->timing = enable != 0;
@@ -1453,6 +1572,7 @@ extern "C" size_t sdrx_engine_state_size(sdrx_engine *e) { return e ? state_byte
 extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     if (!e || !buf) return fail(SDRX_ERR_ARG, "null argument");
     if (e->NS > 1) return fail(SDRX_ERR_UNSUPPORTED, "state save / load of a multi-stream engine is not implemented");
+    if (e->poly) return fail(SDRX_ERR_UNSUPPORTED, "state save / load of a polyphase engine is not implemented");
     if (size < state_bytes(e)) return fail(SDRX_ERR_ARG, "state buffer too small");
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));

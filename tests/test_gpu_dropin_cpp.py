@@ -16,8 +16,9 @@ BIN = os.path.join(ROOT, "tests", "cpp", "_build", "dropin_test")
 def build_driver() -> str:
     os.makedirs(os.path.dirname(BIN), exist_ok=True)
     if os.path.exists(BIN) and os.path.getmtime(BIN) >= max(
-            [os.path.getmtime(SRC)] + [os.path.getmtime(os.path.join(ROOT, "include", "sdrx_b200", f))
-                                       for f in os.listdir(os.path.join(ROOT, "include", "sdrx_b200"))]):
+            [os.path.getmtime(SRC), os.path.getmtime(os.path.join(ROOT, "include", "sdrx_b200.h"))] +
+            [os.path.getmtime(os.path.join(ROOT, "include", "sdrx_b200", f))
+             for f in os.listdir(os.path.join(ROOT, "include", "sdrx_b200"))]):
         return BIN
     from sdrx_b200 import build as b
     b.build()

@@ -38,8 +38,17 @@ def _assert_exact(got, want):
         assert abs(x.pwr_dbfs - y.pwr_dbfs) < 2e-2, f"block {i} power {x.pwr_dbfs} vs {y.pwr_dbfs}"   # display value; tree sum vs the reference's sequential float sum
 
 
-def _assert_close(got, want, lvl):
-    """The 1e-4 bar of the specialised path: decisions exact, signals within relative RMS."""
+IQ_TOL_CLOSED_TGEMM = 5e-4   # table GEMM, channel IQ of channels whose squelch is closed (nothing audible): see _assert_close
+
+
+def _assert_close(got, want, lvl, table_gemm=False):
+    """The 1e-4 bar of the specialised path: decisions exact, signals within relative RMS.
+
+    table_gemm: the fold + table GEMM rounds independently of the reference (the time-domain bank shares the reference's
+    first product x * T[p] bit for bit), so on closed, noise-only channels next to strong carriers -- where the reference's
+    own FP32 result is only good to a few 1e-5 -- its channel IQ differs by up to 1.4e-4.  What north_star bounds, the audio
+    (1e-4) and the squelch decisions (bit-exact), is held as for the bank; the IQ of channels that are open in any block of
+    the run is held to 1e-4 too, the IQ of channels that stay closed to IQ_TOL_CLOSED_TGEMM."""
     sql_g = np.stack([o.sql for o in got])
     sql_w = np.stack([o.sql for o in want])
     margin = min(squelch_margin(o.snr, lvl) for o in want)
@@ -51,9 +60,11 @@ def _assert_close(got, want, lvl):
     assert iq_g.shape == iq_w.shape
     assert rel_rms(iq_g, iq_w) < AUDIO_TOL, f"channel IQ rel rms {rel_rms(iq_g, iq_w):.3e}"
     # per channel, so that a weak channel cannot hide behind a strong one
+    ever_open = sql_w.any(axis=0)
     for c in range(iq_w.shape[1]):
         e = rel_rms(iq_g[:, c], iq_w[:, c])
-        assert e < AUDIO_TOL, f"channel {c} IQ rel rms {e:.3e}"
+        bar = AUDIO_TOL if (not table_gemm or ever_open[c]) else IQ_TOL_CLOSED_TGEMM
+        assert e < bar, f"channel {c} IQ rel rms {e:.3e} (bar {bar:g})"
     au_g = np.stack([o.audio for o in got])
     au_w = np.stack([o.audio for o in want])
     assert np.array_equal(au_g == 0.0, au_w == 0.0), "audio gating (which samples are mixed) differs"
@@ -83,13 +94,16 @@ def test_generic_engine_is_bit_exact_with_oracle(scn):
     _assert_exact(got, run_cpu(scn, "oracle", blocks))
 
 
+@pytest.mark.parametrize("table_gemm", [False, True], ids=["bank", "table_gemm"])
 @pytest.mark.parametrize("scn", [sc.config2(n_blocks=8), sc.config2(sc.FMT_S16, 4), sc.config2(sc.FMT_U8, 4),
-                                 sc.centre_channel()] + sc.config2_variants(), ids=lambda s: s.name)
-def test_default_engine_meets_the_parity_bar(scn):
+                                 sc.centre_channel(), sc.config1()] + sc.config2_variants(), ids=lambda s: s.name)
+def test_default_engine_meets_the_parity_bar(scn, table_gemm):
+    """Boundary A through the time-domain channel bank (the default) and through the fold + table GEMM (SDRX_FLAG_TGEMM,
+    tgemm.cuh; also what a 2.4 MS/s chain gets when asked for it): squelch decisions bit-exact, audio within 1e-4."""
     blocks = _blocks(scn)
-    got, fast = run_engine(scn, blocks=blocks)
+    got, fast = run_engine(scn, blocks=blocks, table_gemm=table_gemm)
     lvl = np.asarray(scn.sql_levels if scn.sql_levels is not None else [9.0] * len(scn.offsets))
-    _assert_close(got, run_cpu(scn, "oracle", blocks), lvl)
+    _assert_close(got, run_cpu(scn, "oracle", blocks), lvl, table_gemm=table_gemm)
 
 def _wrap(d):
     return (d + np.pi) % (2 * np.pi) - np.pi
@@ -180,21 +194,23 @@ def test_engine_reproduces_reference_golden_vectors(name, scn):
         assert rel_rms(got2[b].mix, z["mix"][j]) < AUDIO_TOL or not np.any(z["mix"][j])
 
 
+@pytest.mark.parametrize("bank", [True, False], ids=["bank", "table_gemm"])
 @pytest.mark.parametrize("fmt", [sc.FMT_F32, sc.FMT_S16, sc.FMT_U8], ids=["f32", "s16", "u8"])
-def test_conjugate_paired_bank_meets_the_parity_bar(fmt):
-    """+-offset channels share a lane slot (NCH = 2 kernel); the same scenario with pairing disabled must agree."""
+def test_conjugate_paired_bank_meets_the_parity_bar(fmt, bank):
+    """+-offset channels share a slot (NCH = 2 bank kernel / one row of the table GEMM); the same scenario with pairing
+    disabled must agree."""
     from sdrx_b200 import Engine
     scn = sc.paired_channels(fmt)
     blocks = _blocks(scn)
     want = run_cpu(scn, "oracle", blocks)
-    eng = Engine(scn.plan())
-    assert eng.uses_fast_path and eng.bank_pairs == 4
+    eng = Engine(scn.plan(), table_gemm=not bank)
+    assert eng.uses_fast_path and eng.bank_pairs == 4 and eng.uses_table_gemm == (not bank)
     eng.close()
-    got, _ = run_engine(scn, blocks=blocks)
+    got, _ = run_engine(scn, blocks=blocks, table_gemm=not bank)
     lvl = np.full(len(scn.offsets), 9.0)
-    _assert_close(got, want, lvl)
-    single, _ = run_engine(scn, blocks=blocks, no_pairing=True)
-    _assert_close(single, want, lvl)
+    _assert_close(got, want, lvl, table_gemm=not bank)
+    single, _ = run_engine(scn, blocks=blocks, no_pairing=True, table_gemm=not bank)
+    _assert_close(single, want, lvl, table_gemm=not bank)
     # a pair filters the four real product streams and forms x w / x conj(w) at the end (bank_fast.cuh fast_unmix);
     # the unpaired kernel mixes first: same result up to FP32 rounding, same decisions
     for a, b in zip(got, single):
@@ -225,8 +241,14 @@ def test_full_band_960_channels_against_oracle():
         pass
     from sdrx_b200 import Engine
     eng = Engine(scn.plan())
-    assert eng.bank_pairs == 479          # offsets -479..479 pair up; -480 and 0 ride alone
+    assert eng.bank_pairs == 479 and not eng.uses_table_gemm  # offsets -479..479 pair up; -480 and 0 ride alone
     eng.close()
+    # ... and the same band through the fold + table GEMM (SDRX_FLAG_TGEMM)
+    got_t, fast_t = run_engine(scn, blocks=blocks, table_gemm=True)
+    assert fast_t
+    _assert_close(got_t, want, np.full(len(scn.offsets), 9.0), table_gemm=True)
+    errs_t = np.asarray([rel_rms(np.stack([o.ch_iq for o in got_t])[:, c], iq_w[:, c]) for c in range(iq_w.shape[1])])
+    print(f"config3 table GEMM: channel-IQ rel rms vs oracle: max {errs_t.max():.3e}, median {np.median(errs_t):.3e}")
 
 
 def test_full_band_every_squelch_open_against_oracle():
@@ -320,7 +342,8 @@ def test_sparse_audio_equals_dense_audio():
     eng.close()
 
 
-def test_multi_stream_engine_matches_one_engine_per_stream():
+@pytest.mark.parametrize("table_gemm", [False, True], ids=["bank", "table_gemm"])
+def test_multi_stream_engine_matches_one_engine_per_stream(table_gemm):
     """BASELINE.json config 4 in miniature: several independent 10 MS/s streams that listen to the same channel plan go
     through ONE engine (sdrx_engine_config.n_streams: one launch sequence per block for all of them); every stream's
     results must be what an engine of its own gives, and what the oracle gives."""
@@ -331,9 +354,9 @@ def test_multi_stream_engine_matches_one_engine_per_stream():
     for s_ in range(NS):
         _, car, _ = wl.config4_stream(s_, n_channels=32)
         blocks.append(wl.synth_blocks(car, NB, 100 + s_, noise_sigma=0.002))
-    multi = Engine(plan, n_streams=NS)
-    assert multi.uses_fast_path
-    singles = [Engine(plan) for _ in range(NS)]
+    multi = Engine(plan, n_streams=NS, table_gemm=table_gemm)
+    assert multi.uses_fast_path and multi.uses_table_gemm == table_gemm
+    singles = [Engine(plan, table_gemm=table_gemm) for _ in range(NS)]
     orx = ob.OracleRx(product_tables(10000000), plan.offsets)
     Cs = len(plan.offsets)
     sets = multi.make_output_buffers(pinned=True, want=("audio_rows", "audio_chan", "n_audio", "pcm"))
