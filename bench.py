@@ -455,6 +455,23 @@ def run_ours(args):
     if world > 1 and not args.no_sharded:
         sharded = sharded_leg(args, plan, blocks, hviews, d_ring, blk_bytes, ring, world, rank, local, barrier, max_over_ranks)
 
+    # ---- the two opt-in channelizers (NOT the parity path, not the headline): same workload, same value leg
+    alt = None
+    if world == 1 and not args.no_alt:
+        alt = {}
+        for name, kw in (("table_gemm", {"table_gemm": True}), ("polyphase", {"polyphase": True})):
+            aeng = Engine(plan, device=local, **kw)
+            a_ms, _, _ = value_leg(aeng, args.steps, args.warmup)
+            aeng.set_timing(True)
+            aeng.push_device(d_ring, 2, L)
+            aeng.sync()
+            k_ms, _ = aeng.last_timing()
+            aeng.close()
+            alt[name] = {"ms_per_step": a_ms, "value": C_ * L / (a_ms * 1e-3) / 1e6, "channelizer_kernel_ms": k_ms,
+                         "accuracy": "profiles/r02x_channelizers.json (tools/polyphase_report.py): squelch decisions equal to the oracle's; "
+                                     + ("channel IQ of closed noise-only channels up to 1.4e-4 rel. RMS, audio 5e-5" if name == "table_gemm"
+                                        else "channel IQ up to 1.8e-2 rel. RMS on noise-only channels (exact twiddles vs the reference's float-rounded table), audio 8e-3")}
+
     # ---- parity of the bench's own workload against the oracle (--check): every channel, every distinct block
     check = None
     if args.check and rank == 0:
@@ -482,7 +499,7 @@ def run_ours(args):
                        "specialised_bank": bool(eng.uses_fast_path)},
             "realtime_channels": value / (RATE / 1e6),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "worst_case": worst, "sustained": sustained, "channel_sharded": sharded,
+            "worst_case": worst, "sustained": sustained, "channel_sharded": sharded, "opt_in_channelizers": alt,
         }
         if check is not None:
             line["parity_check"] = check
@@ -735,6 +752,7 @@ def main():
     ap.add_argument("--verbose", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--streams", type=int, default=64, help="config4: independent streams over all GPUs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-alt", action="store_true", help="skip the opt-in channelizer records (table GEMM, polyphase)")
     ap.add_argument("--no-worst", action="store_true", help="skip the worst_case leg (every squelch open)")
     ap.add_argument("--sustain", type=float, default=3.2, help="seconds of back-to-back blocks in the sustained leg (0: skip)")
     ap.add_argument("--no-sharded", action="store_true", help="N > 1: skip the channel-sharded (one stream over N GPUs) leg")

@@ -222,28 +222,43 @@ k_bank_fast(const void *__restrict__ raw_all, int hist, int valid_lo, const floa
         float2 *my_xs = xs + seg * kXSeg;
         const int my_bodies = 5 * my_steps;
         constexpr unsigned kSlotBytes = kXBody * sizeof(float2);
-        const unsigned ring_s = (unsigned)__cvta_generic_to_shared(my_xs) + (unsigned)ch * (unsigned)sizeof(float2);
+        unsigned ring_s = (unsigned)__cvta_generic_to_shared(my_xs) + (unsigned)ch * (unsigned)sizeof(float2);
         const bool second = ch < kBody - 16;               // lanes 0-8 also carry samples 16-24 of a body
         unsigned fo = 0, co = 0;
         long gidx = my_raw0;
         int to_fetch = my_bodies;                          // bodies not yet fetched
+        // The F32 path keeps its two running addresses opaque to the compiler (it would otherwise rebuild them from the
+        // thread index on every fetch to save two registers: ~20 instructions per body in a loop that is issue-bound).
+        const unsigned char *gp = reinterpret_cast<const unsigned char *>(reinterpret_cast<const float2 *>(raw) + my_raw0);
+        unsigned fs = ring_s;                              // shared-memory address the next fetch writes
+        const unsigned ring_end = ring_s + kXRing * kSlotBytes;
+        asm volatile("" : "+l"(gp), "+r"(fs), "+r"(ring_s));
         typename RawTraits<FMT>::vec pre[2];
         long pre_idx = 0;
         unsigned pre_off = 0;
         bool pre_valid = false;
         auto fetch = [&]() {                               // the next body of this segment -> its ring slot
+            if constexpr (FMT == SDRX_FMT_F32) {
+                if (to_fetch > 0) {
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(fs), "l"(gp) : "memory");
+                    if (second) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(fs + 128u), "l"(gp + 128) : "memory");
+                }
+                asm volatile("cp.async.commit_group;" ::: "memory");
+                --to_fetch;
+                gp += kBody * sizeof(float2);
+                fs += kSlotBytes;
+                if (fs == ring_end) fs = ring_s;
+                asm volatile("" : "+l"(gp), "+r"(fs));
+                return;
+            }
             if (to_fetch > 0) {
-                if constexpr (FMT == SDRX_FMT_F32) {
-                    const float2 *g = reinterpret_cast<const float2 *>(raw) + gidx;
-                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ring_s + fo), "l"(g) : "memory");
-                    if (second) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(ring_s + fo + 128u), "l"(g + 16) : "memory");
-                } else if constexpr (FMT == SDRX_FMT_S16) {
+                if constexpr (FMT == SDRX_FMT_S16) {
                     unsigned v0, v1 = 0;
                     asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(v0) : "l"(reinterpret_cast<const short2 *>(raw) + gidx));
                     if (second) asm volatile("ld.global.nc.b32 %0, [%1];" : "=r"(v1) : "l"(reinterpret_cast<const short2 *>(raw) + gidx + 16));
                     pre[0] = make_short2((short)(v0 & 0xffff), (short)(v0 >> 16));
                     pre[1] = make_short2((short)(v1 & 0xffff), (short)(v1 >> 16));
-                } else {
+                } else if constexpr (FMT == SDRX_FMT_U8) {
                     unsigned short v0, v1 = 0;
                     asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(v0) : "l"(reinterpret_cast<const uchar2 *>(raw) + gidx));
                     if (second) asm volatile("ld.global.nc.u16 %0, [%1];" : "=h"(v1) : "l"(reinterpret_cast<const uchar2 *>(raw) + gidx + 16));
@@ -251,8 +266,7 @@ k_bank_fast(const void *__restrict__ raw_all, int hist, int valid_lo, const floa
                     pre[1] = make_uchar2((unsigned char)(v1 & 0xff), (unsigned char)(v1 >> 8));
                 }
             }
-            if constexpr (FMT == SDRX_FMT_F32) asm volatile("cp.async.commit_group;" ::: "memory");
-            else { pre_valid = to_fetch > 0; pre_idx = gidx; pre_off = fo; }
+            pre_valid = to_fetch > 0; pre_idx = gidx; pre_off = fo;
             --to_fetch;
             gidx += kBody;
             fo = fo == 2 * kSlotBytes ? 0u : fo + kSlotBytes;

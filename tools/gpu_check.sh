@@ -16,9 +16,9 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/bench_r
 fi
 if [ "${SKIP_NCU:-0}" != "1" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches.csv \
-    python bench.py --steps 2 --warmup 3 --no-cpu --no-worst --sustain 0 > $OUT/ncu_launches.log 2>&1; echo "ncu launches rc=$?"
+    python bench.py --steps 2 --warmup 3 --no-cpu --no-worst --no-alt --sustain 0 > $OUT/ncu_launches.log 2>&1; echo "ncu launches rc=$?"
 fi
 if [ "${SKIP_FULL:-0}" != "1" ]; then
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_bank_fast -s 3 -c 1 -o $OUT/bank_full -f \
-    python bench.py --steps 2 --warmup 3 --no-cpu --no-worst --sustain 0 > $OUT/ncu_full.log 2>&1; echo "ncu full rc=$?"
+    python bench.py --steps 2 --warmup 3 --no-cpu --no-worst --no-alt --sustain 0 > $OUT/ncu_full.log 2>&1; echo "ncu full rc=$?"
 fi
