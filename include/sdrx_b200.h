@@ -68,6 +68,11 @@ typedef enum { SDRX_FMT_U8 = 0, SDRX_FMT_S16 = 1, SDRX_FMT_F32 = 2 } sdrx_iq_for
                                          decisions meet the parity bar, the channel IQ of closed, noise-only channels next to strong
                                          carriers reaches 1.4e-4 of relative RMS (time-domain bank: 4e-5).  Any chain whose translator
                                          period is a multiple of 16; whole blocks.                                                     */
+#define SDRX_FLAG_TGEMM_TC      0x80u /* OPT-IN: SDRX_FLAG_TGEMM with the matrix product on the 5th-generation tensor cores (tgemm_tc.cuh:
+                                         tcgen05.mma, accumulators in tensor memory, operands through TMA).  Every FP32 operand is split
+                                         into three bf16 planes and all nine plane products are kept, so the products are exact; partial
+                                         sums over 16 table entries are added in FP32 (round to nearest) as in the FP32 kernel.  Same bars
+                                         as SDRX_FLAG_TGEMM.                                                                            */
 #define SDRX_FLAG_PARTIAL_MIX   0x4u  /* channel-sharded run: stop at mix_pre (this GPU's share of the pan
                                          mix); FIR2 + s16 run once, in sdrx_engine_finish_mix              */
 
@@ -213,6 +218,7 @@ uint64_t sdrx_engine_launch_count(sdrx_engine *e);    /* kernels launched so far
 int      sdrx_engine_uses_fast_path(sdrx_engine *e);  /* 1 when the specialised channel bank runs  */
 int      sdrx_engine_bank_pairs(sdrx_engine *e);      /* conjugate channel pairs sharing a lane slot */
 int      sdrx_engine_uses_table_gemm(sdrx_engine *e); /* 1 when boundary A runs as fold + table GEMM   */
+int      sdrx_engine_uses_tensor_cores(sdrx_engine *e); /* 1 when that GEMM runs on tcgen05 (SDRX_FLAG_TGEMM_TC) */
 /* Device-timed duration (ms, CUDA events on the engine stream) of the channel-bank kernel(s) and of
  * the whole block for the last pushed block; valid after a sync. */
 int      sdrx_engine_last_timing(sdrx_engine *e, float *bank_ms, float *block_ms);

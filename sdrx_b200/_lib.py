@@ -14,6 +14,7 @@ c_i16_p = C.POINTER(C.c_int16)
 
 FMT_U8, FMT_S16, FMT_F32 = 0, 1, 2
 FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, FLAG_FTFIR, FLAG_POLYPHASE, FLAG_TGEMM = 0x1, 0x2, 0x4, 0x8, 0x10, 0x20, 0x40
+FLAG_TGEMM_TC = 0x80
 CHUNK = 512
 
 
@@ -85,6 +86,7 @@ PROTOTYPES = [
     ("sdrx_engine_uses_fast_path", C.c_int, [C.c_void_p]),
     ("sdrx_engine_bank_pairs", C.c_int, [C.c_void_p]),
     ("sdrx_engine_uses_table_gemm", C.c_int, [C.c_void_p]),
+    ("sdrx_engine_uses_tensor_cores", C.c_int, [C.c_void_p]),
     ("sdrx_engine_last_timing", C.c_int, [C.c_void_p, c_float_p, c_float_p]),
     ("sdrx_engine_set_timing", C.c_int, [C.c_void_p, C.c_int]),
     ("sdrx_debug_bank_plan_check", C.c_int, [C.c_int, C.c_int, C.c_int, c_int_p, c_int_p, c_int_p]),

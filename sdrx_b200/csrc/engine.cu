@@ -17,6 +17,7 @@
 #include "demod.cuh"
 #include "polyphase.cuh"
 #include "tgemm.cuh"
+#include "tgemm_tc.cuh"
 
 using namespace sdrx;
 static_assert(kFastSideSms == kSideSms, "the bank leaves the SMs the side kernels expect");
@@ -126,6 +127,8 @@ struct sdrx_engine {
     bool use_fast = false;
     TableGemm tg;                         // fold + table GEMM (tgemm.cuh): SDRX_FLAG_TGEMM
     bool use_tgemm = false;
+    TcGemm tc;                            // ... its GEMM on the tensor cores (tgemm_tc.cuh): SDRX_FLAG_TGEMM_TC
+    bool use_tc = false;
     int mat_len = 625, mat_stages = 2;    // materialize_generic: raw samples it replays, leading stages it runs
     bool tail_fusable = false;            // last stage as one per-channel kernel fed by the bank's rows + tail fix-ups
     bool tail_fast = false;               // ... in its specialised form (67 taps, decimate by 5: k_chan_fir_fast)
@@ -223,7 +226,8 @@ namespace {
 
 // The tensor map k_chan_agc reads a block's channel IQ through (demod.cuh).  The encoder lives in the driver library: it
 // is fetched through the runtime (cudaGetDriverEntryPoint), so nothing links against libcuda.
-int make_map_2d(CUtensorMap *map, void *base, cuuint64_t inner, cuuint64_t rows, cuuint64_t pitch_bytes, cuuint32_t box_inner, cuuint32_t box_rows) {
+int make_map_2d(CUtensorMap *map, void *base, cuuint64_t inner, cuuint64_t rows, cuuint64_t pitch_bytes, cuuint32_t box_inner, cuuint32_t box_rows,
+                CUtensorMapDataType dtype = CU_TENSOR_MAP_DATA_TYPE_FLOAT32) {
     typedef CUresult (*encode_fn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
                                   const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -239,7 +243,7 @@ int make_map_2d(CUtensorMap *map, void *base, cuuint64_t inner, cuuint64_t rows,
     const cuuint64_t strides[1] = {pitch_bytes};
     const cuuint32_t box[2] = {box_inner, box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+    const CUresult r = encode(map, dtype, 2, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(SDRX_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
     return SDRX_OK;
@@ -354,6 +358,7 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     for (auto &row : e->tl_ev) for (cudaEvent_t ev : row) if (ev) cudaEventDestroy(ev);
     e->fast.destroy();
     e->tg.destroy();
+    e->tc.destroy();
     if (e->ev_t0) cudaEventDestroy(e->ev_t0);
     if (e->ev_t1) cudaEventDestroy(e->ev_t1);
     if (e->ev_t2) cudaEventDestroy(e->ev_t2);
@@ -433,7 +438,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     if (eligible) e->raw_hist = std::max(e->raw_hist, kFastRawHist);   // also when forced generic: state blobs stay portable
     // fold + table GEMM (opt-in): any chain with translator tables of a period that is a multiple of 16 (1200 at 10 / 6 MS/s,
     // 288 at 2.4 MS/s ...)
-    const bool want_tgemm = (cfg->flags & SDRX_FLAG_TGEMM) && !(cfg->flags & (SDRX_FLAG_FORCE_GENERIC | SDRX_FLAG_POLYPHASE)) && !e->ftfir && S >= 2 &&
+    const bool want_tgemm = (cfg->flags & (SDRX_FLAG_TGEMM | SDRX_FLAG_TGEMM_TC)) && !(cfg->flags & (SDRX_FLAG_FORCE_GENERIC | SDRX_FLAG_POLYPHASE)) && !e->ftfir && S >= 2 &&
                             cfg->translators && cfg->translator_len >= kGemmK && cfg->translator_len % kGemmK == 0;
     if (want_tgemm) {
         long d_all = 1, d_head = 1;
@@ -572,6 +577,17 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if (rc) return rc;
         if ((rc = raise_dyn_smem((const void *)k_tgemm, kGemmSmem))) return rc;
         e->use_tgemm = true;
+        if (cfg->flags & SDRX_FLAG_TGEMM_TC) {
+            // experiment knobs (tools/diag_channelizers.py): plane products kept (9 exact / 6) and 16-entry k-steps per drain unit
+            const char *ep = getenv("SDRX_TC_PRODUCTS"), *es = getenv("SDRX_TC_STEPS");
+            auto bf16_map = [](CUtensorMap *map, void *base, uint64_t inner, uint64_t rows, uint64_t pitch, int box_inner, int box_rows) {
+                return make_map_2d(map, base, inner, rows, pitch, (cuuint32_t)box_inner, (cuuint32_t)box_rows, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
+            };
+            if ((rc = tc_init(e->tc, e->tg, cfg->translators, has_v.data(), e->tg.h_slot_chan, ep ? atoi(ep) : 9, es ? atoi(es) : 1, bf16_map)))
+                return rc;
+            if ((rc = raise_dyn_smem(tc_kernel_ptr(e->tc.products, e->tc.steps), kTcSmem))) return rc;
+            e->use_tc = true;
+        }
     } else if (want_tgemm) {
         e->mat_len = 625; e->mat_stages = 2;
     }
@@ -1133,7 +1149,12 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     if (tgemm) {
         cudaEvent_t b0 = e->timing ? e->ev_b0 : nullptr, b1 = e->timing ? e->ev_b1 : nullptr;
         const long sb = (long)e->raw_stream_bytes;
-        switch (fmt) {
+        if (e->use_tc) switch (fmt) {
+            case SDRX_FMT_U8:  rc = tgemm_tc_launch<SDRX_FMT_U8>(e->tg, e->tc, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
+            case SDRX_FMT_S16: rc = tgemm_tc_launch<SDRX_FMT_S16>(e->tg, e->tc, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
+            default:           rc = tgemm_tc_launch<SDRX_FMT_F32>(e->tg, e->tc, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
+        }
+        else switch (fmt) {
             case SDRX_FMT_U8:  rc = tgemm_launch<SDRX_FMT_U8>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
             case SDRX_FMT_S16: rc = tgemm_launch<SDRX_FMT_S16>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
             default:           rc = tgemm_launch<SDRX_FMT_F32>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
@@ -1519,6 +1540,7 @@ extern "C" int sdrx_debug_bank_trace_read(unsigned long long *out, int max_u64) 
 extern "C" int sdrx_engine_uses_fast_path(sdrx_engine *e) { return e && (e->use_fast || e->use_tgemm) ? 1 : 0; }
 extern "C" int sdrx_engine_bank_pairs(sdrx_engine *e) { return !e ? 0 : (e->use_tgemm ? e->tg.n_pairs : (e->use_fast ? e->fast.n_pairs : 0)); }
 extern "C" int sdrx_engine_uses_table_gemm(sdrx_engine *e) { return e && e->use_tgemm ? 1 : 0; }
+extern "C" int sdrx_engine_uses_tensor_cores(sdrx_engine *e) { return e && e->use_tgemm && e->use_tc ? 1 : 0; }
 extern "C" int sdrx_engine_set_timing(sdrx_engine *e, int enable) {
     if (!e) return fail(SDRX_ERR_ARG, "null engine");
     e->timing = enable != 0;

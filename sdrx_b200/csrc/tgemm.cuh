@@ -175,6 +175,7 @@ struct TableGemm {
     float4 *d_tdup = nullptr;          // [N][slots_pad]
     int *d_slot_chan = nullptr;        // [slots_pad][2]
     float2 *d_U = nullptr;             // [n_streams][N][Mpad]
+    std::vector<int> h_slot_chan;      // host copy of d_slot_chan (the tensor-core variant lays its rows out from it)
     void destroy() {
         cudaFree(d_hc); cudaFree(d_tdup); cudaFree(d_slot_chan); cudaFree(d_U);
         d_hc = nullptr; d_tdup = nullptr; d_slot_chan = nullptr; d_U = nullptr; enabled = false;
@@ -216,6 +217,7 @@ inline int tgemm_init(TableGemm &tg, int C, int N, int n_stages, const int *m, c
             tdup[(size_t)p * tg.slots_pad + s] = make_float4(tr, tr, ti, ti);
         }
     }
+    tg.h_slot_chan = slot_chan;
     tg.Mpad = (max_out + kGemmM - 1) / kGemmM * kGemmM;
     CU(cudaMalloc((void **)&tg.d_hc, sizeof(float) * hcf.size()));
     CU(cudaMemcpy(tg.d_hc, hcf.data(), sizeof(float) * hcf.size(), cudaMemcpyHostToDevice));

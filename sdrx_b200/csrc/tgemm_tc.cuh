@@ -1,0 +1,358 @@
+// sdrx_b200 -- the table GEMM of tgemm.cuh on the 5th-generation tensor cores (tcgen05.mma, accumulators in tensor memory,
+// operands staged by TMA): north_star's "tensor cores only if the mix-plus-FIR is recast as a complex GEMM (channels x taps),
+// and only if that version stays within tolerance".  SDRX_FLAG_TGEMM_TC.
+//
+// The product is the same as k_tgemm's -- per pair slot s and output instant M, over the table period p < N:
+//     P = sum Tr[s][p] Ur[p][M],  R = sum Tr Ui,  S = sum Ti Ur,  Q = sum Ti Ui;   Y_first = (P - Q, R + S),  Y_partner = (P + Q, R - S)
+// (the reference's own translator tables, sdrx.cpp:1682-1690, are the A matrix; msd.hpp:133-154, :251-335 is the map) -- written as
+// ONE real GEMM  D[2 slots x 2 instants] = A[rows = (Tr_s, Ti_s)][p] * B[cols = (Ur_M, Ui_M)][p]^T.
+//
+// Precision.  A tensor-core product takes bf16 (8 significant bits) operands; an FP32 value is EXACTLY the sum of three bf16
+// values (x = x0 + x1 + x2, each the round-to-nearest bf16 of what is left), so a x b = sum over the nine plane products
+// a_i x b_j, every one of them exact in the FP32 accumulator's product (8 x 8 bits).  kProducts = 9 keeps them all (the
+// products are then EXACT and the only rounding left is the accumulation); kProducts = 6 drops the three smallest (a1 b2,
+// a2 b1, a2 b2: <= 2^-23 of the product, about one FP32 rounding of it).
+// Accumulation.  As in k_tgemm a single running sum over the 1200 terms loses weak channels next to strong carriers, so the
+// k range is cut into drain units of kSteps x 16 table entries: every unit is accumulated in its own tensor-memory
+// accumulator (a ring of eight 64-column accumulators = all 512 columns) and the four epilogue warps add the finished
+// units into FP32 register totals with round-to-nearest adds while the tensor core works on the following units.
+//
+//   k_fold_tc<FMT>  the fold of tgemm.cuh, written as the bf16 planes of B, k-major: B[stream][plane][2 M + (re|im)][p]
+//   k_tgemm_tc      one CTA per 128-row x 64-column tile of D (64 pair slots x 32 instants), 6 warps:
+//                     warp 4  TMA producer: per 64-entry k-block the three planes of A (128 x 64 bf16) and of B (64 x 64 bf16)
+//                             through 2-D tensor maps with the 128-byte swizzle, a three-deep ring of 72 KB stages on mbarriers
+//                     warp 5  allocates tensor memory; one lane issues tcgen05.mma (M 128, N 64, K 16, kind::f16 with bf16 inputs,
+//                             FP32 accumulate) and tcgen05.commit onto the ring's mbarriers
+//                     warps 0-3  epilogue: tcgen05.ld of a finished accumulator (32 lanes x 64 columns per warp), add into the
+//                             totals; at the end un-mix the pair (neighbouring lanes hold the Tr and Ti rows of a slot) and store
+#pragma once
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "tgemm.cuh"
+
+namespace sdrx {
+
+constexpr int kTcRows = 128;                  // UMMA M
+constexpr int kTcCols = 64;                   // UMMA N
+constexpr int kTcK = 64;                      // bf16 elements of one staged k-block row = 128 bytes = one swizzle row
+constexpr int kTcKStep = 16;                  // K of one tcgen05.mma with 16-bit inputs
+constexpr int kTcStages = 3;
+constexpr int kTcPlanes = 3;
+constexpr int kTcAcc = 8;                     // accumulators in the tensor-memory ring
+constexpr int kTcTmemCols = kTcAcc * kTcCols; // 512: all of it
+constexpr int kTcThreads = 192;
+constexpr int kTcABytes = kTcRows * kTcK * 2; // 16 KB per plane
+constexpr int kTcBBytes = kTcCols * kTcK * 2; //  8 KB per plane
+constexpr int kTcStageBytes = kTcPlanes * (kTcABytes + kTcBBytes);              // 72 KB
+constexpr size_t kTcSmem = (size_t)kTcStages * kTcStageBytes + 1024 + 256;      // + alignment slack + barriers / tmem slot
+
+// ---- tcgen05 / tensor-memory primitives (inline PTX; SASS: UTCHMMA, LDTM, UTCBAR, UTMALDG)
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_alloc(uint32_t *slot, unsigned cols) {        // whole warp
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(slot)), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_dealloc(uint32_t taddr, unsigned cols) {      // whole warp, the one that allocated
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]^T; one thread issues
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrives on `bar` once every tcgen05.mma issued before it by this thread has completed (implies fence::before_thread_sync)
+__device__ __forceinline__ void tc_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// 32 lanes x 32 consecutive columns: thread t of the warp gets lane (warp % 4) * 32 + t
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t *v) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, "
+        "%21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]),
+          "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+          "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]),
+          "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tc_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor of a K-major operand tile whose rows are 128 bytes (64 bf16) and whose 8-row groups are
+// 1024-byte atoms under the 128-byte swizzle -- exactly what a {64, rows} TMA box with CU_TENSOR_MAP_SWIZZLE_128B writes.
+// bits [0,14) address >> 4, [16,30) leading byte offset >> 4 (unused for this layout: 1, as CUTLASS sets it), [32,46) stride byte offset >> 4 (one
+// atom = 1024 B), [46,48) version 1 (sm_100), [61,64) layout type 2 (SWIZZLE_128B).  A k-step of 16 elements = 32 bytes
+// further along the row is the same descriptor with the address advanced by 32 bytes (+2 in the field).
+__device__ __forceinline__ uint64_t tc_smem_desc(uint32_t saddr) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// Instruction descriptor, kind::f16: [4,6) D format 1 = F32, [7,10) A format 1 = BF16, [10,13) B format 1 = BF16, bit 15 / 16 A / B
+// major 0 = K, [17,23) N >> 3, [24,29) M >> 4.
+constexpr uint32_t kTcIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(kTcCols >> 3) << 17) | ((uint32_t)(kTcRows >> 4) << 24);
+
+__device__ __forceinline__ void bf16_split3(float x, __nv_bfloat16 &h0, __nv_bfloat16 &h1, __nv_bfloat16 &h2) {
+    h0 = __float2bfloat16_rn(x);
+    const float r1 = __fsub_rn(x, __bfloat162float(h0));   // exact
+    h1 = __float2bfloat16_rn(r1);
+    const float r2 = __fsub_rn(r1, __bfloat162float(h1));  // exact
+    h2 = __float2bfloat16_rn(r2);                          // exact: at most 8 significant bits are left
+}
+
+// The fold of tgemm.cuh (k_fold) writing B: [stream][plane][2 M + (re | im)][p] bf16, p contiguous (pitch Kp elements).
+// grid (ceil(n_out / kFoldM), n_streams).
+template <int FMT>
+static __global__ void __launch_bounds__(kFoldThreads)
+k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int valid_lo, int pos0, int D, int N, const float *__restrict__ hc, int Lh,
+          int n_out, __nv_bfloat16 *__restrict__ B, int cols, int Kp) {
+    const void *raw = reinterpret_cast<const unsigned char *>(raw_all) + (long)blockIdx.y * stream_bytes;
+    __nv_bfloat16 *Bs = B + (size_t)blockIdx.y * kTcPlanes * cols * Kp;
+    const size_t plane = (size_t)cols * Kp;
+    const int M0 = blockIdx.x * kFoldM;
+    for (int it = threadIdx.x; it < kFoldM * N; it += kFoldThreads) {
+        const int m = it / N, p = it - m * N;
+        const int M = M0 + m;
+        if (M >= n_out) break;
+        const int nM = D * M + D - 1;
+        int d = (pos0 + nM - p) % N;
+        if (d < 0) d += N;
+        float2 acc = make_float2(0.f, 0.f);
+        for (int j0 = d; j0 < Lh; j0 += 8 * N) {
+            float2 xv[8];
+            float hv[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int j = j0 + q * N;
+                const bool in = j < Lh;
+                xv[q] = in ? load_iq_from<FMT>(raw, (long)hist + nM - j, valid_lo) : make_float2(0.f, 0.f);
+                hv[q] = in ? __ldg(hc + j) : 0.0f;
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                acc.x = fmaf(hv[q], xv[q].x, acc.x);
+                acc.y = fmaf(hv[q], xv[q].y, acc.y);
+            }
+        }
+        __nv_bfloat16 r0, r1, r2, i0, i1, i2;
+        bf16_split3(acc.x, r0, r1, r2);
+        bf16_split3(acc.y, i0, i1, i2);
+        __nv_bfloat16 *re = Bs + (size_t)(2 * M) * Kp + p, *im = re + Kp;
+        re[0] = r0; re[plane] = r1; re[2 * plane] = r2;
+        im[0] = i0; im[plane] = i1; im[2 * plane] = i2;
+    }
+}
+
+// grid (rows_pad / 128, cols / 64, n_streams); A map: [3 rows_pad][N] bf16, box {64, 128}; B map: [n_streams 3 cols][N] bf16, box {64, 64}.
+// kProducts: 9 (all plane products: exact) or 6; kSteps: 16-entry k-steps per drain unit (1, 2 or 4).
+template <int kProducts, int kSteps>
+static __global__ void __launch_bounds__(kTcThreads, 1)
+k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int rows_pad, int cols, int N,
+           const int *__restrict__ slot_chan, int chans_per_stream, float2 *__restrict__ ch_iq, long iq_stride, int n_out) {
+    extern __shared__ unsigned char tc_smem_raw[];
+    unsigned char *sm = reinterpret_cast<unsigned char *>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);   // swizzle atoms: 1024-byte aligned
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (size_t)kTcStages * kTcStageBytes);
+    uint64_t *full = bars, *empty = bars + kTcStages, *tfull = bars + 2 * kTcStages, *tempty = tfull + kTcAcc;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + kTcAcc);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_kb = (N + kTcK - 1) / kTcK;                       // staged k-blocks (the last one zero-filled past N by the TMA unit)
+    const int n_ks = (N + kTcKStep - 1) / kTcKStep;               // k-steps that hold any table entry
+    const int n_units = (n_ks + kSteps - 1) / kSteps;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kTcStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        for (int i = 0; i < kTcAcc; ++i) { mbar_init(tfull + i, 1); mbar_init(tempty + i, 4); }
+        mbar_fence_init();
+    }
+    if (warp == 5) tc_alloc(tmem_slot, kTcTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp == 4) {
+        // ===== TMA producer
+        if (lane == 0) {
+            const int row0 = blockIdx.x * kTcRows;
+            const int col0 = blockIdx.z * kTcPlanes * cols + blockIdx.y * kTcCols;
+            for (int kb = 0; kb < n_kb; ++kb) {
+                const int st = kb % kTcStages;
+                mbar_wait(empty + st, ((unsigned)(kb / kTcStages) & 1u) ^ 1u);
+                mbar_expect_tx(full + st, (unsigned)kTcStageBytes);
+                unsigned char *a = sm + (size_t)st * kTcStageBytes, *b = a + kTcPlanes * kTcABytes;
+#pragma unroll
+                for (int pl = 0; pl < kTcPlanes; ++pl) {
+                    tma_load_2d(a + pl * kTcABytes, &map_a, kb * kTcK, pl * rows_pad + row0, full + st);
+                    tma_load_2d(b + pl * kTcBBytes, &map_b, kb * kTcK, pl * cols + col0, full + st);
+                }
+            }
+        }
+    } else if (warp == 5) {
+        // ===== MMA issuer (one lane)
+        if (lane == 0) {
+            // plane products, smallest first: (a plane, b plane)
+            constexpr int pa[9] = {2, 2, 1, 2, 0, 1, 1, 0, 0};
+            constexpr int pb[9] = {2, 1, 2, 0, 2, 1, 0, 1, 0};
+            constexpr int first_prod = 9 - kProducts;             // 6 products: skip (2,2), (2,1), (1,2)
+            int unit = 0;
+            for (int ks = 0; ks < n_ks; ++ks) {
+                const int kb = ks >> 2, sub = ks & 3, st = kb % kTcStages;
+                if (sub == 0) {
+                    mbar_wait(full + st, (unsigned)(kb / kTcStages) & 1u);
+                    tc_fence_after();
+                }
+                const bool unit_first = (ks % kSteps) == 0;
+                const int acc = unit % kTcAcc;
+                if (unit_first) {
+                    mbar_wait(tempty + acc, ((unsigned)(unit / kTcAcc) & 1u) ^ 1u);
+                    tc_fence_after();
+                }
+                const uint32_t sa = smem_u32(sm + (size_t)st * kTcStageBytes) + sub * (kTcKStep * 2);
+                const uint32_t sb = sa + kTcPlanes * kTcABytes;
+#pragma unroll
+                for (int q = first_prod; q < 9; ++q)
+                    tc_mma_bf16(tmem + acc * kTcCols, tc_smem_desc(sa + pa[q] * kTcABytes), tc_smem_desc(sb + pb[q] * kTcBBytes), kTcIdesc,
+                                (unit_first && q == first_prod) ? 0u : 1u);
+                const bool last = ks == n_ks - 1;
+                if ((ks % kSteps) == kSteps - 1 || last) { tc_commit(tfull + acc); ++unit; }
+                if (sub == 3 || last) tc_commit(empty + st);
+            }
+        }
+    } else {
+        // ===== epilogue warps 0..3: TMEM lanes 32 warp .. 32 warp + 31 = rows of the tile
+        float tot[kTcCols];
+#pragma unroll
+        for (int i = 0; i < kTcCols; ++i) tot[i] = 0.0f;
+        const uint32_t tlane = tmem + ((uint32_t)(warp * 32) << 16);
+        for (int unit = 0; unit < n_units; ++unit) {
+            const int acc = unit % kTcAcc;
+            mbar_wait(tfull + acc, (unsigned)(unit / kTcAcc) & 1u);
+            tc_fence_after();
+            uint32_t v[kTcCols];
+            tc_ld32(tlane + acc * kTcCols, v);
+            tc_ld32(tlane + acc * kTcCols + 32, v + 32);
+            tc_ld_wait();
+            tc_fence_before();
+            if (lane == 0) mbar_arrive(tempty + acc);
+#pragma unroll
+            for (int i = 0; i < kTcCols; ++i) tot[i] = __fadd_rn(tot[i], __uint_as_float(v[i]));
+        }
+        // un-mix: even row = Tr of the slot -> (P, R) per instant, odd row = Ti -> (S, Q); the partner row is the neighbouring lane
+        const int row = blockIdx.x * kTcRows + warp * 32 + lane;
+        const int odd = row & 1;
+        const int c = slot_chan[row];                              // [slot][2]: even row -> first channel, odd row -> conjugate partner
+        const int m0 = blockIdx.y * (kTcCols / 2);
+        float2 *dst = c >= 0 ? ch_iq + ((long)blockIdx.z * chans_per_stream + c) * iq_stride + m0 : nullptr;
+#pragma unroll
+        for (int m = 0; m < kTcCols / 2; m += 2) {
+            float4 y;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const float a = tot[2 * (m + h)], b = tot[2 * (m + h) + 1];
+                const float oa = __shfl_xor_sync(0xffffffffu, a, 1), ob = __shfl_xor_sync(0xffffffffu, b, 1);
+                // even: a = P, b = R, oa = S, ob = Q -> (P - Q, R + S);  odd: a = S, b = Q, oa = P, ob = R -> (P + Q, R - S)
+                const float re = odd ? __fadd_rn(oa, b) : __fsub_rn(a, ob);
+                const float im = odd ? __fsub_rn(ob, a) : __fadd_rn(b, oa);
+                if (h == 0) { y.x = re; y.y = im; } else { y.z = re; y.w = im; }
+            }
+            if (dst && m0 + m < n_out) *reinterpret_cast<float4 *>(dst + m) = y;   // n_out is even (tgemm_eligible)
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 5) tc_dealloc(tmem, kTcTmemCols);
+}
+
+// ---- host side
+struct TcGemm {
+    bool enabled = false;
+    int rows_pad = 0, cols = 0, Kp = 0, products = 9, steps = 1;
+    __nv_bfloat16 *d_a = nullptr;      // [3][rows_pad][Kp]
+    __nv_bfloat16 *d_b = nullptr;      // [n_streams][3][cols][Kp]
+    int *d_row_chan = nullptr;         // [rows_pad]
+    CUtensorMap map_a, map_b;
+    void destroy() {
+        cudaFree(d_a); cudaFree(d_b); cudaFree(d_row_chan);
+        d_a = d_b = nullptr; d_row_chan = nullptr; enabled = false;
+    }
+};
+
+inline void host_bf16_split3(float x, uint16_t out[3]) {
+    auto rn = [](float v) -> uint16_t {                    // float -> bf16, round to nearest even (finite inputs)
+        uint32_t u; memcpy(&u, &v, 4);
+        u += 0x7FFFu + ((u >> 16) & 1u);
+        return (uint16_t)(u >> 16);
+    };
+    auto up = [](uint16_t h) -> float { uint32_t u = (uint32_t)h << 16; float v; memcpy(&v, &u, 4); return v; };
+    float r = x;
+    for (int i = 0; i < 3; ++i) { out[i] = rn(r); r = r - up(out[i]); }
+}
+
+template <typename MakeMap>
+int tc_init(TcGemm &tc, const TableGemm &tg, const float *tables, const uint8_t *has, const std::vector<int> &slot_chan, int products, int steps,
+            MakeMap make_map) {
+    const int N = tg.N;
+    tc.products = products == 6 ? 6 : 9;
+    tc.steps = steps == 4 ? 4 : (steps == 2 ? 2 : 1);
+    tc.Kp = N;
+    tc.rows_pad = (2 * tg.slots + kTcRows - 1) / kTcRows * kTcRows;
+    tc.cols = (2 * tg.Mpad + kTcCols - 1) / kTcCols * kTcCols;
+    std::vector<uint16_t> a((size_t)kTcPlanes * tc.rows_pad * tc.Kp, 0);
+    std::vector<int> row_chan((size_t)tc.rows_pad, -1);
+    const size_t plane = (size_t)tc.rows_pad * tc.Kp;
+    for (int s = 0; s < tg.slots; ++s) {
+        const int c = slot_chan[2 * s];
+        row_chan[2 * s] = c;
+        row_chan[2 * s + 1] = slot_chan[2 * s + 1];
+        for (int p = 0; p < N; ++p) {
+            float t[2] = {1.0f, 0.0f};
+            if (tables && has[c]) { t[0] = tables[((size_t)c * N + p) * 2]; t[1] = tables[((size_t)c * N + p) * 2 + 1]; }
+            for (int ri = 0; ri < 2; ++ri) {
+                uint16_t h[3];
+                host_bf16_split3(t[ri], h);
+                for (int pl = 0; pl < kTcPlanes; ++pl) a[pl * plane + (size_t)(2 * s + ri) * tc.Kp + p] = h[pl];
+            }
+        }
+    }
+    CU(cudaMalloc((void **)&tc.d_a, a.size() * 2));
+    CU(cudaMemcpy(tc.d_a, a.data(), a.size() * 2, cudaMemcpyHostToDevice));
+    const size_t b_elems = (size_t)tg.n_streams * kTcPlanes * tc.cols * tc.Kp;
+    CU(cudaMalloc((void **)&tc.d_b, b_elems * 2));
+    CU(cudaMemset(tc.d_b, 0, b_elems * 2));
+    CU(cudaMalloc((void **)&tc.d_row_chan, sizeof(int) * row_chan.size()));
+    CU(cudaMemcpy(tc.d_row_chan, row_chan.data(), sizeof(int) * row_chan.size(), cudaMemcpyHostToDevice));
+    int rc;
+    if ((rc = make_map(&tc.map_a, tc.d_a, (uint64_t)N, (uint64_t)kTcPlanes * tc.rows_pad, (uint64_t)tc.Kp * 2, kTcK, kTcRows))) return rc;
+    if ((rc = make_map(&tc.map_b, tc.d_b, (uint64_t)N, (uint64_t)tg.n_streams * kTcPlanes * tc.cols, (uint64_t)tc.Kp * 2, kTcK, kTcCols))) return rc;
+    tc.enabled = true;
+    return SDRX_OK;
+}
+
+inline const void *tc_kernel_ptr(int products, int steps) {
+    if (products == 6) return steps == 4 ? (const void *)k_tgemm_tc<6, 4> : steps == 2 ? (const void *)k_tgemm_tc<6, 2> : (const void *)k_tgemm_tc<6, 1>;
+    return steps == 4 ? (const void *)k_tgemm_tc<9, 4> : steps == 2 ? (const void *)k_tgemm_tc<9, 2> : (const void *)k_tgemm_tc<9, 1>;
+}
+
+template <int FMT>
+int tgemm_tc_launch(TableGemm &tg, TcGemm &tc, cudaStream_t st, const void *raw, long stream_bytes, int hist, int valid_lo, int pos0, int n_out,
+                    float2 *ch_iq, long iq_stride, uint64_t *launches, cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr) {
+    k_fold_tc<FMT><<<dim3((n_out + kFoldM - 1) / kFoldM, tg.n_streams), kFoldThreads, 0, st>>>(raw, stream_bytes, hist, valid_lo, pos0, tg.D, tg.N,
+                                                                                              tg.d_hc, tg.Lh, n_out, tc.d_b, tc.cols, tc.Kp);
+    if (ev0) CU(cudaEventRecord(ev0, st));
+    const dim3 grid(tc.rows_pad / kTcRows, (2 * n_out + kTcCols - 1) / kTcCols, tg.n_streams);
+#define SDRX_TC_GO(P, S)                                                                                                                     \
+    k_tgemm_tc<P, S><<<grid, kTcThreads, kTcSmem, st>>>(tc.map_a, tc.map_b, tc.rows_pad, tc.cols, tg.N, tc.d_row_chan, tg.chans, ch_iq, iq_stride, \
+                                                        n_out)
+    if (tc.products == 6) { if (tc.steps == 4) SDRX_TC_GO(6, 4); else if (tc.steps == 2) SDRX_TC_GO(6, 2); else SDRX_TC_GO(6, 1); }
+    else                  { if (tc.steps == 4) SDRX_TC_GO(9, 4); else if (tc.steps == 2) SDRX_TC_GO(9, 2); else SDRX_TC_GO(9, 1); }
+#undef SDRX_TC_GO
+    if (ev1) CU(cudaEventRecord(ev1, st));
+    *launches += 2;
+    CU(cudaGetLastError());
+    return SDRX_OK;
+}
+
+}  // namespace sdrx

@@ -13,7 +13,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import (FMT_F32, FMT_S16, FMT_U8, FLAG_FTFIR, FLAG_POLYPHASE, FLAG_TGEMM, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, CHUNK,
+from ._lib import (FMT_F32, FMT_S16, FMT_U8, FLAG_FTFIR, FLAG_POLYPHASE, FLAG_TGEMM, FLAG_TGEMM_TC, FLAG_FORCE_GENERIC, FLAG_NO_DEMOD, FLAG_PARTIAL_MIX, FLAG_NO_PAIRING, CHUNK,
                    SdrxError,
                    check)
 from .config import ChannelPlan, make_translator, tables
@@ -78,7 +78,8 @@ class Engine:
     def __init__(self, plan: ChannelPlan, device: int = 0, use_lf_agc: bool = False, lf_gain_db: float = 0.0,
                  block_len: Optional[int] = None, force_generic: bool = False, demod: bool = True,
                  translators: Optional[np.ndarray] = None, partial_mix: bool = False, no_pairing: bool = False,
-                 use_ftfir: bool = False, n_streams: int = 1, polyphase: bool = False, table_gemm: bool = False):
+                 use_ftfir: bool = False, n_streams: int = 1, polyphase: bool = False, table_gemm: bool = False,
+                 tensor_cores: bool = False):
         """``n_streams`` > 1: that many independent IQ streams, all listening to ``plan``, in one engine (one launch
         sequence per block for all of them, BASELINE.json config 4): :meth:`push` then takes ``[n_streams][block]``
         and every per-channel result has ``n_streams * len(plan.offsets)`` entries, stream-major."""
@@ -143,7 +144,8 @@ class Engine:
                      | (FLAG_PARTIAL_MIX if partial_mix else 0) | (FLAG_NO_PAIRING if no_pairing else 0)
                      | (FLAG_FTFIR if use_ftfir else 0)      # --ftfir, sdrx.cpp:1199 / msd.hpp:104-131
                      | (FLAG_POLYPHASE if polyphase else 0)   # opt-in polyphase / DFT channelizer: not bit-compatible
-                     | (FLAG_TGEMM if table_gemm else 0))     # opt-in fold + table GEMM instead of the time-domain channel bank
+                     | (FLAG_TGEMM if table_gemm else 0)      # opt-in fold + table GEMM instead of the time-domain channel bank
+                     | (FLAG_TGEMM_TC if tensor_cores else 0))  # ... with the GEMM on tcgen05 (bf16 x 9 split operands)
         self.demod = demod
         h = C.c_void_p()
         check(self.lib.sdrx_engine_create(C.byref(cfg), C.byref(h)))
@@ -302,6 +304,11 @@ class Engine:
     def uses_table_gemm(self) -> bool:
         """Boundary A runs as fold + table GEMM (tgemm.cuh)."""
         return bool(self.lib.sdrx_engine_uses_table_gemm(self.h))
+
+    @property
+    def uses_tensor_cores(self) -> bool:
+        """... and that GEMM runs on the tensor cores (tgemm_tc.cuh, tcgen05.mma)."""
+        return bool(self.lib.sdrx_engine_uses_tensor_cores(self.h))
 
     @property
     def bank_pairs(self) -> int:

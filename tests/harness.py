@@ -41,10 +41,11 @@ def run_cpu(scn: Scenario, backend: str = "oracle", blocks: Optional[List[np.nda
 
 
 def run_engine(scn: Scenario, force_generic: bool = False, blocks: Optional[List[np.ndarray]] = None, device: int = 0,
-               no_pairing: bool = False, table_gemm: bool = False):
+               no_pairing: bool = False, table_gemm: bool = False, tensor_cores: bool = False):
     from sdrx_b200 import Engine
     eng = Engine(scn.plan(), device=device, use_lf_agc=scn.use_lf_agc, lf_gain_db=scn.lf_gain_db,
-                 force_generic=force_generic, no_pairing=no_pairing, use_ftfir=scn.use_ftfir, table_gemm=table_gemm)
+                 force_generic=force_generic, no_pairing=no_pairing, use_ftfir=scn.use_ftfir, table_gemm=table_gemm,
+                 tensor_cores=tensor_cores)
     src = scn.source()
     out = []
     for b in range(scn.n_blocks):

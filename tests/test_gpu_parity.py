@@ -94,16 +94,17 @@ def test_generic_engine_is_bit_exact_with_oracle(scn):
     _assert_exact(got, run_cpu(scn, "oracle", blocks))
 
 
-@pytest.mark.parametrize("table_gemm", [False, True], ids=["bank", "table_gemm"])
+@pytest.mark.parametrize("table_gemm", [False, True, "tc"], ids=["bank", "table_gemm", "tensor_cores"])
 @pytest.mark.parametrize("scn", [sc.config2(n_blocks=8), sc.config2(sc.FMT_S16, 4), sc.config2(sc.FMT_U8, 4),
                                  sc.centre_channel(), sc.config1()] + sc.config2_variants(), ids=lambda s: s.name)
 def test_default_engine_meets_the_parity_bar(scn, table_gemm):
-    """Boundary A through the time-domain channel bank (the default) and through the fold + table GEMM (SDRX_FLAG_TGEMM,
-    tgemm.cuh; also what a 2.4 MS/s chain gets when asked for it): squelch decisions bit-exact, audio within 1e-4."""
+    """Boundary A through the time-domain channel bank (the default), through the fold + table GEMM (SDRX_FLAG_TGEMM,
+    tgemm.cuh; also what a 2.4 MS/s chain gets when asked for it) and through the same GEMM on the tensor cores
+    (SDRX_FLAG_TGEMM_TC, tgemm_tc.cuh): squelch decisions bit-exact, audio within 1e-4."""
     blocks = _blocks(scn)
-    got, fast = run_engine(scn, blocks=blocks, table_gemm=table_gemm)
+    got, fast = run_engine(scn, blocks=blocks, table_gemm=bool(table_gemm), tensor_cores=table_gemm == "tc")
     lvl = np.asarray(scn.sql_levels if scn.sql_levels is not None else [9.0] * len(scn.offsets))
-    _assert_close(got, run_cpu(scn, "oracle", blocks), lvl, table_gemm=table_gemm)
+    _assert_close(got, run_cpu(scn, "oracle", blocks), lvl, table_gemm=bool(table_gemm))
 
 def _wrap(d):
     return (d + np.pi) % (2 * np.pi) - np.pi
@@ -249,6 +250,12 @@ def test_full_band_960_channels_against_oracle():
     _assert_close(got_t, want, np.full(len(scn.offsets), 9.0), table_gemm=True)
     errs_t = np.asarray([rel_rms(np.stack([o.ch_iq for o in got_t])[:, c], iq_w[:, c]) for c in range(iq_w.shape[1])])
     print(f"config3 table GEMM: channel-IQ rel rms vs oracle: max {errs_t.max():.3e}, median {np.median(errs_t):.3e}")
+    # ... and with that GEMM on the tensor cores (SDRX_FLAG_TGEMM_TC: bf16 x 9 split operands, tcgen05.mma)
+    got_c, fast_c = run_engine(scn, blocks=blocks, tensor_cores=True)
+    assert fast_c
+    _assert_close(got_c, want, np.full(len(scn.offsets), 9.0), table_gemm=True)
+    errs_c = np.asarray([rel_rms(np.stack([o.ch_iq for o in got_c])[:, c], iq_w[:, c]) for c in range(iq_w.shape[1])])
+    print(f"config3 tensor-core table GEMM: channel-IQ rel rms vs oracle: max {errs_c.max():.3e}, median {np.median(errs_c):.3e}")
 
 
 def test_full_band_every_squelch_open_against_oracle():
@@ -342,7 +349,7 @@ def test_sparse_audio_equals_dense_audio():
     eng.close()
 
 
-@pytest.mark.parametrize("table_gemm", [False, True], ids=["bank", "table_gemm"])
+@pytest.mark.parametrize("table_gemm", [False, True, "tc"], ids=["bank", "table_gemm", "tensor_cores"])
 def test_multi_stream_engine_matches_one_engine_per_stream(table_gemm):
     """BASELINE.json config 4 in miniature: several independent 10 MS/s streams that listen to the same channel plan go
     through ONE engine (sdrx_engine_config.n_streams: one launch sequence per block for all of them); every stream's
@@ -354,9 +361,10 @@ def test_multi_stream_engine_matches_one_engine_per_stream(table_gemm):
     for s_ in range(NS):
         _, car, _ = wl.config4_stream(s_, n_channels=32)
         blocks.append(wl.synth_blocks(car, NB, 100 + s_, noise_sigma=0.002))
-    multi = Engine(plan, n_streams=NS, table_gemm=table_gemm)
-    assert multi.uses_fast_path and multi.uses_table_gemm == table_gemm
-    singles = [Engine(plan, table_gemm=table_gemm) for _ in range(NS)]
+    tc, table_gemm = table_gemm == "tc", bool(table_gemm)
+    multi = Engine(plan, n_streams=NS, table_gemm=table_gemm, tensor_cores=tc)
+    assert multi.uses_fast_path and multi.uses_table_gemm == table_gemm and multi.uses_tensor_cores == tc
+    singles = [Engine(plan, table_gemm=table_gemm, tensor_cores=tc) for _ in range(NS)]
     orx = ob.OracleRx(product_tables(10000000), plan.offsets)
     Cs = len(plan.offsets)
     sets = multi.make_output_buffers(pinned=True, want=("audio_rows", "audio_chan", "n_audio", "pcm"))
