@@ -69,10 +69,14 @@ struct sdrx_engine {
     // its own predecessor -- squelch state, AGC state, FIR2 ring -- and on the previous kernel of its own block), so a
     // step costs the longest of them, not their sum
     cudaStream_t s_side = nullptr;        // k_chan_head<kHeadDetect>
-    cudaStream_t s_recur = nullptr;       // k_chan_recur
+    cudaStream_t s_recur = nullptr;       // k_chan_agc
+    cudaStream_t s_lf = nullptr;          // k_chan_env + k_chan_lfagc: block b's LfAGC runs next to block b + 1's AGC
     cudaStream_t s_mix = nullptr;         // k_mix_fir2_pcm
     cudaEvent_t ev_head_done = nullptr;   // the last MSD stage of the current block has been queued behind this point (main -> side)
     cudaEvent_t ev_det_done[kNOut] = {}, ev_recur_done[kNOut] = {};
+    cudaEvent_t ev_agc_done[2] = {}, ev_env_done[2] = {};   // d_agc_iq[par] written / read (ping-pong between the two recurrence streams)
+    bool env_pending[2] = {false, false};
+    unsigned agc_par = 0;
     cudaEvent_t ev_side_done[kNOut] = {};   // all of boundary B that reads / writes output set b is complete (recorded behind the mix)
     bool side_pending[kNOut] = {};
     cudaStream_t s_out = nullptr;         // asynchronous result fetch (sdrx_engine_fetch_outputs): D2H overlaps the next block
@@ -106,7 +110,7 @@ struct sdrx_engine {
     float *d_c_adj = nullptr, *d_fir_hist = nullptr;
     float *d_parts = nullptr;             // staging of the per-GPU partial mixes (sdrx_engine_finish_mix)
     size_t parts_cap = 0;
-    float2 *d_agc_iq = nullptr;           // [512][Cpad] gain-adjusted channel IQ, sample-major (k_chan_agc -> k_chan_env)
+    float2 *d_agc_iq[2] = {nullptr, nullptr};   // [512][Cpad] gain-adjusted channel IQ, sample-major (k_chan_agc -> k_chan_env), ping-pong
     float *d_env = nullptr;               // [512][Cpad] envelope / discriminator output (k_chan_env -> k_chan_lfagc)
     float2 *d_fm_new = nullptr;           // [C] prev_sample of the FM demodulators after this block (k_chan_env -> k_chan_lfagc)
     // debug timeline (sdrx_debug_timeline): completion time of every kernel of the last kTlBlocks blocks
@@ -276,6 +280,7 @@ int reset_state(sdrx_engine *e) {
     const size_t C = (size_t)e->C;
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_recur));
+    CU(cudaStreamSynchronize(e->s_lf));
     CU(cudaStreamSynchronize(e->s_mix));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;
@@ -350,7 +355,8 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     cudaFree(e->d_window); cudaFree(e->d_shape); cudaFree(e->d_ramp_up); cudaFree(e->d_ramp_down);
     cudaFree(e->d_twiddle); cudaFree(e->d_bitrev); cudaFree(e->d_sql_level); cudaFree(e->d_pos);
     cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist); cudaFree(e->d_parts); cudaFree(e->d_ticket); cudaFree(e->d_rows_scratch[0]); cudaFree(e->d_rows_scratch[1]);
-    cudaFree(e->d_agc_iq); cudaFree(e->d_env); cudaFree(e->d_fm_new);
+    cudaFree(e->d_agc_iq[0]); cudaFree(e->d_agc_iq[1]); cudaFree(e->d_env); cudaFree(e->d_fm_new);
+    for (int b = 0; b < 2; ++b) { if (e->ev_agc_done[b]) cudaEventDestroy(e->ev_agc_done[b]); if (e->ev_env_done[b]) cudaEventDestroy(e->ev_env_done[b]); }
     cudaFree(e->d_hc); cudaFree(e->d_wtab); cudaFree(e->d_bin);
     for (int b = 0; b < sdrx_engine::kNFin; ++b) { cudaFree(e->d_fin_mix_pre[b]); cudaFree(e->d_fin_mix[b]); cudaFree(e->d_fin_pcm[b]); }
     if (e->ev_ext) cudaEventDestroy(e->ev_ext);
@@ -368,6 +374,7 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     if (e->s_copy) cudaStreamDestroy(e->s_copy);
     if (e->s_side) cudaStreamDestroy(e->s_side);
     if (e->s_recur) cudaStreamDestroy(e->s_recur);
+    if (e->s_lf) cudaStreamDestroy(e->s_lf);
     if (e->s_mix) cudaStreamDestroy(e->s_mix);
     if (e->s_out) cudaStreamDestroy(e->s_out);
     delete e;
@@ -459,10 +466,15 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         int lo = 0, hi = 0;
         CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
         CU(cudaStreamCreateWithPriority(&e->s_recur, cudaStreamNonBlocking, hi));
+        CU(cudaStreamCreateWithPriority(&e->s_lf, cudaStreamNonBlocking, hi));
         CU(cudaStreamCreateWithPriority(&e->s_mix, cudaStreamNonBlocking, hi));
     }
     CU(cudaStreamCreateWithFlags(&e->s_out, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&e->ev_head_done, cudaEventDisableTiming));
+    for (int b = 0; b < 2; ++b) {
+        CU(cudaEventCreateWithFlags(&e->ev_agc_done[b], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&e->ev_env_done[b], cudaEventDisableTiming));
+    }
     CU(cudaEventCreateWithFlags(&e->ev_ext, cudaEventDisableTiming));
     for (int b = 0; b < 2; ++b) CU(cudaEventCreateWithFlags(&e->ev_tail_done[b], cudaEventDisableTiming));
     for (int b = 0; b < kNOut; ++b) {
@@ -579,11 +591,11 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         e->use_tgemm = true;
         if (cfg->flags & SDRX_FLAG_TGEMM_TC) {
             // experiment knobs (tools/diag_channelizers.py): plane products kept (9 exact / 6) and 16-entry k-steps per drain unit
-            const char *ep = getenv("SDRX_TC_PRODUCTS"), *es = getenv("SDRX_TC_STEPS");
+            const char *ep = getenv("SDRX_TC_PRODUCTS"), *es = getenv("SDRX_TC_STEPS"), *ec = getenv("SDRX_TC_CLUSTER");
             auto bf16_map = [](CUtensorMap *map, void *base, uint64_t inner, uint64_t rows, uint64_t pitch, int box_inner, int box_rows) {
                 return make_map_2d(map, base, inner, rows, pitch, (cuuint32_t)box_inner, (cuuint32_t)box_rows, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
             };
-            if ((rc = tc_init(e->tc, e->tg, cfg->translators, has_v.data(), e->tg.h_slot_chan, ep ? atoi(ep) : 9, es ? atoi(es) : 1, bf16_map)))
+            if ((rc = tc_init(e->tc, e->tg, cfg->translators, has_v.data(), e->tg.h_slot_chan, ep ? atoi(ep) : 9, es ? atoi(es) : 1, ec ? atoi(ec) : 1, bf16_map)))
                 return rc;
             if ((rc = raise_dyn_smem(tc_kernel_ptr(e->tc.products, e->tc.steps), kTcSmem))) return rc;
             e->use_tc = true;
@@ -683,7 +695,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if ((rc = dalloc(&e->d_ticket, 2 * (size_t)NS))) return rc;
         if ((rc = raise_dyn_smem((const void *)k_chan_agc, kAgcSmem)) || (rc = raise_dyn_smem((const void *)k_chan_lfagc, kLfSmem)))
             return rc;
-        if ((rc = dalloc(&e->d_agc_iq, (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_env, (size_t)e->Cpad * kChunk)) ||
+        if ((rc = dalloc(&e->d_agc_iq[0], (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_agc_iq[1], (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_env, (size_t)e->Cpad * kChunk)) ||
             (rc = dalloc(&e->d_fm_new, C)))
             return rc;
         e->tb = DemodTables{e->d_window, e->d_twiddle, e->d_bitrev, e->d_shape, e->d_ramp_up, e->d_ramp_down};
@@ -954,17 +966,24 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
                                                                    e->d_sql_level, o.snr, e->d_gate[idx], snap);
     tl_mark(e, TL_DET, e->s_side);
     CU(cudaEventRecord(e->ev_det_done[idx], e->s_side));
-    // the AGC runs whatever the squelch state (sdrx.cpp:457): next to the detector, not behind it
-    k_chan_agc<<<recur_ctas(e->C), kRecurThreads, kAgcSmem, e->s_recur>>>(o.iq_map, e->st, e->agc, e->d_agc_iq, e->Cpad, snap, e->C);
+    // the AGC runs whatever the squelch state (sdrx.cpp:457): next to the detector, not behind it -- and on a stream of its
+    // own, so that block b + 1's AGC recurrence runs next to block b's LfAGC recurrence (gain-adjusted IQ in a ping-pong)
+    const unsigned par = e->agc_par++ & 1u;
+    if (e->env_pending[par]) CU(cudaStreamWaitEvent(e->s_recur, e->ev_env_done[par], 0));
+    k_chan_agc<<<recur_ctas(e->C), kRecurThreads, kAgcSmem, e->s_recur>>>(o.iq_map, e->st, e->agc, e->d_agc_iq[par], e->Cpad, snap, e->C);
     tl_mark(e, TL_AGC, e->s_recur);
-    CU(cudaStreamWaitEvent(e->s_recur, e->ev_det_done[idx], 0));
-    k_chan_env<<<dim3(e->Cpad / 32, kChunk / 4), dim3(32, 4), 0, e->s_recur>>>(e->d_agc_iq, e->Cpad, e->st, e->d_gate[idx], e->d_env,
-                                                                                e->d_fm_new, e->C);
-    tl_mark(e, TL_ENV, e->s_recur);
-    k_chan_lfagc<<<recur_ctas(e->C), kRecurThreads, kLfSmem, e->s_recur>>>(e->d_env, e->Cpad, e->st, e->d_gate[idx], e->tb, e->lf, e->lf_active, o.audio, snap,
-                                                           e->C, o.mixed, e->d_fm_new);
-    tl_mark(e, TL_LFAGC, e->s_recur);
-    CU(cudaEventRecord(e->ev_recur_done[idx], e->s_recur));
+    CU(cudaEventRecord(e->ev_agc_done[par], e->s_recur));
+    CU(cudaStreamWaitEvent(e->s_lf, e->ev_agc_done[par], 0));
+    CU(cudaStreamWaitEvent(e->s_lf, e->ev_det_done[idx], 0));
+    k_chan_env<<<dim3(e->Cpad / 32, kChunk / 4), dim3(32, 4), 0, e->s_lf>>>(e->d_agc_iq[par], e->Cpad, e->st, e->d_gate[idx], e->d_env,
+                                                                             e->d_fm_new, e->C);
+    tl_mark(e, TL_ENV, e->s_lf);
+    CU(cudaEventRecord(e->ev_env_done[par], e->s_lf));
+    e->env_pending[par] = true;
+    k_chan_lfagc<<<recur_ctas(e->C), kRecurThreads, kLfSmem, e->s_lf>>>(e->d_env, e->Cpad, e->st, e->d_gate[idx], e->tb, e->lf, e->lf_active, o.audio, snap,
+                                                        e->C, o.mixed, e->d_fm_new);
+    tl_mark(e, TL_LFAGC, e->s_lf);
+    CU(cudaEventRecord(e->ev_recur_done[idx], e->s_lf));
     CU(cudaStreamWaitEvent(e->s_mix, e->ev_recur_done[idx], 0));
     e->launches += 4;
     int rc = launch_mix(e, e->s_mix, o, e->d_pwr_partial[idx], have_power ? kPwrPartials : 0, n_samples,
@@ -1279,6 +1298,7 @@ extern "C" int sdrx_engine_sync(sdrx_engine *e) {
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_recur));
+    CU(cudaStreamSynchronize(e->s_lf));
     CU(cudaStreamSynchronize(e->s_mix));
     CU(cudaStreamSynchronize(e->s_out));
     return SDRX_OK;
@@ -1601,6 +1621,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_recur));
+    CU(cudaStreamSynchronize(e->s_lf));
     CU(cudaStreamSynchronize(e->s_mix));
     if (e->generic_stale) {      // the blob always carries the stage delay lines (a generic engine can load it)
         const int last_ = (int)((e->pushes & 1) ^ 1);
@@ -1661,6 +1682,7 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_recur));
+    CU(cudaStreamSynchronize(e->s_lf));
     CU(cudaStreamSynchronize(e->s_mix));
     CU(cudaStreamSynchronize(e->s_out));
     for (int b = 0; b < kNOut; ++b) e->side_pending[b] = e->fetch_pending[b] = false;

@@ -66,6 +66,22 @@ __device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, ui
 __device__ __forceinline__ void tc_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// ... the same arrival on the barrier at this offset in every CTA of the cluster named by `mask`
+__device__ __forceinline__ void tc_commit_mc(uint64_t *bar, uint16_t mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+// one box of a 2-D tensor map into the shared memory of every CTA of the cluster named by `mask` (same offset in each),
+// completing its bytes on the barrier at `bar`'s offset in each of them
+__device__ __forceinline__ void tma_load_2d_mc(void *dst, const void *tmap, int x, int y, uint64_t *bar, uint16_t mask) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%2, %3}], [%4], %5;"
+                 ::"r"(smem_u32(dst)), "l"(tmap), "r"(x), "r"(y), "r"(smem_u32(bar)), "h"(mask) : "memory");
+}
+__device__ __forceinline__ unsigned cluster_rank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -146,12 +162,12 @@ k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int val
     }
 }
 
-// grid (rows_pad / 128, cols / 64, n_streams); A map: [3 rows_pad][N] bf16, box {64, 128}; B map: [n_streams 3 cols][N] bf16, box {64, 64}.
+// grid (rows_pad / 128, cols / 64, n_streams), clusters of (1, cl, 1) CTAs (cl = 1: none); A map box {64, 128 / cl}; A map: [3 rows_pad][N] bf16, box {64, 128}; B map: [n_streams 3 cols][N] bf16, box {64, 64}.
 // kProducts: 9 (all plane products: exact) or 6; kSteps: 16-entry k-steps per drain unit (1, 2 or 4).
 template <int kProducts, int kSteps>
 static __global__ void __launch_bounds__(kTcThreads, 1)
 k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int rows_pad, int cols, int N,
-           const int *__restrict__ slot_chan, int chans_per_stream, float2 *__restrict__ ch_iq, long iq_stride, int n_out) {
+           const int *__restrict__ slot_chan, int chans_per_stream, float2 *__restrict__ ch_iq, long iq_stride, int n_out, int cl) {
     extern __shared__ unsigned char tc_smem_raw[];
     unsigned char *sm = reinterpret_cast<unsigned char *>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);   // swizzle atoms: 1024-byte aligned
     uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (size_t)kTcStages * kTcStageBytes);
@@ -163,15 +179,17 @@ k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
     const int n_units = (n_ks + kSteps - 1) / kSteps;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kTcStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, 1); }
+        for (int i = 0; i < kTcStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, (unsigned)cl); }
         for (int i = 0; i < kTcAcc; ++i) { mbar_init(tfull + i, 1); mbar_init(tempty + i, 4); }
         mbar_fence_init();
     }
     if (warp == 5) tc_alloc(tmem_slot, kTcTmemCols);
     tc_fence_before();
     __syncthreads();
+    if (cl > 1) cluster_sync_all();                               // every CTA's barriers exist before a neighbour's copy or commit lands on them
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
+    const uint16_t mc_mask = (uint16_t)((1u << cl) - 1u);
 
     if (warp == 4) {
         // ===== TMA producer
@@ -183,10 +201,20 @@ k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                 mbar_wait(empty + st, ((unsigned)(kb / kTcStages) & 1u) ^ 1u);
                 mbar_expect_tx(full + st, (unsigned)kTcStageBytes);
                 unsigned char *a = sm + (size_t)st * kTcStageBytes, *b = a + kTcPlanes * kTcABytes;
+                if (cl > 1) {
+                    // the CTAs of a cluster share the row tile: each fetches 1 / cl of every A plane and multicasts it to all of them
+                    const int rank = (int)cluster_rank(), slice = kTcRows / cl;
 #pragma unroll
-                for (int pl = 0; pl < kTcPlanes; ++pl) {
-                    tma_load_2d(a + pl * kTcABytes, &map_a, kb * kTcK, pl * rows_pad + row0, full + st);
-                    tma_load_2d(b + pl * kTcBBytes, &map_b, kb * kTcK, pl * cols + col0, full + st);
+                    for (int pl = 0; pl < kTcPlanes; ++pl) {
+                        tma_load_2d_mc(a + pl * kTcABytes + rank * slice * (kTcK * 2), &map_a, kb * kTcK, pl * rows_pad + row0 + rank * slice, full + st, mc_mask);
+                        tma_load_2d(b + pl * kTcBBytes, &map_b, kb * kTcK, pl * cols + col0, full + st);
+                    }
+                } else {
+#pragma unroll
+                    for (int pl = 0; pl < kTcPlanes; ++pl) {
+                        tma_load_2d(a + pl * kTcABytes, &map_a, kb * kTcK, pl * rows_pad + row0, full + st);
+                        tma_load_2d(b + pl * kTcBBytes, &map_b, kb * kTcK, pl * cols + col0, full + st);
+                    }
                 }
             }
         }
@@ -218,7 +246,7 @@ k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                                 (unit_first && q == first_prod) ? 0u : 1u);
                 const bool last = ks == n_ks - 1;
                 if ((ks % kSteps) == kSteps - 1 || last) { tc_commit(tfull + acc); ++unit; }
-                if (sub == 3 || last) tc_commit(empty + st);
+                if (sub == 3 || last) { if (cl > 1) tc_commit_mc(empty + st, mc_mask); else tc_commit(empty + st); }
             }
         }
     } else {
@@ -263,13 +291,14 @@ k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
     }
     tc_fence_before();
     __syncthreads();
+    if (cl > 1) cluster_sync_all();                               // no CTA leaves while a neighbour's commit may still arrive on its barriers
     if (warp == 5) tc_dealloc(tmem, kTcTmemCols);
 }
 
 // ---- host side
 struct TcGemm {
     bool enabled = false;
-    int rows_pad = 0, cols = 0, Kp = 0, products = 9, steps = 1;
+    int rows_pad = 0, cols = 0, Kp = 0, products = 9, steps = 1, cluster = 1;
     __nv_bfloat16 *d_a = nullptr;      // [3][rows_pad][Kp]
     __nv_bfloat16 *d_b = nullptr;      // [n_streams][3][cols][Kp]
     int *d_row_chan = nullptr;         // [rows_pad]
@@ -293,10 +322,11 @@ inline void host_bf16_split3(float x, uint16_t out[3]) {
 
 template <typename MakeMap>
 int tc_init(TcGemm &tc, const TableGemm &tg, const float *tables, const uint8_t *has, const std::vector<int> &slot_chan, int products, int steps,
-            MakeMap make_map) {
+            int cluster, MakeMap make_map) {
     const int N = tg.N;
     tc.products = products == 6 ? 6 : 9;
     tc.steps = steps == 4 ? 4 : (steps == 2 ? 2 : 1);
+    tc.cluster = (cluster == 2 || cluster == 4 || cluster == 8) ? cluster : 1;
     tc.Kp = N;
     tc.rows_pad = (2 * tg.slots + kTcRows - 1) / kTcRows * kTcRows;
     tc.cols = (2 * tg.Mpad + kTcCols - 1) / kTcCols * kTcCols;
@@ -325,7 +355,7 @@ int tc_init(TcGemm &tc, const TableGemm &tg, const float *tables, const uint8_t 
     CU(cudaMalloc((void **)&tc.d_row_chan, sizeof(int) * row_chan.size()));
     CU(cudaMemcpy(tc.d_row_chan, row_chan.data(), sizeof(int) * row_chan.size(), cudaMemcpyHostToDevice));
     int rc;
-    if ((rc = make_map(&tc.map_a, tc.d_a, (uint64_t)N, (uint64_t)kTcPlanes * tc.rows_pad, (uint64_t)tc.Kp * 2, kTcK, kTcRows))) return rc;
+    if ((rc = make_map(&tc.map_a, tc.d_a, (uint64_t)N, (uint64_t)kTcPlanes * tc.rows_pad, (uint64_t)tc.Kp * 2, kTcK, kTcRows / tc.cluster))) return rc;
     if ((rc = make_map(&tc.map_b, tc.d_b, (uint64_t)N, (uint64_t)tg.n_streams * kTcPlanes * tc.cols, (uint64_t)tc.Kp * 2, kTcK, kTcCols))) return rc;
     tc.enabled = true;
     return SDRX_OK;
@@ -343,9 +373,17 @@ int tgemm_tc_launch(TableGemm &tg, TcGemm &tc, cudaStream_t st, const void *raw,
                                                                                               tg.d_hc, tg.Lh, n_out, tc.d_b, tc.cols, tc.Kp);
     if (ev0) CU(cudaEventRecord(ev0, st));
     const dim3 grid(tc.rows_pad / kTcRows, (2 * n_out + kTcCols - 1) / kTcCols, tg.n_streams);
-#define SDRX_TC_GO(P, S)                                                                                                                     \
-    k_tgemm_tc<P, S><<<grid, kTcThreads, kTcSmem, st>>>(tc.map_a, tc.map_b, tc.rows_pad, tc.cols, tg.N, tc.d_row_chan, tg.chans, ch_iq, iq_stride, \
-                                                        n_out)
+    const int cl = (tc.cluster > 1 && grid.y % tc.cluster == 0) ? tc.cluster : 1;
+    if (cl != tc.cluster) return fail(SDRX_ERR_UNSUPPORTED, "tensor-core table GEMM: the column tiles of this block length do not fill whole clusters");
+    cudaLaunchConfig_t lc{};
+    lc.gridDim = grid; lc.blockDim = dim3(kTcThreads); lc.dynamicSmemBytes = kTcSmem; lc.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = (unsigned)cl; at[0].val.clusterDim.z = 1;
+    lc.attrs = at; lc.numAttrs = cl > 1 ? 1 : 0;
+#define SDRX_TC_GO(P, S)                                                                                                                    \
+    CU(cudaLaunchKernelEx(&lc, k_tgemm_tc<P, S>, tc.map_a, tc.map_b, tc.rows_pad, tc.cols, tg.N, (const int *)tc.d_row_chan, tg.chans, ch_iq, \
+                          iq_stride, n_out, cl))
     if (tc.products == 6) { if (tc.steps == 4) SDRX_TC_GO(6, 4); else if (tc.steps == 2) SDRX_TC_GO(6, 2); else SDRX_TC_GO(6, 1); }
     else                  { if (tc.steps == 4) SDRX_TC_GO(9, 4); else if (tc.steps == 2) SDRX_TC_GO(9, 2); else SDRX_TC_GO(9, 1); }
 #undef SDRX_TC_GO

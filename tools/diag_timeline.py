@@ -10,11 +10,12 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--open-all", action="store_true")
 ap.add_argument("--blocks", type=int, default=12)
 ap.add_argument("--out", default=None)
+ap.add_argument("--mode", default="bank", choices=["bank", "tgemm", "tc", "poly"])
 a = ap.parse_args()
 plan, carriers, desc = wl.config3(960, 0.0 if a.open_all else None)
 blocks = wl.synth_blocks(carriers, 8, 1)
 lib = _lib.load()
-eng = Engine(plan)
+eng = Engine(plan, table_gemm=a.mode == "tgemm", tensor_cores=a.mode == "tc", polyphase=a.mode == "poly")
 L = plan.rate.block_len
 nb = blocks[0].nbytes
 d = lib.sdrx_device_alloc(0, 8 * nb)
@@ -27,6 +28,8 @@ for i in range(40):
     eng.push_device(d + (i % 8) * nb, 2, L)
 out = np.zeros((16, 9), np.float32)
 n = lib.sdrx_debug_timeline_read(eng.h, out.ctypes.data_as(_lib.c_float_p), a.blocks)
+if n <= 0:
+    print("timeline read failed:", lib.sdrx_last_error().decode(), file=sys.stderr)
 names = ["start", "prep", "bank", "tail", "det", "agc", "env", "lfagc", "mix"]
 t = out[:n] * 1e3
 print(("open-all " if a.open_all else "") + "completion times, us after block start on the main stream; step = start-to-start")
