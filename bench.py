@@ -57,6 +57,18 @@ def workload(name: str, sql_level=None):
     raise SystemExit(f"unknown workload {name}")
 
 
+# boundary A: which channelizer the engine runs (sdrx_engine_config.flags)
+MODE_KW = {"bank": {}, "tensor_cores": {"tensor_cores": True}, "table_gemm": {"table_gemm": True}, "polyphase": {"polyphase": True}}
+MODE_WHAT = {
+    "bank": "time-domain channel bank (FP32 CUDA cores; the bit-comparable default of the library)",
+    "tensor_cores": "fold + table GEMM on the tensor cores (SDRX_FLAG_TGEMM_TC: tcgen05.mma, bf16 x 9 split operands = exact FP32 products, "
+                    "FP32 accumulation in 16-entry partial sums); north_star's complex-GEMM recast, inside its tolerance "
+                    "(audio <= 1e-4, squelch decisions bit-exact)",
+    "table_gemm": "fold + table GEMM on the FP32 CUDA cores (SDRX_FLAG_TGEMM)",
+    "polyphase": "exact-twiddle polyphase / DFT channelizer (SDRX_FLAG_POLYPHASE; NOT a parity mode)",
+}
+
+
 N_DISTINCT = 8            # distinct synthetic blocks (two keying epochs of the carriers); the device ring cycles them
 
 
@@ -275,7 +287,8 @@ def run_ours(args):
     C_ = len(plan.offsets)
     L = plan.rate.block_len
     lib = _lib.load()
-    eng = Engine(plan, device=local)
+    mode = args.channelizer
+    eng = Engine(plan, device=local, **MODE_KW[mode])
     try:
         uuid = torch.cuda.get_device_properties(local).uuid
     except Exception:
@@ -326,7 +339,7 @@ def run_ours(args):
         device->host->device round trip is off the critical path.  Every step moves its own input and its own results
         across the host link inside the timed region; d2h bytes are counted from what actually crossed."""
         stream = torch.cuda.ExternalStream(e.stream, device=torch.device("cuda", local))
-        LAG = 3
+        LAG = int(os.environ.get("SDRX_BENCH_LAG", "5"))   # blocks between a fetch and its wait: a block's results are ~300 us behind its push
         want = ("audio_rows", "audio_chan", "n_audio", "sql_state", "snr", "mix", "pcm", "pwr_dbfs")
         osets = [e.make_output_buffers(pinned=True, want=want) for _ in range(LAG + 1)]
         fixed = C_ * 1 + C_ * 4 + 1024 * 4 + 1024 * 2 + 4 + 4            # sql, snr, mix, pcm, pwr, n_audio
@@ -384,31 +397,61 @@ def run_ours(args):
     eng.set_timing(False)
     bank_ms = statistics.mean(bank)
     peak, peak_how = fp32_peak()
-    flop_bank = FLOP_BANK if eng.uses_fast_path else FLOP_CHAIN
-    achieved = flop_bank * C_ * L / (bank_ms * 1e-3) / 1e12
-    roofline = {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "peak_nominal": NOMINAL_FP32_TFLOPS, "frac_nominal": achieved / NOMINAL_FP32_TFLOPS,
-                "traffic": None, "kernel": "channel bank (mix + decimating FIR stages)" if eng.uses_fast_path
-                else "generic channelizer kernels (all stages)",
-                "kernel_ms": bank_ms, "block_ms_serialised": statistics.mean(whole),
-                "share_of_step": bank_ms / per_step_ms, "share_of_serialised_block": bank_ms / statistics.mean(whole),
-                "chain_frac": FLOP_CHAIN * C_ * L / (per_step_ms * 1e-3) / 1e12 / peak,
-                "algorithmic_flop_per_channel_sample": flop_bank, "peak_source": peak_how}
-    prof = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(prof):
-        with open(prof) as f:
-            roofline["traffic"] = json.load(f).get("bank_dram_bytes_per_launch")
-    # the HBM view of the same kernel, for completeness (the path is FP32-bound, HBM is irrelevant):
-    # algorithmic bytes per launch = the block read once + the stage-3 rows written once
     mp = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    hbm_peak = None
+    measured = {}
     if os.path.exists(mp):
         with open(mp) as f:
-            hbm_peak = json.load(f).get("hbm_gbs")
-    alg_bytes = L * 8 + C_ * (L // 125) * 8
-    roofline["hbm"] = {"algorithmic_bytes_per_launch": alg_bytes, "achieved": alg_bytes / (bank_ms * 1e-3) / 1e9,
-                       "peak": hbm_peak, "unit": "GB/s",
-                       "frac": (alg_bytes / (bank_ms * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None}
+            measured = json.load(f)
+    hbm_peak = measured.get("hbm_gbs")
+    if mode in ("tensor_cores", "table_gemm"):
+        # The dominant kernel is the table GEMM.  `achieved` is the ALGORITHMIC work of the path as the reference computes it
+        # (19.232 flop per channel and input sample for mix + stages 1-3, + stage 4 -- the GEMM covers all four)
+        # over the GEMM kernel's time; the tensor cores execute 2 x rows x columns x N x 9 plane products for it.
+        n_tab, n_inst = 1200, L // 625
+        rows = 2 * ((C_ + 1) // 2 + 1)                       # (Tr, Ti) per conjugate-pair slot
+        executed = 2.0 * rows * (2 * n_inst) * n_tab * (9 if mode == "tensor_cores" else 1)
+        alg = FLOP_CHAIN * C_ * L
+        tpeak = float(measured.get("bf16_tflops", 1590.0)) if mode == "tensor_cores" else peak
+        achieved = alg / (bank_ms * 1e-3) / 1e12
+        roofline = {"bound": "tensor" if mode == "tensor_cores" else "fp32", "achieved": achieved, "peak": tpeak, "unit": "TFLOP/s",
+                    "frac": achieved / tpeak, "traffic": None,
+                    "kernel": "k_tgemm_tc (tcgen05.mma, bf16 x 9)" if mode == "tensor_cores" else "k_tgemm (FP32 FFMA2)",
+                    "kernel_ms": bank_ms, "block_ms_serialised": statistics.mean(whole), "share_of_step": bank_ms / per_step_ms,
+                    "algorithmic_flop_per_channel_sample": FLOP_CHAIN,
+                    "executed_tflops": executed / (bank_ms * 1e-3) / 1e12, "executed_frac": executed / (bank_ms * 1e-3) / 1e12 / tpeak,
+                    "executed_flop_per_launch": executed,
+                    "of_fp32_cuda_core_peak": achieved / peak,
+                    "chain_of_fp32_cuda_core_peak": FLOP_CHAIN * C_ * L / (per_step_ms * 1e-3) / 1e12 / peak,
+                    "peak_source": ("measured (MEASURED_PEAKS.json bf16_tflops, cuBLAS burst)" if "bf16_tflops" in measured
+                                    else "fallback 1.59 PFLOP/s (B200_PROFILING.md)") if mode == "tensor_cores" else peak_how,
+                    "note": "the algorithmic count is the reference's time-domain chain; the GEMM form needs 2.4 GFLOP per block instead of "
+                            "5.9 (shared fold, conjugate pairs) and the bf16 x 9 split multiplies that by 9, so `frac` understates the "
+                            "tensor pipe's load: see executed_frac and profiles/r02y_tc_ncu_details.txt (tensor pipe 60 % of active cycles)"}
+        prof = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(prof):
+            with open(prof) as f:
+                roofline["traffic"] = json.load(f).get("tc_gemm_dram_bytes_per_launch")
+    else:
+        flop_bank = FLOP_BANK if eng.uses_fast_path else FLOP_CHAIN
+        achieved = flop_bank * C_ * L / (bank_ms * 1e-3) / 1e12
+        roofline = {"bound": "fp32", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                    "peak_nominal": NOMINAL_FP32_TFLOPS, "frac_nominal": achieved / NOMINAL_FP32_TFLOPS,
+                    "traffic": None, "kernel": "channel bank (mix + decimating FIR stages)" if eng.uses_fast_path
+                    else "generic channelizer kernels (all stages)",
+                    "kernel_ms": bank_ms, "block_ms_serialised": statistics.mean(whole),
+                    "share_of_step": bank_ms / per_step_ms, "share_of_serialised_block": bank_ms / statistics.mean(whole),
+                    "chain_frac": FLOP_CHAIN * C_ * L / (per_step_ms * 1e-3) / 1e12 / peak,
+                    "algorithmic_flop_per_channel_sample": flop_bank, "peak_source": peak_how}
+        prof = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(prof):
+            with open(prof) as f:
+                roofline["traffic"] = json.load(f).get("bank_dram_bytes_per_launch")
+        # the HBM view of the same kernel, for completeness (the path is FP32-bound, HBM is irrelevant):
+        # algorithmic bytes per launch = the block read once + the stage-3 rows written once
+        alg_bytes = L * 8 + C_ * (L // 125) * 8
+        roofline["hbm"] = {"algorithmic_bytes_per_launch": alg_bytes, "achieved": alg_bytes / (bank_ms * 1e-3) / 1e9,
+                           "peak": hbm_peak, "unit": "GB/s",
+                           "frac": (alg_bytes / (bank_ms * 1e-3) / 1e9 / hbm_peak) if hbm_peak else None}
 
     # ---- e2e leg
     e2e = e2e_leg(eng, args.steps)
@@ -441,7 +484,7 @@ def run_ours(args):
     worst = None
     if not args.no_worst:
         wplan, _, _ = workload(args.workload, sql_level=0.0)
-        weng = Engine(wplan, device=local)
+        weng = Engine(wplan, device=local, **MODE_KW[mode])
         w_ms, _, _ = value_leg(weng, args.steps, args.warmup)
         w_e2e = e2e_leg(weng, args.steps)
         worst = {"what": "same blocks, sql_level 0 on every channel: all squelches open (sdrx.cpp:569)",
@@ -455,27 +498,40 @@ def run_ours(args):
     if world > 1 and not args.no_sharded:
         sharded = sharded_leg(args, plan, blocks, hviews, d_ring, blk_bytes, ring, world, rank, local, barrier, max_over_ranks)
 
-    # ---- the two opt-in channelizers (NOT the parity path, not the headline): same workload, same value leg
+    # ---- the other channelizers on the same workload, same value leg (the time-domain bank also with its FP32 roofline)
     alt = None
     if world == 1 and not args.no_alt:
         alt = {}
-        for name, kw in (("table_gemm", {"table_gemm": True}), ("polyphase", {"polyphase": True})):
-            aeng = Engine(plan, device=local, **kw)
+        acc = {"bank": "bit-comparable path: channel IQ <= 4.4e-5 rel. RMS per channel, audio 2.1e-5, squelch decisions equal (profiles/r02y_tc_report.json)",
+               "tensor_cores": "squelch decisions equal to the oracle's, audio <= 5.4e-5, channel IQ <= 8.2e-5 on every channel that ever opens, "
+                               "1.36e-4 on closed noise-only channels next to strong carriers (profiles/r02y_tc_report.json)",
+               "table_gemm": "squelch decisions equal to the oracle's; channel IQ of closed noise-only channels up to 1.4e-4 rel. RMS, audio 5e-5",
+               "polyphase": "NOT a parity mode: channel IQ up to 1.8e-2 rel. RMS on noise-only channels (exact twiddles vs the reference's "
+                            "float-rounded table), audio 8e-3; squelch decisions equal on this workload (profiles/r02x_channelizers.json)"}
+        for name in ("bank", "tensor_cores", "table_gemm", "polyphase"):
+            if name == mode:
+                continue
+            aeng = Engine(plan, device=local, **MODE_KW[name])
             a_ms, _, _ = value_leg(aeng, args.steps, args.warmup)
             aeng.set_timing(True)
-            aeng.push_device(d_ring, 2, L)
-            aeng.sync()
-            k_ms, _ = aeng.last_timing()
+            ks = []
+            for i in range(5):
+                aeng.push_device(d_ring + i * blk_bytes, 2, L)
+                aeng.sync()
+                ks.append(aeng.last_timing()[0])
             aeng.close()
-            alt[name] = {"ms_per_step": a_ms, "value": C_ * L / (a_ms * 1e-3) / 1e6, "channelizer_kernel_ms": k_ms,
-                         "accuracy": "profiles/r02x_channelizers.json (tools/polyphase_report.py): squelch decisions equal to the oracle's; "
-                                     + ("channel IQ of closed noise-only channels up to 1.4e-4 rel. RMS, audio 5e-5" if name == "table_gemm"
-                                        else "channel IQ up to 1.8e-2 rel. RMS on noise-only channels (exact twiddles vs the reference's float-rounded table), audio 8e-3")}
+            k_ms = statistics.median(ks)
+            alt[name] = {"what": MODE_WHAT[name], "ms_per_step": a_ms, "value": C_ * L / (a_ms * 1e-3) / 1e6, "channelizer_kernel_ms": k_ms,
+                         "accuracy": acc[name]}
+            if name == "bank":
+                alt[name]["roofline"] = {"bound": "fp32", "achieved": FLOP_BANK * C_ * L / (k_ms * 1e-3) / 1e12, "peak": peak, "unit": "TFLOP/s",
+                                         "frac": FLOP_BANK * C_ * L / (k_ms * 1e-3) / 1e12 / peak,
+                                         "chain_frac": FLOP_CHAIN * C_ * L / (a_ms * 1e-3) / 1e12 / peak}
 
     # ---- parity of the bench's own workload against the oracle (--check): every channel, every distinct block
     check = None
     if args.check and rank == 0:
-        check = check_against_oracle(plan, blocks, local)
+        check = check_against_oracle(plan, blocks, local, MODE_KW[mode])
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only): bounded sample of the same workload
     cpu = None
@@ -493,13 +549,16 @@ def run_ours(args):
             "metric": "channel-MS/s", "value": value, "unit": "channel-MS/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per_step_ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "arithmetic": ("FP32 results from bf16 x 9 split operands on tcgen05 (every plane product exact), FP32 accumulation; boundary B in FP32 "
+                           "as the reference" if mode == "tensor_cores" else "FP32 CUDA cores throughout, as the reference"),
             "config": {"workload": desc, "channels": C_, "block_len": L, "sample_rate": RATE, "wire_format": "f32",
                        "parallelism": f"stream-sharded x{world} (one independent 10 MS/s stream per GPU, no collective)",
                        "l2": f"inputs cycle through a {ring}-block device ring ({ring * blk_bytes / 1e6:.0f} MB > 126 MB L2)",
+                       "channelizer": mode + ": " + MODE_WHAT[mode],
                        "specialised_bank": bool(eng.uses_fast_path)},
             "realtime_channels": value / (RATE / 1e6),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
-            "worst_case": worst, "sustained": sustained, "channel_sharded": sharded, "opt_in_channelizers": alt,
+            "worst_case": worst, "sustained": sustained, "channel_sharded": sharded, "other_channelizers": alt,
         }
         if check is not None:
             line["parity_check"] = check
@@ -714,15 +773,16 @@ def sharded_leg(args, plan, blocks, hviews, d_ring, blk_bytes, ring, world, rank
     return out if rank == 0 else None
 
 
-def check_against_oracle(plan, blocks, device):
+def check_against_oracle(plan, blocks, device, mode_kw=None):
     """bench.py --check: the bench's own blocks through the CUDA engine and through the CPU oracle (the checker, never
     the thing measured): squelch decisions must agree exactly, channel IQ / audio within 1e-4 relative RMS per channel."""
     from oracle import bindings as ob
     from sdrx_b200 import Engine
     from tests.harness import product_tables, rel_rms, squelch_margin
     orx = ob.OracleRx(product_tables(RATE), plan.offsets, plan.sql_levels)
-    eng = Engine(plan, device=device)
-    worst_iq = worst_au = 0.0
+    eng = Engine(plan, device=device, **(mode_kw or {}))
+    worst_iq = worst_au = worst_iq_open = 0.0
+    per_block = []
     margin = float("inf")
     sql_ok, opened = True, 0
     for blk in blocks:
@@ -731,14 +791,18 @@ def check_against_oracle(plan, blocks, device):
         sql_ok = sql_ok and bool(np.array_equal(g.sql, w.sql))
         opened += int(w.sql.sum())
         margin = min(margin, squelch_margin(w.snr, np.asarray(plan.sql_levels)))
+        errs = np.asarray([rel_rms(g.ch_iq[c], w.ch_iq[c]) for c in range(len(plan.offsets))])
+        per_block.append((errs, w.sql.copy()))
+        worst_iq = max(worst_iq, float(errs.max()))
         for c in range(len(plan.offsets)):
-            worst_iq = max(worst_iq, rel_rms(g.ch_iq[c], w.ch_iq[c]))
             if np.any(w.audio[c] != 0.0):
                 worst_au = max(worst_au, rel_rms(g.audio[c], w.audio[c]))
     eng.close()
+    ever_open = np.stack([q for _, q in per_block]).any(axis=0)
+    worst_iq_open = float(np.stack([e_ for e_, _ in per_block])[:, ever_open].max()) if ever_open.any() else 0.0
     return {"blocks": len(blocks), "channels": len(plan.offsets), "squelch_decisions_equal": sql_ok,
             "open_channel_blocks": opened, "oracle_squelch_margin_db": margin, "worst_channel_iq_rel_rms": worst_iq,
-            "worst_audio_rel_rms": worst_au, "bar": 1e-4}
+            "worst_channel_iq_rel_rms_channels_ever_open": worst_iq_open, "worst_audio_rel_rms": worst_au, "bar": 1e-4}
 
 
 def main():
@@ -751,8 +815,11 @@ def main():
     ap.add_argument("--seed-rank", type=int, default=-1, help=argparse.SUPPRESS)
     ap.add_argument("--verbose", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--streams", type=int, default=64, help="config4: independent streams over all GPUs")
+    ap.add_argument("--channelizer", default="tensor_cores", choices=list(MODE_KW),
+                    help="boundary A of the measured engine (config3/config2): tensor_cores = fold + table GEMM on tcgen05 (default), "
+                         "bank = the bit-comparable time-domain channel bank, table_gemm / polyphase = the other opt-in forms")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
-    ap.add_argument("--no-alt", action="store_true", help="skip the opt-in channelizer records (table GEMM, polyphase)")
+    ap.add_argument("--no-alt", action="store_true", help="skip the legs of the other channelizers (bank, table GEMM, polyphase)")
     ap.add_argument("--no-worst", action="store_true", help="skip the worst_case leg (every squelch open)")
     ap.add_argument("--sustain", type=float, default=3.2, help="seconds of back-to-back blocks in the sustained leg (0: skip)")
     ap.add_argument("--no-sharded", action="store_true", help="N > 1: skip the channel-sharded (one stream over N GPUs) leg")

@@ -170,8 +170,8 @@ int  sdrx_engine_get_channel_iq(sdrx_engine *e, float *ch_iq);
 int  sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
 /* Streaming form: queue the read-back of the last pushed block and return; push the next block(s) at once (their
  * H2D and kernels overlap this read-back); the host buffers (pinned) are valid after
- * sdrx_engine_wait_outputs(e, back), back = number of blocks pushed since the fetch (0..4: the engine keeps a ring
- * of six output sets, so a caller may run a few blocks ahead of the results it reads -- enough to take the
+ * sdrx_engine_wait_outputs(e, back), back = number of blocks pushed since the fetch (0..8: the engine keeps a ring
+ * of ten output sets, so a caller may run a few blocks ahead of the results it reads -- enough to take the
  * side-stream kernels + device->host->device round trip off the critical path).                                                   */
 int  sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_outputs *out);
 int  sdrx_engine_wait_outputs(sdrx_engine *e, int back);
@@ -193,7 +193,7 @@ int  sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_parts, flo
  *   wait_stream          the next push_block_device's ingest is ordered behind everything queued on `cuda_stream` so far
  *   stream_wait_ingest   `cuda_stream` waits until the last pushed block has been copied out of the caller's buffer
  *   stream_wait_outputs  `cuda_stream` waits until boundary B of the last pushed block is complete
- *   device_outputs       DEVICE pointers of the results of the block pushed `back` pushes ago (0 = last; valid until four
+ *   device_outputs       DEVICE pointers of the results of the block pushed `back` pushes ago (0 = last; valid until eight
  *                        more blocks have been pushed; audio_rows is NULL, audio_chan / n_audio are the device-side list)
  *   finish_mix_async     sdrx_engine_finish_mix with the partials already on the device (`d_parts`, [n_parts][1024]), queued
  *                        on `cuda_stream`; mix_pre / mix / pcm (pinned host, may be NULL) are valid once the caller has

@@ -25,7 +25,7 @@ static_assert(kFastSideSms == kSideSms, "the bank leaves the SMs the side kernel
 namespace {
 
 constexpr int kNBuf = 2;          // ping-pong depth of raw input
-constexpr int kNOut = 6;          // ring of output sets: a streaming caller may run up to kNOut-1 blocks ahead of the results it reads
+constexpr int kNOut = 10;         // ring of output sets: a streaming caller may run up to kNOut-1 blocks ahead of the results it reads
 constexpr int kPwrPartials = 296;     // power CTAs of k_prep: two per SM
 constexpr uint32_t kStateMagic = 0x58524453u;  // "SDRX"
 
@@ -111,8 +111,10 @@ struct sdrx_engine {
     float *d_parts = nullptr;             // staging of the per-GPU partial mixes (sdrx_engine_finish_mix)
     size_t parts_cap = 0;
     float2 *d_agc_iq[2] = {nullptr, nullptr};   // [512][Cpad] gain-adjusted channel IQ, sample-major (k_chan_agc -> k_chan_env), ping-pong
-    float *d_env = nullptr;               // [512][Cpad] envelope / discriminator output (k_chan_env -> k_chan_lfagc)
-    float2 *d_fm_new = nullptr;           // [C] prev_sample of the FM demodulators after this block (k_chan_env -> k_chan_lfagc)
+    float *d_env[2] = {nullptr, nullptr}; // [512][Cpad] envelope / discriminator output (k_chan_env -> k_chan_lfagc), ping-pong
+    float2 *d_fm[2] = {nullptr, nullptr}; // [C] Demod::prev_sample (sdrx.cpp:202) as a ping-pong pair: d_fm[0] is st.fm_prev's allocation; block b's
+                                          // envelope reads d_fm[fm_cur] and writes the other one for every channel
+    int fm_cur = 0;
     // debug timeline (sdrx_debug_timeline): completion time of every kernel of the last kTlBlocks blocks
     static constexpr int kTlBlocks = 16, kTlKinds = 10;
     bool tl_on = false;
@@ -163,7 +165,8 @@ struct sdrx_engine {
     int phase[SDRX_MAX_STAGES] = {0};    // inputs seen since the stage's last output (m - isn_)
     int ft_k = 0;                        // S::k_ of stage 0 (msd.hpp:434), same for every channel
     int fmt = -1;                        // wire format of the stream so far
-    uint64_t blocks = 0;                 // output sets handed out so far (push_block and demod_block): selects out[blocks % kNOut]
+    int ring = kNOut;                    // output sets in use (<= kNOut; SDRX_RING overrides it for experiments)
+    uint64_t blocks = 0;                 // output sets handed out so far (push_block and demod_block): selects out[blocks % e->ring]
     uint64_t pushes = 0;                 // blocks through the channelizer: its parity selects the raw ping-pong buffer
     unsigned prev_n = 0;                 // samples of the previous block (for the raw carry)
     uint64_t total = 0;                  // samples pushed so far (what of the raw history belongs to the stream)
@@ -299,7 +302,8 @@ int reset_state(sdrx_engine *e) {
         CU(cudaMemsetAsync(e->st.sql_state, 0, C, e->s_main));
         CU(cudaMemsetAsync(e->st.sql_prev, 0, C, e->s_main));
         for (int b = 0; b < kNOut; ++b) CU(cudaMemsetAsync(e->out[b].mixed, 0, (size_t)e->Cpad, e->s_main));
-        CU(cudaMemsetAsync(e->st.fm_prev, 0, C * sizeof(float2), e->s_main));
+        CU(cudaMemsetAsync(e->d_fm[0], 0, C * sizeof(float2), e->s_main));
+        CU(cudaMemsetAsync(e->d_fm[1], 0, C * sizeof(float2), e->s_main));
         CU(cudaMemsetAsync(e->d_fir_hist, 0, sizeof(float) * e->NS * 2 * (size_t)std::max(e->fir2_ntaps - 1, 1), e->s_main));
         CU(cudaMemsetAsync(e->d_ticket, 0, 2 * sizeof(unsigned) * e->NS, e->s_main));
         CU(cudaStreamSynchronize(e->s_main));   // the host vectors above die here
@@ -350,12 +354,12 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     for (int s = 0; s < SDRX_MAX_STAGES; ++s) cudaFree(e->d_stage_in[s]);
     cudaFree(e->d_table_t); cudaFree(e->d_has_tr); cudaFree(e->d_taps); cudaFree(e->d_hk);
     cudaFree(e->st.agc_gain); cudaFree(e->st.agc_power); cudaFree(e->st.lf_gain); cudaFree(e->st.lf_power);
-    cudaFree(e->st.fm_prev); cudaFree(e->d_mod);
+    cudaFree(e->d_fm[0]); cudaFree(e->d_fm[1]); cudaFree(e->d_mod);
     cudaFree(e->st.sql_state); cudaFree(e->st.sql_prev);
     cudaFree(e->d_window); cudaFree(e->d_shape); cudaFree(e->d_ramp_up); cudaFree(e->d_ramp_down);
     cudaFree(e->d_twiddle); cudaFree(e->d_bitrev); cudaFree(e->d_sql_level); cudaFree(e->d_pos);
     cudaFree(e->d_c_adj); cudaFree(e->d_fir_hist); cudaFree(e->d_parts); cudaFree(e->d_ticket); cudaFree(e->d_rows_scratch[0]); cudaFree(e->d_rows_scratch[1]);
-    cudaFree(e->d_agc_iq[0]); cudaFree(e->d_agc_iq[1]); cudaFree(e->d_env); cudaFree(e->d_fm_new);
+    cudaFree(e->d_agc_iq[0]); cudaFree(e->d_agc_iq[1]); cudaFree(e->d_env[0]); cudaFree(e->d_env[1]);
     for (int b = 0; b < 2; ++b) { if (e->ev_agc_done[b]) cudaEventDestroy(e->ev_agc_done[b]); if (e->ev_env_done[b]) cudaEventDestroy(e->ev_env_done[b]); }
     cudaFree(e->d_hc); cudaFree(e->d_wtab); cudaFree(e->d_bin);
     for (int b = 0; b < sdrx_engine::kNFin; ++b) { cudaFree(e->d_fin_mix_pre[b]); cudaFree(e->d_fin_mix[b]); cudaFree(e->d_fin_pcm[b]); }
@@ -386,6 +390,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     const int NS = std::max(cfg->n_streams, 1), Cs = cfg->n_channels;
     const int C = NS * Cs, S = cfg->n_stages;            // per-channel arrays below: stream-major, the plan repeated per stream
     e->dev = cfg->device;
+    if (const char *er = getenv("SDRX_RING")) e->ring = std::min(kNOut, std::max(3, atoi(er)));
     e->flags = cfg->flags;
     e->NS = NS; e->Cs = Cs;
     e->C = C;
@@ -457,7 +462,13 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         e->raw_hist = std::max(e->raw_hist, (std::max(lh - (int)d_all, e->mat_len) + 7) / 8 * 8);
     }
 
-    CU(cudaStreamCreateWithFlags(&e->s_main, cudaStreamNonBlocking));
+    {
+        // experiment knob: SDRX_MAIN_PRIO = 1 puts the channelizer stream at the highest priority too (its whole-SM CTAs first in line)
+        int lo = 0, hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        const char *mp = getenv("SDRX_MAIN_PRIO");
+        CU(cudaStreamCreateWithPriority(&e->s_main, cudaStreamNonBlocking, (mp && atoi(mp) == 1) ? hi : lo));
+    }
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_side, cudaStreamNonBlocking));
     {
@@ -598,6 +609,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             if ((rc = tc_init(e->tc, e->tg, cfg->translators, has_v.data(), e->tg.h_slot_chan, ep ? atoi(ep) : 9, es ? atoi(es) : 1, ec ? atoi(ec) : 1, bf16_map)))
                 return rc;
             if ((rc = raise_dyn_smem(tc_kernel_ptr(e->tc.products, e->tc.steps), kTcSmem))) return rc;
+            if (const char *ed = getenv("SDRX_TC_DEBUG")) e->tc.debug = atoi(ed);   // timing experiments only: results are wrong
             e->use_tc = true;
         }
     } else if (want_tgemm) {
@@ -648,7 +660,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if ((rc = dalloc(&e->st.agc_gain, C)) || (rc = dalloc(&e->st.agc_power, C)) ||
             (rc = dalloc(&e->st.lf_gain, C)) || (rc = dalloc(&e->st.lf_power, C)) ||
             (rc = dalloc(&e->st.sql_state, C)) || (rc = dalloc(&e->st.sql_prev, C)) ||
-            (rc = dalloc(&e->st.fm_prev, C)) || (rc = dalloc(&e->d_mod, C)))
+            (rc = dalloc(&e->d_fm[0], C)) || (rc = dalloc(&e->d_fm[1], C)) || (rc = dalloc(&e->d_mod, C)))
             return rc;
         {
             std::vector<uint8_t> mod(C, SDRX_MOD_AM);
@@ -695,8 +707,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         if ((rc = dalloc(&e->d_ticket, 2 * (size_t)NS))) return rc;
         if ((rc = raise_dyn_smem((const void *)k_chan_agc, kAgcSmem)) || (rc = raise_dyn_smem((const void *)k_chan_lfagc, kLfSmem)))
             return rc;
-        if ((rc = dalloc(&e->d_agc_iq[0], (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_agc_iq[1], (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_env, (size_t)e->Cpad * kChunk)) ||
-            (rc = dalloc(&e->d_fm_new, C)))
+        if ((rc = dalloc(&e->d_agc_iq[0], (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_agc_iq[1], (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_env[0], (size_t)e->Cpad * kChunk)) ||
+            (rc = dalloc(&e->d_env[1], (size_t)e->Cpad * kChunk)))
             return rc;
         e->tb = DemodTables{e->d_window, e->d_twiddle, e->d_bitrev, e->d_shape, e->d_ramp_up, e->d_ramp_down};
         if ((size_t)C * 4 > 160 * 1024) return fail(SDRX_ERR_UNSUPPORTED, "more than 40960 channels per engine");
@@ -737,6 +749,8 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     }
     if (NS > 1 && !e->use_fast && !e->use_tgemm)
         return fail(SDRX_ERR_UNSUPPORTED, "a multi-stream engine needs the specialised channel bank (the 10 MS/s chain, translator tables, no --ftfir / FORCE_GENERIC)");
+    // dalloc's memsets were queued on the legacy default stream, which the engine's non-blocking streams never wait for
+    CU(cudaDeviceSynchronize());
     return reset_state(e);
 }
 
@@ -969,21 +983,29 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
     // the AGC runs whatever the squelch state (sdrx.cpp:457): next to the detector, not behind it -- and on a stream of its
     // own, so that block b + 1's AGC recurrence runs next to block b's LfAGC recurrence (gain-adjusted IQ in a ping-pong)
     const unsigned par = e->agc_par++ & 1u;
-    if (e->env_pending[par]) CU(cudaStreamWaitEvent(e->s_recur, e->ev_env_done[par], 0));
+    // ... where boundary A is short (table GEMM / polyphase) and boundary B sets the step.  Under the time-domain bank the
+    // recurrences have the three SMs its schedule leaves free and a whole bank's time: one stream, so that two blocks'
+    // recurrence CTAs never hold more SMs than that when the next bank launch needs its own
+    cudaStream_t s_lf = (e->use_tgemm || e->poly) ? e->s_lf : e->s_recur;
     k_chan_agc<<<recur_ctas(e->C), kRecurThreads, kAgcSmem, e->s_recur>>>(o.iq_map, e->st, e->agc, e->d_agc_iq[par], e->Cpad, snap, e->C);
     tl_mark(e, TL_AGC, e->s_recur);
+    // the envelope follows the AGC on its stream (it needs the detector's gate); the LfAGC recurrence has a stream to itself
+    if (e->env_pending[par]) CU(cudaStreamWaitEvent(e->s_recur, e->ev_env_done[par], 0));   // the LfAGC of two blocks ago read d_env[par]
+    CU(cudaStreamWaitEvent(e->s_recur, e->ev_det_done[idx], 0));
+    ChannelState st_env = e->st;
+    st_env.fm_prev = e->d_fm[e->fm_cur];
+    k_chan_env<<<dim3(e->Cpad / 32, kChunk / 4), dim3(32, 4), 0, e->s_recur>>>(e->d_agc_iq[par], e->Cpad, st_env, e->d_gate[idx], e->d_env[par],
+                                                                                e->d_fm[e->fm_cur ^ 1], e->C);
+    e->fm_cur ^= 1;
+    tl_mark(e, TL_ENV, e->s_recur);
     CU(cudaEventRecord(e->ev_agc_done[par], e->s_recur));
-    CU(cudaStreamWaitEvent(e->s_lf, e->ev_agc_done[par], 0));
-    CU(cudaStreamWaitEvent(e->s_lf, e->ev_det_done[idx], 0));
-    k_chan_env<<<dim3(e->Cpad / 32, kChunk / 4), dim3(32, 4), 0, e->s_lf>>>(e->d_agc_iq[par], e->Cpad, e->st, e->d_gate[idx], e->d_env,
-                                                                             e->d_fm_new, e->C);
-    tl_mark(e, TL_ENV, e->s_lf);
-    CU(cudaEventRecord(e->ev_env_done[par], e->s_lf));
+    CU(cudaStreamWaitEvent(s_lf, e->ev_agc_done[par], 0));
+    k_chan_lfagc<<<recur_ctas(e->C), kRecurThreads, kLfSmem, s_lf>>>(e->d_env[par], e->Cpad, e->st, e->d_gate[idx], e->tb, e->lf, e->lf_active, o.audio, snap,
+                                                        e->C, o.mixed);
+    tl_mark(e, TL_LFAGC, s_lf);
+    CU(cudaEventRecord(e->ev_env_done[par], s_lf));          // d_env[par] (and with it d_agc_iq[par]) are free again
     e->env_pending[par] = true;
-    k_chan_lfagc<<<recur_ctas(e->C), kRecurThreads, kLfSmem, e->s_lf>>>(e->d_env, e->Cpad, e->st, e->d_gate[idx], e->tb, e->lf, e->lf_active, o.audio, snap,
-                                                        e->C, o.mixed, e->d_fm_new);
-    tl_mark(e, TL_LFAGC, e->s_lf);
-    CU(cudaEventRecord(e->ev_recur_done[idx], e->s_lf));
+    CU(cudaEventRecord(e->ev_recur_done[idx], s_lf));
     CU(cudaStreamWaitEvent(e->s_mix, e->ev_recur_done[idx], 0));
     e->launches += 4;
     int rc = launch_mix(e, e->s_mix, o, e->d_pwr_partial[idx], have_power ? kPwrPartials : 0, n_samples,
@@ -1078,7 +1100,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     e->fmt = fmt;
     const int bps = raw_bytes_per_sample(fmt);
     const int cur = (int)(e->pushes & 1), prv = cur ^ 1;      // raw ping-pong
-    const int oc = (int)(e->blocks % kNOut);                 // output set of this block
+    const int oc = (int)(e->blocks % e->ring);                 // output set of this block
     uint8_t *buf = e->d_raw[cur];
     const size_t hist_bytes = (size_t)e->raw_hist * bps;
 
@@ -1317,8 +1339,8 @@ extern "C" int sdrx_engine_get_channel_iq(sdrx_engine *e, float *ch_iq) {
     if (!e || !ch_iq) return fail(SDRX_ERR_ARG, "null argument");
     if (e->blocks == 0) return fail(SDRX_ERR_STATE, "no block pushed yet");
     DevGuard g(e->dev);
-    const OutSet &o = e->out[(e->blocks - 1) % kNOut];
-    { int rc = wait_side(e, (int)((e->blocks - 1) % kNOut)); if (rc) return rc; }   // the last stage may run on a side stream
+    const OutSet &o = e->out[(e->blocks - 1) % e->ring];
+    { int rc = wait_side(e, (int)((e->blocks - 1) % e->ring)); if (rc) return rc; }   // the last stage may run on a side stream
     if (e->last_out_len > 0)
         CU(cudaMemcpy2DAsync(ch_iq, (size_t)e->last_out_len * sizeof(float2), o.ch_iq, (size_t)e->chiq_stride * sizeof(float2),
                              (size_t)e->last_out_len * sizeof(float2), (size_t)e->C, cudaMemcpyDeviceToHost, e->s_main));
@@ -1332,8 +1354,8 @@ extern "C" int sdrx_engine_get_outputs(sdrx_engine *e, const sdrx_block_outputs 
     if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
     if (!e->last_demod) return fail(SDRX_ERR_STATE, "the last block did not yield 512 samples per channel; boundary B did not run");
     DevGuard g(e->dev);
-    int rc = wait_side(e, (int)((e->blocks - 1) % kNOut));
-    if (!rc) rc = copy_outputs(e, e->out[(e->blocks - 1) % kNOut], out, e->s_main, true);
+    int rc = wait_side(e, (int)((e->blocks - 1) % e->ring));
+    if (!rc) rc = copy_outputs(e, e->out[(e->blocks - 1) % e->ring], out, e->s_main, true);
     if (rc) return rc;
     CU(cudaStreamSynchronize(e->s_main));
     return SDRX_OK;
@@ -1349,7 +1371,7 @@ extern "C" int sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_output
     if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
     if (!e->last_demod) return fail(SDRX_ERR_STATE, "the last block did not yield 512 samples per channel; boundary B did not run");
     DevGuard g(e->dev);
-    const int idx = (int)((e->blocks - 1) % kNOut);
+    const int idx = (int)((e->blocks - 1) % e->ring);
     if (e->side_pending[idx]) CU(cudaStreamWaitEvent(e->s_out, e->ev_side_done[idx], 0));
     int rc = copy_outputs(e, e->out[idx], out, e->s_out, false);
     if (rc) return rc;
@@ -1359,10 +1381,10 @@ extern "C" int sdrx_engine_fetch_outputs(sdrx_engine *e, const sdrx_block_output
 }
 
 extern "C" int sdrx_engine_wait_outputs(sdrx_engine *e, int back) {
-    if (!e || back < 0 || back > kNOut - 2) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) .. 4");
+    if (!e || back < 0 || back > e->ring - 2) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) .. 8");
     if (e->blocks < (uint64_t)back + 1) return fail(SDRX_ERR_STATE, "no such block");
     DevGuard g(e->dev);
-    const int idx = (int)((e->blocks - 1 - back) % kNOut);
+    const int idx = (int)((e->blocks - 1 - back) % e->ring);
     if (!e->fetch_pending[idx]) return fail(SDRX_ERR_STATE, "no fetch was queued for that block");
     CU(cudaEventSynchronize(e->ev_fetch_done[idx]));
     return SDRX_OK;
@@ -1372,7 +1394,7 @@ extern "C" int sdrx_engine_demod_block(sdrx_engine *e, const float *ch_iq, float
     if (!e || !ch_iq) return fail(SDRX_ERR_ARG, "null argument");
     if (e->flags & SDRX_FLAG_NO_DEMOD) return fail(SDRX_ERR_STATE, "engine was created with SDRX_FLAG_NO_DEMOD");
     DevGuard g(e->dev);
-    const int idx = (int)(e->blocks % kNOut);
+    const int idx = (int)(e->blocks % e->ring);
     OutSet &o = e->out[idx];
     { int rc = wait_side(e, idx); if (rc) return rc; }
     CU(cudaMemcpy2DAsync(o.ch_iq, (size_t)e->chiq_stride * sizeof(float2), ch_iq, (size_t)kChunk * sizeof(float2),
@@ -1400,7 +1422,7 @@ extern "C" int sdrx_engine_finish_mix(sdrx_engine *e, const float *parts, int n_
         CU(cudaMalloc((void **)&e->d_parts, bytes));
         e->parts_cap = (size_t)n_parts;
     }
-    const int idx = e->blocks ? (int)((e->blocks - 1) % kNOut) : 0;
+    const int idx = e->blocks ? (int)((e->blocks - 1) % e->ring) : 0;
     OutSet &o = e->out[idx];
     { int rc = wait_side(e, idx); if (rc) return rc; }
     CU(cudaMemcpyAsync(e->d_parts, parts, bytes, cudaMemcpyHostToDevice, e->s_main));
@@ -1462,15 +1484,15 @@ extern "C" int sdrx_engine_stream_wait_outputs(sdrx_engine *e, void *cuda_stream
     if (!e) return fail(SDRX_ERR_ARG, "null engine");
     if (e->blocks == 0) return SDRX_OK;
     DevGuard g(e->dev);
-    const int idx = (int)((e->blocks - 1) % kNOut);
+    const int idx = (int)((e->blocks - 1) % e->ring);
     if (e->side_pending[idx]) CU(cudaStreamWaitEvent((cudaStream_t)cuda_stream, e->ev_side_done[idx], 0));
     else CU(cudaStreamWaitEvent((cudaStream_t)cuda_stream, e->ev_head_done, 0));
     return SDRX_OK;
 }
 extern "C" int sdrx_engine_device_outputs(sdrx_engine *e, int back, sdrx_block_outputs *dev) {
-    if (!e || !dev || back < 0 || back > kNOut - 2) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) .. 4");
+    if (!e || !dev || back < 0 || back > e->ring - 2) return fail(SDRX_ERR_ARG, "back must be 0 (last pushed block) .. 8");
     if (e->blocks < (uint64_t)back + 1) return fail(SDRX_ERR_STATE, "no such block");
-    const OutSet &o = e->out[(e->blocks - 1 - back) % kNOut];
+    const OutSet &o = e->out[(e->blocks - 1 - back) % e->ring];
     memset(dev, 0, sizeof(*dev));
     dev->audio = nullptr;         /* on the device the audio is sample-major: not part of this view */
     dev->sql_state = o.sql; dev->snr = o.snr; dev->mix_pre = o.mix_pre; dev->mix = o.mix; dev->pcm = o.pcm;
@@ -1656,7 +1678,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
         CU(cudaMemcpy(p, e->st.lf_power, C * 4, cudaMemcpyDeviceToHost)); p += C * 4;
         CU(cudaMemcpy(p, e->st.sql_state, C, cudaMemcpyDeviceToHost)); p += C;
         CU(cudaMemcpy(p, e->st.sql_prev, C, cudaMemcpyDeviceToHost)); p += C;
-        CU(cudaMemcpy(p, e->st.fm_prev, C * sizeof(float2), cudaMemcpyDeviceToHost)); p += C * sizeof(float2);
+        CU(cudaMemcpy(p, e->d_fm[e->fm_cur], C * sizeof(float2), cudaMemcpyDeviceToHost)); p += C * sizeof(float2);
         const size_t fb = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1);
         if (fb) CU(cudaMemcpy(p, e->d_fir_hist, fb, cudaMemcpyDeviceToHost));
         p += fb;
@@ -1710,7 +1732,7 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
         CU(cudaMemcpy(e->st.lf_power, p, C * 4, cudaMemcpyHostToDevice)); p += C * 4;
         CU(cudaMemcpy(e->st.sql_state, p, C, cudaMemcpyHostToDevice)); p += C;
         CU(cudaMemcpy(e->st.sql_prev, p, C, cudaMemcpyHostToDevice)); p += C;
-        CU(cudaMemcpy(e->st.fm_prev, p, C * sizeof(float2), cudaMemcpyHostToDevice)); p += C * sizeof(float2);
+        CU(cudaMemcpy(e->d_fm[e->fm_cur], p, C * sizeof(float2), cudaMemcpyHostToDevice)); p += C * sizeof(float2);
         const size_t fb = sizeof(float) * 2 * (size_t)(e->fir2_ntaps - 1);
         if (fb) CU(cudaMemcpy(e->d_fir_hist, p, fb, cudaMemcpyHostToDevice));
         p += fb;

@@ -167,14 +167,14 @@ k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int val
 template <int kProducts, int kSteps>
 static __global__ void __launch_bounds__(kTcThreads, 1)
 k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int rows_pad, int cols, int N,
-           const int *__restrict__ slot_chan, int chans_per_stream, float2 *__restrict__ ch_iq, long iq_stride, int n_out, int cl) {
+           const int *__restrict__ slot_chan, int chans_per_stream, float2 *__restrict__ ch_iq, long iq_stride, int n_out, int cl, int dbg) {
     extern __shared__ unsigned char tc_smem_raw[];
     unsigned char *sm = reinterpret_cast<unsigned char *>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);   // swizzle atoms: 1024-byte aligned
     uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (size_t)kTcStages * kTcStageBytes);
     uint64_t *full = bars, *empty = bars + kTcStages, *tfull = bars + 2 * kTcStages, *tempty = tfull + kTcAcc;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + kTcAcc);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_kb = (N + kTcK - 1) / kTcK;                       // staged k-blocks (the last one zero-filled past N by the TMA unit)
+    const int n_kb = (N + kTcK - 1) / kTcK;                       // staged k-blocks (the planes are zero past N)
     const int n_ks = (N + kTcKStep - 1) / kTcKStep;               // k-steps that hold any table entry
     const int n_units = (n_ks + kSteps - 1) / kSteps;
 
@@ -199,6 +199,7 @@ k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
             for (int kb = 0; kb < n_kb; ++kb) {
                 const int st = kb % kTcStages;
                 mbar_wait(empty + st, ((unsigned)(kb / kTcStages) & 1u) ^ 1u);
+                if (dbg & 2) { mbar_arrive(full + st); continue; }   // timing experiment (SDRX_TC_DEBUG=2): no operand loads, wrong results
                 mbar_expect_tx(full + st, (unsigned)kTcStageBytes);
                 unsigned char *a = sm + (size_t)st * kTcStageBytes, *b = a + kTcPlanes * kTcABytes;
                 if (cl > 1) {
@@ -242,8 +243,9 @@ k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
                 const uint32_t sb = sa + kTcPlanes * kTcABytes;
 #pragma unroll
                 for (int q = first_prod; q < 9; ++q)
+                    if (!(dbg & 1) || q == 8)                     // timing experiment (SDRX_TC_DEBUG=1): one product instead of nine, wrong results
                     tc_mma_bf16(tmem + acc * kTcCols, tc_smem_desc(sa + pa[q] * kTcABytes), tc_smem_desc(sb + pb[q] * kTcBBytes), kTcIdesc,
-                                (unit_first && q == first_prod) ? 0u : 1u);
+                                (unit_first && (q == first_prod || (dbg & 1))) ? 0u : 1u);
                 const bool last = ks == n_ks - 1;
                 if ((ks % kSteps) == kSteps - 1 || last) { tc_commit(tfull + acc); ++unit; }
                 if (sub == 3 || last) { if (cl > 1) tc_commit_mc(empty + st, mc_mask); else tc_commit(empty + st); }
@@ -298,7 +300,7 @@ k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
 // ---- host side
 struct TcGemm {
     bool enabled = false;
-    int rows_pad = 0, cols = 0, Kp = 0, products = 9, steps = 1, cluster = 1;
+    int rows_pad = 0, cols = 0, Kp = 0, products = 9, steps = 1, cluster = 1, debug = 0;
     __nv_bfloat16 *d_a = nullptr;      // [3][rows_pad][Kp]
     __nv_bfloat16 *d_b = nullptr;      // [n_streams][3][cols][Kp]
     int *d_row_chan = nullptr;         // [rows_pad]
@@ -327,7 +329,7 @@ int tc_init(TcGemm &tc, const TableGemm &tg, const float *tables, const uint8_t 
     tc.products = products == 6 ? 6 : 9;
     tc.steps = steps == 4 ? 4 : (steps == 2 ? 2 : 1);
     tc.cluster = (cluster == 2 || cluster == 4 || cluster == 8) ? cluster : 1;
-    tc.Kp = N;
+    tc.Kp = (N + kTcK - 1) / kTcK * kTcK;                      // row pitch a multiple of 128 bytes: every box row is one aligned L2 line
     tc.rows_pad = (2 * tg.slots + kTcRows - 1) / kTcRows * kTcRows;
     tc.cols = (2 * tg.Mpad + kTcCols - 1) / kTcCols * kTcCols;
     std::vector<uint16_t> a((size_t)kTcPlanes * tc.rows_pad * tc.Kp, 0);
@@ -355,8 +357,8 @@ int tc_init(TcGemm &tc, const TableGemm &tg, const float *tables, const uint8_t 
     CU(cudaMalloc((void **)&tc.d_row_chan, sizeof(int) * row_chan.size()));
     CU(cudaMemcpy(tc.d_row_chan, row_chan.data(), sizeof(int) * row_chan.size(), cudaMemcpyHostToDevice));
     int rc;
-    if ((rc = make_map(&tc.map_a, tc.d_a, (uint64_t)N, (uint64_t)kTcPlanes * tc.rows_pad, (uint64_t)tc.Kp * 2, kTcK, kTcRows / tc.cluster))) return rc;
-    if ((rc = make_map(&tc.map_b, tc.d_b, (uint64_t)N, (uint64_t)tg.n_streams * kTcPlanes * tc.cols, (uint64_t)tc.Kp * 2, kTcK, kTcCols))) return rc;
+    if ((rc = make_map(&tc.map_a, tc.d_a, (uint64_t)tc.Kp, (uint64_t)kTcPlanes * tc.rows_pad, (uint64_t)tc.Kp * 2, kTcK, kTcRows / tc.cluster))) return rc;
+    if ((rc = make_map(&tc.map_b, tc.d_b, (uint64_t)tc.Kp, (uint64_t)tg.n_streams * kTcPlanes * tc.cols, (uint64_t)tc.Kp * 2, kTcK, kTcCols))) return rc;
     tc.enabled = true;
     return SDRX_OK;
 }
@@ -383,7 +385,7 @@ int tgemm_tc_launch(TableGemm &tg, TcGemm &tc, cudaStream_t st, const void *raw,
     lc.attrs = at; lc.numAttrs = cl > 1 ? 1 : 0;
 #define SDRX_TC_GO(P, S)                                                                                                                    \
     CU(cudaLaunchKernelEx(&lc, k_tgemm_tc<P, S>, tc.map_a, tc.map_b, tc.rows_pad, tc.cols, tg.N, (const int *)tc.d_row_chan, tg.chans, ch_iq, \
-                          iq_stride, n_out, cl))
+                          iq_stride, n_out, cl, tc.debug))
     if (tc.products == 6) { if (tc.steps == 4) SDRX_TC_GO(6, 4); else if (tc.steps == 2) SDRX_TC_GO(6, 2); else SDRX_TC_GO(6, 1); }
     else                  { if (tc.steps == 4) SDRX_TC_GO(9, 4); else if (tc.steps == 2) SDRX_TC_GO(9, 2); else SDRX_TC_GO(9, 1); }
 #undef SDRX_TC_GO
