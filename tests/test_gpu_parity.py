@@ -602,7 +602,7 @@ def test_streaming_fetch_equals_blocking_get_outputs(lag):
         assert np.array_equal(g["snr"], r.snr, equal_nan=True) and np.array_equal(g["mix"], r.mix)
         assert np.array_equal(g["pcm"], r.pcm) and np.array_equal(g["agc_gain"], r.agc_gain)
     with pytest.raises(Exception):
-        eng.wait_outputs(5)
+        eng.wait_outputs(9)                          # the ring holds ten output sets: back = 0 .. 8
     eng.close()
 
 
