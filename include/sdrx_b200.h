@@ -270,6 +270,15 @@ typedef struct sdrx_agc_state {   /* agc.hpp:72-79 / :134-142 */
 } sdrx_agc_state;
 int sdrx_agc_adjust(int device, sdrx_agc_state *s, const float *in, unsigned n, float *out);    /* agc.hpp:48  */
 int sdrx_lfagc_adjust(int device, sdrx_agc_state *s, const float *in, unsigned n, float *out);  /* agc.hpp:106 */
+/* sdrx_agc_adjust for callers that may not allocate (tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in
+ * the reference.  Same arguments, same results bit for bit, but the staged input,
+ * output and (gain, power) live in one fixed device array inside the library (129 KB on every GPU that loads it, until exit)
+ * instead of grow-only cudaMalloc'ed buffers: the call allocates nothing, on the device or through any library.  At most
+ * SDRX_AGC_NOALLOC_MAX complex samples per call (SDRX_ERR_ARG beyond that).  Every call on a device shares the array: calls are
+ * serialised by a mutex and synchronous, so they never overlap on the GPU through this entry point; a caller that reaches the
+ * same device from another process image or bypasses the mutex would race.                                                   */
+#define SDRX_AGC_NOALLOC_MAX 8192u
+int sdrx_agc_adjust_noalloc(int device, sdrx_agc_state *s, const float *in, unsigned n, float *out);
 
 typedef struct sdrx_fir sdrx_fir;
 /* kind 1 FIR (fir.hpp:78), 2 FIR2 (fir.hpp:130), 3 FIR3<iqsample_t> (fir.hpp:28) */

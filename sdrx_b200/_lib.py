@@ -110,6 +110,7 @@ PROTOTYPES = [
     ("sdrx_msd_decimate", C.c_int, [C.c_void_p, c_float_p, C.c_size_t, c_float_p, C.POINTER(C.c_size_t)]),
     ("sdrx_agc_adjust", C.c_int, [C.c_int, C.POINTER(AgcState), c_float_p, C.c_uint, c_float_p]),
     ("sdrx_lfagc_adjust", C.c_int, [C.c_int, C.POINTER(AgcState), c_float_p, C.c_uint, c_float_p]),
+    ("sdrx_agc_adjust_noalloc", C.c_int, [C.c_int, C.POINTER(AgcState), c_float_p, C.c_uint, c_float_p]),
     ("sdrx_fir_create", C.c_int, [C.c_int, c_float_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
     ("sdrx_fir_clone", C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
     ("sdrx_fir_destroy", None, [C.c_void_p]),

@@ -214,6 +214,48 @@ extern "C" int sdrx_lfagc_adjust(int device, sdrx_agc_state *s, const float *in,
     return agc_run<true>(device, s, in, n, out);
 }
 
+// ---- sdrx_agc_adjust without any allocation (no counterpart in the reference)
+// The scratch sdrx_agc_adjust keeps in grow-only cudaMalloc'ed buffers -- the staged input, the staged output and the
+// (gain, power) pair -- lives in ONE file-scope device array of a fixed size instead: every GPU that loads the library
+// holds these 129 KB until exit.  In host code `g_agc_static` is only a stand-in for the symbol; the device address comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+constexpr unsigned kAgcStaticMax = SDRX_AGC_NOALLOC_MAX;          // complex samples per call
+static __device__ __align__(256) float g_agc_static[2 * kAgcStaticMax /* in */ + 2 * kAgcStaticMax /* out */ + 64 /* gain, power */];
+namespace {
+std::mutex g_agc_static_mu;
+float *g_agc_static_ptr[64] = {};
+}  // namespace
+
+extern "C" int sdrx_agc_adjust_noalloc(int device, sdrx_agc_state *s, const float *in, unsigned n, float *out) {
+    if (!s || (!in && n) || (!out && n)) return fail(SDRX_ERR_ARG, "null argument");
+    if (n > kAgcStaticMax)
+        return fail(SDRX_ERR_ARG, "sdrx_agc_adjust_noalloc: " + std::to_string(n) + " samples in one call, the static scratch holds " +
+                                      std::to_string(kAgcStaticMax) + " (SDRX_AGC_NOALLOC_MAX): split the call or use sdrx_agc_adjust");
+    if (n == 0) return SDRX_OK;
+    if (device < 0 || device >= 64) return fail(SDRX_ERR_ARG, "device ordinal out of range");
+    DevGuard g(device);
+    if (!g.ok) return fail(SDRX_ERR_CUDA, "no CUDA device: sdrx_b200 has no CPU path");
+    std::lock_guard<std::mutex> lk(g_agc_static_mu);             // calls share the one array: serialised here, and synchronous below
+    float *base = g_agc_static_ptr[device];
+    if (!base) {
+        CU(cudaGetSymbolAddress((void **)&base, g_agc_static));  // this device's copy of the array (the device is current)
+        g_agc_static_ptr[device] = base;
+    }
+    float *d_in = base, *d_out = base + 2 * kAgcStaticMax, *d_gp = base + 4 * kAgcStaticMax;
+    // nothing has to start at zero: the n input samples and (gain, power) are overwritten here, the kernel writes all n outputs,
+    // and only those are read back -- what an earlier call left behind in the rest of the array is never looked at
+    float gp[2] = {s->gain, s->power};
+    CU(cudaMemcpy(d_in, in, (size_t)n * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d_gp, gp, 8, cudaMemcpyHostToDevice));
+    AgcParams a{s->attack, s->decay, s->reference, s->min_gain, s->max_gain, s->alpha};
+    k_agc_adjust<<<1, 1>>>((const float2 *)d_in, n, (float2 *)d_out, a, d_gp);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(out, d_out, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(gp, d_gp, 8, cudaMemcpyDeviceToHost));
+    s->gain = gp[0]; s->power = gp[1];
+    return SDRX_OK;
+}
+
 // ---------------------------------------------------------------------- FIR / FIR2 / FIR3 (fir.hpp)
 struct sdrx_fir {
     int kind = 1, device = 0, n = 0;

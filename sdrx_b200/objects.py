@@ -102,6 +102,18 @@ class AGC:
                                        _fp(out.view(np.float32))))
         return out
 
+    def adjust_noalloc(self, x: np.ndarray) -> np.ndarray:
+        """``adjust`` through sdrx_agc_adjust_noalloc: the fixed device array inside the library as scratch, no allocation;
+        at most ``AGC_NOALLOC_MAX`` samples per call."""
+        x = np.ascontiguousarray(x, np.complex64)
+        out = np.empty_like(x)
+        check(self.lib.sdrx_agc_adjust_noalloc(self.device, C.byref(self.s), _fp(x.view(np.float32)), x.size,
+                                               _fp(out.view(np.float32))))
+        return out
+
+
+AGC_NOALLOC_MAX = 8192      # SDRX_AGC_NOALLOC_MAX (include/sdrx_b200.h)
+
 
 class LfAGC(AGC):
     _lf = True
