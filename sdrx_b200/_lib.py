@@ -5,7 +5,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libsdrx_b200.so")
+LIB_PATH = os.environ.get("SDRX_B200_LIB") or os.path.join(HERE, "libsdrx_b200.so")   # the override is for A/B runs of two builds
 
 c_float_p = C.POINTER(C.c_float)
 c_int_p = C.POINTER(C.c_int)

@@ -667,3 +667,32 @@ def test_bank_trace_reports_every_cta_of_the_schedule():
     assert np.all(t[:, :, 1] > t[:, :, 0])
     span_us = (t[:, :, 1].max() - t[:, :, 0].min()) / 1e3
     assert 0.5 * bank_ms * 1e3 < span_us <= bank_ms * 1e3 + 1.0, (span_us, bank_ms)
+
+
+@pytest.mark.parametrize("mode", ["tensor_cores", "bank"])
+def test_recurrence_ctas_without_an_open_channel_survive_a_long_run(mode):
+    """Carriers in one third of the band only: two of the three 320-channel LfAGC CTAs have nothing to mix, so none of their
+    chain warps waits for a tile.  The mover warp used to fetch tiles all the same; a CTA that retired with those TMA copies in
+    flight let them land on the ring barriers of the next CTA on that SM, whose wait then trapped ("unspecified launch
+    failure" after ~350 back-to-back blocks -- tools/stress_recur.py).  1200 blocks: the run must end without a fault, with no
+    open channel where there is no carrier."""
+    import ctypes as C
+    from sdrx_b200 import Engine, _lib, workloads as wl
+    plan, carriers, _ = wl.config3(960)
+    carriers = [c for c in carriers if c.offset < -160]
+    blocks = wl.synth_blocks(carriers, 8, 1)
+    lib = _lib.load()
+    L, nb = plan.rate.block_len, blocks[0].nbytes
+    d = lib.sdrx_device_alloc(0, 8 * nb)
+    for i, b in enumerate(blocks):
+        _lib.check(lib.sdrx_device_upload(0, C.c_void_p(d + i * nb), b.ctypes.data_as(C.c_void_p), nb))
+    eng = Engine(plan, tensor_cores=mode == "tensor_cores")
+    n = 1200
+    for i in range(n):
+        eng.push_device(d + (i % 8) * nb, 2, L)
+    eng.sync()
+    got = eng.outputs()
+    eng.close()
+    lib.sdrx_device_free(0, C.c_void_p(d))
+    assert not got.sql[320:].any()
+    assert np.isfinite(got.mix).all()
