@@ -610,6 +610,11 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
                 return rc;
             if ((rc = raise_dyn_smem(tc_kernel_ptr(e->tc.products, e->tc.steps), kTcSmem))) return rc;
             if (const char *ed = getenv("SDRX_TC_DEBUG")) e->tc.debug = atoi(ed);   // timing experiments only: results are wrong
+            if (e->tc.debug & 16) {
+                CU(cudaMalloc((void **)&e->tc.d_trace, 8 * 24 * 4096));
+                CU(cudaMemset(e->tc.d_trace, 0, 8 * 24 * 4096));
+                e->tc.trace_left = 40;
+            }
             e->use_tc = true;
         }
     } else if (want_tgemm) {

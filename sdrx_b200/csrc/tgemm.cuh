@@ -175,6 +175,7 @@ struct TableGemm {
     float4 *d_tdup = nullptr;          // [N][slots_pad]
     int *d_slot_chan = nullptr;        // [slots_pad][2]
     float2 *d_U = nullptr;             // [n_streams][N][Mpad]
+    std::vector<double> h_hc64;        // the composite prototype in double (the tensor-core variant folds with it)
     std::vector<int> h_slot_chan;      // host copy of d_slot_chan (the tensor-core variant lays its rows out from it)
     void destroy() {
         cudaFree(d_hc); cudaFree(d_tdup); cudaFree(d_slot_chan); cudaFree(d_U);
@@ -198,6 +199,7 @@ inline int tgemm_init(TableGemm &tg, int C, int N, int n_stages, const int *m, c
     }
     tg.D = (int)up; tg.Lh = (int)hc.size();
     std::vector<float> hcf(hc.begin(), hc.end());
+    tg.h_hc64 = hc;
     std::vector<int> slot_chan;
     for (int c = 0; c < C; ++c) {
         if (partner[c] >= 0 && partner[c] < c) continue;   // rides in its partner's slot

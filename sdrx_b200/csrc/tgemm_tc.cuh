@@ -18,12 +18,12 @@
 // units into FP32 register totals with round-to-nearest adds while the tensor core works on the following units.
 //
 //   k_fold_tc<FMT>  the fold of tgemm.cuh, written as the bf16 planes of B, k-major: B[stream][plane][2 M + (re|im)][p]
-//   k_tgemm_tc      one CTA per 128-row x 64-column tile of D (64 pair slots x 32 instants), 6 warps:
-//                     warp 4  TMA producer: per 64-entry k-block the three planes of A (128 x 64 bf16) and of B (64 x 64 bf16)
+//   k_tgemm_tc      one CTA per 128-row x 64-column tile of D (64 pair slots x 32 instants), 10 warps:
+//                     warp 8  TMA producer: per 64-entry k-block the three planes of A (128 x 64 bf16) and of B (64 x 64 bf16)
 //                             through 2-D tensor maps with the 128-byte swizzle, a three-deep ring of 72 KB stages on mbarriers
-//                     warp 5  allocates tensor memory; one lane issues tcgen05.mma (M 128, N 64, K 16, kind::f16 with bf16 inputs,
+//                     warp 9  allocates tensor memory; one lane issues tcgen05.mma (M 128, N 64, K 16, kind::f16 with bf16 inputs,
 //                             FP32 accumulate) and tcgen05.commit onto the ring's mbarriers
-//                     warps 0-3  epilogue: tcgen05.ld of a finished accumulator (32 lanes x 64 columns per warp), add into the
+//                     warps 0-7  epilogue: tcgen05.ld of a finished accumulator (32 lanes x 32 columns per warp), add into the
 //                             totals; at the end un-mix the pair (neighbouring lanes hold the Tr and Ti rows of a slot) and store
 #pragma once
 #include <cuda.h>
@@ -37,15 +37,17 @@ constexpr int kTcRows = 128;                  // UMMA M
 constexpr int kTcCols = 64;                   // UMMA N
 constexpr int kTcK = 64;                      // bf16 elements of one staged k-block row = 128 bytes = one swizzle row
 constexpr int kTcKStep = 16;                  // K of one tcgen05.mma with 16-bit inputs
-constexpr int kTcStages = 3;
+constexpr int kTcStages = 3;                  // at most; the launch picks 2 or 3 (TcGemm::stages)
 constexpr int kTcPlanes = 3;
 constexpr int kTcAcc = 8;                     // accumulators in the tensor-memory ring
 constexpr int kTcTmemCols = kTcAcc * kTcCols; // 512: all of it
-constexpr int kTcThreads = 192;
+constexpr int kTcEpiWarps = 8;                // epilogue warps: warp w drains TMEM lanes 32 (w % 4) .. + 31, columns 32 (w / 4) .. + 31 of an accumulator
+constexpr int kTcThreads = (kTcEpiWarps + 2) * 32;
 constexpr int kTcABytes = kTcRows * kTcK * 2; // 16 KB per plane
 constexpr int kTcBBytes = kTcCols * kTcK * 2; //  8 KB per plane
 constexpr int kTcStageBytes = kTcPlanes * (kTcABytes + kTcBBytes);              // 72 KB
-constexpr size_t kTcSmem = (size_t)kTcStages * kTcStageBytes + 1024 + 256;      // + alignment slack + barriers / tmem slot
+inline size_t tc_smem_bytes(int stages) { return (size_t)stages * kTcStageBytes + 1024 + 256; }   // + alignment slack + barriers / tmem slot
+constexpr size_t kTcSmem = (size_t)kTcStages * kTcStageBytes + 1024 + 256;
 
 // ---- tcgen05 / tensor-memory primitives (inline PTX; SASS: UTCHMMA, LDTM, UTCBAR, UTMALDG)
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -81,6 +83,12 @@ __device__ __forceinline__ unsigned cluster_rank() { unsigned r; asm volatile("m
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// one lane of the (converged) warp, chosen by the hardware: the warp-uniform way to issue single-thread instructions
+__device__ __forceinline__ bool tc_elect_one() {
+    uint32_t p;
+    asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(p));
+    return p != 0;
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -123,7 +131,7 @@ __device__ __forceinline__ void bf16_split3(float x, __nv_bfloat16 &h0, __nv_bfl
 // grid (ceil(n_out / kFoldM), n_streams).
 template <int FMT>
 static __global__ void __launch_bounds__(kFoldThreads)
-k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int valid_lo, int pos0, int D, int N, const float *__restrict__ hc, int Lh,
+k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int valid_lo, int pos0, int D, int N, const double *__restrict__ hc, int Lh,
           int n_out, __nv_bfloat16 *__restrict__ B, int cols, int Kp) {
     const void *raw = reinterpret_cast<const unsigned char *>(raw_all) + (long)blockIdx.y * stream_bytes;
     __nv_bfloat16 *Bs = B + (size_t)blockIdx.y * kTcPlanes * cols * Kp;
@@ -136,23 +144,26 @@ k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int val
         const int nM = D * M + D - 1;
         int d = (pos0 + nM - p) % N;
         if (d < 0) d += N;
-        float2 acc = make_float2(0.f, 0.f);
+        // the 7-8 terms of a bin in double precision with the composite taps in double (the exact convolution of the reference's
+        // float stage taps): u is the fold to ~1e-16, rounded ONCE to FP32 -- which the three bf16 planes below hold exactly
+        double ar = 0.0, ai = 0.0;
         for (int j0 = d; j0 < Lh; j0 += 8 * N) {
             float2 xv[8];
-            float hv[8];
+            double hv[8];
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
                 const int j = j0 + q * N;
                 const bool in = j < Lh;
                 xv[q] = in ? load_iq_from<FMT>(raw, (long)hist + nM - j, valid_lo) : make_float2(0.f, 0.f);
-                hv[q] = in ? __ldg(hc + j) : 0.0f;
+                hv[q] = in ? __ldg(hc + j) : 0.0;
             }
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
-                acc.x = fmaf(hv[q], xv[q].x, acc.x);
-                acc.y = fmaf(hv[q], xv[q].y, acc.y);
+                ar = fma(hv[q], (double)xv[q].x, ar);
+                ai = fma(hv[q], (double)xv[q].y, ai);
             }
         }
+        const float2 acc = make_float2(__double2float_rn(ar), __double2float_rn(ai));
         __nv_bfloat16 r0, r1, r2, i0, i1, i2;
         bf16_split3(acc.x, r0, r1, r2);
         bf16_split3(acc.y, i0, i1, i2);
@@ -167,23 +178,27 @@ k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int val
 template <int kProducts, int kSteps>
 static __global__ void __launch_bounds__(kTcThreads, 1)
 k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int rows_pad, int cols, int N,
-           const int *__restrict__ slot_chan, int chans_per_stream, float2 *__restrict__ ch_iq, long iq_stride, int n_out, int cl, int dbg) {
+           const int *__restrict__ slot_chan, int chans_per_stream, float2 *__restrict__ ch_iq, long iq_stride, int n_out, int cl, int dbg, unsigned long long *__restrict__ trace) {
+    const bool comp = !(dbg & 4);                                 // SDRX_TC_DEBUG=4: plain FP32 adds of the unit sums (experiment)
     extern __shared__ unsigned char tc_smem_raw[];
     unsigned char *sm = reinterpret_cast<unsigned char *>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);   // swizzle atoms: 1024-byte aligned
-    uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (size_t)kTcStages * kTcStageBytes);
+    const int n_st = (dbg & 8) ? 2 : kTcStages;                  // operand stages in the ring (bit 3 of the knob word: two)
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sm + (size_t)n_st * kTcStageBytes);
     uint64_t *full = bars, *empty = bars + kTcStages, *tfull = bars + 2 * kTcStages, *tempty = tfull + kTcAcc;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(tempty + kTcAcc);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_kb = (N + kTcK - 1) / kTcK;                       // staged k-blocks (the planes are zero past N)
-    const int n_ks = (N + kTcKStep - 1) / kTcKStep;               // k-steps that hold any table entry
-    const int n_units = (n_ks + kSteps - 1) / kSteps;
+    // SDRX_TC_DEBUG bit 4: per-role cycle counts (total, spent waiting) of every CTA into `trace`
+    long long t_wait = 0, t_wait2 = 0, t_sec = 0, t_sec2 = 0;
+    const long long t_begin = trace ? clock64() : 0;
+#define TC_TIMED_WAIT(acc_, bar_, par_) do { if (trace) { const long long w0_ = clock64(); mbar_wait(bar_, par_); acc_ += clock64() - w0_; } else mbar_wait(bar_, par_); } while (0)
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kTcStages; ++i) { mbar_init(full + i, 1); mbar_init(empty + i, (unsigned)cl); }
-        for (int i = 0; i < kTcAcc; ++i) { mbar_init(tfull + i, 1); mbar_init(tempty + i, 4); }
+        for (int i = 0; i < kTcAcc; ++i) { mbar_init(tfull + i, 1); mbar_init(tempty + i, kTcEpiWarps); }   // [0..1] used: one pair per accumulator group
         mbar_fence_init();
     }
-    if (warp == 5) tc_alloc(tmem_slot, kTcTmemCols);
+    if (warp == kTcEpiWarps + 1) tc_alloc(tmem_slot, kTcTmemCols);
     tc_fence_before();
     __syncthreads();
     if (cl > 1) cluster_sync_all();                               // every CTA's barriers exist before a neighbour's copy or commit lands on them
@@ -191,110 +206,160 @@ k_tgemm_tc(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CU
     const uint32_t tmem = *tmem_slot;
     const uint16_t mc_mask = (uint16_t)((1u << cl) - 1u);
 
-    if (warp == 4) {
-        // ===== TMA producer
-        if (lane == 0) {
-            const int row0 = blockIdx.x * kTcRows;
-            const int col0 = blockIdx.z * kTcPlanes * cols + blockIdx.y * kTcCols;
-            for (int kb = 0; kb < n_kb; ++kb) {
-                const int st = kb % kTcStages;
-                mbar_wait(empty + st, ((unsigned)(kb / kTcStages) & 1u) ^ 1u);
-                if (dbg & 2) { mbar_arrive(full + st); continue; }   // timing experiment (SDRX_TC_DEBUG=2): no operand loads, wrong results
-                mbar_expect_tx(full + st, (unsigned)kTcStageBytes);
+    if (warp == kTcEpiWarps) {
+        // ===== TMA producer: the whole warp walks the loop, one elected lane issues (no divergent region around the bulk copies)
+        const int row0 = blockIdx.x * kTcRows;
+        const int col0 = blockIdx.z * kTcPlanes * cols + blockIdx.y * kTcCols;
+        int st = 0;
+        unsigned ph = 1;                                          // parity of "the consumer has freed the stage": a fresh barrier passes
+        for (int kb = 0; kb < n_kb; ++kb) {
+            TC_TIMED_WAIT(t_wait, empty + st, ph);
+            if (tc_elect_one()) {
                 unsigned char *a = sm + (size_t)st * kTcStageBytes, *b = a + kTcPlanes * kTcABytes;
-                if (cl > 1) {
-                    // the CTAs of a cluster share the row tile: each fetches 1 / cl of every A plane and multicasts it to all of them
-                    const int rank = (int)cluster_rank(), slice = kTcRows / cl;
+                if (dbg & 2) mbar_arrive(full + st);              // timing experiment (SDRX_TC_DEBUG=2): no operand loads, wrong results
+                else {
+                    mbar_expect_tx(full + st, (unsigned)kTcStageBytes);
+                    if (cl > 1) {
+                        // the CTAs of a cluster share the row tile: each fetches 1 / cl of every A plane and multicasts it to all of them
+                        const int rank = (int)cluster_rank(), slice = kTcRows / cl;
 #pragma unroll
-                    for (int pl = 0; pl < kTcPlanes; ++pl) {
-                        tma_load_2d_mc(a + pl * kTcABytes + rank * slice * (kTcK * 2), &map_a, kb * kTcK, pl * rows_pad + row0 + rank * slice, full + st, mc_mask);
-                        tma_load_2d(b + pl * kTcBBytes, &map_b, kb * kTcK, pl * cols + col0, full + st);
-                    }
-                } else {
+                        for (int pl = 0; pl < kTcPlanes; ++pl) {
+                            tma_load_2d_mc(a + pl * kTcABytes + rank * slice * (kTcK * 2), &map_a, kb * kTcK, pl * rows_pad + row0 + rank * slice, full + st, mc_mask);
+                            tma_load_2d(b + pl * kTcBBytes, &map_b, kb * kTcK, pl * cols + col0, full + st);
+                        }
+                    } else {
 #pragma unroll
-                    for (int pl = 0; pl < kTcPlanes; ++pl) {
-                        tma_load_2d(a + pl * kTcABytes, &map_a, kb * kTcK, pl * rows_pad + row0, full + st);
-                        tma_load_2d(b + pl * kTcBBytes, &map_b, kb * kTcK, pl * cols + col0, full + st);
+                        for (int pl = 0; pl < kTcPlanes; ++pl) {
+                            tma_load_2d(a + pl * kTcABytes, &map_a, kb * kTcK, pl * rows_pad + row0, full + st);
+                            tma_load_2d(b + pl * kTcBBytes, &map_b, kb * kTcK, pl * cols + col0, full + st);
+                        }
                     }
                 }
             }
+            __syncwarp();
+            if (++st == n_st) { st = 0; ph ^= 1u; }
         }
-    } else if (warp == 5) {
-        // ===== MMA issuer (one lane)
-        if (lane == 0) {
-            // plane products, smallest first: (a plane, b plane)
-            constexpr int pa[9] = {2, 2, 1, 2, 0, 1, 1, 0, 0};
-            constexpr int pb[9] = {2, 1, 2, 0, 2, 1, 0, 1, 0};
-            constexpr int first_prod = 9 - kProducts;             // 6 products: skip (2,2), (2,1), (1,2)
-            int unit = 0;
-            for (int ks = 0; ks < n_ks; ++ks) {
-                const int kb = ks >> 2, sub = ks & 3, st = kb % kTcStages;
-                if (sub == 0) {
-                    mbar_wait(full + st, (unsigned)(kb / kTcStages) & 1u);
-                    tc_fence_after();
-                }
-                const bool unit_first = (ks % kSteps) == 0;
-                const int acc = unit % kTcAcc;
-                if (unit_first) {
-                    mbar_wait(tempty + acc, ((unsigned)(unit / kTcAcc) & 1u) ^ 1u);
-                    tc_fence_after();
-                }
-                const uint32_t sa = smem_u32(sm + (size_t)st * kTcStageBytes) + sub * (kTcKStep * 2);
-                const uint32_t sb = sa + kTcPlanes * kTcABytes;
+    } else if (warp == kTcEpiWarps + 1) {
+        // ===== MMA issuer: warp-uniform loop, one elected lane issues.  Per staged k-block four k-steps of 16 table entries; a drain
+        // unit is kSteps of them (kSteps divides 4, so units never straddle a stage).
+        constexpr int pa[9] = {2, 2, 1, 2, 0, 1, 1, 0, 0};      // plane products, smallest first: (a plane, b plane)
+        constexpr int pb[9] = {2, 1, 2, 0, 2, 1, 0, 1, 0};
+        constexpr int first_prod = 9 - kProducts;                 // 6 products: skip (2,2), (2,1), (1,2)
+        // Accumulators are handed over in GROUPS of four (one staged k-block = four k-steps): a tcgen05.commit costs the tensor pipe
+        // ~300 cycles of drain (measured: the fixed cost per commit), so there is one per k-block, not one per 16-entry unit -- the
+        // units stay 16 entries long (that is what bounds the rounding inside the tensor core), each in its own accumulator.
+        int st = 0, grp = 0;
+        unsigned ph = 0, gph = 1;                                 // stage-full parity; group-free parity (fresh barriers pass)
+        for (int kb = 0; kb < n_kb; ++kb) {
+            TC_TIMED_WAIT(t_wait, full + st, ph);
+            TC_TIMED_WAIT(t_wait2, tempty + grp, gph);
+            tc_fence_after();
+            const uint64_t da = tc_smem_desc(smem_u32(sm + (size_t)st * kTcStageBytes));
+            const uint64_t db = tc_smem_desc(smem_u32(sm + (size_t)st * kTcStageBytes + kTcPlanes * kTcABytes));
+            const long long s0_ = trace ? clock64() : 0;
+            if (tc_elect_one()) {
 #pragma unroll
-                for (int q = first_prod; q < 9; ++q)
-                    if (!(dbg & 1) || q == 8)                     // timing experiment (SDRX_TC_DEBUG=1): one product instead of nine, wrong results
-                    tc_mma_bf16(tmem + acc * kTcCols, tc_smem_desc(sa + pa[q] * kTcABytes), tc_smem_desc(sb + pb[q] * kTcBBytes), kTcIdesc,
-                                (unit_first && (q == first_prod || (dbg & 1))) ? 0u : 1u);
-                const bool last = ks == n_ks - 1;
-                if ((ks % kSteps) == kSteps - 1 || last) { tc_commit(tfull + acc); ++unit; }
-                if (sub == 3 || last) { if (cl > 1) tc_commit_mc(empty + st, mc_mask); else tc_commit(empty + st); }
+                for (int sub = 0; sub < 4; ++sub) {
+                    const bool unit_first = (sub % kSteps) == 0;
+                    const uint32_t d_tmem = tmem + (uint32_t)((grp * 4 + sub / kSteps) * kTcCols);
+#pragma unroll
+                    for (int q = first_prod; q < 9; ++q)
+                        if (!(dbg & 1) || q == 8)                 // timing experiment (SDRX_TC_DEBUG=1): one product instead of nine, wrong results
+                            tc_mma_bf16(d_tmem, da + (uint64_t)((pa[q] * kTcABytes + sub * (kTcKStep * 2)) >> 4),
+                                        db + (uint64_t)((pb[q] * kTcBBytes + sub * (kTcKStep * 2)) >> 4), kTcIdesc,
+                                        (unit_first && (q == first_prod || (dbg & 1))) ? 0u : 1u);
+                }
+                if (cl > 1) tc_commit_mc(empty + st, mc_mask); else tc_commit(empty + st);   // the stage is free once these have read it
+                tc_commit(tfull + grp);                                                       // ... and the group's accumulators are final
             }
+            __syncwarp();
+            if (trace) t_sec += clock64() - s0_;
+            if (++grp == 2) { grp = 0; gph ^= 1u; }
+            if (++st == n_st) { st = 0; ph ^= 1u; }
         }
     } else {
-        // ===== epilogue warps 0..3: TMEM lanes 32 warp .. 32 warp + 31 = rows of the tile
-        float tot[kTcCols];
+        // ===== epilogue warps 0..7: warp w owns TMEM lanes 32 (w % 4) .. + 31 (the rows of the tile; a warp can only reach its own
+        // lane quadrant) and columns 32 (w / 4) .. + 31 of every accumulator.
+        // Unit sums are added with Kahan compensation: tot - cmp is the sum of the units to ~48 bits, so what is left of FP32
+        // rounding is what the tensor core does inside a unit (16 entries).  It matters because of the pairing: P and Q are each
+        // as large as the STRONGER channel of a +-offset pair, and the weaker one is their small difference.
+        constexpr int kEc = kTcCols * 4 / kTcEpiWarps;            // columns per warp: 32
+        static_assert(kEc == 32, "the drain is one 32-column tcgen05.ld per warp");
+        const int quad = warp & 3, chalf = warp >> 2;
+        float tot[kEc], cmp[kEc];
 #pragma unroll
-        for (int i = 0; i < kTcCols; ++i) tot[i] = 0.0f;
-        const uint32_t tlane = tmem + ((uint32_t)(warp * 32) << 16);
-        for (int unit = 0; unit < n_units; ++unit) {
-            const int acc = unit % kTcAcc;
-            mbar_wait(tfull + acc, (unsigned)(unit / kTcAcc) & 1u);
+        for (int i = 0; i < kEc; ++i) tot[i] = cmp[i] = 0.0f;
+        const uint32_t tlane = tmem + ((uint32_t)(quad * 32) << 16) + chalf * kEc;
+        int grp = 0;
+        unsigned gph = 0;
+        for (int kb = 0; kb < n_kb; ++kb) {
+            TC_TIMED_WAIT(t_wait, tfull + grp, gph);
             tc_fence_after();
-            uint32_t v[kTcCols];
-            tc_ld32(tlane + acc * kTcCols, v);
-            tc_ld32(tlane + acc * kTcCols + 32, v + 32);
-            tc_ld_wait();
-            tc_fence_before();
-            if (lane == 0) mbar_arrive(tempty + acc);
+            constexpr int kUnits = 4 / kSteps;                    // accumulators of a group in use
+            constexpr int kBatch = kUnits >= 2 ? 2 : 1;           // accumulators read per tcgen05.wait::ld (register budget)
 #pragma unroll
-            for (int i = 0; i < kTcCols; ++i) tot[i] = __fadd_rn(tot[i], __uint_as_float(v[i]));
+            for (int u0 = 0; u0 < kUnits; u0 += kBatch) {
+                uint32_t v[kBatch][kEc];
+#pragma unroll
+                for (int u = 0; u < kBatch; ++u) tc_ld32(tlane + (uint32_t)((grp * 4 + u0 + u) * kTcCols), v[u]);
+                tc_ld_wait();
+                if (u0 + kBatch == kUnits) {
+                    tc_fence_before();
+                    if (lane == 0) mbar_arrive(tempty + grp);     // this warp's part of the group is in registers
+                }
+#pragma unroll
+                for (int u = 0; u < kBatch; ++u)                  // unit by unit, in k order
+#pragma unroll
+                    for (int j = 0; j < kEc; ++j) {
+                        if (comp) {
+                            const float y = __fsub_rn(__uint_as_float(v[u][j]), cmp[j]);
+                            const float t = __fadd_rn(tot[j], y);
+                            cmp[j] = __fsub_rn(__fsub_rn(t, tot[j]), y);
+                            tot[j] = t;
+                        } else {
+                            tot[j] = __fadd_rn(tot[j], __uint_as_float(v[u][j]));
+                        }
+                    }
+            }
+            if (++grp == 2) { grp = 0; gph ^= 1u; }
         }
         // un-mix: even row = Tr of the slot -> (P, R) per instant, odd row = Ti -> (S, Q); the partner row is the neighbouring lane
-        const int row = blockIdx.x * kTcRows + warp * 32 + lane;
+        const int row = blockIdx.x * kTcRows + quad * 32 + lane;
         const int odd = row & 1;
         const int c = slot_chan[row];                              // [slot][2]: even row -> first channel, odd row -> conjugate partner
-        const int m0 = blockIdx.y * (kTcCols / 2);
+        const int m0 = blockIdx.y * (kTcCols / 2) + chalf * (kEc / 2);
         float2 *dst = c >= 0 ? ch_iq + ((long)blockIdx.z * chans_per_stream + c) * iq_stride + m0 : nullptr;
 #pragma unroll
-        for (int m = 0; m < kTcCols / 2; m += 2) {
+        for (int m = 0; m < kEc / 2; m += 2) {
             float4 y;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const float a = tot[2 * (m + h)], b = tot[2 * (m + h) + 1];
                 const float oa = __shfl_xor_sync(0xffffffffu, a, 1), ob = __shfl_xor_sync(0xffffffffu, b, 1);
                 // even: a = P, b = R, oa = S, ob = Q -> (P - Q, R + S);  odd: a = S, b = Q, oa = P, ob = R -> (P + Q, R - S)
-                const float re = odd ? __fadd_rn(oa, b) : __fsub_rn(a, ob);
-                const float im = odd ? __fsub_rn(ob, a) : __fadd_rn(b, oa);
+                float re = odd ? __fadd_rn(oa, b) : __fsub_rn(a, ob);
+                float im = odd ? __fsub_rn(ob, a) : __fadd_rn(b, oa);
+                if (comp) {                                        // the low parts: every total is tot - cmp
+                    const float ca = cmp[2 * (m + h)], cb = cmp[2 * (m + h) + 1];
+                    const float oca = __shfl_xor_sync(0xffffffffu, ca, 1), ocb = __shfl_xor_sync(0xffffffffu, cb, 1);
+                    re = __fsub_rn(re, odd ? __fadd_rn(oca, cb) : __fsub_rn(ca, ocb));
+                    im = __fsub_rn(im, odd ? __fsub_rn(ocb, ca) : __fadd_rn(cb, oca));
+                }
                 if (h == 0) { y.x = re; y.y = im; } else { y.z = re; y.w = im; }
             }
             if (dst && m0 + m < n_out) *reinterpret_cast<float4 *>(dst + m) = y;   // n_out is even (tgemm_eligible)
         }
     }
+    if (trace && lane == 0 && (warp == 0 || warp >= kTcEpiWarps)) {
+        const int cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x, role = warp == 0 ? 0 : warp - kTcEpiWarps + 1;   // 0 epilogue, 1 producer, 2 issuer
+        unsigned long long *o = trace + ((size_t)cta * 3 + role) * 8;
+        o[0] = (unsigned long long)(clock64() - t_begin); o[1] = (unsigned long long)t_wait; o[2] = (unsigned long long)t_wait2; o[3] = (unsigned long long)t_sec; o[4] = (unsigned long long)t_sec2;
+    }
+#undef TC_TIMED_WAIT
     tc_fence_before();
     __syncthreads();
     if (cl > 1) cluster_sync_all();                               // no CTA leaves while a neighbour's commit may still arrive on its barriers
-    if (warp == 5) tc_dealloc(tmem, kTcTmemCols);
+    if (warp == kTcEpiWarps + 1) tc_dealloc(tmem, kTcTmemCols);
 }
 
 // ---- host side
@@ -303,11 +368,14 @@ struct TcGemm {
     int rows_pad = 0, cols = 0, Kp = 0, products = 9, steps = 1, cluster = 1, debug = 0;
     __nv_bfloat16 *d_a = nullptr;      // [3][rows_pad][Kp]
     __nv_bfloat16 *d_b = nullptr;      // [n_streams][3][cols][Kp]
+    double *d_hc64 = nullptr;          // the composite prototype in double (the fold's taps)
+    unsigned long long *d_trace = nullptr;   // SDRX_TC_DEBUG bit 4: [ctas][3 roles][4]
+    int trace_left = 0;
     int *d_row_chan = nullptr;         // [rows_pad]
     CUtensorMap map_a, map_b;
     void destroy() {
-        cudaFree(d_a); cudaFree(d_b); cudaFree(d_row_chan);
-        d_a = d_b = nullptr; d_row_chan = nullptr; enabled = false;
+        cudaFree(d_a); cudaFree(d_b); cudaFree(d_row_chan); cudaFree(d_hc64); cudaFree(d_trace); d_trace = nullptr;
+        d_a = d_b = nullptr; d_row_chan = nullptr; d_hc64 = nullptr; enabled = false;
     }
 };
 
@@ -354,6 +422,8 @@ int tc_init(TcGemm &tc, const TableGemm &tg, const float *tables, const uint8_t 
     const size_t b_elems = (size_t)tg.n_streams * kTcPlanes * tc.cols * tc.Kp;
     CU(cudaMalloc((void **)&tc.d_b, b_elems * 2));
     CU(cudaMemset(tc.d_b, 0, b_elems * 2));
+    CU(cudaMalloc((void **)&tc.d_hc64, sizeof(double) * tg.h_hc64.size()));
+    CU(cudaMemcpy(tc.d_hc64, tg.h_hc64.data(), sizeof(double) * tg.h_hc64.size(), cudaMemcpyHostToDevice));
     CU(cudaMalloc((void **)&tc.d_row_chan, sizeof(int) * row_chan.size()));
     CU(cudaMemcpy(tc.d_row_chan, row_chan.data(), sizeof(int) * row_chan.size(), cudaMemcpyHostToDevice));
     int rc;
@@ -372,26 +442,43 @@ template <int FMT>
 int tgemm_tc_launch(TableGemm &tg, TcGemm &tc, cudaStream_t st, const void *raw, long stream_bytes, int hist, int valid_lo, int pos0, int n_out,
                     float2 *ch_iq, long iq_stride, uint64_t *launches, cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr) {
     k_fold_tc<FMT><<<dim3((n_out + kFoldM - 1) / kFoldM, tg.n_streams), kFoldThreads, 0, st>>>(raw, stream_bytes, hist, valid_lo, pos0, tg.D, tg.N,
-                                                                                              tg.d_hc, tg.Lh, n_out, tc.d_b, tc.cols, tc.Kp);
+                                                                                              tc.d_hc64, tg.Lh, n_out, tc.d_b, tc.cols, tc.Kp);
     if (ev0) CU(cudaEventRecord(ev0, st));
     const dim3 grid(tc.rows_pad / kTcRows, (2 * n_out + kTcCols - 1) / kTcCols, tg.n_streams);
     const int cl = (tc.cluster > 1 && grid.y % tc.cluster == 0) ? tc.cluster : 1;
     if (cl != tc.cluster) return fail(SDRX_ERR_UNSUPPORTED, "tensor-core table GEMM: the column tiles of this block length do not fill whole clusters");
     cudaLaunchConfig_t lc{};
-    lc.gridDim = grid; lc.blockDim = dim3(kTcThreads); lc.dynamicSmemBytes = kTcSmem; lc.stream = st;
+    lc.gridDim = grid; lc.blockDim = dim3(kTcThreads); lc.dynamicSmemBytes = tc_smem_bytes((tc.debug & 8) ? 2 : kTcStages); lc.stream = st;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
     at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = (unsigned)cl; at[0].val.clusterDim.z = 1;
     lc.attrs = at; lc.numAttrs = cl > 1 ? 1 : 0;
 #define SDRX_TC_GO(P, S)                                                                                                                    \
     CU(cudaLaunchKernelEx(&lc, k_tgemm_tc<P, S>, tc.map_a, tc.map_b, tc.rows_pad, tc.cols, tg.N, (const int *)tc.d_row_chan, tg.chans, ch_iq, \
-                          iq_stride, n_out, cl, tc.debug))
+                          iq_stride, n_out, cl, tc.debug, tc.d_trace))
     if (tc.products == 6) { if (tc.steps == 4) SDRX_TC_GO(6, 4); else if (tc.steps == 2) SDRX_TC_GO(6, 2); else SDRX_TC_GO(6, 1); }
     else                  { if (tc.steps == 4) SDRX_TC_GO(9, 4); else if (tc.steps == 2) SDRX_TC_GO(9, 2); else SDRX_TC_GO(9, 1); }
 #undef SDRX_TC_GO
     if (ev1) CU(cudaEventRecord(ev1, st));
     *launches += 2;
     CU(cudaGetLastError());
+    if (tc.d_trace && tc.trace_left > 0 && --tc.trace_left == 0) {       // debug only: the 40th launch's role timings to stderr
+        CU(cudaStreamSynchronize(st));
+        const int n_cta = (int)(grid.x * grid.y * grid.z);
+        std::vector<unsigned long long> h((size_t)n_cta * 24);
+        CU(cudaMemcpy(h.data(), tc.d_trace, h.size() * 8, cudaMemcpyDeviceToHost));
+        const char *names[3] = {"epilogue warp 0", "TMA producer", "MMA issuer"};
+        for (int r = 0; r < 3; ++r) {
+            double tot = 0, w = 0, w2 = 0, s1 = 0, s2 = 0;
+            for (int c = 0; c < n_cta; ++c) {
+                const unsigned long long *o = &h[((size_t)c * 3 + r) * 8];
+                tot += (double)o[0]; w += (double)o[1]; w2 += (double)o[2]; s1 += (double)o[3]; s2 += (double)o[4];
+            }
+            fprintf(stderr, "[tc trace] %-16s cycles %9.0f  waiting %9.0f (%s)  waiting %9.0f (%s)  mma issue %9.0f  commits %9.0f\n", names[r], tot / n_cta,
+                    w / n_cta, r == 0 ? "accumulator full" : r == 1 ? "stage empty" : "stage full", w2 / n_cta, r == 2 ? "accumulator empty" : "-",
+                    s1 / n_cta, s2 / n_cta);
+        }
+    }
     return SDRX_OK;
 }
 
