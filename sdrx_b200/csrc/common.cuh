@@ -72,6 +72,9 @@ __device__ __forceinline__ void mbar_fence_init() {          // make the initial
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, unsigned bytes) {   // one arrival + `bytes` still to land
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {                      // one plain arrival (a consumer frees a buffer)
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, unsigned parity) {
     unsigned ok, spins = 0;
     do {

@@ -165,6 +165,8 @@ struct sdrx_engine {
     int phase[SDRX_MAX_STAGES] = {0};    // inputs seen since the stage's last output (m - isn_)
     int ft_k = 0;                        // S::k_ of stage 0 (msd.hpp:434), same for every channel
     int fmt = -1;                        // wire format of the stream so far
+    size_t agc_smem = kAgcSmem, lf_smem = kLfSmem;   // dynamic shared memory the recurrence kernels are launched with
+    int agc_bufs = 3, lf_bufs = 3;                   // ... and their tile ring depths
     int ring = kNOut;                    // output sets in use (<= kNOut; SDRX_RING overrides it for experiments)
     uint64_t blocks = 0;                 // output sets handed out so far (push_block and demod_block): selects out[blocks % e->ring]
     uint64_t pushes = 0;                 // blocks through the channelizer: its parity selects the raw ping-pong buffer
@@ -606,7 +608,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             auto bf16_map = [](CUtensorMap *map, void *base, uint64_t inner, uint64_t rows, uint64_t pitch, int box_inner, int box_rows) {
                 return make_map_2d(map, base, inner, rows, pitch, (cuuint32_t)box_inner, (cuuint32_t)box_rows, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
             };
-            if ((rc = tc_init(e->tc, e->tg, cfg->translators, has_v.data(), e->tg.h_slot_chan, ep ? atoi(ep) : 9, es ? atoi(es) : 1, ec ? atoi(ec) : 1, bf16_map)))
+            if ((rc = tc_init(e->tc, e->tg, cfg->translators, has_v.data(), e->tg.h_slot_chan, ep ? atoi(ep) : 6, es ? atoi(es) : 1, ec ? atoi(ec) : 1, bf16_map)))
                 return rc;
             if ((rc = raise_dyn_smem(tc_kernel_ptr(e->tc.products, e->tc.steps), kTcSmem))) return rc;
             if (const char *ed = getenv("SDRX_TC_DEBUG")) e->tc.debug = atoi(ed);   // timing experiments only: results are wrong
@@ -710,7 +712,18 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             (rc = dalloc(&e->d_fir_hist, (size_t)NS * 2 * (size_t)std::max(cfg->fir2_ntaps - 1, 1))))
             return rc;
         if ((rc = dalloc(&e->d_ticket, 2 * (size_t)NS))) return rc;
-        if ((rc = raise_dyn_smem((const void *)k_chan_agc, kAgcSmem)) || (rc = raise_dyn_smem((const void *)k_chan_lfagc, kLfSmem)))
+        {
+            // Where boundary A is short (table GEMM / polyphase) the recurrence CTAs ask for (nearly) all of an SM's shared memory and
+            // run deep tile rings: nothing else -- detector, envelope, mix, fold CTAs -- is placed beside a dependent chain whose issue
+            // slots it would share.  Under the time-domain bank they keep the three-tile rings that fit the SMs its schedule leaves.
+            const char *ex = getenv("SDRX_RECUR_EXCL");
+            const bool deep = ((e->use_tgemm || e->poly) && (!ex || atoi(ex) != 0)) || (ex && atoi(ex) == 2);   // 2: in every mode (experiment)
+            e->agc_bufs = deep ? kAgcBufs : 3;
+            e->lf_bufs = deep ? kLfBufs : 3;
+            e->agc_smem = deep ? kRecurExclusiveSmem : agc_smem_bytes(3);
+            e->lf_smem = deep ? kRecurExclusiveSmem : std::max<size_t>(lf_smem_bytes(3), 120 * 1024);
+        }
+        if ((rc = raise_dyn_smem((const void *)k_chan_agc, e->agc_smem)) || (rc = raise_dyn_smem((const void *)k_chan_lfagc, e->lf_smem)))
             return rc;
         if ((rc = dalloc(&e->d_agc_iq[0], (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_agc_iq[1], (size_t)e->Cpad * kChunk)) || (rc = dalloc(&e->d_env[0], (size_t)e->Cpad * kChunk)) ||
             (rc = dalloc(&e->d_env[1], (size_t)e->Cpad * kChunk)))
@@ -992,7 +1005,7 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
     // recurrences have the three SMs its schedule leaves free and a whole bank's time: one stream, so that two blocks'
     // recurrence CTAs never hold more SMs than that when the next bank launch needs its own
     cudaStream_t s_lf = (e->use_tgemm || e->poly) ? e->s_lf : e->s_recur;
-    k_chan_agc<<<recur_ctas(e->C), kRecurThreads, kAgcSmem, e->s_recur>>>(o.iq_map, e->st, e->agc, e->d_agc_iq[par], e->Cpad, snap, e->C);
+    k_chan_agc<<<recur_ctas(e->C), kRecurThreads, e->agc_smem, e->s_recur>>>(o.iq_map, e->st, e->agc, e->d_agc_iq[par], e->Cpad, snap, e->C, e->agc_bufs);
     tl_mark(e, TL_AGC, e->s_recur);
     // the envelope follows the AGC on its stream (it needs the detector's gate); the LfAGC recurrence has a stream to itself
     if (e->env_pending[par]) CU(cudaStreamWaitEvent(e->s_recur, e->ev_env_done[par], 0));   // the LfAGC of two blocks ago read d_env[par]
@@ -1005,8 +1018,8 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
     tl_mark(e, TL_ENV, e->s_recur);
     CU(cudaEventRecord(e->ev_agc_done[par], e->s_recur));
     CU(cudaStreamWaitEvent(s_lf, e->ev_agc_done[par], 0));
-    k_chan_lfagc<<<recur_ctas(e->C), kRecurThreads, kLfSmem, s_lf>>>(e->d_env[par], e->Cpad, e->st, e->d_gate[idx], e->tb, e->lf, e->lf_active, o.audio, snap,
-                                                        e->C, o.mixed);
+    k_chan_lfagc<<<recur_ctas(e->C), kRecurThreads, e->lf_smem, s_lf>>>(e->d_env[par], e->Cpad, e->st, e->d_gate[idx], e->tb, e->lf, e->lf_active, o.audio, snap,
+                                                        e->C, o.mixed, e->lf_bufs);
     tl_mark(e, TL_LFAGC, s_lf);
     CU(cudaEventRecord(e->ev_env_done[par], s_lf));          // d_env[par] (and with it d_agc_iq[par]) are free again
     e->env_pending[par] = true;
@@ -1161,12 +1174,29 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     // ---- still on the copy stream, off the compute stream's critical path: the raw delay line (last raw_hist
     //      samples of the previous [hist | block] move in front of this block) and, when boundary B will run,
     //      the block power partials.  The partials of set `oc` were last read by block b-kNOut's mix kernel.
+    bool tc_block = false;
+    const int valid_lo_early = (int)std::max<long>(0, (long)e->raw_hist - (long)std::min<uint64_t>(e->total, (uint64_t)e->raw_hist));
+    if (e->use_tgemm && e->use_tc && n > 0) {
+        bool pz = true;
+        for (int s = 0; s < e->S; ++s) pz = pz && phase_in[s] == 0;
+        tc_block = pz && n % (unsigned)e->tg.D == 0 && tgemm_eligible(e->N, (int)out_len) && (int)out_len <= e->tg.Mpad;
+    }
     {
         if (e->side_pending[oc]) CU(cudaStreamWaitEvent(e->s_copy, e->ev_side_done[oc], 0));
         int rc = launch_prep(e, e->s_copy, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps,
                              e->d_pwr_partial[oc]);
         if (rc) return rc;
         tl_mark(e, TL_PREP, e->s_copy);
+        if (tc_block) {
+            // tensor-core table GEMM: the fold of this block runs here, on the copy stream, under the previous block's GEMM
+            const long sb = (long)e->raw_stream_bytes;
+            switch (fmt) {
+                case SDRX_FMT_U8:  rc = tgemm_tc_fold<SDRX_FMT_U8>(e->tg, e->tc, e->s_copy, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
+                case SDRX_FMT_S16: rc = tgemm_tc_fold<SDRX_FMT_S16>(e->tg, e->tc, e->s_copy, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
+                default:           rc = tgemm_tc_fold<SDRX_FMT_F32>(e->tg, e->tc, e->s_copy, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
+            }
+            if (rc) return rc;
+        }
         CU(cudaEventRecord(e->ev_copied[cur], e->s_copy));
         CU(cudaStreamWaitEvent(e->s_main, e->ev_copied[cur], 0));
         CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));   // every kernel that read buffer `prv` is queued before this point
@@ -1195,11 +1225,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     if (tgemm) {
         cudaEvent_t b0 = e->timing ? e->ev_b0 : nullptr, b1 = e->timing ? e->ev_b1 : nullptr;
         const long sb = (long)e->raw_stream_bytes;
-        if (e->use_tc) switch (fmt) {
-            case SDRX_FMT_U8:  rc = tgemm_tc_launch<SDRX_FMT_U8>(e->tg, e->tc, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
-            case SDRX_FMT_S16: rc = tgemm_tc_launch<SDRX_FMT_S16>(e->tg, e->tc, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
-            default:           rc = tgemm_tc_launch<SDRX_FMT_F32>(e->tg, e->tc, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
-        }
+        if (e->use_tc) rc = tgemm_tc_launch(e->tg, e->tc, e->s_main, cur, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1);
         else switch (fmt) {
             case SDRX_FMT_U8:  rc = tgemm_launch<SDRX_FMT_U8>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
             case SDRX_FMT_S16: rc = tgemm_launch<SDRX_FMT_S16>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;

@@ -90,9 +90,6 @@ __device__ __forceinline__ bool tc_elect_one() {
     asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(p));
     return p != 0;
 }
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
 // 32 lanes x 32 consecutive columns: thread t of the warp gets lane (warp % 4) * 32 + t
 __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t *v) {
     asm volatile(
@@ -367,15 +364,20 @@ struct TcGemm {
     bool enabled = false;
     int rows_pad = 0, cols = 0, Kp = 0, products = 9, steps = 1, cluster = 1, debug = 0;
     __nv_bfloat16 *d_a = nullptr;      // [3][rows_pad][Kp]
-    __nv_bfloat16 *d_b = nullptr;      // [n_streams][3][cols][Kp]
+    __nv_bfloat16 *d_b[2] = {nullptr, nullptr};   // [n_streams][3][cols][Kp], ping-pong: the fold of block b + 1 (copy stream) writes one while
+                                                  // the GEMM of block b (main stream) reads the other
+    cudaEvent_t ev_b_free[2] = {nullptr, nullptr};  // the GEMM that read d_b[par] has run
+    bool b_busy[2] = {false, false};
     double *d_hc64 = nullptr;          // the composite prototype in double (the fold's taps)
     unsigned long long *d_trace = nullptr;   // SDRX_TC_DEBUG bit 4: [ctas][3 roles][4]
     int trace_left = 0;
     int *d_row_chan = nullptr;         // [rows_pad]
-    CUtensorMap map_a, map_b;
+    CUtensorMap map_a, map_b[2];
     void destroy() {
-        cudaFree(d_a); cudaFree(d_b); cudaFree(d_row_chan); cudaFree(d_hc64); cudaFree(d_trace); d_trace = nullptr;
-        d_a = d_b = nullptr; d_row_chan = nullptr; d_hc64 = nullptr; enabled = false;
+        cudaFree(d_a); cudaFree(d_b[0]); cudaFree(d_b[1]); cudaFree(d_row_chan);
+        for (int i = 0; i < 2; ++i) { if (ev_b_free[i]) cudaEventDestroy(ev_b_free[i]); ev_b_free[i] = nullptr; b_busy[i] = false; }
+        cudaFree(d_hc64); cudaFree(d_trace); d_trace = nullptr;
+        d_a = d_b[0] = d_b[1] = nullptr; d_row_chan = nullptr; d_hc64 = nullptr; enabled = false;
     }
 };
 
@@ -420,15 +422,19 @@ int tc_init(TcGemm &tc, const TableGemm &tg, const float *tables, const uint8_t 
     CU(cudaMalloc((void **)&tc.d_a, a.size() * 2));
     CU(cudaMemcpy(tc.d_a, a.data(), a.size() * 2, cudaMemcpyHostToDevice));
     const size_t b_elems = (size_t)tg.n_streams * kTcPlanes * tc.cols * tc.Kp;
-    CU(cudaMalloc((void **)&tc.d_b, b_elems * 2));
-    CU(cudaMemset(tc.d_b, 0, b_elems * 2));
+    for (int i = 0; i < 2; ++i) {
+        CU(cudaMalloc((void **)&tc.d_b[i], b_elems * 2));
+        CU(cudaMemset(tc.d_b[i], 0, b_elems * 2));
+        CU(cudaEventCreateWithFlags(&tc.ev_b_free[i], cudaEventDisableTiming));
+    }
     CU(cudaMalloc((void **)&tc.d_hc64, sizeof(double) * tg.h_hc64.size()));
     CU(cudaMemcpy(tc.d_hc64, tg.h_hc64.data(), sizeof(double) * tg.h_hc64.size(), cudaMemcpyHostToDevice));
     CU(cudaMalloc((void **)&tc.d_row_chan, sizeof(int) * row_chan.size()));
     CU(cudaMemcpy(tc.d_row_chan, row_chan.data(), sizeof(int) * row_chan.size(), cudaMemcpyHostToDevice));
     int rc;
     if ((rc = make_map(&tc.map_a, tc.d_a, (uint64_t)tc.Kp, (uint64_t)kTcPlanes * tc.rows_pad, (uint64_t)tc.Kp * 2, kTcK, kTcRows / tc.cluster))) return rc;
-    if ((rc = make_map(&tc.map_b, tc.d_b, (uint64_t)tc.Kp, (uint64_t)tg.n_streams * kTcPlanes * tc.cols, (uint64_t)tc.Kp * 2, kTcK, kTcCols))) return rc;
+    for (int i = 0; i < 2; ++i)
+        if ((rc = make_map(&tc.map_b[i], tc.d_b[i], (uint64_t)tc.Kp, (uint64_t)tg.n_streams * kTcPlanes * tc.cols, (uint64_t)tc.Kp * 2, kTcK, kTcCols))) return rc;
     tc.enabled = true;
     return SDRX_OK;
 }
@@ -438,11 +444,21 @@ inline const void *tc_kernel_ptr(int products, int steps) {
     return steps == 4 ? (const void *)k_tgemm_tc<9, 4> : steps == 2 ? (const void *)k_tgemm_tc<9, 2> : (const void *)k_tgemm_tc<9, 1>;
 }
 
+// The fold of one block into the B planes d_b[par], on `st` (the engine's copy stream: it runs under the previous block's GEMM).
 template <int FMT>
-int tgemm_tc_launch(TableGemm &tg, TcGemm &tc, cudaStream_t st, const void *raw, long stream_bytes, int hist, int valid_lo, int pos0, int n_out,
-                    float2 *ch_iq, long iq_stride, uint64_t *launches, cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr) {
+int tgemm_tc_fold(TableGemm &tg, TcGemm &tc, cudaStream_t st, int par, const void *raw, long stream_bytes, int hist, int valid_lo, int pos0, int n_out,
+                  uint64_t *launches) {
+    if (tc.b_busy[par]) CU(cudaStreamWaitEvent(st, tc.ev_b_free[par], 0));     // the GEMM of two blocks ago read these planes
     k_fold_tc<FMT><<<dim3((n_out + kFoldM - 1) / kFoldM, tg.n_streams), kFoldThreads, 0, st>>>(raw, stream_bytes, hist, valid_lo, pos0, tg.D, tg.N,
-                                                                                              tc.d_hc64, tg.Lh, n_out, tc.d_b, tc.cols, tc.Kp);
+                                                                                              tc.d_hc64, tg.Lh, n_out, tc.d_b[par], tc.cols, tc.Kp);
+    *launches += 1;
+    CU(cudaGetLastError());
+    return SDRX_OK;
+}
+
+// The GEMM over the planes d_b[par], on `st` (the main stream; the caller has made it wait for the fold).
+inline int tgemm_tc_launch(TableGemm &tg, TcGemm &tc, cudaStream_t st, int par, int n_out, float2 *ch_iq, long iq_stride, uint64_t *launches,
+                           cudaEvent_t ev0 = nullptr, cudaEvent_t ev1 = nullptr) {
     if (ev0) CU(cudaEventRecord(ev0, st));
     const dim3 grid(tc.rows_pad / kTcRows, (2 * n_out + kTcCols - 1) / kTcCols, tg.n_streams);
     const int cl = (tc.cluster > 1 && grid.y % tc.cluster == 0) ? tc.cluster : 1;
@@ -454,13 +470,15 @@ int tgemm_tc_launch(TableGemm &tg, TcGemm &tc, cudaStream_t st, const void *raw,
     at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = (unsigned)cl; at[0].val.clusterDim.z = 1;
     lc.attrs = at; lc.numAttrs = cl > 1 ? 1 : 0;
 #define SDRX_TC_GO(P, S)                                                                                                                    \
-    CU(cudaLaunchKernelEx(&lc, k_tgemm_tc<P, S>, tc.map_a, tc.map_b, tc.rows_pad, tc.cols, tg.N, (const int *)tc.d_row_chan, tg.chans, ch_iq, \
+    CU(cudaLaunchKernelEx(&lc, k_tgemm_tc<P, S>, tc.map_a, tc.map_b[par], tc.rows_pad, tc.cols, tg.N, (const int *)tc.d_row_chan, tg.chans, ch_iq, \
                           iq_stride, n_out, cl, tc.debug, tc.d_trace))
     if (tc.products == 6) { if (tc.steps == 4) SDRX_TC_GO(6, 4); else if (tc.steps == 2) SDRX_TC_GO(6, 2); else SDRX_TC_GO(6, 1); }
     else                  { if (tc.steps == 4) SDRX_TC_GO(9, 4); else if (tc.steps == 2) SDRX_TC_GO(9, 2); else SDRX_TC_GO(9, 1); }
 #undef SDRX_TC_GO
     if (ev1) CU(cudaEventRecord(ev1, st));
-    *launches += 2;
+    CU(cudaEventRecord(tc.ev_b_free[par], st));
+    tc.b_busy[par] = true;
+    *launches += 1;
     CU(cudaGetLastError());
     if (tc.d_trace && tc.trace_left > 0 && --tc.trace_left == 0) {       // debug only: the 40th launch's role timings to stderr
         CU(cudaStreamSynchronize(st));
