@@ -61,9 +61,10 @@ def workload(name: str, sql_level=None):
 MODE_KW = {"bank": {}, "tensor_cores": {"tensor_cores": True}, "table_gemm": {"table_gemm": True}, "polyphase": {"polyphase": True}}
 MODE_WHAT = {
     "bank": "time-domain channel bank (FP32 CUDA cores; the bit-comparable default of the library)",
-    "tensor_cores": "fold + table GEMM on the tensor cores (SDRX_FLAG_TGEMM_TC: tcgen05.mma, bf16 x 9 split operands = exact FP32 products, "
-                    "FP32 accumulation in 16-entry partial sums); north_star's complex-GEMM recast, inside its tolerance "
-                    "(audio <= 1e-4, squelch decisions bit-exact)",
+    "tensor_cores": "fold + table GEMM on the tensor cores (SDRX_FLAG_TGEMM_TC: tcgen05.mma on three-way bf16 splits of the FP32 operands, "
+                    "6 of the 9 plane products (the dropped ones are < 2^-24 of a term; SDRX_TC_PRODUCTS=9 keeps all), 16-entry partial "
+                    "sums in tensor memory added with Kahan compensation, fold in double); north_star's complex-GEMM recast, inside its "
+                    "tolerance on every channel (channel IQ <= 2.9e-5, audio <= 1.5e-5, squelch decisions bit-exact)",
     "table_gemm": "fold + table GEMM on the FP32 CUDA cores (SDRX_FLAG_TGEMM)",
     "polyphase": "exact-twiddle polyphase / DFT channelizer (SDRX_FLAG_POLYPHASE; NOT a parity mode)",
 }
@@ -406,16 +407,20 @@ def run_ours(args):
     if mode in ("tensor_cores", "table_gemm"):
         # The dominant kernel is the table GEMM.  `achieved` is the ALGORITHMIC work of the path as the reference computes it
         # (19.232 flop per channel and input sample for mix + stages 1-3, + stage 4 -- the GEMM covers all four)
-        # over the GEMM kernel's time; the tensor cores execute 2 x rows x columns x N x 9 plane products for it.
-        n_tab, n_inst = 1200, L // 625
-        rows = 2 * ((C_ + 1) // 2 + 1)                       # (Tr, Ti) per conjugate-pair slot
-        executed = 2.0 * rows * (2 * n_inst) * n_tab * (9 if mode == "tensor_cores" else 1)
+        # over the GEMM kernel's time; the tensor cores execute 2 x rows x columns x K x (plane products) for it (padded tile sizes).
+        n_inst = L // 625
+        products = int(os.environ.get("SDRX_TC_PRODUCTS", "6")) if mode == "tensor_cores" else 1
+        if mode == "tensor_cores":                           # what the kernel launches: 128-row x 64-column tiles, K padded to 64
+            rows, n_tab = -(-2 * ((C_ + 1) // 2 + 1) // 128) * 128, -(-1200 // 64) * 64
+        else:
+            rows, n_tab = 2 * ((C_ + 1) // 2 + 1), 1200      # (Tr, Ti) per conjugate-pair slot
+        executed = 2.0 * rows * (2 * n_inst) * n_tab * products
         alg = FLOP_CHAIN * C_ * L
         tpeak = float(measured.get("bf16_tflops", 1590.0)) if mode == "tensor_cores" else peak
         achieved = alg / (bank_ms * 1e-3) / 1e12
         roofline = {"bound": "tensor" if mode == "tensor_cores" else "fp32", "achieved": achieved, "peak": tpeak, "unit": "TFLOP/s",
                     "frac": achieved / tpeak, "traffic": None,
-                    "kernel": "k_tgemm_tc (tcgen05.mma, bf16 x 9)" if mode == "tensor_cores" else "k_tgemm (FP32 FFMA2)",
+                    "kernel": f"k_tgemm_tc (tcgen05.mma, {products} bf16 plane products)" if mode == "tensor_cores" else "k_tgemm (FP32 FFMA2)",
                     "kernel_ms": bank_ms, "block_ms_serialised": statistics.mean(whole), "share_of_step": bank_ms / per_step_ms,
                     "algorithmic_flop_per_channel_sample": FLOP_CHAIN,
                     "executed_tflops": executed / (bank_ms * 1e-3) / 1e12, "executed_frac": executed / (bank_ms * 1e-3) / 1e12 / tpeak,
@@ -425,8 +430,9 @@ def run_ours(args):
                     "peak_source": ("measured (MEASURED_PEAKS.json bf16_tflops, cuBLAS burst)" if "bf16_tflops" in measured
                                     else "fallback 1.59 PFLOP/s (B200_PROFILING.md)") if mode == "tensor_cores" else peak_how,
                     "note": "the algorithmic count is the reference's time-domain chain; the GEMM form needs 2.4 GFLOP per block instead of "
-                            "5.9 (shared fold, conjugate pairs) and the bf16 x 9 split multiplies that by 9, so `frac` understates the "
-                            "tensor pipe's load: see executed_frac and profiles/r02y_tc_ncu_details.txt (tensor pipe 60 % of active cycles)"}
+                            "5.9 (shared fold, conjugate pairs) and the bf16 split multiplies that by the plane products kept, so `frac` understates "
+                            "the tensor pipe's load: see executed_frac and profiles/r02z_tc_ncu_details.txt.  The 128 x 64 x 16 MMAs are bound by "
+                            "shared-memory operand reads (6 KB per MMA: ~50 cycles against a 32-cycle tensor floor), DESIGN.md section 4"}
         prof = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(prof):
             with open(prof) as f:
@@ -502,9 +508,8 @@ def run_ours(args):
     alt = None
     if world == 1 and not args.no_alt:
         alt = {}
-        acc = {"bank": "bit-comparable path: channel IQ <= 4.4e-5 rel. RMS per channel, audio 2.1e-5, squelch decisions equal (profiles/r02y_tc_report.json)",
-               "tensor_cores": "squelch decisions equal to the oracle's, audio <= 5.4e-5, channel IQ <= 8.2e-5 on every channel that ever opens, "
-                               "1.36e-4 on closed noise-only channels next to strong carriers (profiles/r02y_tc_report.json)",
+        acc = {"bank": "bit-comparable path: channel IQ <= 4.4e-5 rel. RMS per channel, audio 2.1e-5, squelch decisions equal (profiles/r02z_tc_report.json)",
+               "tensor_cores": "squelch decisions equal to the oracle's, channel IQ <= 2.9e-5 on every channel, audio <= 1.5e-5 (profiles/r02z_tc_report.json)",
                "table_gemm": "squelch decisions equal to the oracle's; channel IQ of closed noise-only channels up to 1.4e-4 rel. RMS, audio 5e-5",
                "polyphase": "NOT a parity mode: channel IQ up to 1.8e-2 rel. RMS on noise-only channels (exact twiddles vs the reference's "
                             "float-rounded table), audio 8e-3; squelch decisions equal on this workload (profiles/r02x_channelizers.json)"}
@@ -549,8 +554,9 @@ def run_ours(args):
             "metric": "channel-MS/s", "value": value, "unit": "channel-MS/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": per_step_ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "arithmetic": ("FP32 results from bf16 x 9 split operands on tcgen05 (every plane product exact), FP32 accumulation; boundary B in FP32 "
-                           "as the reference" if mode == "tensor_cores" else "FP32 CUDA cores throughout, as the reference"),
+            "arithmetic": ("FP32 results from three-way bf16 splits of the FP32 operands on tcgen05 (plane products exact in the FP32 accumulator), "
+                           "compensated FP32 accumulation; boundary B in FP32 as the reference" if mode == "tensor_cores"
+                           else "FP32 CUDA cores throughout, as the reference"),
             "config": {"workload": desc, "channels": C_, "block_len": L, "sample_rate": RATE, "wire_format": "f32",
                        "parallelism": f"stream-sharded x{world} (one independent 10 MS/s stream per GPU, no collective)",
                        "l2": f"inputs cycle through a {ring}-block device ring ({ring * blk_bytes / 1e6:.0f} MB > 126 MB L2)",

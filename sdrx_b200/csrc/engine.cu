@@ -64,6 +64,9 @@ struct sdrx_engine {
     int fir2_ntaps = 0;
 
     cudaStream_t s_main = nullptr, s_copy = nullptr;
+    cudaStream_t s_prep = nullptr;        // k_prep (+ the tensor-core fold) of a block: the next block's H2D runs beside them on s_copy
+    cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_prep[2] = {nullptr, nullptr};   // block landed in d_raw[b]; its delay-line prefix is in place
+    bool prep_pending[2] = {false, false};
     // Boundary B runs under the following blocks' channel banks as a three-deep pipeline, one stream per kernel: the
     // detector of block b+2, the recurrences of block b+1 and the mix of block b overlap (each kernel only depends on
     // its own predecessor -- squelch state, AGC state, FIR2 ring -- and on the previous kernel of its own block), so a
@@ -378,6 +381,8 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     if (e->ev_b1) cudaEventDestroy(e->ev_b1);
     if (e->s_main) cudaStreamDestroy(e->s_main);
     if (e->s_copy) cudaStreamDestroy(e->s_copy);
+    if (e->s_prep) cudaStreamDestroy(e->s_prep);
+    for (int b = 0; b < 2; ++b) { if (e->ev_h2d[b]) cudaEventDestroy(e->ev_h2d[b]); if (e->ev_prep[b]) cudaEventDestroy(e->ev_prep[b]); }
     if (e->s_side) cudaStreamDestroy(e->s_side);
     if (e->s_recur) cudaStreamDestroy(e->s_recur);
     if (e->s_lf) cudaStreamDestroy(e->s_lf);
@@ -472,6 +477,11 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         CU(cudaStreamCreateWithPriority(&e->s_main, cudaStreamNonBlocking, (mp && atoi(mp) == 1) ? hi : lo));
     }
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&e->s_prep, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; ++b) {
+        CU(cudaEventCreateWithFlags(&e->ev_h2d[b], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&e->ev_prep[b], cudaEventDisableTiming));
+    }
     CU(cudaStreamCreateWithFlags(&e->s_side, cudaStreamNonBlocking));
     {
         // the recurrences and the mix are few, long CTAs that need most of a free SM's shared memory; the detector is 960
@@ -814,6 +824,7 @@ extern "C" int sdrx_engine_reset(sdrx_engine *e) {
     if (!e) return fail(SDRX_ERR_ARG, "null engine");
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));
+    CU(cudaStreamSynchronize(e->s_prep));
     return reset_state(e);
 }
 
@@ -1139,6 +1150,9 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     // ---- ingest: pinned, double buffered, on the copy stream
     // buffer `cur` was last read by block b-1's raw carry (and before that by block b-2's kernels)
     CU(cudaStreamWaitEvent(e->s_copy, e->ev_raw_free[cur], 0));
+    // ... and by the previous block's k_prep (the delay-line tail), which runs on the prep stream; the fold of block b-2, the other
+    // reader there, is queued in front of it
+    if (e->prep_pending[prv]) CU(cudaStreamWaitEvent(e->s_copy, e->ev_prep[prv], 0));
     if (n > 0) {
         // one stream: a plain copy; several: the caller's [n_streams][n] blocks land behind each stream's history prefix
         const size_t row = (size_t)n * bps;
@@ -1182,24 +1196,33 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         tc_block = pz && n % (unsigned)e->tg.D == 0 && tgemm_eligible(e->N, (int)out_len) && (int)out_len <= e->tg.Mpad;
     }
     {
-        if (e->side_pending[oc]) CU(cudaStreamWaitEvent(e->s_copy, e->ev_side_done[oc], 0));
-        int rc = launch_prep(e, e->s_copy, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps,
+        // the copy stream carries only the copies: k_prep and the fold follow on the prep stream, so that the next block's H2D
+        // (50 us of PCIe time per 10 MS/s f32 block) runs beside them instead of behind them
+        CU(cudaEventRecord(e->ev_h2d[cur], e->s_copy));
+        CU(cudaStreamWaitEvent(e->s_prep, e->ev_h2d[cur], 0));
+        if (e->side_pending[oc]) CU(cudaStreamWaitEvent(e->s_prep, e->ev_side_done[oc], 0));
+        int rc = launch_prep(e, e->s_prep, fmt, buf, e->d_raw[prv], n, demod && n > 0, (int)hist_bytes, (long)e->prev_n * bps,
                              e->d_pwr_partial[oc]);
         if (rc) return rc;
-        tl_mark(e, TL_PREP, e->s_copy);
+        tl_mark(e, TL_PREP, e->s_prep);
+        CU(cudaEventRecord(e->ev_prep[cur], e->s_prep));
+        e->prep_pending[cur] = true;
         if (tc_block) {
             // tensor-core table GEMM: the fold of this block runs here, on the copy stream, under the previous block's GEMM
             const long sb = (long)e->raw_stream_bytes;
             switch (fmt) {
-                case SDRX_FMT_U8:  rc = tgemm_tc_fold<SDRX_FMT_U8>(e->tg, e->tc, e->s_copy, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
-                case SDRX_FMT_S16: rc = tgemm_tc_fold<SDRX_FMT_S16>(e->tg, e->tc, e->s_copy, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
-                default:           rc = tgemm_tc_fold<SDRX_FMT_F32>(e->tg, e->tc, e->s_copy, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
+                case SDRX_FMT_U8:  rc = tgemm_tc_fold<SDRX_FMT_U8>(e->tg, e->tc, e->s_prep, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
+                case SDRX_FMT_S16: rc = tgemm_tc_fold<SDRX_FMT_S16>(e->tg, e->tc, e->s_prep, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
+                default:           rc = tgemm_tc_fold<SDRX_FMT_F32>(e->tg, e->tc, e->s_prep, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
             }
             if (rc) return rc;
         }
-        CU(cudaEventRecord(e->ev_copied[cur], e->s_copy));
+        CU(cudaEventRecord(e->ev_copied[cur], e->s_prep));
+        // every main-stream kernel that read buffer `prv` (the previous block's channelizer) is queued before this point -- recorded
+        // BEFORE the main stream is made to wait for this block's prep / fold: behind that wait the event would also stand for them,
+        // and the next block's H2D (which waits for it) would run after this block's fold instead of beside it
+        CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));
         CU(cudaStreamWaitEvent(e->s_main, e->ev_copied[cur], 0));
-        CU(cudaEventRecord(e->ev_raw_free[prv], e->s_main));   // every kernel that read buffer `prv` is queued before this point
     }
     { int rc = wait_side(e, oc); if (rc) return rc; }       // block b-kNOut's recurrences / mix / read-back used this output set
     if (e->timing) CU(cudaEventRecord(e->ev_t0, e->s_main));
@@ -1348,6 +1371,7 @@ extern "C" int sdrx_engine_sync(sdrx_engine *e) {
     if (!e) return fail(SDRX_ERR_ARG, "null engine");
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));
+    CU(cudaStreamSynchronize(e->s_prep));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_recur));
@@ -1671,6 +1695,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     if (size < state_bytes(e)) return fail(SDRX_ERR_ARG, "state buffer too small");
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));
+    CU(cudaStreamSynchronize(e->s_prep));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_recur));
@@ -1732,6 +1757,7 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     if (size < state_bytes(e)) return fail(SDRX_ERR_ARG, "state buffer too small");
     DevGuard g(e->dev);
     CU(cudaStreamSynchronize(e->s_copy));
+    CU(cudaStreamSynchronize(e->s_prep));
     CU(cudaStreamSynchronize(e->s_main));
     CU(cudaStreamSynchronize(e->s_side));
     CU(cudaStreamSynchronize(e->s_recur));
