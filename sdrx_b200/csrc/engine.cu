@@ -24,7 +24,7 @@ static_assert(kFastSideSms == kSideSms, "the bank leaves the SMs the side kernel
 
 namespace {
 
-constexpr int kNBuf = 2;          // ping-pong depth of raw input
+constexpr int kNBuf = 3;          // raw input ring: block b lands in d_raw[b % 3] while block b-1's prep / fold and block b-2's readers still run
 constexpr int kNOut = 10;         // ring of output sets: a streaming caller may run up to kNOut-1 blocks ahead of the results it reads
 constexpr int kPwrPartials = 296;     // power CTAs of k_prep: two per SM
 constexpr uint32_t kStateMagic = 0x58524453u;  // "SDRX"
@@ -65,8 +65,8 @@ struct sdrx_engine {
 
     cudaStream_t s_main = nullptr, s_copy = nullptr;
     cudaStream_t s_prep = nullptr;        // k_prep (+ the tensor-core fold) of a block: the next block's H2D runs beside them on s_copy
-    cudaEvent_t ev_h2d[2] = {nullptr, nullptr}, ev_prep[2] = {nullptr, nullptr};   // block landed in d_raw[b]; its delay-line prefix is in place
-    bool prep_pending[2] = {false, false};
+    cudaEvent_t ev_h2d[kNBuf] = {}, ev_prep[kNBuf] = {};   // block landed in d_raw[b]; its delay-line prefix is in place
+    bool prep_pending[kNBuf] = {};
     // Boundary B runs under the following blocks' channel banks as a three-deep pipeline, one stream per kernel: the
     // detector of block b+2, the recurrences of block b+1 and the mix of block b overlap (each kernel only depends on
     // its own predecessor -- squelch state, AGC state, FIR2 ring -- and on the previous kernel of its own block), so a
@@ -86,14 +86,14 @@ struct sdrx_engine {
     cudaEvent_t ev_fetch_done[kNOut] = {};
     bool fetch_pending[kNOut] = {};
     uint8_t *d_gate[kNOut] = {};            // [C] squelch state entering the block (k_chan_head -> k_chan_recur)
-    cudaEvent_t ev_copied[kNBuf] = {nullptr, nullptr};
-    cudaEvent_t ev_raw_free[kNBuf] = {nullptr, nullptr};   // last reader of d_raw[b] has been queued
+    cudaEvent_t ev_copied[kNBuf] = {};
+    cudaEvent_t ev_raw_free[kNBuf] = {};   // last reader of d_raw[b] has been queued
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr, ev_t2 = nullptr, ev_b0 = nullptr, ev_b1 = nullptr;
     bool bank_timed = false;
     bool timing = false, timing_valid = false;
 
     // device memory
-    uint8_t *d_raw[kNBuf] = {nullptr, nullptr};
+    uint8_t *d_raw[kNBuf] = {};
     size_t raw_buf_bytes = 0;
     float2 *d_table_t = nullptr;         // [N][Cpad]
     uint8_t *d_has_tr = nullptr;
@@ -160,8 +160,8 @@ struct sdrx_engine {
     float2 *d_hk = nullptr;               // [ft_sets * H0][Cpad]
 
     // pinned staging for pageable callers
-    uint8_t *h_stage[kNBuf] = {nullptr, nullptr};
-    bool stage_busy[kNBuf] = {false, false};
+    uint8_t *h_stage[kNBuf] = {};
+    bool stage_busy[kNBuf] = {};
 
     // carried host-side state
     long trans_pos = 0;                  // MSD::trans_pos_ (msd.hpp:440), same for every channel
@@ -382,7 +382,7 @@ extern "C" void sdrx_engine_destroy(sdrx_engine *e) {
     if (e->s_main) cudaStreamDestroy(e->s_main);
     if (e->s_copy) cudaStreamDestroy(e->s_copy);
     if (e->s_prep) cudaStreamDestroy(e->s_prep);
-    for (int b = 0; b < 2; ++b) { if (e->ev_h2d[b]) cudaEventDestroy(e->ev_h2d[b]); if (e->ev_prep[b]) cudaEventDestroy(e->ev_prep[b]); }
+    for (int b = 0; b < kNBuf; ++b) { if (e->ev_h2d[b]) cudaEventDestroy(e->ev_h2d[b]); if (e->ev_prep[b]) cudaEventDestroy(e->ev_prep[b]); }
     if (e->s_side) cudaStreamDestroy(e->s_side);
     if (e->s_recur) cudaStreamDestroy(e->s_recur);
     if (e->s_lf) cudaStreamDestroy(e->s_lf);
@@ -478,7 +478,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
     }
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
     CU(cudaStreamCreateWithFlags(&e->s_prep, cudaStreamNonBlocking));
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < kNBuf; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_h2d[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_prep[b], cudaEventDisableTiming));
     }
@@ -1128,7 +1128,8 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
         return fail(SDRX_ERR_STATE, "wire format changed mid-stream (the carried raw history is format specific); reset first");
     e->fmt = fmt;
     const int bps = raw_bytes_per_sample(fmt);
-    const int cur = (int)(e->pushes & 1), prv = cur ^ 1;      // raw ping-pong
+    const int cur = (int)(e->pushes % kNBuf), prv = (cur + kNBuf - 1) % kNBuf;   // raw ring: this block's buffer, the previous block's
+    const int bpar = (int)(e->pushes & 1);                     // ping-pong of the tensor-core fold's B planes
     const int oc = (int)(e->blocks % e->ring);                 // output set of this block
     uint8_t *buf = e->d_raw[cur];
     const size_t hist_bytes = (size_t)e->raw_hist * bps;
@@ -1148,11 +1149,12 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     OutSet &o = e->out[oc];
     const bool demod = !(e->flags & SDRX_FLAG_NO_DEMOD) && out_len == (unsigned)kChunk;
     // ---- ingest: pinned, double buffered, on the copy stream
-    // buffer `cur` was last read by block b-1's raw carry (and before that by block b-2's kernels)
+    // buffer `cur` was last read by block b-2's raw carry (and before that by block b-3's kernels)
     CU(cudaStreamWaitEvent(e->s_copy, e->ev_raw_free[cur], 0));
-    // ... and by the previous block's k_prep (the delay-line tail), which runs on the prep stream; the fold of block b-2, the other
-    // reader there, is queued in front of it
-    if (e->prep_pending[prv]) CU(cudaStreamWaitEvent(e->s_copy, e->ev_prep[prv], 0));
+    // ... and on the prep stream by block b-2's k_prep (the delay-line tail) with block b-3's fold queued in front of it: both a
+    // whole block back, so the H2D of block b never waits for anything of block b-1
+    { const int b2 = (cur + 1) % kNBuf;                        // the buffer of block b-2, whose k_prep read this buffer's tail
+      if (e->prep_pending[b2]) CU(cudaStreamWaitEvent(e->s_copy, e->ev_prep[b2], 0)); }
     if (n > 0) {
         // one stream: a plain copy; several: the caller's [n_streams][n] blocks land behind each stream's history prefix
         const size_t row = (size_t)n * bps;
@@ -1211,9 +1213,9 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
             // tensor-core table GEMM: the fold of this block runs here, on the copy stream, under the previous block's GEMM
             const long sb = (long)e->raw_stream_bytes;
             switch (fmt) {
-                case SDRX_FMT_U8:  rc = tgemm_tc_fold<SDRX_FMT_U8>(e->tg, e->tc, e->s_prep, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
-                case SDRX_FMT_S16: rc = tgemm_tc_fold<SDRX_FMT_S16>(e->tg, e->tc, e->s_prep, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
-                default:           rc = tgemm_tc_fold<SDRX_FMT_F32>(e->tg, e->tc, e->s_prep, cur, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
+                case SDRX_FMT_U8:  rc = tgemm_tc_fold<SDRX_FMT_U8>(e->tg, e->tc, e->s_prep, bpar, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
+                case SDRX_FMT_S16: rc = tgemm_tc_fold<SDRX_FMT_S16>(e->tg, e->tc, e->s_prep, bpar, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
+                default:           rc = tgemm_tc_fold<SDRX_FMT_F32>(e->tg, e->tc, e->s_prep, bpar, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
             }
             if (rc) return rc;
         }
@@ -1248,7 +1250,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
     if (tgemm) {
         cudaEvent_t b0 = e->timing ? e->ev_b0 : nullptr, b1 = e->timing ? e->ev_b1 : nullptr;
         const long sb = (long)e->raw_stream_bytes;
-        if (e->use_tc) rc = tgemm_tc_launch(e->tg, e->tc, e->s_main, cur, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1);
+        if (e->use_tc) rc = tgemm_tc_launch(e->tg, e->tc, e->s_main, bpar, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1);
         else switch (fmt) {
             case SDRX_FMT_U8:  rc = tgemm_launch<SDRX_FMT_U8>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
             case SDRX_FMT_S16: rc = tgemm_launch<SDRX_FMT_S16>(e->tg, e->s_main, buf, sb, e->raw_hist, valid_lo, (int)e->trans_pos, (int)out_len, o.ch_iq, e->chiq_stride, &e->launches, b0, b1); break;
@@ -1358,7 +1360,7 @@ extern "C" int sdrx_engine_wait_event(sdrx_engine *e, void *cuda_event) {
 // may overwrite the buffer it handed to push_block_device after this.
 extern "C" void *sdrx_engine_ingest_event(sdrx_engine *e) {
     if (!e || e->pushes == 0) return nullptr;
-    return (void *)e->ev_copied[(e->pushes - 1) & 1];
+    return (void *)e->ev_copied[(e->pushes + kNBuf - 1) % kNBuf];
 }
 
 extern "C" int sdrx_engine_last_out_len(sdrx_engine *e, unsigned *out_len) {
@@ -1532,7 +1534,7 @@ extern "C" int sdrx_engine_stream_wait_ingest(sdrx_engine *e, void *cuda_stream)
     if (!e) return fail(SDRX_ERR_ARG, "null engine");
     if (e->pushes == 0) return SDRX_OK;
     DevGuard g(e->dev);
-    CU(cudaStreamWaitEvent((cudaStream_t)cuda_stream, e->ev_copied[(e->pushes - 1) & 1], 0));
+    CU(cudaStreamWaitEvent((cudaStream_t)cuda_stream, e->ev_copied[(e->pushes + kNBuf - 1) % kNBuf], 0));
     return SDRX_OK;
 }
 extern "C" int sdrx_engine_stream_wait_outputs(sdrx_engine *e, void *cuda_stream) {
@@ -1702,7 +1704,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     CU(cudaStreamSynchronize(e->s_lf));
     CU(cudaStreamSynchronize(e->s_mix));
     if (e->generic_stale) {      // the blob always carries the stage delay lines (a generic engine can load it)
-        const int last_ = (int)((e->pushes & 1) ^ 1);
+        const int last_ = (int)((e->pushes + kNBuf - 1) % kNBuf);
         int rc = materialize_generic(e, e->fmt, e->d_raw[last_], (long)e->raw_hist + (long)e->prev_n, e->total);
         if (rc) return rc;
         CU(cudaStreamSynchronize(e->s_main));
@@ -1717,7 +1719,7 @@ extern "C" int sdrx_engine_save_state(sdrx_engine *e, void *buf, size_t size) {
     h.ft_k = e->ft_k; h.ftfir = e->ftfir ? 1 : 0;
     memcpy(p, &h, sizeof(h)); p += sizeof(h);
     const int bps = e->fmt >= 0 ? raw_bytes_per_sample(e->fmt) : 8;
-    const int last = (int)((e->pushes & 1) ^ 1);
+    const int last = (int)((e->pushes + kNBuf - 1) % kNBuf);
     memset(p, 0, (size_t)e->raw_hist * 8);
     CU(cudaMemcpy(p, e->d_raw[last] + (size_t)e->prev_n * bps, (size_t)e->raw_hist * bps, cudaMemcpyDeviceToHost));
     p += (size_t)e->raw_hist * 8;
@@ -1773,7 +1775,7 @@ extern "C" int sdrx_engine_load_state(sdrx_engine *e, const void *buf, size_t si
     e->ft_k = h.ft_k;
     e->prev_n = 0;          // the history is parked at the very front of the "previous" buffer
     e->last_out_len = 0; e->last_demod = false; e->timing_valid = false;
-    const int last = (int)((e->pushes & 1) ^ 1);
+    const int last = (int)((e->pushes + kNBuf - 1) % kNBuf);
     CU(cudaMemcpy(e->d_raw[last], p, (size_t)e->raw_hist * 8, cudaMemcpyHostToDevice));
     p += (size_t)e->raw_hist * 8;
     for (int s = 1; s < e->S; ++s) {

@@ -10,6 +10,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--open-all", action="store_true")
 ap.add_argument("--blocks", type=int, default=12)
 ap.add_argument("--out", default=None)
+ap.add_argument("--host", action="store_true", help="push from pinned host buffers (H2D inside the pipeline) instead of device-resident blocks")
 ap.add_argument("--mode", default="bank", choices=["bank", "tgemm", "tc", "poly"])
 a = ap.parse_args()
 plan, carriers, desc = wl.config3(960, 0.0 if a.open_all else None)
@@ -21,11 +22,20 @@ nb = blocks[0].nbytes
 d = lib.sdrx_device_alloc(0, 8 * nb)
 for i, b in enumerate(blocks):
     _lib.check(lib.sdrx_device_upload(0, C.c_void_p(d + i * nb), b.ctypes.data_as(C.c_void_p), nb))
+if a.host:
+    from sdrx_b200 import PinnedBuffer
+    pins = [PinnedBuffer(nb) for _ in blocks]
+    hv = []
+    for p_, b in zip(pins, blocks):
+        v = p_.view(np.complex64, L); v[:] = b; hv.append(v)
+    feed = lambda i: eng.push(hv[i % 8])
+else:
+    feed = lambda i: eng.push_device(d + (i % 8) * nb, 2, L)
 for i in range(40):
-    eng.push_device(d + (i % 8) * nb, 2, L)
+    feed(i)
 _lib.check(lib.sdrx_debug_timeline(eng.h, 1))
 for i in range(40):
-    eng.push_device(d + (i % 8) * nb, 2, L)
+    feed(i)
 out = np.zeros((16, 9), np.float32)
 n = lib.sdrx_debug_timeline_read(eng.h, out.ctypes.data_as(_lib.c_float_p), a.blocks)
 if n <= 0:

@@ -8,14 +8,20 @@ from sdrx_b200 import Engine, PinnedBuffer, workloads as wl
 ap = argparse.ArgumentParser()
 ap.add_argument("--mode", default="tc")
 ap.add_argument("--steps", type=int, default=400)
+ap.add_argument("--fmt", default="f32", choices=["f32", "s16"], help="wire format of the pushed blocks (s16: half the bytes across the link)")
 a = ap.parse_args()
 plan, carriers, _ = wl.config3(960)
 blocks = wl.synth_blocks(carriers, 8, 1)
 L = plan.rate.block_len
-pins = [PinnedBuffer(b.nbytes) for b in blocks]
 hv = []
-for p, b in zip(pins, blocks):
-    v = p.view(np.complex64, L); v[:] = b; hv.append(v)
+if a.fmt == "s16":
+    pins = [PinnedBuffer(b.nbytes // 2) for b in blocks]
+    for p, b in zip(pins, blocks):
+        v = p.view(np.int16, 2 * L); v[:] = np.clip(np.round(b.view(np.float32) * 32768.0), -32768, 32767).astype(np.int16); hv.append(v)
+else:
+    pins = [PinnedBuffer(b.nbytes) for b in blocks]
+    for p, b in zip(pins, blocks):
+        v = p.view(np.complex64, L); v[:] = b; hv.append(v)
 eng = Engine(plan, tensor_cores=a.mode == "tc", polyphase=a.mode == "poly")
 want = ("audio_rows", "audio_chan", "n_audio", "sql_state", "snr", "mix", "pcm", "pwr_dbfs")
 LAG = 5
