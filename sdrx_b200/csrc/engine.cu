@@ -477,7 +477,15 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
         CU(cudaStreamCreateWithPriority(&e->s_main, cudaStreamNonBlocking, (mp && atoi(mp) == 1) ? hi : lo));
     }
     CU(cudaStreamCreateWithFlags(&e->s_copy, cudaStreamNonBlocking));
-    CU(cudaStreamCreateWithFlags(&e->s_prep, cudaStreamNonBlocking));
+    {
+        // k_prep and the tensor-core fold are short, latency-critical links of the block-to-block loop (the next GEMM waits for the
+        // fold, the next k_prep for this fold's stream slot): at the default priority their CTAs queued behind the detector's 960 and
+        // took 22 + 40 us in the pipeline for 6 + 17 us of work -- and that loop, not boundary B, set the step
+        int lo = 0, hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        const char *pp = getenv("SDRX_PREP_PRIO");
+        CU(cudaStreamCreateWithPriority(&e->s_prep, cudaStreamNonBlocking, (pp && atoi(pp) == 0) ? lo : hi));
+    }
     for (int b = 0; b < kNBuf; ++b) {
         CU(cudaEventCreateWithFlags(&e->ev_h2d[b], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&e->ev_prep[b], cudaEventDisableTiming));
@@ -621,6 +629,7 @@ int create_impl(const sdrx_engine_config *cfg, sdrx_engine *e) {
             if ((rc = tc_init(e->tc, e->tg, cfg->translators, has_v.data(), e->tg.h_slot_chan, ep ? atoi(ep) : 6, es ? atoi(es) : 1, ec ? atoi(ec) : 1, bf16_map)))
                 return rc;
             if ((rc = raise_dyn_smem(tc_kernel_ptr(e->tc.products, e->tc.steps), kTcSmem))) return rc;
+            if (const char *fd = getenv("SDRX_TC_FOLD_DOUBLE")) e->tc.fold_double = atoi(fd);
             if (const char *ed = getenv("SDRX_TC_DEBUG")) e->tc.debug = atoi(ed);   // timing experiments only: results are wrong
             if (e->tc.debug & 16) {
                 CU(cudaMalloc((void **)&e->tc.d_trace, 8 * 24 * 4096));
@@ -1000,7 +1009,7 @@ int launch_demod(sdrx_engine *e, int idx, bool have_power, unsigned n_samples, c
             ++e->launches;
         }
         CU(cudaGetLastError());
-        tl_mark(e, TL_TAIL, e->s_main);
+        if (!e->use_tc) tl_mark(e, TL_TAIL, e->s_main);
         CU(cudaEventRecord(e->ev_head_done, e->s_main));
         CU(cudaStreamWaitEvent(e->s_side, e->ev_head_done, 0));
         CU(cudaStreamWaitEvent(e->s_recur, e->ev_head_done, 0));
@@ -1218,6 +1227,7 @@ int enqueue_block(sdrx_engine *e, const void *src, SrcKind kind, int fmt, unsign
                 default:           rc = tgemm_tc_fold<SDRX_FMT_F32>(e->tg, e->tc, e->s_prep, bpar, buf, sb, e->raw_hist, valid_lo_early, (int)e->trans_pos, (int)out_len, &e->launches); break;
             }
             if (rc) return rc;
+            tl_mark(e, TL_TAIL, e->s_prep);                      // (timeline: the `tail` column is the fold in this mode)
         }
         CU(cudaEventRecord(e->ev_copied[cur], e->s_prep));
         // every main-stream kernel that read buffer `prv` (the previous block's channelizer) is queued before this point -- recorded

@@ -125,42 +125,68 @@ __device__ __forceinline__ void bf16_split3(float x, __nv_bfloat16 &h0, __nv_bfl
 }
 
 // The fold of tgemm.cuh (k_fold) writing B: [stream][plane][2 M + (re | im)][p] bf16, p contiguous (pitch Kp elements).
-// grid (ceil(n_out / kFoldM), n_streams).
+// grid (ceil(n_out / kFoldTcM), n_streams).  Small CTAs, one output instant each: the fold runs under the previous block's GEMM, whose
+// CTAs leave room for ~420 more threads per SM -- 128-thread CTAs fit three beside each (one wave), 256-thread CTAs fit one (two
+// waves: 55 us in the pipeline for 17 us of work, and the next GEMM waits for the fold).
+constexpr int kFoldTcM = 1, kFoldTcThreads = 128;
 template <int FMT>
-static __global__ void __launch_bounds__(kFoldThreads)
+static __global__ void __launch_bounds__(kFoldTcThreads)
 k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int valid_lo, int pos0, int D, int N, const double *__restrict__ hc, int Lh,
-          int n_out, __nv_bfloat16 *__restrict__ B, int cols, int Kp) {
+          int n_out, __nv_bfloat16 *__restrict__ B, int cols, int Kp, const float *__restrict__ hc32, int dbl) {
     const void *raw = reinterpret_cast<const unsigned char *>(raw_all) + (long)blockIdx.y * stream_bytes;
     __nv_bfloat16 *Bs = B + (size_t)blockIdx.y * kTcPlanes * cols * Kp;
     const size_t plane = (size_t)cols * Kp;
-    const int M0 = blockIdx.x * kFoldM;
-    for (int it = threadIdx.x; it < kFoldM * N; it += kFoldThreads) {
+    const int M0 = blockIdx.x * kFoldTcM;
+    for (int it = threadIdx.x; it < kFoldTcM * N; it += kFoldTcThreads) {
         const int m = it / N, p = it - m * N;
         const int M = M0 + m;
         if (M >= n_out) break;
         const int nM = D * M + D - 1;
         int d = (pos0 + nM - p) % N;
         if (d < 0) d += N;
-        // the 7-8 terms of a bin in double precision with the composite taps in double (the exact convolution of the reference's
-        // float stage taps): u is the fold to ~1e-16, rounded ONCE to FP32 -- which the three bf16 planes below hold exactly
-        double ar = 0.0, ai = 0.0;
-        for (int j0 = d; j0 < Lh; j0 += 8 * N) {
-            float2 xv[8];
-            double hv[8];
+        // the 7-8 terms of a bin.  kFoldDouble: double taps (the exact convolution of the reference's float stage taps) and a double
+        // sum, rounded once to FP32; otherwise float taps and an FP32 fma chain (half the tap bytes through L2, no FP64: step -3 %).
+        // Measured against the oracle: worst channel IQ 2.89e-5 / 2.97e-5, median 0.97e-5 / 1.18e-5 -- the accuracy lever is the
+        // compensated accumulation of the GEMM, the fold in double only polishes the median
+        float2 acc;
+        if (dbl) {
+            double ar = 0.0, ai = 0.0;
+            for (int j0 = d; j0 < Lh; j0 += 8 * N) {
+                float2 xv[8];
+                double hv[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const int j = j0 + q * N;
-                const bool in = j < Lh;
-                xv[q] = in ? load_iq_from<FMT>(raw, (long)hist + nM - j, valid_lo) : make_float2(0.f, 0.f);
-                hv[q] = in ? __ldg(hc + j) : 0.0;
+                for (int q = 0; q < 8; ++q) {
+                    const int j = j0 + q * N;
+                    const bool in = j < Lh;
+                    xv[q] = in ? load_iq_from<FMT>(raw, (long)hist + nM - j, valid_lo) : make_float2(0.f, 0.f);
+                    hv[q] = in ? __ldg(hc + j) : 0.0;
+                }
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    ar = fma(hv[q], (double)xv[q].x, ar);
+                    ai = fma(hv[q], (double)xv[q].y, ai);
+                }
             }
+            acc = make_float2(__double2float_rn(ar), __double2float_rn(ai));
+        } else {
+            acc = make_float2(0.f, 0.f);
+            for (int j0 = d; j0 < Lh; j0 += 8 * N) {
+                float2 xv[8];
+                float hv[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                ar = fma(hv[q], (double)xv[q].x, ar);
-                ai = fma(hv[q], (double)xv[q].y, ai);
+                for (int q = 0; q < 8; ++q) {
+                    const int j = j0 + q * N;
+                    const bool in = j < Lh;
+                    xv[q] = in ? load_iq_from<FMT>(raw, (long)hist + nM - j, valid_lo) : make_float2(0.f, 0.f);
+                    hv[q] = in ? __ldg(hc32 + j) : 0.0f;
+                }
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    acc.x = fmaf(hv[q], xv[q].x, acc.x);
+                    acc.y = fmaf(hv[q], xv[q].y, acc.y);
+                }
             }
         }
-        const float2 acc = make_float2(__double2float_rn(ar), __double2float_rn(ai));
         __nv_bfloat16 r0, r1, r2, i0, i1, i2;
         bf16_split3(acc.x, r0, r1, r2);
         bf16_split3(acc.y, i0, i1, i2);
@@ -371,6 +397,7 @@ struct TcGemm {
     double *d_hc64 = nullptr;          // the composite prototype in double (the fold's taps)
     unsigned long long *d_trace = nullptr;   // SDRX_TC_DEBUG bit 4: [ctas][3 roles][4]
     int trace_left = 0;
+    int fold_double = 1;               // the fold with double taps and a double sum (SDRX_TC_FOLD_DOUBLE=0: float taps, FP32 fma chain)
     int *d_row_chan = nullptr;         // [rows_pad]
     CUtensorMap map_a, map_b[2];
     void destroy() {
@@ -449,8 +476,8 @@ template <int FMT>
 int tgemm_tc_fold(TableGemm &tg, TcGemm &tc, cudaStream_t st, int par, const void *raw, long stream_bytes, int hist, int valid_lo, int pos0, int n_out,
                   uint64_t *launches) {
     if (tc.b_busy[par]) CU(cudaStreamWaitEvent(st, tc.ev_b_free[par], 0));     // the GEMM of two blocks ago read these planes
-    k_fold_tc<FMT><<<dim3((n_out + kFoldM - 1) / kFoldM, tg.n_streams), kFoldThreads, 0, st>>>(raw, stream_bytes, hist, valid_lo, pos0, tg.D, tg.N,
-                                                                                              tc.d_hc64, tg.Lh, n_out, tc.d_b[par], tc.cols, tc.Kp);
+    k_fold_tc<FMT><<<dim3((n_out + kFoldTcM - 1) / kFoldTcM, tg.n_streams), kFoldTcThreads, 0, st>>>(raw, stream_bytes, hist, valid_lo, pos0, tg.D, tg.N,
+                                                                                              tc.d_hc64, tg.Lh, n_out, tc.d_b[par], tc.cols, tc.Kp, tg.d_hc, tc.fold_double);
     *launches += 1;
     CU(cudaGetLastError());
     return SDRX_OK;

@@ -50,6 +50,8 @@ for i in range(n):
 dur = {"bank": t[1:, 2] - np.maximum(t[1:, 0], t[1:, 1]), "tail": t[1:, 3] - t[1:, 2],
        "det": t[1:, 4] - np.maximum(t[1:, 3], t[:-1, 4]), "agc": t[1:, 5] - np.maximum(t[1:, 3], t[:-1, 7]),
        "env": t[1:, 6] - np.maximum(t[1:, 5], t[1:, 4]), "lfagc": t[1:, 7] - t[1:, 6], "mix": t[1:, 8] - np.maximum(t[1:, 7], t[:-1, 8])}
+if a.mode == "tc":       # in this mode the engine marks the fold's completion in the `tail` slot (prep stream, behind k_prep)
+    dur["tail"] = t[1:, 3] - t[1:, 1]
 print("durations in the pipeline (completion minus the later of its stream predecessor and its dependency), us, median:")
 print("  " + "  ".join(f"{k} {np.median(v):.1f}" for k, v in dur.items()) + f"  step {np.median(np.diff(t[:, 0])):.1f}")
 if a.out:
