@@ -129,6 +129,7 @@ __device__ __forceinline__ void bf16_split3(float x, __nv_bfloat16 &h0, __nv_bfl
 // CTAs leave room for ~420 more threads per SM -- 128-thread CTAs fit three beside each (one wave), 256-thread CTAs fit one (two
 // waves: 55 us in the pipeline for 17 us of work, and the next GEMM waits for the fold).
 constexpr int kFoldTcM = 1, kFoldTcThreads = 128;
+constexpr int kFoldTcSplit = 4;               // CTAs per output instant (blockIdx.z: a quarter of the table period each): 2.3 items per thread
 template <int FMT>
 static __global__ void __launch_bounds__(kFoldTcThreads)
 k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int valid_lo, int pos0, int D, int N, const double *__restrict__ hc, int Lh,
@@ -137,7 +138,9 @@ k_fold_tc(const void *__restrict__ raw_all, long stream_bytes, int hist, int val
     __nv_bfloat16 *Bs = B + (size_t)blockIdx.y * kTcPlanes * cols * Kp;
     const size_t plane = (size_t)cols * Kp;
     const int M0 = blockIdx.x * kFoldTcM;
-    for (int it = threadIdx.x; it < kFoldTcM * N; it += kFoldTcThreads) {
+    const int per = (kFoldTcM * N + kFoldTcSplit - 1) / kFoldTcSplit;
+    const int it_end = min(kFoldTcM * N, (int)(blockIdx.z + 1) * per);
+    for (int it = blockIdx.z * per + threadIdx.x; it < it_end; it += kFoldTcThreads) {
         const int m = it / N, p = it - m * N;
         const int M = M0 + m;
         if (M >= n_out) break;
@@ -476,7 +479,7 @@ template <int FMT>
 int tgemm_tc_fold(TableGemm &tg, TcGemm &tc, cudaStream_t st, int par, const void *raw, long stream_bytes, int hist, int valid_lo, int pos0, int n_out,
                   uint64_t *launches) {
     if (tc.b_busy[par]) CU(cudaStreamWaitEvent(st, tc.ev_b_free[par], 0));     // the GEMM of two blocks ago read these planes
-    k_fold_tc<FMT><<<dim3((n_out + kFoldTcM - 1) / kFoldTcM, tg.n_streams), kFoldTcThreads, 0, st>>>(raw, stream_bytes, hist, valid_lo, pos0, tg.D, tg.N,
+    k_fold_tc<FMT><<<dim3((n_out + kFoldTcM - 1) / kFoldTcM, tg.n_streams, kFoldTcSplit), kFoldTcThreads, 0, st>>>(raw, stream_bytes, hist, valid_lo, pos0, tg.D, tg.N,
                                                                                               tc.d_hc64, tg.Lh, n_out, tc.d_b[par], tc.cols, tc.Kp, tg.d_hc, tc.fold_double);
     *launches += 1;
     CU(cudaGetLastError());
