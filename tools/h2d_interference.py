@@ -13,7 +13,8 @@ L, nb = plan.rate.block_len, blocks[0].nbytes
 d = lib.sdrx_device_alloc(0, 8 * nb)
 for i, b in enumerate(blocks):
     _lib.check(lib.sdrx_device_upload(0, C.c_void_p(d + i * nb), b.ctypes.data_as(C.c_void_p), nb))
-eng = Engine(plan, tensor_cores=True)
+mode = sys.argv[1] if len(sys.argv) > 1 else "tc"
+eng = Engine(plan, tensor_cores=mode == "tc", polyphase=mode == "poly")
 hbuf = torch.empty(nb, dtype=torch.uint8, pin_memory=True)
 dbuf = torch.empty(nb, dtype=torch.uint8, device="cuda")
 side = torch.cuda.Stream()
@@ -35,4 +36,4 @@ def run(n, copies):
     return (t1 - t0) / n * 1e6
 
 for copies in (0, 1, 2):
-    print(f"{copies} x 2.56 MB H2D per block beside the pipeline: {run(600, copies):6.1f} us per block", flush=True)
+    print(f"{mode}: {copies} x 2.56 MB H2D per block beside the pipeline: {run(600, copies):6.1f} us per block", flush=True)
