@@ -10,21 +10,28 @@
 // Precision.  A tensor-core product takes bf16 (8 significant bits) operands; an FP32 value is EXACTLY the sum of three bf16
 // values (x = x0 + x1 + x2, each the round-to-nearest bf16 of what is left), so a x b = sum over the nine plane products
 // a_i x b_j, every one of them exact in the FP32 accumulator's product (8 x 8 bits).  kProducts = 9 keeps them all (the
-// products are then EXACT and the only rounding left is the accumulation); kProducts = 6 drops the three smallest (a1 b2,
-// a2 b1, a2 b2: <= 2^-23 of the product, about one FP32 rounding of it).
-// Accumulation.  As in k_tgemm a single running sum over the 1200 terms loses weak channels next to strong carriers, so the
-// k range is cut into drain units of kSteps x 16 table entries: every unit is accumulated in its own tensor-memory
-// accumulator (a ring of eight 64-column accumulators = all 512 columns) and the four epilogue warps add the finished
-// units into FP32 register totals with round-to-nearest adds while the tensor core works on the following units.
+// products are then EXACT and the only rounding left is the accumulation); kProducts = 6 (the default) drops the three
+// smallest (a1 b2, a2 b1, a2 b2: < 2^-23 of the term together; measured accuracy identical).
+// Accumulation is the accuracy lever.  A single running sum over the 1200 terms loses weak channels, and so does rounding P and
+// Q -- each as large as the STRONGER channel of a +-offset pair -- before the weaker one is formed as their difference.  So
+// every 16 table entries (one k-step) get their own tensor-memory accumulator (longer units put more of the tensor core's own
+// accumulate rounding into the result), the epilogue warps add the finished units into FP32 register totals with Kahan
+// compensation while the tensor core works on the following ones, and the pair is un-mixed from both the totals and the
+// compensation terms.  Measured on config 3: worst channel IQ 2.9e-5 against the oracle (1.36e-4 without compensation).
 //
-//   k_fold_tc<FMT>  the fold of tgemm.cuh, written as the bf16 planes of B, k-major: B[stream][plane][2 M + (re|im)][p]
+//   k_fold_tc<FMT>  the fold of tgemm.cuh (by default in double, rounded once to FP32), written as the three bf16 planes of B,
+//                   k-major: B[stream][plane][2 M + (re|im)][p]; four 128-thread CTAs per output instant, on the engine's prep
+//                   stream under the previous block's GEMM (B planes ping-pong)
 //   k_tgemm_tc      one CTA per 128-row x 64-column tile of D (64 pair slots x 32 instants), 10 warps:
 //                     warp 8  TMA producer: per 64-entry k-block the three planes of A (128 x 64 bf16) and of B (64 x 64 bf16)
 //                             through 2-D tensor maps with the 128-byte swizzle, a three-deep ring of 72 KB stages on mbarriers
-//                     warp 9  allocates tensor memory; one lane issues tcgen05.mma (M 128, N 64, K 16, kind::f16 with bf16 inputs,
-//                             FP32 accumulate) and tcgen05.commit onto the ring's mbarriers
-//                     warps 0-7  epilogue: tcgen05.ld of a finished accumulator (32 lanes x 32 columns per warp), add into the
-//                             totals; at the end un-mix the pair (neighbouring lanes hold the Tr and Ti rows of a slot) and store
+//                     warp 9  allocates tensor memory; from a warp-uniform loop one elected lane issues tcgen05.mma (M 128, N 64,
+//                             K 16, kind::f16 with bf16 inputs, FP32 accumulate) -- four k-steps x kProducts per k-block into a
+//                             GROUP of four accumulators -- and ONE tcgen05.commit per k-block (a commit drains the tensor pipe:
+//                             ~300 cycles each); two groups = eight 64-column accumulators = all 512 columns
+//                     warps 0-7  epilogue: tcgen05.ld of the group's accumulators (32 lanes x 32 columns per warp: a warp reaches
+//                             only its own lane quadrant, two warps share a quadrant's columns), Kahan add into the totals; at
+//                             the end un-mix the pair (neighbouring lanes hold the Tr and Ti rows of a slot) and store
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
